@@ -1,0 +1,160 @@
+/*
+ * pn_b200.h — C-ABI of libpn_b200.so: the B200 (sm_100a) implementation of the
+ * PacedNegatives LCE / self-paced monoT5 hot path.
+ *
+ * The reference (Parry-Parry/PacedNegatives) is pure Python and has no FFI; the
+ * drop-in boundary is its Python call surface.  Every entry point below names the
+ * reference function (file:line under the reference tree) whose arithmetic it
+ * replaces; the Python shims in pacednegatives_b200/ bind these with ctypes and
+ * keep the reference's class / method names.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - calls enqueue work and return without a host sync unless stated;
+ *   - return 0 on success, a negative PN_E* code otherwise; the message is in
+ *     pn_last_error() (thread-local).  Nothing here calls exit()/abort() — the
+ *     reference's `exit()` on sampler failure (dataloader.py:149-151) becomes
+ *     PN_E_INFEASIBLE reported through a status word;
+ *   - the library never owns caller buffers; only PnT5 handles own memory.
+ */
+#ifndef PN_B200_H
+#define PN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PN_VERSION 100
+
+enum {
+  PN_OK = 0,
+  PN_E_BADARG = -1,      /* null pointer, negative size, unsupported enum value */
+  PN_E_ARCH = -2,        /* device is not compute capability 10.x */
+  PN_E_LAUNCH = -3,      /* CUDA launch / runtime error */
+  PN_E_INFEASIBLE = -4,  /* sampler: fewer non-zero pmf entries than k */
+  PN_E_UNSUPPORTED = -5, /* shape outside what the kernels are built for */
+  PN_E_OOM = -6
+};
+
+int pn_version(void);
+const char* pn_last_error(void);
+/* 0 when the current device is sm_100 (B200); PN_E_ARCH otherwise. */
+int pn_device_check(void);
+/* number of kernels this library has launched in this process (bench.py gpu_launches). */
+int64_t pn_launch_count(void);
+
+/* ------------------------------------------------------------------ a4 / a5
+ * Self-paced eta-threshold weights.
+ *   variant 0 (PN_W_LCE): w = l/eta        if !(l > eta) else (l*mask)*eta
+ *       lceT5.py:91-99 (mask == 0), weights.py:59-78
+ *   variant 1 (PN_W_ETA): w = (-(l/eta))+1 if !(l > eta) else (l*mask)*eta
+ *       weights.py:26-45
+ * fp32 IEEE ops in the reference's order, so w and the keep mask are bit-exact.
+ * keep_out[i] = !(loss[i] > eta)  (nullable).
+ * stats_out (nullable, double[6], overwritten):
+ *   [0] sum w   [1] sum w*l   [2] d(sum w*l)/d eta   [3] #(l < eta)  (old/eta_bound.py:57-58)
+ *   [4] sum l   [5] #(!(l > eta))
+ */
+enum { PN_W_LCE = 0, PN_W_ETA = 1 };
+int pn_weights_fwd(const float* loss, int64_t n, const float* eta, float mask, int variant,
+                   float* w_out, uint8_t* keep_out, double* stats_out, void* stream);
+
+/* ------------------------------------------------------------------ a6
+ * Per-sample weight table row update (pairwrapper.py:219-239, weights.py:87-88):
+ *   g_i = (ce_p ? ce_p[i]*inv_len : 0) + (ce_n ? ce_n[i]*inv_len : 0) - 1
+ *   row[i] = sigmoid(row[i] - lr * g_i)
+ * ce_p / ce_n are nullable (NewWrapper only differentiates the negative term).
+ */
+int pn_weights_table_update(float* row, const float* ce_p, const float* ce_n, int64_t n,
+                            float inv_len, float lr, void* stream);
+
+/* ------------------------------------------------------------------ a3
+ * Token cross-entropy, reduction='none' (lceT5.py:110,117-118; pairwrapper.py:48):
+ *   ce[r] = logsumexp(logits[r,:]) - logits[r,target[r]],  0 when target[r]==ignore_index.
+ * logits is [rows, V] row-major, dtype 0 = fp32, 1 = bf16.  lse_out nullable.
+ */
+int pn_token_ce_fwd(const void* logits, int dtype, int64_t rows, int32_t V, const int64_t* target,
+                    int64_t ignore_index, float* ce_out, float* lse_out, void* stream);
+/* dlogits[r,v] = g[r] * (softmax(logits[r,:])[v] - [v==target[r]]), fp32 out. */
+int pn_token_ce_bwd(const void* logits, int dtype, int64_t rows, int32_t V, const int64_t* target,
+                    int64_t ignore_index, const float* lse, const float* g, float* dlogits,
+                    void* stream);
+
+/* Group reduce of the reference's LCE loss (lceT5.py:119-121; utilities/loss.py:9-12):
+ *   ce[i] = pce[i] + (use_mean ? mean : sum)(nce[i*k : (i+1)*k]),  i in [0, m)
+ * m = Q*T, nce has m*k entries in the reference's flat order.  stats_out nullable double[1] = sum ce. */
+int pn_group_loss_fwd(const float* pce, const float* nce, int64_t m, int32_t k, int use_mean,
+                      float* ce_out, double* stats_out, void* stream);
+/* d pce[i] = g[i];  d nce[i*k+j] = g[i] * (use_mean ? 1/k : 1). */
+int pn_group_loss_bwd(const float* g, int64_t m, int32_t k, int use_mean, float* dpce, float* dnce,
+                      void* stream);
+
+/* Restricted-head LCE (canonical localized contrastive estimation over the two-row head):
+ *   s[d] = log_softmax([z_true[d], z_false[d]])[0]  (distill/wrapper.py:34-38)
+ *   loss[q] = logsumexp_j s[q*G+j] - s[q*G+0]       (doc 0 of each group is the positive)
+ * z2 is [Q*G, 2] fp32 (true, false).  score_out nullable [Q*G]. */
+int pn_lce_restricted_fwd(const float* z2, int64_t Q, int32_t G, float* loss_out, float* score_out,
+                          void* stream);
+int pn_lce_restricted_bwd(const float* z2, int64_t Q, int32_t G, const float* g, float* dz2,
+                          void* stream);
+
+/* ------------------------------------------------------------------ a7
+ * Level-paced negative pick (dataloader.py:29-33): r = floor|ceil(w * n_neg), n_neg = C-1,
+ * computed in fp64 like the Python float the reference multiplies.
+ * cand is int32 doc ids, layout 0 = row-major [Q,C], 1 = rank-major [C,Q].
+ * Out-of-range r (reference: IndexError / negative wrap) gives idx=-1, doc=-1 and bumps status_out[0].
+ */
+enum { PN_LAYOUT_ROW = 0, PN_LAYOUT_RANK = 1 };
+int pn_select_level_scalar(const int32_t* cand, int64_t Q, int32_t C, int layout, double w,
+                           int use_ceil, int32_t* idx_out /*[1]*/, int32_t* doc_out /*[Q]*/,
+                           int32_t* status_out, void* stream);
+/* per-item weights (PairLoader.get_batch, dataloader.py:46-56): w[q] is the fp32 the reference
+ * reads with tensor.item(). */
+int pn_select_level_items(const int32_t* cand, int64_t Q, int32_t C, int layout, const float* w,
+                          int use_ceil, int32_t* idx_out /*[Q]*/, int32_t* doc_out /*[Q]*/,
+                          int32_t* status_out, void* stream);
+
+/* ------------------------------------------------------------------ a8
+ * Binomial-paced sampling of k ranks without replacement (dataloader.py:134-151 =
+ * scipy binom.pmf + numpy legacy RandomState.choice(replace=False, p)).
+ *
+ * pn_binomial_table: p = clip(mean) -> pmf(arange(C); C-1, mean) -> p/sum -> var rescale -> p/sum,
+ *   then the first-round cdf = cumsum(p)/cumsum(p)[-1], all fp64 in numpy's summation order.
+ *   table_out is double[2*C]: p then cdf.  pmf_in (nullable, double[C]) overrides the device
+ *   lgamma pmf with a caller-supplied one (scipy's, for strict parity).  status_out[0] = number of
+ *   non-zero p entries, status_out[1] = PN_E_INFEASIBLE flag if the variance step produced non-finite p.
+ */
+int pn_binomial_table(double mean, double clip_min, double clip_max, double var, int32_t C,
+                      const double* pmf_in, double* table_out, int32_t* status_out, void* stream);
+/* pn_select_binomial: for each query draw k distinct ranks with numpy's algorithm.
+ *   uniforms (nullable): double [Q, U] per-query substreams (stream_mode 0) or one flat stream of
+ *     length U consumed by the queries in order (stream_mode 1, the reference's global RNG);
+ *     NULL = counter-based Philox4x32-10 stream keyed by (philox_seed, query).
+ *   idx_out int32 [Q,k] rank indices in numpy's order; doc_out (nullable) cand[q][idx]; cand nullable
+ *   when doc_out is.  consumed_out (nullable) [Q] uniforms used.  status_out[0] = #queries that ran
+ *   out of uniforms or were infeasible (their rows are filled with -1).
+ */
+int pn_select_binomial(const int32_t* cand, int64_t Q, int32_t C, int layout, const double* table,
+                       int32_t k, const double* uniforms, int64_t U, int stream_mode,
+                       uint64_t philox_seed, int32_t* idx_out, int32_t* doc_out,
+                       int32_t* consumed_out, int32_t* status_out, void* stream);
+
+/* ------------------------------------------------------------------ a12
+ * Per-query ranking + trec_eval measures (eval.py:26,41-43): sort C candidates by
+ * (score desc, docid desc), emit the top K and ndcg_cut_K (linear gain, log2(i+1) discount, ideal from
+ * the query's rels), recip_rank (whole list), recip_rank cut at K, and average precision.
+ * rels uint8 [Q,C] graded relevance of each candidate.  metrics_out float [Q,4] =
+ * (ndcg@K, rr, rr@K, ap).  C <= 4096.  top_* nullable.
+ */
+int pn_topk_metrics(const float* scores, const int32_t* docids, const uint8_t* rels, int64_t Q,
+                    int32_t C, int32_t K, int32_t* top_ids, float* top_scores, float* metrics_out,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PN_B200_H */

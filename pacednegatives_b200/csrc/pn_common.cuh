@@ -1,0 +1,85 @@
+// Shared host/device helpers for libpn_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <atomic>
+
+#include "../../include/pn_b200.h"
+
+#define PN_SM_COUNT 148
+
+extern thread_local char g_pn_err[512];
+extern std::atomic<int64_t> g_pn_launches;
+
+static inline int pn_fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_pn_err, sizeof(g_pn_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define PN_CHECK_ARG(cond)                                                             \
+  do {                                                                                 \
+    if (!(cond)) return pn_fail(PN_E_BADARG, "%s: bad argument: %s", __func__, #cond); \
+  } while (0)
+
+#define PN_CUDA(call)                                                                              \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess)                                                                        \
+      return pn_fail(PN_E_LAUNCH, "%s: %s failed: %s", __func__, #call, cudaGetErrorString(e__)); \
+  } while (0)
+
+// after a <<<>>> launch
+#define PN_LAUNCHED()                                                                         \
+  do {                                                                                        \
+    g_pn_launches.fetch_add(1, std::memory_order_relaxed);                                    \
+    cudaError_t e__ = cudaGetLastError();                                                     \
+    if (e__ != cudaSuccess)                                                                   \
+      return pn_fail(PN_E_LAUNCH, "%s: launch failed: %s", __func__, cudaGetErrorString(e__)); \
+  } while (0)
+
+// grid for a grid-stride bandwidth kernel: a multiple of the SM count, capped by the work
+static inline int pn_grid(int64_t work_items, int threads, int items_per_thread, int ctas_per_sm) {
+  int64_t need = (work_items + (int64_t)threads * items_per_thread - 1) /
+                 ((int64_t)threads * items_per_thread);
+  int64_t cap = (int64_t)PN_SM_COUNT * ctas_per_sm;
+  if (need < 1) need = 1;
+  if (need > cap) need = cap;
+  return (int)need;
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float pn_warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double pn_warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float pn_warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// streaming 128-bit load that does not allocate in L1 (inputs are touched once)
+__device__ __forceinline__ float4 pn_ldg_stream(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void pn_stg_stream(float4* p, float4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),
+               "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+#endif

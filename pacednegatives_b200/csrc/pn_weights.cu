@@ -1,0 +1,169 @@
+// Self-paced weighting kernels.
+//   pn_weights_fwd           lceT5.py:91-99, weights.py:26-45,59-78
+//   pn_weights_table_update  pairwrapper.py:219-239, weights.py:87-88
+// HBM-bound: 4 B read + 4 B write (+1 B keep mask) per element; the six reductions ride along
+// in registers -> warp shuffle -> one fp64 atomic per CTA per statistic.
+#include "pn_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kUnroll = 4;  // float4 loads in flight per thread
+
+struct WStats {
+  double sw, swl, dswl, nlt, sl, nkeep;
+};
+
+template <int VARIANT>
+__device__ __forceinline__ float weight_one(float l, float eta, float mask, WStats& s) {
+  const bool over = l > eta;  // the reference's `if loss[i] > self.eta`
+  float w;
+  if (over) {
+    w = __fmul_rn(__fmul_rn(l, mask), eta);
+  } else {
+    const float q = __fdiv_rn(l, eta);
+    w = (VARIANT == PN_W_LCE) ? q : __fadd_rn(-q, 1.0f);
+  }
+  const double ld = (double)l, ed = (double)eta;
+  s.sw += (double)w;
+  s.swl += (double)w * ld;
+  if (over) {
+    s.dswl += (double)mask * ld * ld;
+  } else {
+    const double t = ld * ld / (ed * ed);
+    s.dswl += (VARIANT == PN_W_LCE) ? -t : t;
+    s.nkeep += 1.0;
+  }
+  if (l < eta) s.nlt += 1.0;
+  s.sl += ld;
+  return w;
+}
+
+template <int VARIANT, bool VEC>
+__global__ void __launch_bounds__(kThreads)
+weights_fwd_kernel(const float* __restrict__ loss, int64_t n, const float* __restrict__ eta_p,
+                   float mask, float* __restrict__ w_out, uint8_t* __restrict__ keep_out,
+                   double* __restrict__ stats) {
+  const float eta = __ldg(eta_p);
+  WStats s = {0, 0, 0, 0, 0, 0};
+  const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  const int64_t nthreads = (int64_t)gridDim.x * kThreads;
+
+  if (VEC) {
+    const int64_t n4 = n >> 2;
+    const float4* in4 = reinterpret_cast<const float4*>(loss);
+    float4* out4 = reinterpret_cast<float4*>(w_out);
+    for (int64_t base = tid; base < n4; base += nthreads * kUnroll) {
+      float4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * nthreads;
+        if (i < n4) v[u] = pn_ldg_stream(in4 + i);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * nthreads;
+        if (i < n4) {
+          float4 w;
+          w.x = weight_one<VARIANT>(v[u].x, eta, mask, s);
+          w.y = weight_one<VARIANT>(v[u].y, eta, mask, s);
+          w.z = weight_one<VARIANT>(v[u].z, eta, mask, s);
+          w.w = weight_one<VARIANT>(v[u].w, eta, mask, s);
+          pn_stg_stream(out4 + i, w);
+          if (keep_out) {
+            uchar4 k;
+            k.x = !(v[u].x > eta);
+            k.y = !(v[u].y > eta);
+            k.z = !(v[u].z > eta);
+            k.w = !(v[u].w > eta);
+            reinterpret_cast<uchar4*>(keep_out)[i] = k;
+          }
+        }
+      }
+    }
+    // scalar tail
+    for (int64_t i = (n4 << 2) + tid; i < n; i += nthreads) {
+      const float l = loss[i];
+      w_out[i] = weight_one<VARIANT>(l, eta, mask, s);
+      if (keep_out) keep_out[i] = !(l > eta);
+    }
+  } else {
+    for (int64_t i = tid; i < n; i += nthreads) {
+      const float l = loss[i];
+      w_out[i] = weight_one<VARIANT>(l, eta, mask, s);
+      if (keep_out) keep_out[i] = !(l > eta);
+    }
+  }
+
+  if (stats == nullptr) return;
+  __shared__ double red[6][kThreads / 32];
+  double vals[6] = {s.sw, s.swl, s.dswl, s.nlt, s.sl, s.nkeep};
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const double r = pn_warp_sum(vals[k]);
+    if (lane == 0) red[k][warp] = r;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    double r = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) r += red[threadIdx.x][w];
+    atomicAdd(stats + threadIdx.x, r);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+table_update_kernel(float* __restrict__ row, const float* __restrict__ ce_p,
+                    const float* __restrict__ ce_n, int64_t n, float inv_len, float lr) {
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * kThreads) {
+    float g = -1.0f;
+    float acc = 0.0f;
+    if (ce_p) acc = __fmul_rn(ce_p[i], inv_len);
+    if (ce_n) acc = ce_p ? __fadd_rn(acc, __fmul_rn(ce_n[i], inv_len)) : __fmul_rn(ce_n[i], inv_len);
+    g = __fadd_rn(acc, -1.0f);
+    const float x = __fsub_rn(row[i], __fmul_rn(lr, g));
+    row[i] = 1.0f / (1.0f + expf(-x));
+  }
+}
+
+}  // namespace
+
+extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, float mask,
+                              int variant, float* w_out, uint8_t* keep_out, double* stats_out,
+                              void* stream) {
+  PN_CHECK_ARG(n >= 0);
+  PN_CHECK_ARG(variant == PN_W_LCE || variant == PN_W_ETA);
+  PN_CHECK_ARG(eta != nullptr);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (stats_out) PN_CUDA(cudaMemsetAsync(stats_out, 0, 6 * sizeof(double), st));
+  if (n == 0) return PN_OK;
+  PN_CHECK_ARG(loss != nullptr && w_out != nullptr);
+  const bool vec = (((uintptr_t)loss | (uintptr_t)w_out) & 15) == 0 &&
+                   (keep_out == nullptr || ((uintptr_t)keep_out & 3) == 0);
+  const int grid = pn_grid(n, kThreads, vec ? 4 * kUnroll : 4, 8);
+#define LAUNCH(V, VEC)                                                                       \
+  weights_fwd_kernel<V, VEC><<<grid, kThreads, 0, st>>>(loss, n, eta, mask, w_out, keep_out, \
+                                                        stats_out)
+  if (variant == PN_W_LCE) {
+    if (vec) LAUNCH(PN_W_LCE, true); else LAUNCH(PN_W_LCE, false);
+  } else {
+    if (vec) LAUNCH(PN_W_ETA, true); else LAUNCH(PN_W_ETA, false);
+  }
+#undef LAUNCH
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+extern "C" int pn_weights_table_update(float* row, const float* ce_p, const float* ce_n, int64_t n,
+                                       float inv_len, float lr, void* stream) {
+  PN_CHECK_ARG(n >= 0);
+  if (n == 0) return PN_OK;
+  PN_CHECK_ARG(row != nullptr);
+  PN_CHECK_ARG(ce_p != nullptr || ce_n != nullptr);
+  const int grid = pn_grid(n, kThreads, 4, 8);
+  table_update_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(row, ce_p, ce_n, n, inv_len, lr);
+  PN_LAUNCHED();
+  return PN_OK;
+}

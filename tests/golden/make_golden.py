@@ -1,0 +1,320 @@
+"""Generate golden vectors by running the REFERENCE itself (build container only).
+
+The reference ships no tests or fixtures, so parity is pinned against its own functions executed here:
+this script imports /root/reference/pacednegatives (with stubs for the packages that are absent
+offline: lightning, ir_datasets, transformers.AdamW), runs the hot-path functions on seeded inputs and
+writes inputs + outputs to tests/golden/*.npz.  /root/reference does not exist on the GPU box, so the
+tests only ever read the .npz files.
+
+    python tests/golden/make_golden.py
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+
+
+def import_reference():
+    """Stub the absent third-party packages, then import the reference modules unmodified."""
+    import torch.nn as nn
+
+    class _Hp(dict):
+        __getattr__ = dict.__getitem__
+        __setattr__ = dict.__setitem__
+
+    class LightningModule(nn.Module):
+        def __init__(self):
+            super().__init__()
+            object.__setattr__(self, "_hp", _Hp())
+
+        @property
+        def hparams(self):
+            return self._hp
+
+        def save_hyperparameters(self):
+            pass
+
+    lightning = types.ModuleType("lightning")
+    lightning.LightningModule = LightningModule
+    lightning.LightningDataModule = object
+    lightning.Callback = object
+    sys.modules["lightning"] = lightning
+    irds = types.ModuleType("ir_datasets")
+    irds.load = lambda name: None
+    sys.modules["ir_datasets"] = irds
+    import transformers
+
+    def adamw(params, lr):  # transformers.AdamW was removed upstream; same defaults (eps 1e-6, wd 0)
+        return torch.optim.AdamW(params, lr=lr, eps=1e-6, weight_decay=0.0)
+
+    def patch():
+        for mod in {transformers, sys.modules["transformers"]}:
+            mod.__dict__["AdamW"] = adamw
+
+    sys.path.insert(0, REF)
+    import pacednegatives.weights as rw
+    import pacednegatives.dataloader as rd
+    import pacednegatives.utilities.loss as rl
+    patch()
+    import pacednegatives.lceT5 as rt
+    patch()
+    import pacednegatives.pairwrapper as rp
+    return rw, rd, rl, rt, rp
+
+
+class FakeCorpus:
+    """Duck-type of the ir_datasets corpus the reference iterates (dataloader.py:20-21)."""
+
+    def __init__(self, n_docs, n_queries):
+        self.n_docs, self.n_queries = n_docs, n_queries
+
+    def docs_iter(self):
+        for i in range(self.n_docs):
+            yield {"doc_id": str(i), "text": f"d{i}"}
+
+    def queries_iter(self):
+        for i in range(self.n_queries):
+            yield {"query_id": str(i), "text": f"q{i}"}
+
+
+def gold_weights(rw, rt, out):
+    rng = np.random.RandomState(5678)
+    loss = rng.exponential(0.7, size=257).astype(np.float32)
+    loss[:4] = [0.1, 0.5, 0.7, 0.3]
+    etas = np.array([0.1, 0.3466, 0.5, 1.0], dtype=np.float32)
+    loss[5] = etas[1]  # boundary: loss == eta takes the else branch
+    res = {"loss": loss, "etas": etas}
+    for ei, eta in enumerate(etas):
+        hp = types.SimpleNamespace(eta=float(eta))
+        m = rt.LCEWeights(hp)
+        lt = torch.tensor(loss)
+        w = m(lt)
+        (w * lt).mean().backward()
+        res[f"lce_w_{ei}"] = w.detach().numpy()
+        res[f"lce_dmean_deta_{ei}"] = m.eta.grad.numpy().copy()
+        for mask in (0.0, 0.25):
+            for name, cls in (("eta", rw.EtaWeights), ("lce", rw.LCEWeights)):
+                mod = cls(float(eta), device=torch.device("cpu"))
+                mod.set_mask(mask)
+                wn = mod.no_grad(lt, torch.tensor([float(eta)]))
+                res[f"nograd_{name}_{ei}_m{int(mask * 100)}"] = wn.numpy()
+    np.savez_compressed(out, **res)
+
+
+def gold_loss(rl, rt, out):
+    rng = np.random.RandomState(91)
+    V = 97
+    res = {}
+    case = 0
+    for T in (1, 2):
+        for n in (2, 7, 15):
+            for use_mean in (True, False):
+                Q = 4
+                p = rng.randn(Q, T, V).astype(np.float32) * 3
+                nl = rng.randn(Q * n, T, V).astype(np.float32) * 3
+                op = rng.randint(0, V, size=(Q, T)).astype(np.int64)
+                on = rng.randint(0, V, size=(Q * n, T)).astype(np.int64)
+                if case % 3 == 0:
+                    on[1, 0] = -100  # ignore_index path
+                fn = rl.init_LCEcrossentropy(ignore_index=-100, use_mean=use_mean)
+                # the callers re-view the negatives as [-1, n, V] first (lceT5.py:134)
+                nview = torch.tensor(nl).view(-1, n, V)
+                loss_mean = fn(torch.tensor(p), nview, torch.tensor(op), torch.tensor(on))
+                model = types.SimpleNamespace(
+                    loss_fn=torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none"),
+                    hparams=types.SimpleNamespace(use_mean=use_mean))
+                ce = rt.LCEModel.pair_loss(model, torch.tensor(p), nview, torch.tensor(op),
+                                           torch.tensor(on))
+                res[f"c{case}_meta"] = np.array([T, n, int(use_mean), Q, V])
+                res[f"c{case}_p"] = p
+                res[f"c{case}_n"] = nl
+                res[f"c{case}_op"] = op
+                res[f"c{case}_on"] = on
+                res[f"c{case}_pair_loss"] = ce.numpy()
+                res[f"c{case}_lcece_mean"] = np.array(loss_mean.item(), dtype=np.float32)
+                case += 1
+    res["n_cases"] = np.array(case)
+    np.savez_compressed(out, **res)
+
+
+def gold_select(rd, out):
+    res = {}
+    # level mode: TripletDataset.get_items
+    Q, C = 6, 101
+    cand = ((np.arange(Q)[:, None] * 7919 + np.arange(C)[None, :] * 104729) % 5003).astype(np.int32)
+    neg_idx = [[str(x) for x in row] for row in cand]
+    pairs = [(str(q), str(q)) for q in range(Q)]
+    corpus = FakeCorpus(5003, Q)
+    n_neg = C - 1
+    ws = [0.0, 1.0, 0.5, 0.3466, 1e-10, 1 - 1e-10]
+    for kk in range(0, n_neg + 1, 7):
+        x = kk / n_neg
+        ws += [x, float(np.nextafter(x, 0)), float(np.nextafter(x, 1))]
+    ws = [w for w in ws if 0.0 <= w <= 1.0]
+    w32 = np.array(ws, dtype=np.float32)
+    for use_max in (False, True):
+        ds = rd.TripletDataset(pairs, neg_idx, corpus, max=use_max)
+        got64 = np.zeros((len(ws), Q), dtype=np.int32)
+        got32 = np.zeros((len(ws), Q), dtype=np.int32)
+        for wi, w in enumerate(ws):
+            for q in range(Q):
+                got64[wi, q] = int(ds.get_items(q, w)[2][1:])
+                got32[wi, q] = int(ds.get_items(q, torch.tensor(w32)[wi].item())[2][1:])
+        res[f"level_doc64_max{int(use_max)}"] = got64
+        res[f"level_doc32_max{int(use_max)}"] = got32
+    res["level_cand"] = cand
+    res["level_w64"] = np.array(ws, dtype=np.float64)
+    res["level_w32"] = w32
+    # binomial mode: LCEDataset.sample with the global numpy RNG
+    from scipy.stats import binom
+    C = 1000
+    Qb = 3
+    candb = ((np.arange(Qb)[:, None] * 7919 + np.arange(C)[None, :] * 104729) % 8841823).astype(np.int32)
+    neg_idx = [[str(x) for x in row] for row in candb]
+    docs = {}
+
+    class Corpus2:
+        def docs_iter(self):
+            seen = set()
+            for row in candb:
+                for x in row:
+                    if int(x) not in seen:
+                        seen.add(int(x))
+                        yield {"doc_id": str(int(x)), "text": f"d{int(x)}"}
+            for q in range(Qb):
+                if -q - 1 not in seen:
+                    yield {"doc_id": f"p{q}", "text": f"pos{q}"}
+
+        def queries_iter(self):
+            for q in range(Qb):
+                yield {"query_id": str(q), "text": f"q{q}"}
+
+    pairs = [(str(q), f"p{q}") for q in range(Qb)]
+    means = [1e-10, 0.01, 0.3466, 0.5, 0.9, 1.5]
+    ks = [2, 7, 15, 31]
+    seeds = list(range(6))
+    res["binom_cand"] = candb
+    res["binom_means"] = np.array(means)
+    res["binom_ks"] = np.array(ks)
+    res["binom_seeds"] = np.array(seeds)
+    for mi, mean in enumerate(means):
+        res[f"binom_pmf_{mi}"] = binom.pmf(np.arange(C), C - 1, np.clip(mean, 1e-10, 1 - 1e-10))
+        for ki, k in enumerate(ks):
+            for var in (0.01, 0.1):
+                ds = rd.LCEDataset(pairs, neg_idx, Corpus2(), None, mean, 16, var=var, n=k,
+                                   min=1e-10, max=1 - 1e-10)
+                per_seed = np.zeros((len(seeds), k), dtype=np.int64)
+                for si, seed in enumerate(seeds):
+                    np.random.seed(seed)
+                    per_seed[si] = ds.sample(mean)
+                res[f"binom_idx_m{mi}_k{ki}_v{int(var * 100)}"] = per_seed
+            # one global stream over the Qb queries via __getitem__ (the reference's DataLoader order)
+            ds = rd.LCEDataset(pairs, neg_idx, Corpus2(), None, mean, 16, var=0.01, n=k,
+                               min=1e-10, max=1 - 1e-10)
+            np.random.seed(1234)
+            docs_seq = np.zeros((Qb, k), dtype=np.int32)
+            for q in range(Qb):
+                item = ds[q]
+                docs_seq[q] = [int(s.split(" Document: d")[1].split(" Relevant:")[0])
+                               for s in item["neg"]]
+            res[f"binom_seqdocs_m{mi}_k{ki}"] = docs_seq
+    np.savez_compressed(out, **res)
+
+
+def gold_table_update(rp, rw, out):
+    """NewWrapper.meta_loop (pairwrapper.py:219-239) with a fake model/tokenizer/loader."""
+    B, V = 8, 23
+    rng = np.random.RandomState(7)
+    logits_p = torch.tensor(rng.randn(B, 1, V).astype(np.float32) * 2)
+    logits_n = torch.tensor(rng.randn(B, 1, V).astype(np.float32) * 2)
+    o_p = torch.tensor(rng.randint(0, V, size=(B, 1)))
+    o_n = torch.tensor(rng.randint(0, V, size=(B, 1)))
+    wrap = object.__new__(rp.NewWrapper)
+    wrap.device = torch.device("cpu")
+    wrap.loss_fn = torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none")
+    wrap.weights = rw.Weights((2, B), device=torch.device("cpu"))
+    init = rng.rand(B).astype(np.float32)
+    with torch.no_grad():
+        wrap.weights.weight[1] = torch.tensor(init)
+    wrap.train_loader = types.SimpleNamespace(get_batch=lambda j, w: ("px", "nx", "op", "on"))
+    wrap.prep_batch = lambda batch: ("px", "nx", o_p, o_n)
+    wrap.model = lambda input_ids, labels: types.SimpleNamespace(
+        logits=logits_p if input_ids == "px" else logits_n)
+    lr = 0.05
+    wrap.scheduler = types.SimpleNamespace(get_last_lr=lambda: [lr])
+    wrap.meta_loop(1)
+    ce_p = wrap.loss_fn(logits_p.view(-1, V), o_p.view(-1)).numpy()
+    ce_n = wrap.loss_fn(logits_n.view(-1, V), o_n.view(-1)).numpy()
+    np.savez_compressed(out, init=init, ce_p=ce_p, ce_n=ce_n, lr=np.float32(lr),
+                        updated=wrap.weights.weight[1].detach().numpy(),
+                        logits_p=logits_p.numpy(), logits_n=logits_n.numpy(),
+                        o_p=o_p.numpy(), o_n=o_n.numpy())
+
+
+def gold_t5(rt, out):
+    """HF T5ForConditionalGeneration itself (the reference's model, lceT5.py:106) on seeded inputs."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    from transformers import T5Config, T5ForConditionalGeneration
+    dims = ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2,
+                     n_heads=2)
+    w = ot.init_weights(dims, seed=11)
+    cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
+                   num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
+                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   pad_token_id=0, eos_token_id=1, feed_forward_proj="relu",
+                   tie_word_embeddings=True)
+    m = T5ForConditionalGeneration(cfg).eval()
+    sd = dict(w)
+    sd["encoder.embed_tokens.weight"] = sd["decoder.embed_tokens.weight"] = w["shared.weight"]
+    sd["lm_head.weight"] = w["shared.weight"]
+    missing = m.load_state_dict(sd, strict=False)
+    assert not missing.missing_keys and not missing.unexpected_keys, missing
+    rng = np.random.RandomState(1234)
+    Q, k, S = 2, 3, 128
+    rel_id, nrel_id = 117, 213
+    pids = rng.randint(2, dims.vocab, size=(Q, S)).astype(np.int64)
+    nids = rng.randint(2, dims.vocab, size=(Q * k, S)).astype(np.int64)
+    pids[:, -1] = 1
+    nids[:, -1] = 1
+    plab = np.tile([[rel_id, 1]], (Q, 1)).astype(np.int64)
+    nlab = np.tile([[nrel_id, 1]], (Q * k, 1)).astype(np.int64)
+    with torch.no_grad():
+        pl = m(input_ids=torch.tensor(pids), labels=torch.tensor(plab)).logits
+        nl = m(input_ids=torch.tensor(nids), labels=torch.tensor(nlab)).logits
+        # pairwrapper / re-rank path: one decoder step (pairwrapper.py:81-82, distill/wrapper.py:34-38)
+        p1 = m(input_ids=torch.tensor(pids), labels=torch.tensor(plab[:, :1])).logits
+        score = torch.log_softmax(p1[:, 0, (rel_id, nrel_id)], dim=1)[:, 0]
+    model = types.SimpleNamespace(
+        loss_fn=torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none"),
+        hparams=types.SimpleNamespace(use_mean=True))
+    ce = rt.LCEModel.pair_loss(model, pl, nl.view(-1, k, dims.vocab), torch.tensor(plab),
+                               torch.tensor(nlab))
+    np.savez_compressed(
+        out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers,
+                            dims.n_dec_layers, dims.n_heads]), seed=np.array(11),
+        pids=pids, nids=nids, plab=plab, nlab=nlab, plogits=pl.numpy(), nlogits=nl.numpy(),
+        p1_z2=p1[:, 0, (rel_id, nrel_id)].numpy(), p1_score=score.numpy(),
+        pair_loss=ce.numpy(), rel_ids=np.array([rel_id, nrel_id]), k=np.array(k))
+
+
+def main():
+    rw, rd, rl, rt, rp = import_reference()
+    gold_weights(rw, rt, os.path.join(HERE, "weights_golden.npz"))
+    gold_loss(rl, rt, os.path.join(HERE, "loss_golden.npz"))
+    gold_select(rd, os.path.join(HERE, "select_golden.npz"))
+    gold_table_update(rp, rw, os.path.join(HERE, "table_update_golden.npz"))
+    gold_t5(rt, os.path.join(HERE, "t5_tiny_golden.npz"))
+    for f in sorted(os.listdir(HERE)):
+        if f.endswith(".npz"):
+            print(f, os.path.getsize(os.path.join(HERE, f)))
+
+
+if __name__ == "__main__":
+    main()
