@@ -63,6 +63,11 @@ enum { PN_W_LCE = 0, PN_W_ETA = 1 };
 int pn_weights_fwd(const float* loss, int64_t n, const float* eta, float mask, int variant,
                    float* w_out, uint8_t* keep_out, double* stats_out, void* stream);
 
+/* Backward of pn_weights_fwd for an upstream gradient g[n] (autograd of weights.forward):
+ *   deta_out[0] (double) = sum_i g[i] * dw_i/deta,  dloss_out[i] (nullable) = g[i] * dw_i/dloss_i. */
+int pn_weights_bwd(const float* loss, int64_t n, const float* eta, float mask, int variant,
+                   const float* g, float* dloss_out, double* deta_out, void* stream);
+
 /* ------------------------------------------------------------------ a6
  * Per-sample weight table row update (pairwrapper.py:219-239, weights.py:87-88):
  *   g_i = (ce_p ? ce_p[i]*inv_len : 0) + (ce_n ? ce_n[i]*inv_len : 0) - 1

@@ -128,7 +128,60 @@ table_update_kernel(float* __restrict__ row, const float* __restrict__ ce_p,
   }
 }
 
+template <int VARIANT>
+__global__ void __launch_bounds__(kThreads)
+weights_bwd_kernel(const float* __restrict__ loss, int64_t n, const float* __restrict__ eta_p,
+                   float mask, const float* __restrict__ g, float* __restrict__ dloss,
+                   double* __restrict__ deta) {
+  const float eta = __ldg(eta_p);
+  const double ed = (double)eta;
+  double acc = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * kThreads) {
+    const float l = loss[i], gi = g[i];
+    double dwde, dwdl;
+    if (l > eta) {
+      dwde = (double)l * (double)mask;
+      dwdl = (double)mask * ed;
+    } else {
+      const double sgn = (VARIANT == PN_W_LCE) ? 1.0 : -1.0;
+      dwde = -sgn * (double)l / (ed * ed);
+      dwdl = sgn / ed;
+    }
+    acc += (double)gi * dwde;
+    if (dloss) dloss[i] = (float)((double)gi * dwdl);
+  }
+  acc = pn_warp_sum(acc);
+  __shared__ double red[kThreads / 32];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double r = 0;
+    for (int w = 0; w < kThreads / 32; ++w) r += red[w];
+    atomicAdd(deta, r);
+  }
+}
+
 }  // namespace
+
+extern "C" int pn_weights_bwd(const float* loss, int64_t n, const float* eta, float mask,
+                              int variant, const float* g, float* dloss_out, double* deta_out,
+                              void* stream) {
+  PN_CHECK_ARG(n >= 0);
+  PN_CHECK_ARG(variant == PN_W_LCE || variant == PN_W_ETA);
+  PN_CHECK_ARG(eta != nullptr && deta_out != nullptr);
+  cudaStream_t st = (cudaStream_t)stream;
+  PN_CUDA(cudaMemsetAsync(deta_out, 0, sizeof(double), st));
+  if (n == 0) return PN_OK;
+  PN_CHECK_ARG(loss != nullptr && g != nullptr);
+  const int grid = pn_grid(n, kThreads, 4, 8);
+  if (variant == PN_W_LCE)
+    weights_bwd_kernel<PN_W_LCE><<<grid, kThreads, 0, st>>>(loss, n, eta, mask, g, dloss_out, deta_out);
+  else
+    weights_bwd_kernel<PN_W_ETA><<<grid, kThreads, 0, st>>>(loss, n, eta, mask, g, dloss_out, deta_out);
+  PN_LAUNCHED();
+  return PN_OK;
+}
 
 extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, float mask,
                               int variant, float* w_out, uint8_t* keep_out, double* stats_out,
