@@ -159,6 +159,16 @@ int pn_topk_metrics(const float* scores, const int32_t* docids, const uint8_t* r
                     int32_t C, int32_t K, int32_t* top_ids, float* top_scores, float* metrics_out,
                     void* stream);
 
+/* ------------------------------------------------------------------ a1 (building block)
+ * bf16 GEMM on the tcgen05 tensor path, the T5 linear layers (HF modeling_t5.py:277,298-299,338,92-103):
+ *   C[M,N] = A[M,K] . B[N,K]^T, A row-major activations (lda), B an nn.Linear weight [out,in] (ldb).
+ *   mode 0: bf16 out[M,ldc] = relu?(acc * row_scale[row]?) ; mode 1: fp32 out[M,ldc] += acc * row_scale?.
+ *   K % 64 == 0, N % 128 == 0, 16-byte aligned operands.  cta_group 1 = single-SM tiles 128xN,
+ *   2 = CTA-pair tiles 256xN (cta_group::2). */
+int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* out, int64_t ldc,
+                 int64_t M, int64_t N, int64_t K, int mode, int relu, const float* row_scale,
+                 int cta_group, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,6 +37,8 @@ SIGNATURES = {
     "pn_binomial_table": (c_int, [c_f64, c_f64, c_f64, c_f64, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "pn_select_binomial": (c_int, [c_vp, c_i64, c_i32, c_int, c_vp, c_i32, c_vp, c_i64, c_int,
                                    c_u64, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "pn_gemm_bf16": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_int,
+                             c_vp, c_int, c_vp]),
     "pn_topk_metrics": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
 }
 

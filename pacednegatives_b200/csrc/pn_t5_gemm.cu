@@ -1,0 +1,319 @@
+// Persistent warp-specialised bf16 GEMM for the T5 linears (HF:277,298-299,338 q/k/v/o,
+// HF:92-103 wi/wo), hand-written for sm_100a:
+//   C[M,N] = A[M,K] . B[N,K]^T      A = activations (row-major), B = nn.Linear weight [out,in]
+// TMA (128-byte swizzle) -> shared-memory ring -> tcgen05.mma with fp32 accumulators in TMEM
+// (double-buffered) -> tcgen05.ld epilogue straight to global.  cta_group::2 pairs two SMs on a
+// 256 x BLOCK_N tile (each CTA loads its half of A and B); cta_group::1 is the single-SM variant.
+// Warp roles: 0 = TMA producer, 1 = MMA issuer (leader CTA only), 2 = TMEM allocator, 4..7 = epilogue.
+#include "pn_common.cuh"
+#include "pn_tc.cuh"
+#include "pn_t5_internal.cuh"
+
+using namespace pntc;
+
+namespace {
+
+constexpr int BLOCK_M = 128;  // rows per CTA
+constexpr int BLOCK_K = 64;   // one 128-byte swizzle atom of bf16
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 256;
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
+
+template <int kCtaGroup, int BLOCK_N>
+struct GemmCfg {
+  static constexpr int B_ROWS = BLOCK_N / kCtaGroup;        // B rows this CTA loads
+  static constexpr int B_STAGE_BYTES = B_ROWS * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int kStages = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int kAccStages = 2;
+  static constexpr int TMEM_COLS = kAccStages * BLOCK_N;    // 512 or 256 (power of two)
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr uint32_t IDESC = make_idesc_bf16(BLOCK_M * kCtaGroup, BLOCK_N, 0, 0);
+};
+
+struct GemmArgs {
+  int M, N, K;
+  void* out;               // bf16 [M, ldc] (mode 0) or fp32 [M, ldc] (mode 1, accumulated in place)
+  int ldc;
+  int mode;                // PN_EPI_*
+  int relu;
+  const float* row_scale;  // nullable: out = acc * row_scale[row] (fused RMSNorm scale)
+};
+
+template <int kCtaGroup, int BLOCK_N>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const GemmArgs args) {
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + kStages * Cfg::STAGE_BYTES;
+  // barrier layout: full[kStages] empty[kStages] tmem_full[2] tmem_empty[2] | tmem ptr
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
+  uint32_t* tmem_slot_gen =
+      reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = (kCtaGroup == 2) ? cluster_ctarank() : 0;
+  const bool leader = cta_rank == 0;
+  const int num_groups = gridDim.x / kCtaGroup;   // CTAs (1) or CTA pairs (2)
+  const int group_id = blockIdx.x / kCtaGroup;
+
+  const int tile_m = BLOCK_M * kCtaGroup;
+  const int m_tiles = (args.M + tile_m - 1) / tile_m;
+  const int n_tiles = args.N / BLOCK_N;
+  const int num_tiles = m_tiles * n_tiles;
+  const int num_kb = args.K / BLOCK_K;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 4 * kCtaGroup);  // one arrive per epilogue warp per CTA
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<kCtaGroup>(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish<kCtaGroup>();
+  }
+  tc_fence_before();
+  if (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_gen;
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    int s = 0;
+    uint32_t ph = 0;
+    for (int tile = group_id; tile < num_tiles; tile += num_groups) {
+      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int m0 = m_blk * tile_m + (int)cta_rank * BLOCK_M;
+      const int n0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(empty_bar(s), ph ^ 1);
+        const uint32_t sa = smem_base + s * Cfg::STAGE_BYTES;
+        const uint32_t sb = sa + A_STAGE_BYTES;
+        if (kCtaGroup == 1) {
+          mbar_arrive_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
+          tma_load_2d(sa, &tmA, full_bar(s), kb * BLOCK_K, m0);
+          tma_load_2d(sb, &tmB, full_bar(s), kb * BLOCK_K, n0);
+        } else {
+          // both CTAs' loads complete on the leader's barrier, which expects both halves
+          if (leader) mbar_arrive_expect_tx(full_bar(s), 2 * Cfg::STAGE_BYTES);
+          tma_load_2d_2sm(sa, &tmA, full_bar(s), kb * BLOCK_K, m0);
+          tma_load_2d_2sm(sb, &tmB, full_bar(s), kb * BLOCK_K, n0);
+        }
+        if (++s == kStages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && leader) {
+    // ===================== MMA issuer =====================
+    int s = 0;
+    uint32_t ph = 0;
+    int it = 0;
+    for (int tile = group_id; tile < num_tiles; tile += num_groups, ++it) {
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      mbar_wait_cluster(tempty_bar(as), aph ^ 1);  // epilogues of both CTAs drained this stage
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full_bar(s), ph);
+        tc_fence_after();
+        const uint32_t sa = smem_base + s * Cfg::STAGE_BYTES;
+        const uint64_t adesc = make_desc_kmajor_sw128(sa);
+        const uint64_t bdesc = make_desc_kmajor_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+          // advance 32 bytes (16 bf16) inside the swizzle atom: +2 in the 16-byte address field
+          umma_bf16<kCtaGroup>(d_tmem, adesc + 2u * k, bdesc + 2u * k, Cfg::IDESC,
+                               (kb | k) ? 1u : 0u);
+        }
+        umma_commit<kCtaGroup>(empty_bar(s));  // frees the smem slot (in both CTAs) when MMAs retire
+        if (++s == kStages) { s = 0; ph ^= 1; }
+      }
+      umma_commit<kCtaGroup>(tfull_bar(as));   // accumulator ready (signalled in both CTAs)
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> global =====================
+    const int ew = warp - 4;  // TMEM lane quarter this warp may access (= warp % 4)
+    int it = 0;
+    for (int tile = group_id; tile < num_tiles; tile += num_groups, ++it) {
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int row = m_blk * tile_m + (int)cta_rank * BLOCK_M + ew * 32 + lane;
+      const int col0 = n_blk * BLOCK_N;
+      mbar_wait(tfull_bar(as), aph);
+      tc_fence_after();
+      const bool live = row < args.M;
+      float rs = 1.0f;
+      if (args.row_scale && live) rs = args.row_scale[row];
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N + c * 32, v);
+        tmem_ld_wait();
+        if (live) {
+          if (args.mode == PN_EPI_BF16) {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(args.out) +
+                               (size_t)row * args.ldc + col0 + c * 32;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float a = __uint_as_float(v[j * 8 + 2 * e]) * rs;
+                float b = __uint_as_float(v[j * 8 + 2 * e + 1]) * rs;
+                if (args.relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
+                __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+                pk[e] = *reinterpret_cast<uint32_t*>(&h);
+              }
+              *reinterpret_cast<uint4*>(o + j * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+          } else {  // PN_EPI_RESID_F32: out += acc
+            float* o = reinterpret_cast<float*>(args.out) + (size_t)row * args.ldc + col0 + c * 32;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float4 r = *reinterpret_cast<float4*>(o + j * 4);
+              r.x += __uint_as_float(v[j * 4 + 0]) * rs;
+              r.y += __uint_as_float(v[j * 4 + 1]) * rs;
+              r.z += __uint_as_float(v[j * 4 + 2]) * rs;
+              r.w += __uint_as_float(v[j * 4 + 3]) * rs;
+              *reinterpret_cast<float4*>(o + j * 4) = r;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (kCtaGroup == 1) mbar_arrive(tempty_bar(as));
+        else mbar_arrive_remote(tempty_bar(as), 0);  // the leader's MMA warp owns the wait
+      }
+    }
+  }
+
+  // ---- teardown (single-lane role loops rejoin their warps before the aligned barrier)
+  __syncwarp();
+  tc_fence_before();
+  if (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 2) tmem_dealloc<kCtaGroup>(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+}  // namespace
+
+// bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128-byte swizzle
+int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                         uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return pn_fail(PN_E_LAUNCH, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return pn_fail(PN_E_LAUNCH, "cuTensorMapEncodeTiled failed (%d) rows=%llu cols=%llu", (int)r,
+                   (unsigned long long)rows, (unsigned long long)cols);
+  return PN_OK;
+}
+
+template <int kCtaGroup, int BLOCK_N>
+static int launch_gemm(const void* A, int lda, const void* B, int ldb, const GemmArgs& args,
+                       cudaStream_t st) {
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N>;
+  CUtensorMap tmA, tmB;
+  int rc = pn_make_tmap_bf16_2d(&tmA, A, args.M, args.K, lda, BLOCK_M, BLOCK_K);
+  if (rc) return rc;
+  rc = pn_make_tmap_bf16_2d(&tmB, B, args.N, args.K, ldb, Cfg::B_ROWS, BLOCK_K);
+  if (rc) return rc;
+  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    PN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_done = true;
+  }
+  const int tile_m = BLOCK_M * kCtaGroup;
+  const int tiles = ((args.M + tile_m - 1) / tile_m) * (args.N / BLOCK_N);
+  int groups = PN_SM_COUNT / kCtaGroup;
+  if (tiles < groups) groups = tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(groups * kCtaGroup);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCtaGroup;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, args));
+  g_pn_launches.fetch_add(1, std::memory_order_relaxed);
+  return PN_OK;
+}
+
+int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M,
+                          int N, int K, int mode, int relu, const float* row_scale, int cta_group,
+                          cudaStream_t st) {
+  if (M <= 0 || N <= 0 || K <= 0) return pn_fail(PN_E_BADARG, "pn_gemm: empty problem");
+  if (K % BLOCK_K) return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: K=%d must be a multiple of 64", K);
+  if (N % 128) return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: N=%d must be a multiple of 128", N);
+  if ((lda % 8) || (ldb % 8) || (ldc % 8) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) ||
+      ((uintptr_t)out & 15))
+    return pn_fail(PN_E_BADARG, "pn_gemm: operands must be 16-byte aligned with ld %% 8 == 0");
+  if (mode != PN_EPI_BF16 && mode != PN_EPI_RESID_F32) return pn_fail(PN_E_BADARG, "pn_gemm: mode");
+  GemmArgs a;
+  a.M = M; a.N = N; a.K = K; a.out = out; a.ldc = ldc; a.mode = mode; a.relu = relu;
+  a.row_scale = row_scale;
+  const bool n256 = (N % 256) == 0;
+  if (cta_group == 2) {
+    return n256 ? launch_gemm<2, 256>(A, lda, B, ldb, a, st) : launch_gemm<2, 128>(A, lda, B, ldb, a, st);
+  } else if (cta_group == 1) {
+    return n256 ? launch_gemm<1, 256>(A, lda, B, ldb, a, st) : launch_gemm<1, 128>(A, lda, B, ldb, a, st);
+  }
+  return pn_fail(PN_E_BADARG, "pn_gemm: cta_group must be 1 or 2");
+}
+
+extern "C" int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* out,
+                            int64_t ldc, int64_t M, int64_t N, int64_t K, int mode, int relu,
+                            const float* row_scale, int cta_group, void* stream) {
+  PN_CHECK_ARG(A && B && out);
+  return pn_gemm_bf16_internal(A, (int)lda, B, (int)ldb, out, (int)ldc, (int)M, (int)N, (int)K, mode,
+                               relu, row_scale, cta_group, (cudaStream_t)stream);
+}

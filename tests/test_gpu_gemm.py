@@ -1,0 +1,73 @@
+"""GPU parity: the tcgen05 GEMM (T5 linears) vs a plain fp32 torch matmul of the same bf16 operands."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gemm(A, B, out, mode=0, relu=0, row_scale=None, cta_group=2):
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    M, K = A.shape
+    N = B.shape[0]
+    _lib.check(_lib.lib().pn_gemm_bf16(_lib.ptr(A), A.stride(0), _lib.ptr(B), B.stride(0),
+                                       _lib.ptr(out), out.stride(0), M, N, K, mode, relu,
+                                       _lib.ptr(row_scale), cta_group, _lib.stream()))
+    return out
+
+
+def ref_mm(A, B):
+    return A.float() @ B.float().t()
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 256, 128), (512, 768, 768), (1000, 128, 192),
+                                   (77, 384, 512), (4096, 2304, 768), (2048, 768, 3072),
+                                   (148 * 128 * 3 + 40, 1536, 768)])
+def test_gemm_bf16_out(cta_group, M, N, K):
+    torch.manual_seed(M + N + K)
+    A = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    B = (torch.randn(N, K, device="cuda") * 0.5).bfloat16()
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    run_gemm(A, B, out, cta_group=cta_group)
+    torch.cuda.synchronize()
+    ref = ref_mm(A, B)
+    err = (out.float() - ref).abs().max().item()
+    tol = 0.02 * (K ** 0.5) * 0.25 + 0.02
+    assert err <= tol, f"max err {err} > {tol}"
+    # bf16 rounding of the exact fp32 result is the only error allowed: check tightly in relative terms
+    assert torch.allclose(out.float(), ref, rtol=1.6e-2, atol=1e-2 * K ** 0.5 * 0.05)
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+def test_gemm_relu_rowscale_and_residual(cta_group):
+    torch.manual_seed(5)
+    M, N, K = 640, 512, 256
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    rs = torch.rand(M, device="cuda") + 0.5
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    run_gemm(A, B, out, relu=1, row_scale=rs, cta_group=cta_group)
+    ref = torch.relu(ref_mm(A, B) * rs[:, None])
+    assert torch.allclose(out.float(), ref, rtol=1e-2, atol=2e-2)
+    resid = torch.randn(M, N, device="cuda")
+    acc = resid.clone()
+    run_gemm(A, B, acc, mode=1, cta_group=cta_group)
+    assert torch.allclose(acc, resid + ref_mm(A, B), rtol=1e-4, atol=1e-3)
+    # strided views: A is a column slice of a wider buffer, out a slice too
+    wide = torch.randn(M, K + 128, device="cuda").bfloat16()
+    Av = wide[:, 64:64 + K]
+    outw = torch.zeros(M, N + 256, device="cuda", dtype=torch.bfloat16)
+    run_gemm(Av, B, outw[:, 128:128 + N], cta_group=cta_group)
+    assert torch.allclose(outw[:, 128:128 + N].float(), ref_mm(Av, B), rtol=1.6e-2, atol=2e-2)
+    assert (outw[:, :128] == 0).all() and (outw[:, 128 + N:] == 0).all()
+
+
+def test_gemm_rejects_bad_shapes():
+    from pacednegatives_b200 import _lib
+    A = torch.zeros(64, 100, device="cuda", dtype=torch.bfloat16)
+    B = torch.zeros(128, 100, device="cuda", dtype=torch.bfloat16)
+    out = torch.zeros(64, 128, device="cuda", dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError):
+        run_gemm(A, B, out)
