@@ -169,6 +169,41 @@ int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* o
                  int64_t M, int64_t N, int64_t K, int mode, int relu, const float* row_scale,
                  int cta_group, void* stream);
 
+/* ------------------------------------------------------------------ a1 / a9 / a12: monoT5 scorer
+ * Replaces transformers.T5ForConditionalGeneration as the reference calls it (lceT5.py:106,132-133,
+ * 149-150; pairwrapper.py:223-247; the re-rank formula distill/wrapper.py:34-38).  ReLU FFN, RMSNorm,
+ * 32-bucket relative bias, tied embedding/head scaled by d_model^-0.5, d_kv = 64, no attention mask
+ * (the reference passes none), dropout off.
+ */
+typedef struct PnT5 PnT5;
+typedef struct PnT5Config {
+  int32_t vocab, d_model, d_kv, d_ff, n_layers, n_dec_layers, n_heads;
+  int32_t rel_buckets, rel_max_dist;
+  int32_t pad_id; /* also decoder_start_token_id */
+  float eps;
+} PnT5Config;
+
+int pn_t5_create(const PnT5Config* cfg, PnT5** out);
+int pn_t5_destroy(PnT5* m);
+/* options: "cta_group" = 1 | 2 (tcgen05 tile mode of the linears) */
+int pn_t5_set_option(PnT5* m, const char* name, int64_t value);
+/* One parameter by its HuggingFace state_dict name (e.g. "encoder.block.3.layer.0.SelfAttention.q.weight"),
+ * fp32 contiguous DEVICE tensor in HF's layout; converted into the handle's packed bf16 buffers. */
+int pn_t5_load_weight(PnT5* m, const char* hf_name, const float* src, int64_t numel, void* stream);
+/* checks every parameter arrived, expands the relative-position bias tables (syncs the stream) */
+int pn_t5_finalize(PnT5* m, void* stream);
+int64_t pn_t5_workspace_bytes(const PnT5* m, int64_t docs, int32_t S, int32_t T, int want_logits);
+int32_t pn_t5_vocab_pad(const PnT5* m);
+/* Re-rank scores for `docs` prompts of S token ids (int32 [docs,S]): encoder, one decoder step from the
+ * start token, two-row head: z2_out[d] = (z_true, z_false), score_out[d] = log_softmax(z2)[0]. */
+int pn_t5_score(PnT5* m, const int32_t* ids, int64_t docs, int32_t S, int32_t rel_id, int32_t nrel_id,
+                float* score_out, float* z2_out, void* workspace, int64_t workspace_bytes, void* stream);
+/* model(input_ids=ids, labels=labels).logits for T = 1 or 2 label positions (int64 [docs,T]):
+ * logits_out fp32 [docs*T, pn_t5_vocab_pad()] (nullable), z2_out fp32 [docs*T, 2] (nullable). */
+int pn_t5_logits(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S, int32_t T,
+                 int32_t rel_id, int32_t nrel_id, float* logits_out, float* z2_out, void* workspace,
+                 int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

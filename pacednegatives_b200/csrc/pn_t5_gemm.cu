@@ -184,6 +184,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               }
               *reinterpret_cast<uint4*>(o + j * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             }
+          } else if (args.mode == PN_EPI_F32) {  // fp32 store
+            float* o = reinterpret_cast<float*>(args.out) + (size_t)row * args.ldc + col0 + c * 32;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float4 r;
+              r.x = __uint_as_float(v[j * 4 + 0]) * rs;
+              r.y = __uint_as_float(v[j * 4 + 1]) * rs;
+              r.z = __uint_as_float(v[j * 4 + 2]) * rs;
+              r.w = __uint_as_float(v[j * 4 + 3]) * rs;
+              *reinterpret_cast<float4*>(o + j * 4) = r;
+            }
           } else {  // PN_EPI_RESID_F32: out += acc
             float* o = reinterpret_cast<float*>(args.out) + (size_t)row * args.ldc + col0 + c * 32;
 #pragma unroll
@@ -297,7 +308,8 @@ int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* 
   if ((lda % 8) || (ldb % 8) || (ldc % 8) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) ||
       ((uintptr_t)out & 15))
     return pn_fail(PN_E_BADARG, "pn_gemm: operands must be 16-byte aligned with ld %% 8 == 0");
-  if (mode != PN_EPI_BF16 && mode != PN_EPI_RESID_F32) return pn_fail(PN_E_BADARG, "pn_gemm: mode");
+  if (mode != PN_EPI_BF16 && mode != PN_EPI_RESID_F32 && mode != PN_EPI_F32)
+    return pn_fail(PN_E_BADARG, "pn_gemm: mode");
   GemmArgs a;
   a.M = M; a.N = N; a.K = K; a.out = out; a.ldc = ldc; a.mode = mode; a.relu = relu;
   a.row_scale = row_scale;

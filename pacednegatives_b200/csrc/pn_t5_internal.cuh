@@ -4,7 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-enum { PN_EPI_BF16 = 0, PN_EPI_RESID_F32 = 1 };
+enum { PN_EPI_BF16 = 0, PN_EPI_RESID_F32 = 1, PN_EPI_F32 = 2 };
 
 // C = A[M,K] . B[N,K]^T on the tcgen05 path (pn_t5_gemm.cu).  mode PN_EPI_BF16: bf16 out (optional
 // ReLU, optional per-row scale); PN_EPI_RESID_F32: fp32 out += acc.
@@ -14,3 +14,14 @@ int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* 
 
 int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                          uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols);
+
+#include <cuda_bf16.h>
+// T5 encoder self-attention on tcgen05 (pn_t5_attn.cu).  qkv rows are doc*S + position.
+int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
+                    int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out,
+                    cudaStream_t st);
+// decoder self / cross attention for T <= 2 query tokens per document
+int pn_t5_dec_attn(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_bfloat16* k,
+                   const __nv_bfloat16* v, int ld_kv, int k_col, int v_col, int docs, int T, int Sk,
+                   int n_heads, int causal, const float* bias, __nv_bfloat16* out, int ld_out,
+                   cudaStream_t st);

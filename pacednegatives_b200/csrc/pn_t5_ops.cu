@@ -1,0 +1,169 @@
+// Bandwidth-bound pieces of the T5 forward: embedding gather, T5 RMSNorm (HF:55-69),
+// weight conversion, and the two-row monoT5 head (HF:1107-1110 + distill/wrapper.py:34-38).
+#include "pn_common.cuh"
+#include "pn_t5_internal.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// hidden[row, :] = table[ids[row], :]   (fp32 table -> fp32 residual stream), one warp per row
+__global__ void __launch_bounds__(kThreads)
+embed_kernel(const int32_t* __restrict__ ids, const float* __restrict__ table, int64_t rows, int d,
+             int vocab, float* __restrict__ hidden) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
+  for (int64_t r = w; r < rows; r += nw) {
+    int id = ids[r];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    const float4* src = reinterpret_cast<const float4*>(table + (size_t)id * d);
+    float4* dst = reinterpret_cast<float4*>(hidden + (size_t)r * d);
+    for (int i = lane; i < d / 4; i += 32) dst[i] = src[i];
+  }
+}
+
+// out[row, :] = bf16( x * rsqrt(mean(x^2) + eps) * w ), one warp per row, row held in registers
+template <int MAXV>  // float4 per lane
+__global__ void __launch_bounds__(kThreads)
+rmsnorm_kernel(const float* __restrict__ x, const float* __restrict__ w, int64_t rows, int d,
+               float eps, __nv_bfloat16* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t wid = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
+  const int nv = d / 4;
+  for (int64_t r = wid; r < rows; r += nw) {
+    const float4* src = reinterpret_cast<const float4*>(x + (size_t)r * d);
+    float4 v[MAXV];
+    float ss = 0.0f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        v[i] = src[c];
+        ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+      }
+    }
+    ss = pn_warp_sum(ss);
+    const float rs = rsqrtf(ss / (float)d + eps);
+    uint2* dst = reinterpret_cast<uint2*>(out + (size_t)r * d);
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        const float4 g = reinterpret_cast<const float4*>(w)[c];
+        __nv_bfloat162 a = __floats2bfloat162_rn(v[i].x * rs * g.x, v[i].y * rs * g.y);
+        __nv_bfloat162 b = __floats2bfloat162_rn(v[i].z * rs * g.z, v[i].w * rs * g.w);
+        dst[c] = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+f32_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * kThreads)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+// One warp per (doc, t): y = rmsnorm(x) * w * d^-0.5 ; z = y . E[rel], y . E[nrel]
+// score = log_softmax([z_true, z_false])[0]
+__global__ void __launch_bounds__(kThreads)
+head2_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ emb,
+             int64_t rows, int d, float eps, int rel_id, int nrel_id, float* __restrict__ score,
+             float* __restrict__ z2) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  if (r >= rows) return;
+  const float* xr = x + (size_t)r * d;
+  const float* et = emb + (size_t)rel_id * d;
+  const float* ef = emb + (size_t)nrel_id * d;
+  float ss = 0.0f, zt = 0.0f, zf = 0.0f;
+  for (int i = lane; i < d; i += 32) {
+    const float v = xr[i];
+    ss += v * v;
+    const float y = v * w[i];
+    zt += y * et[i];
+    zf += y * ef[i];
+  }
+  ss = pn_warp_sum(ss);
+  zt = pn_warp_sum(zt);
+  zf = pn_warp_sum(zf);
+  if (lane == 0) {
+    const float k = rsqrtf(ss / (float)d + eps) * rsqrtf((float)d);
+    zt *= k; zf *= k;
+    const float dlt = zf - zt;
+    const float s = dlt > 0.0f ? -(dlt + log1pf(expf(-dlt))) : -log1pf(expf(dlt));
+    if (score) score[r] = s;
+    if (z2) { z2[2 * r] = zt; z2[2 * r + 1] = zf; }
+  }
+}
+
+// bf16 y = rmsnorm(x) * w * d^-0.5 for the full-vocabulary head GEMM
+__global__ void __launch_bounds__(kThreads)
+head_prep_kernel(const float* __restrict__ x, const float* __restrict__ w, int64_t rows, int d,
+                 float eps, __nv_bfloat16* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  if (r >= rows) return;
+  const float* xr = x + (size_t)r * d;
+  float ss = 0.0f;
+  for (int i = lane; i < d; i += 32) ss += xr[i] * xr[i];
+  ss = pn_warp_sum(ss);
+  const float k = rsqrtf(ss / (float)d + eps) * rsqrtf((float)d);
+  for (int i = lane; i < d; i += 32) out[(size_t)r * d + i] = __float2bfloat16_rn(xr[i] * w[i] * k);
+}
+
+// hidden[row, :] = table[ids[row], :] for the decoder inputs (ids int32 [rows])
+}  // namespace
+
+int pn_t5_embed(const int32_t* ids, const float* table, int64_t rows, int d, int vocab, float* hidden,
+                cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  if (d % 4) return pn_fail(PN_E_UNSUPPORTED, "embed: d_model %% 4 != 0");
+  embed_kernel<<<pn_grid(rows * 32, kThreads, 1, 8), kThreads, 0, st>>>(ids, table, rows, d, vocab,
+                                                                        hidden);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_rmsnorm(const float* x, const float* w, int64_t rows, int d, float eps, __nv_bfloat16* out,
+                  cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  if (d % 4 || d > 32 * 4 * 16) return pn_fail(PN_E_UNSUPPORTED, "rmsnorm: d_model=%d unsupported", d);
+  const int grid = pn_grid(rows * 32, kThreads, 1, 8);
+  if (d <= 32 * 4 * 4)
+    rmsnorm_kernel<4><<<grid, kThreads, 0, st>>>(x, w, rows, d, eps, out);
+  else if (d <= 32 * 4 * 8)
+    rmsnorm_kernel<8><<<grid, kThreads, 0, st>>>(x, w, rows, d, eps, out);
+  else
+    rmsnorm_kernel<16><<<grid, kThreads, 0, st>>>(x, w, rows, d, eps, out);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_f32_to_bf16(const float* src, __nv_bfloat16* dst, int64_t n, cudaStream_t st) {
+  if (n == 0) return PN_OK;
+  f32_to_bf16_kernel<<<pn_grid(n, kThreads, 4, 8), kThreads, 0, st>>>(src, dst, n);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, int d, float eps,
+                int rel_id, int nrel_id, float* score, float* z2, cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  head2_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(
+      x, w, emb, rows, d, eps, rel_id, nrel_id, score, z2);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float eps,
+                    __nv_bfloat16* out, cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  head_prep_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(
+      x, w, rows, d, eps, out);
+  PN_LAUNCHED();
+  return PN_OK;
+}
