@@ -169,6 +169,12 @@ int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* o
                  int64_t M, int64_t N, int64_t K, int mode, int relu, const float* row_scale,
                  int cta_group, void* stream);
 
+/* T5 encoder self-attention (HF modeling_t5.py:308-336): out = softmax(Q K^T + bias[h, j-i]) V per
+ * (document, head), no 1/sqrt(d) scaling, d_kv = 64, S <= 512, no mask.  qkv bf16 [docs*S, 3*H*64] holds
+ * q | k | v column blocks; bias fp32 [H, 1023] indexed by (j - i + 511); out bf16 [docs*S, H*64]. */
+int pn_t5_self_attention(const void* qkv, int32_t docs, int32_t S, int32_t n_heads, const float* bias,
+                         void* out, void* stream);
+
 /* ------------------------------------------------------------------ a1 / a9 / a12: monoT5 scorer
  * Replaces transformers.T5ForConditionalGeneration as the reference calls it (lceT5.py:106,132-133,
  * 149-150; pairwrapper.py:223-247; the re-rank formula distill/wrapper.py:34-38).  ReLU FFN, RMSNorm,

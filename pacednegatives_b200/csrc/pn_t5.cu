@@ -439,3 +439,12 @@ extern "C" int pn_t5_logits(PnT5* m, const int32_t* ids, const int64_t* labels, 
 }
 
 extern "C" int32_t pn_t5_vocab_pad(const PnT5* m) { return m ? m->vocab_pad : -1; }
+
+extern "C" int pn_t5_self_attention(const void* qkv, int32_t docs, int32_t S, int32_t n_heads,
+                                    const float* bias, void* out, void* stream) {
+  PN_CHECK_ARG(qkv && bias && out && docs >= 0 && n_heads > 0);
+  if (docs == 0) return PN_OK;
+  const int di = n_heads * 64;
+  return pn_t5_self_attn((const __nv_bfloat16*)qkv, 3 * di, 0, di, 2 * di, docs, S, n_heads, bias,
+                         (__nv_bfloat16*)out, di, (cudaStream_t)stream);
+}

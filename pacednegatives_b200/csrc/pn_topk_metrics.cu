@@ -14,7 +14,8 @@ namespace {
 constexpr int kThreads = 256;
 
 __device__ __forceinline__ uint32_t orderable(float f) {
-  const uint32_t u = __float_as_uint(f);
+  // -0.0f ties with +0.0f (trec_eval compares the floats), so both map to the key of +0.0f
+  const uint32_t u = (f == 0.0f) ? 0u : __float_as_uint(f);
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 __device__ __forceinline__ float unorderable(uint32_t o) {

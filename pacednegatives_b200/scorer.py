@@ -153,19 +153,3 @@ class MonoT5Scorer:
         out["scores"] = scores
         return out
 
-
-def smoke():
-    """Tiny end-to-end scorer call on cuda:0 checked against the fp32 CPU oracle."""
-    import numpy as np
-    from oracle import t5 as ot
-    dims = ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
-    w = ot.init_weights(dims, seed=11)
-    m = MonoT5Scorer(T5Dims(**dims.__dict__), w, rel_id=117, nrel_id=213)
-    rng = np.random.RandomState(0)
-    ids = rng.randint(2, dims.vocab, size=(5, 128)).astype(np.int64)
-    ids[:, -1] = 1
-    got = m.score(ids).cpu().numpy()
-    exp, _ = ot.score(w, dims, ids, 117, 213)
-    err = float(np.abs(got - exp).max())
-    assert err < 2e-2, f"scorer smoke mismatch {err}"
-    return err

@@ -11,9 +11,11 @@ def run_gemm(A, B, out, mode=0, relu=0, row_scale=None, cta_group=2):
     _lib.require_gpu()
     M, K = A.shape
     N = B.shape[0]
-    _lib.check(_lib.lib().pn_gemm_bf16(_lib.ptr(A), A.stride(0), _lib.ptr(B), B.stride(0),
-                                       _lib.ptr(out), out.stride(0), M, N, K, mode, relu,
-                                       _lib.ptr(row_scale), cta_group, _lib.stream()))
+    import ctypes
+    vp = lambda t: ctypes.c_void_p(t.data_ptr())  # row-strided views are allowed (lda/ldc)
+    _lib.check(_lib.lib().pn_gemm_bf16(vp(A), A.stride(0), vp(B), B.stride(0), vp(out), out.stride(0),
+                                       M, N, K, mode, relu, _lib.ptr(row_scale), cta_group,
+                                       _lib.stream()))
     return out
 
 

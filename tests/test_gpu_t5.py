@@ -1,0 +1,147 @@
+"""GPU parity: the monoT5 scorer (tcgen05 GEMMs + fused attention) vs the fp32 CPU oracle and the
+HF-generated golden vectors.  Tolerance from BASELINE.json north_star: scores and losses within 2e-2
+absolute in bf16."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import t5 as ot, loss as ol
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+
+def make(dims, seed, **kw):
+    from pacednegatives_b200.scorer import MonoT5Scorer, T5Dims
+    w = ot.init_weights(dims, seed=seed)
+    return w, MonoT5Scorer(T5Dims(**dims.__dict__), w, **kw)
+
+
+def rand_ids(rng, n, S, vocab):
+    ids = rng.randint(2, vocab, size=(n, S)).astype(np.int64)
+    ids[:, -1] = 1
+    return ids
+
+
+def test_self_attention_kernel_vs_torch():
+    """The tcgen05 attention kernel alone: softmax(QK^T + bias) V per (doc, head)."""
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    lib = _lib.lib()
+    torch.manual_seed(0)
+    for docs, S, H in [(3, 512, 2), (2, 128, 4), (2, 384, 1), (1, 200, 2), (2, 77, 2)]:
+        di = H * 64
+        qkv = (torch.randn(docs * S, 3 * di, device="cuda") * 0.5).bfloat16()
+        bias = torch.randn(H, 1023, device="cuda")
+        out = torch.zeros(docs * S, di, device="cuda", dtype=torch.bfloat16)
+        _lib.check(lib.pn_t5_self_attention(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(out),
+                                            _lib.stream()))
+        q, k, v = [t.float().view(docs, S, H, 64).transpose(1, 2) for t in qkv.split(di, dim=1)]
+        pos = torch.arange(S, device="cuda")
+        b = bias[:, (pos[None, :] - pos[:, None]) + 511]       # [H, S, S]
+        p = torch.softmax(q @ k.transpose(2, 3) + b[None], dim=-1)
+        ref = (p @ v).transpose(1, 2).reshape(docs * S, di)
+        err = (out.float() - ref).abs().max().item()
+        assert err < 2e-2, f"docs={docs} S={S} H={H}: max err {err}"
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+def test_score_tiny_golden(golden_dir, cta_group):
+    g = np.load(os.path.join(golden_dir, "t5_tiny_golden.npz"))
+    v, d, kv, ff, L, Ld, H = [int(x) for x in g["dims"]]
+    dims = ot.T5Dims(vocab=v, d_model=d, d_kv=kv, d_ff=ff, n_layers=L, n_dec_layers=Ld, n_heads=H)
+    rel, nrel = [int(x) for x in g["rel_ids"]]
+    w, m = make(dims, int(g["seed"]), rel_id=rel, nrel_id=nrel, cta_group=cta_group)
+    s, z2 = m.score(g["pids"], return_z2=True)
+    np.testing.assert_allclose(z2.cpu().numpy(), g["p1_z2"], atol=TOL)
+    np.testing.assert_allclose(s.cpu().numpy(), g["p1_score"], atol=TOL)
+    # LCE path: two label positions, full-vocabulary logits, reference pair_loss
+    k = int(g["k"])
+    pl, pz = m.logits(g["pids"], g["plab"])
+    nl, nz = m.logits(g["nids"], g["nlab"])
+    np.testing.assert_allclose(pl.cpu().numpy(), g["plogits"], atol=3e-2)
+    np.testing.assert_allclose(nl.cpu().numpy(), g["nlogits"], atol=3e-2)
+    from pacednegatives_b200.loss import pair_loss
+    ce = pair_loss(pl.contiguous(), nl.contiguous().view(-1, k, v), torch.tensor(g["plab"]).cuda(),
+                   torch.tensor(g["nlab"]).cuda(), True)
+    np.testing.assert_allclose(ce.cpu().numpy(), g["pair_loss"], atol=TOL)
+    np.testing.assert_allclose(pz.cpu().numpy()[:, 0], g["plogits"][:, 0, [rel, nrel]], atol=3e-2)
+
+
+@pytest.mark.parametrize("S", [128, 200, 512])
+def test_score_small_vs_oracle(S):
+    dims = ot.T5Dims(vocab=1024, d_model=256, d_kv=64, d_ff=512, n_layers=3, n_dec_layers=3, n_heads=4)
+    w, m = make(dims, 3, rel_id=17, nrel_id=23, chunk_docs=4)
+    ids = rand_ids(np.random.RandomState(S), 6, S, dims.vocab)   # 6 docs, chunks of 4: ragged last chunk
+    s, z2 = m.score(ids, return_z2=True)
+    es, ez = ot.score(w, dims, ids, 17, 23)
+    np.testing.assert_allclose(z2.cpu().numpy(), ez, atol=TOL)
+    np.testing.assert_allclose(s.cpu().numpy(), es, atol=TOL)
+
+
+def test_cfg1_t5_small_lce_plumbing():
+    """BASELINE config 0: t5-small, 8 queries x (1 pos + 7 negs), seq 128: pair_loss + weights."""
+    dims = ot.T5_SMALL
+    w, m = make(dims, 0, rel_id=1176, nrel_id=6136)
+    rng = np.random.RandomState(1234)
+    Q, k, S = 8, 7, 128
+    pids, nids = rand_ids(rng, Q, S, 32100), rand_ids(rng, Q * k, S, 32100)
+    plab = np.tile([[1176, 1]], (Q, 1)).astype(np.int64)
+    nlab = np.tile([[6136, 1]], (Q * k, 1)).astype(np.int64)
+    pl, _ = m.logits(pids, plab)
+    nl, _ = m.logits(nids, nlab)
+    from pacednegatives_b200.loss import pair_loss
+    from pacednegatives_b200.weights import spl_weights
+    ce = pair_loss(pl.contiguous(), nl.contiguous().view(-1, k, dims.vocab), torch.tensor(plab).cuda(),
+                   torch.tensor(nlab).cuda(), True)
+    epl = ot.logits(w, dims, pids, plab)
+    enl = ot.logits(w, dims, nids, nlab)
+    ece = ol.pair_loss(epl, enl.reshape(-1, k, dims.vocab), plab, nlab, True)
+    assert ce.shape == (Q * 2,)
+    np.testing.assert_allclose(ce.cpu().numpy(), ece, atol=TOL)
+    # weights from the GPU losses are bit-exact against the oracle applied to the same losses
+    from oracle import weights as ow
+    wts, keep, _ = spl_weights(ce, torch.tensor([0.3466]).cuda(), 0.0, 0, True, False)
+    ew, ek = ow.spl_weights(ce.cpu().numpy(), 0.3466)
+    np.testing.assert_array_equal(wts.cpu().numpy(), ew)
+    np.testing.assert_array_equal(keep.cpu().numpy().astype(bool), ek)
+
+
+def test_base_dims_score_vs_oracle():
+    """monoT5-base dimensions (the bench workload's model) on a few documents."""
+    dims = ot.T5_BASE
+    w, m = make(dims, 5, rel_id=1176, nrel_id=6136)
+    ids = rand_ids(np.random.RandomState(2345), 3, 512, 32100)
+    s, z2 = m.score(ids, return_z2=True)
+    es, ez = ot.score(w, dims, ids, 1176, 6136)
+    np.testing.assert_allclose(z2.cpu().numpy(), ez, atol=TOL)
+    np.testing.assert_allclose(s.cpu().numpy(), es, atol=TOL)
+
+
+def test_rerank_end_to_end_ranking_matches_oracle():
+    dims = ot.T5Dims(vocab=512, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
+    w, m = make(dims, 9, rel_id=5, nrel_id=6)
+    rng = np.random.RandomState(7)
+    Q, C, S = 3, 40, 128
+    ids = rand_ids(rng, Q * C, S, dims.vocab).reshape(Q, C, S)
+    rels = rng.choice(4, size=(Q, C), p=[.8, .1, .06, .04]).astype(np.uint8)
+    docids = np.stack([rng.permutation(1000)[:C] for _ in range(Q)]).astype(np.int32)
+    out = m.rerank(ids, torch.tensor(docids).cuda(), torch.tensor(rels).cuda(), K=10)
+    from oracle import metrics as om
+    # ranking of the GPU scores must equal the oracle ranking of the same scores (bit-exact stage)
+    eids, esc, em = om.batch_metrics(out["scores"].cpu().numpy(), docids, rels, 10)
+    np.testing.assert_array_equal(out["top_ids"].cpu().numpy(), eids)
+    np.testing.assert_allclose(out["metrics"].cpu().numpy(), em, rtol=1e-6, atol=1e-7)
+    es, _ = ot.score(w, dims, ids.reshape(Q * C, S), 5, 6)
+    np.testing.assert_allclose(out["scores"].cpu().numpy().reshape(-1), es, atol=TOL)
+
+
+def test_missing_weight_is_an_error():
+    from pacednegatives_b200.scorer import MonoT5Scorer, T5Dims
+    dims = ot.T5Dims(vocab=256, d_model=128, d_kv=64, d_ff=256, n_layers=1, n_dec_layers=1, n_heads=2)
+    w = ot.init_weights(dims, seed=1)
+    del w["decoder.block.0.layer.1.EncDecAttention.k.weight"]
+    with pytest.raises(ValueError, match="missing weight"):
+        MonoT5Scorer(T5Dims(**dims.__dict__), w)
