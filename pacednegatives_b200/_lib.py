@@ -50,6 +50,8 @@ SIGNATURES = {
     "pn_t5_score": (c_int, [c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "pn_t5_logits": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp,
                              c_i64, c_vp]),
+    "pn_prof_enable": (c_int, [c_int]),
+    "pn_prof_read": (c_int, [c_int, c_vp, c_vp, c_vp]),
     "pn_topk_metrics": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
 }
 

@@ -43,6 +43,24 @@ static inline int pn_fail(int code, const char* fmt, ...) {
       return pn_fail(PN_E_LAUNCH, "%s: launch failed: %s", __func__, cudaGetErrorString(e__)); \
   } while (0)
 
+// ---- per-kernel-class device timing (pn_prof_*, pn_api.cu): CUDA events recorded on the launching
+// stream around a launch when profiling is enabled; bench.py reads the sums for its roofline object.
+enum { PN_PROF_GEMM = 0, PN_PROF_ATTN = 1, PN_PROF_ELEMWISE = 2, PN_PROF_WGRAD = 3, PN_PROF_ATTN_BWD = 4,
+       PN_PROF_KINDS = 8 };
+extern std::atomic<int> g_pn_prof_on;
+void pn_prof_begin_impl(int kind, double work, cudaStream_t st);
+void pn_prof_end_impl(cudaStream_t st);
+struct PnProfScope {
+  cudaStream_t st;
+  bool on;
+  PnProfScope(int kind, double work, cudaStream_t s) : st(s), on(g_pn_prof_on.load(std::memory_order_relaxed) != 0) {
+    if (on) pn_prof_begin_impl(kind, work, st);
+  }
+  ~PnProfScope() {
+    if (on) pn_prof_end_impl(st);
+  }
+};
+
 // grid for a grid-stride bandwidth kernel: a multiple of the SM count, capped by the work
 static inline int pn_grid(int64_t work_items, int threads, int items_per_thread, int ctas_per_sm) {
   int64_t need = (work_items + (int64_t)threads * items_per_thread - 1) /

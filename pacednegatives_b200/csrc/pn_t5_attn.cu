@@ -358,6 +358,7 @@ int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, 
                                  ATTN_SMEM));
     attr_done = true;
   }
+  PnProfScope prof(PN_PROF_ATTN, 4.0 * docs * n_heads * (double)S * S * DK, st);
   t5_self_attn_kernel<<<docs * n_heads, kAttnThreads, ATTN_SMEM, st>>>(tm, a);
   PN_LAUNCHED();
   return PN_OK;

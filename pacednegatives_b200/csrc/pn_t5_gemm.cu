@@ -294,6 +294,7 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, const Gem
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  PnProfScope prof(PN_PROF_GEMM, 2.0 * args.M * args.N * args.K, st);
   PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, args));
   g_pn_launches.fetch_add(1, std::memory_order_relaxed);
   return PN_OK;

@@ -57,6 +57,37 @@ def flops_per_doc(dims, S, T=1, full_vocab=False):
                 + Ld * (6 * d * di + 2 * d * ff) * T + Ld * (2 * T * T + 2 * T * S) * di + R * d * T)
 
 
+def random_state_dict(dims, seed=0, device="cuda"):
+    """Random-init weights under HuggingFace state_dict names with HF's initialiser std
+    (T5PreTrainedModel._init_weights, initializer_factor 1.0): what `T5ForConditionalGeneration(config)`
+    gives the reference when no checkpoint is loaded (there is no network for real checkpoints)."""
+    g = torch.Generator(device=device).manual_seed(int(seed))
+    d, di, ff = dims.d_model, dims.d_inner, dims.d_ff
+
+    def normal(shape, std):
+        return torch.randn(shape, generator=g, dtype=torch.float32, device=device) * std
+
+    w = {"shared.weight": normal((dims.vocab, d), 1.0)}
+    for stack, L, dec in (("encoder", dims.n_layers, False), ("decoder", dims.n_dec_layers, True)):
+        for i in range(L):
+            p = f"{stack}.block.{i}.layer."
+            for pre in (["0.SelfAttention."] + (["1.EncDecAttention."] if dec else [])):
+                w[p + pre + "q.weight"] = normal((di, d), (d * dims.d_kv) ** -0.5)
+                w[p + pre + "k.weight"] = normal((di, d), d ** -0.5)
+                w[p + pre + "v.weight"] = normal((di, d), d ** -0.5)
+                w[p + pre + "o.weight"] = normal((d, di), di ** -0.5)
+            if i == 0:
+                w[p + "0.SelfAttention.relative_attention_bias.weight"] = normal(
+                    (dims.rel_buckets, dims.n_heads), d ** -0.5)
+            ffi = 2 if dec else 1
+            w[p + f"{ffi}.DenseReluDense.wi.weight"] = normal((ff, d), d ** -0.5)
+            w[p + f"{ffi}.DenseReluDense.wo.weight"] = normal((d, ff), ff ** -0.5)
+            for j in range(ffi + 1):
+                w[p + f"{j}.layer_norm.weight"] = torch.ones(d, dtype=torch.float32, device=device)
+        w[f"{stack}.final_layer_norm.weight"] = torch.ones(d, dtype=torch.float32, device=device)
+    return w
+
+
 class MonoT5Scorer:
     """dims: T5Dims; state_dict: {hf_name: tensor} (any float dtype, CPU or CUDA)."""
 
