@@ -342,9 +342,9 @@ dec_attn_kernel(const DecAttnArgs a) {
 
 }  // namespace
 
-int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
-                    int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out,
-                    cudaStream_t st) {
+int pn_t5_self_attn_v1(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
+                       int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out,
+                       cudaStream_t st) {
   if (S < 1 || S > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "self-attention: S=%d not in [1,512]", S);
   CUtensorMap tm;
   int rc = pn_make_tmap_bf16_2d(&tm, qkv, (uint64_t)docs * S, (uint64_t)ld_qkv, ld_qkv, 128, DK);

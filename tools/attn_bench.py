@@ -1,0 +1,48 @@
+"""Correctness + timing of the encoder self-attention kernel alone (PN_ATTN_IMPL=1|2 selects the generation)."""
+import os, sys, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from pacednegatives_b200 import _lib
+_lib.require_gpu()
+lib = _lib.lib()
+torch.manual_seed(0)
+
+def run(docs, S, H, check=True, iters=0, scale=0.5):
+    di = H * 64
+    qkv = (torch.randn(docs * S, 3 * di, device="cuda") * scale).bfloat16()
+    bias = torch.randn(H, 1023, device="cuda")
+    out = torch.zeros(docs * S, di, device="cuda", dtype=torch.bfloat16)
+    _lib.check(lib.pn_t5_self_attention(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(out), _lib.stream()))
+    torch.cuda.synchronize()
+    err = None
+    if check:
+        nd = min(docs, 4)
+        q, k, v = [t[: nd * S].float().view(nd, S, H, 64).transpose(1, 2) for t in qkv.split(di, dim=1)]
+        pos = torch.arange(S, device="cuda")
+        b = bias[:, (pos[None, :] - pos[:, None]) + 511]
+        p = torch.softmax(q @ k.transpose(2, 3) + b[None], dim=-1)
+        ref = (p @ v).transpose(1, 2).reshape(nd * S, di)
+        err = (out[: nd * S].float() - ref).abs().max().item()
+        # last docs too (persistent loop tail)
+        q, k, v = [t[-S:].float().view(1, S, H, 64).transpose(1, 2) for t in qkv.split(di, dim=1)]
+        p = torch.softmax(q @ k.transpose(2, 3) + b[None], dim=-1)
+        ref = (p @ v).transpose(1, 2).reshape(S, di)
+        err = max(err, (out[-S:].float() - ref).abs().max().item())
+    ms = None
+    if iters:
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        for _ in range(iters):
+            lib.pn_t5_self_attention(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(out), _lib.stream())
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+    fl = 4.0 * docs * H * S * S * 64
+    print(f"impl={os.environ.get('PN_ATTN_IMPL','2')} docs={docs} S={S} H={H} scale={scale} err={err} ms={ms} "
+          f"TFLOP/s={(fl / ms / 1e9) if ms else None}", flush=True)
+
+for cfg in [(3, 512, 2), (2, 128, 4), (2, 384, 1), (1, 200, 2), (2, 77, 2), (40, 512, 12), (7, 300, 8)]:
+    run(*cfg)
+run(3, 512, 2, scale=3.0)     # large logits: exercises the lazy rescale
+run(3, 512, 2, scale=6.0)     # huge logits: exercises the exact-redo path
+run(2, 300, 4, scale=6.0)
+run(250, 512, 12, check=True, iters=10)
+run(64, 128, 8, check=True, iters=10)
