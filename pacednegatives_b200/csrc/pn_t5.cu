@@ -18,7 +18,9 @@
 #include <string.h>
 
 int pn_t5_embed(const int32_t* ids, const float* table, int64_t rows, int d, int vocab, float* hidden,
-                cudaStream_t st);
+                __nv_bfloat16* copy, float* sumsq, cudaStream_t st);
+int pn_t5_pack_weight(const float* master, const float* colscale, int64_t rows, int cols,
+                      __nv_bfloat16* packed, cudaStream_t st);
 int pn_t5_rmsnorm(const float* x, const float* w, int64_t rows, int d, float eps, __nv_bfloat16* out,
                   cudaStream_t st);
 int pn_t5_f32_to_bf16(const float* src, __nv_bfloat16* dst, int64_t n, cudaStream_t st);
@@ -27,15 +29,24 @@ int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, 
 int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float eps,
                     __nv_bfloat16* out, cudaStream_t st);
 
+#define RC(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+
 namespace {
 
+// One linear: the fp32 master in HF's [out, in] layout (what the optimiser updates) and the packed bf16 copy
+// the tcgen05 GEMM reads, with the RMSNorm weight of its input folded into the columns (pn_t5_finalize).
+struct Lin {
+  float* master = nullptr;
+  __nv_bfloat16* packed = nullptr;
+  int64_t rows = 0;
+  int cols = 0;
+};
 struct EncLayer {
-  __nv_bfloat16 *wqkv = nullptr, *wo = nullptr, *wi = nullptr, *wo2 = nullptr;
+  Lin wqkv, wo, wi, wo2;
   float *ln0 = nullptr, *ln1 = nullptr;
 };
 struct DecLayer {
-  __nv_bfloat16 *wqkv = nullptr, *wo = nullptr, *cq = nullptr, *ckv = nullptr, *co = nullptr,
-                *wi = nullptr, *wo2 = nullptr;
+  Lin wqkv, wo, cq, ckv, co, wi, wo2;
   float *ln0 = nullptr, *ln1 = nullptr, *ln2 = nullptr;
 };
 
@@ -95,14 +106,41 @@ int rel_bucket_bidir(int rel, int num_buckets, int max_distance) {
   return ret + val;
 }
 
-int gemm(const PnT5* m, const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M,
-         int N, int K, int mode, int relu, cudaStream_t st) {
-  return pn_gemm_bf16_internal(A, lda, B, ldb, out, ldc, M, N, K, mode, relu, nullptr, m->cta_group, st);
+// y = RMSNorm(h) . W^T with the norm fused: A = bf16 copy of h, W has the norm weight folded in, and the
+// epilogue scales each row by rsqrt(mean(h^2) + eps) from the partial sums of squares `ss` ([parts][M])
+int gemm_normed(const PnT5* m, const __nv_bfloat16* hb, const float* ss, int parts, const Lin& W, void* out,
+                int ldc, int M, int relu, cudaStream_t st) {
+  PnGemmExtra ex = {};
+  ex.sumsq_in = ss; ex.sumsq_parts = parts; ex.norm_dim = m->cfg.d_model; ex.eps = m->cfg.eps;
+  return pn_gemm_bf16_ex(hb, W.cols, W.packed, W.cols, out, ldc, M, (int)W.rows, W.cols, PN_EPI_BF16, relu, &ex,
+                         m->cta_group, st);
+}
+// h += x . W^T, also refreshing the bf16 copy of h and its per-n-tile sums of squares for the next fused norm
+int gemm_resid(const PnT5* m, const __nv_bfloat16* x, const Lin& W, float* h, __nv_bfloat16* hb, float* ss,
+               int M, cudaStream_t st) {
+  PnGemmExtra ex = {};
+  ex.copy_out = hb; ex.ld_copy = (int)W.rows; ex.sumsq_out = ss;
+  return pn_gemm_bf16_ex(x, W.cols, W.packed, W.cols, h, (int)W.rows, M, (int)W.rows, W.cols, PN_EPI_RESID_F32, 0,
+                         &ex, m->cta_group, st);
+}
+
+// bf16 GEMM operands from the fp32 masters, with each RMSNorm weight folded into the linear that consumes the
+// normalised activations (encoder final norm -> every decoder layer's cross K/V projection)
+int pack_all(PnT5* m, cudaStream_t st) {
+  auto pk = [&](const Lin& L, const float* ln) { return pn_t5_pack_weight(L.master, ln, L.rows, L.cols, L.packed, st); };
+  for (auto& L : m->enc) {
+    RC(pk(L.wqkv, L.ln0)); RC(pk(L.wo, nullptr)); RC(pk(L.wi, L.ln1)); RC(pk(L.wo2, nullptr));
+  }
+  for (auto& L : m->dec) {
+    RC(pk(L.wqkv, L.ln0)); RC(pk(L.wo, nullptr)); RC(pk(L.cq, L.ln1)); RC(pk(L.ckv, m->enc_final));
+    RC(pk(L.co, nullptr)); RC(pk(L.wi, L.ln2)); RC(pk(L.wo2, nullptr));
+  }
+  return PN_OK;
 }
 
 struct Workspace {
-  float* hidden; __nv_bfloat16 *xn, *ctx, *big;
-  float* dh; __nv_bfloat16 *dxn, *dctx, *dbig;
+  float* hidden; __nv_bfloat16 *xn, *ctx, *big; float* ss;
+  float* dh; __nv_bfloat16 *dxn, *dctx, *dbig; float* dss;
   int32_t* dec_ids;
   __nv_bfloat16* head_in; float* logits;
 };
@@ -113,41 +151,45 @@ size_t carve(const PnT5* m, int64_t docs, int S, int T, int want_logits, uint8_t
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff;
   const size_t rows = (size_t)docs * S, drows = (size_t)docs * T;
   const size_t bigc = (size_t)(3 * di > ff ? 3 * di : ff);
+  const size_t parts = (size_t)pn_gemm_sumsq_parts(d);
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes); return base ? base + o : nullptr; };
   w->hidden = (float*)take(rows * d * 4);
   w->xn = (__nv_bfloat16*)take(rows * d * 2);
   w->ctx = (__nv_bfloat16*)take(rows * di * 2);
   w->big = (__nv_bfloat16*)take(rows * bigc * 2);
+  w->ss = (float*)take(rows * parts * 4);
   w->dh = (float*)take(drows * d * 4);
   w->dxn = (__nv_bfloat16*)take(drows * d * 2);
   w->dctx = (__nv_bfloat16*)take(drows * di * 2);
   w->dbig = (__nv_bfloat16*)take(drows * bigc * 2);
+  w->dss = (float*)take(drows * parts * 4);
   w->dec_ids = (int32_t*)take(drows * 4);
   w->head_in = (__nv_bfloat16*)take(drows * d * 2);
   w->logits = (float*)take(want_logits ? drows * (size_t)m->vocab_pad * 4 : 0);
   return off;
 }
 
-#define RC(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
-
+// Encoder: xn always holds the bf16 copy of the residual stream and ss its row sums of squares, so every
+// RMSNorm is fused into the GEMM that consumes it (no standalone norm kernel, no extra pass over hidden).
+// On return xn/ss describe the PRE-final-norm encoder output; the final norm is folded into the cross K/V
+// projections of the decoder.
 int encoder_forward(const PnT5* m, const int32_t* ids, int64_t docs, int S, const Workspace& w,
                     cudaStream_t st) {
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
   const int rows = (int)(docs * S);
-  const float eps = m->cfg.eps;
-  RC(pn_t5_embed(ids, m->emb, rows, d, m->cfg.vocab, w.hidden, st));
+  const int parts = pn_gemm_sumsq_parts(d);
+  RC(pn_t5_embed(ids, m->emb, rows, d, m->cfg.vocab, w.hidden, w.xn, w.ss, st));
+  int cur_parts = 1;
   for (size_t l = 0; l < m->enc.size(); ++l) {
     const EncLayer& L = m->enc[l];
-    RC(pn_t5_rmsnorm(w.hidden, L.ln0, rows, d, eps, w.xn, st));
-    RC(gemm(m, w.xn, d, L.wqkv, d, w.big, 3 * di, rows, 3 * di, d, PN_EPI_BF16, 0, st));
+    RC(gemm_normed(m, w.xn, w.ss, cur_parts, L.wqkv, w.big, 3 * di, rows, 0, st));
     RC(pn_t5_self_attn(w.big, 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx, di, st));
-    RC(gemm(m, w.ctx, di, L.wo, di, w.hidden, d, rows, d, di, PN_EPI_RESID_F32, 0, st));
-    RC(pn_t5_rmsnorm(w.hidden, L.ln1, rows, d, eps, w.xn, st));
-    RC(gemm(m, w.xn, d, L.wi, d, w.big, ff, rows, ff, d, PN_EPI_BF16, 1, st));
-    RC(gemm(m, w.big, ff, L.wo2, ff, w.hidden, d, rows, d, ff, PN_EPI_RESID_F32, 0, st));
+    RC(gemm_resid(m, w.ctx, L.wo, w.hidden, w.xn, w.ss, rows, st));
+    cur_parts = parts;
+    RC(gemm_normed(m, w.xn, w.ss, cur_parts, L.wi, w.big, ff, rows, 1, st));
+    RC(gemm_resid(m, w.big, L.wo2, w.hidden, w.xn, w.ss, rows, st));
   }
-  RC(pn_t5_rmsnorm(w.hidden, m->enc_final, rows, d, eps, w.xn, st));  // xn = encoder output
   return PN_OK;
 }
 
@@ -155,27 +197,28 @@ int encoder_forward(const PnT5* m, const int32_t* ids, int64_t docs, int S, cons
 int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& w, cudaStream_t st) {
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
   const int rows = (int)(docs * S), drows = (int)(docs * T);
-  const float eps = m->cfg.eps;
-  RC(pn_t5_embed(w.dec_ids, m->emb, drows, d, m->cfg.vocab, w.dh, st));
+  const int parts = pn_gemm_sumsq_parts(d);
+  const int enc_parts = m->enc.empty() ? 1 : parts;
+  RC(pn_t5_embed(w.dec_ids, m->emb, drows, d, m->cfg.vocab, w.dh, w.dxn, w.dss, st));
+  int cur_parts = 1;
   for (size_t l = 0; l < m->dec.size(); ++l) {
     const DecLayer& L = m->dec[l];
     // self-attention over the <= T decoder tokens (causal + decoder bias)
-    RC(pn_t5_rmsnorm(w.dh, L.ln0, drows, d, eps, w.dxn, st));
-    RC(gemm(m, w.dxn, d, L.wqkv, d, w.dbig, 3 * di, drows, 3 * di, d, PN_EPI_BF16, 0, st));
+    RC(gemm_normed(m, w.dxn, w.dss, cur_parts, L.wqkv, w.dbig, 3 * di, drows, 0, st));
     RC(pn_t5_dec_attn(w.dbig, 3 * di, 0, w.dbig, w.dbig, 3 * di, di, 2 * di, (int)docs, T, T, H, 1,
                       m->dec_bias, w.dctx, di, st));
-    RC(gemm(m, w.dctx, di, L.wo, di, w.dh, d, drows, d, di, PN_EPI_RESID_F32, 0, st));
-    // cross-attention: K/V projection of all S encoder states (the 13% of FLOPs), no bias
-    RC(pn_t5_rmsnorm(w.dh, L.ln1, drows, d, eps, w.dxn, st));
-    RC(gemm(m, w.dxn, d, L.cq, d, w.dbig, di, drows, di, d, PN_EPI_BF16, 0, st));
-    RC(gemm(m, w.xn, d, L.ckv, d, w.big, 2 * di, rows, 2 * di, d, PN_EPI_BF16, 0, st));
+    RC(gemm_resid(m, w.dctx, L.wo, w.dh, w.dxn, w.dss, drows, st));
+    cur_parts = parts;
+    // cross-attention: K/V projection of all S encoder states (the 13% of FLOPs), no bias; the encoder's
+    // final RMSNorm is fused into this GEMM
+    RC(gemm_normed(m, w.dxn, w.dss, cur_parts, L.cq, w.dbig, di, drows, 0, st));
+    RC(gemm_normed(m, w.xn, w.ss, enc_parts, L.ckv, w.big, 2 * di, rows, 0, st));
     RC(pn_t5_dec_attn(w.dbig, di, 0, w.big, w.big, 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
                       w.dctx, di, st));
-    RC(gemm(m, w.dctx, di, L.co, di, w.dh, d, drows, d, di, PN_EPI_RESID_F32, 0, st));
+    RC(gemm_resid(m, w.dctx, L.co, w.dh, w.dxn, w.dss, drows, st));
     // FFN
-    RC(pn_t5_rmsnorm(w.dh, L.ln2, drows, d, eps, w.dxn, st));
-    RC(gemm(m, w.dxn, d, L.wi, d, w.dbig, ff, drows, ff, d, PN_EPI_BF16, 1, st));
-    RC(gemm(m, w.dbig, ff, L.wo2, ff, w.dh, d, drows, d, ff, PN_EPI_RESID_F32, 0, st));
+    RC(gemm_normed(m, w.dxn, w.dss, cur_parts, L.wi, w.dbig, ff, drows, 1, st));
+    RC(gemm_resid(m, w.dbig, L.wo2, w.dh, w.dxn, w.dss, drows, st));
   }
   return PN_OK;
 }
@@ -245,9 +288,17 @@ extern "C" int pn_t5_load_weight(PnT5* m, const char* name, const float* src, in
                      (long long)numel, (long long)want);
     return PN_OK;
   };
-  auto put_bf16 = [&](__nv_bfloat16** slot, size_t total, size_t offset, int64_t cnt) -> int {
-    if (!*slot) RC(dev_alloc(m, slot, total));
-    return pn_t5_f32_to_bf16(src, *slot + offset, cnt, st);
+  // fp32 master [rows_total, cols]; this parameter fills rows [row_off, row_off + cnt / cols)
+  auto put_lin = [&](Lin* L, int64_t rows_total, int cols, int64_t row_off, int64_t cnt) -> int {
+    if (!L->master) {
+      RC(dev_alloc(m, &L->master, (size_t)rows_total * cols));
+      RC(dev_alloc(m, &L->packed, (size_t)rows_total * cols));
+      L->rows = rows_total;
+      L->cols = cols;
+    }
+    PN_CUDA(cudaMemcpyAsync(L->master + row_off * cols, src, cnt * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    m->finalized = false;
+    return PN_OK;
   };
   auto put_f32 = [&](float** slot, int64_t cnt) -> int {
     if (!*slot) RC(dev_alloc(m, slot, (size_t)cnt));
@@ -287,33 +338,33 @@ extern "C" int pn_t5_load_weight(PnT5* m, const char* name, const float* src, in
   if (!is_dec) {
     EncLayer& L = m->enc[blk];
     if (sub == 0) {
-      if (r == "SelfAttention.q.weight") { RC(expect(dd)); return put_bf16(&L.wqkv, 3 * dd, 0, dd); }
-      if (r == "SelfAttention.k.weight") { RC(expect(dd)); return put_bf16(&L.wqkv, 3 * dd, dd, dd); }
-      if (r == "SelfAttention.v.weight") { RC(expect(dd)); return put_bf16(&L.wqkv, 3 * dd, 2 * dd, dd); }
-      if (r == "SelfAttention.o.weight") { RC(expect(dd)); return put_bf16(&L.wo, dd, 0, dd); }
+      if (r == "SelfAttention.q.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 0, dd); }
+      if (r == "SelfAttention.k.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, di, dd); }
+      if (r == "SelfAttention.v.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 2 * di, dd); }
+      if (r == "SelfAttention.o.weight") { RC(expect(dd)); return put_lin(&L.wo, d, di, 0, dd); }
       if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln0, d); }
     } else if (sub == 1) {
-      if (r == "DenseReluDense.wi.weight") { RC(expect((int64_t)ff * d)); return put_bf16(&L.wi, (size_t)ff * d, 0, (int64_t)ff * d); }
-      if (r == "DenseReluDense.wo.weight") { RC(expect((int64_t)ff * d)); return put_bf16(&L.wo2, (size_t)ff * d, 0, (int64_t)ff * d); }
+      if (r == "DenseReluDense.wi.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wi, ff, d, 0, (int64_t)ff * d); }
+      if (r == "DenseReluDense.wo.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wo2, d, ff, 0, (int64_t)ff * d); }
       if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln1, d); }
     }
   } else {
     DecLayer& L = m->dec[blk];
     if (sub == 0) {
-      if (r == "SelfAttention.q.weight") { RC(expect(dd)); return put_bf16(&L.wqkv, 3 * dd, 0, dd); }
-      if (r == "SelfAttention.k.weight") { RC(expect(dd)); return put_bf16(&L.wqkv, 3 * dd, dd, dd); }
-      if (r == "SelfAttention.v.weight") { RC(expect(dd)); return put_bf16(&L.wqkv, 3 * dd, 2 * dd, dd); }
-      if (r == "SelfAttention.o.weight") { RC(expect(dd)); return put_bf16(&L.wo, dd, 0, dd); }
+      if (r == "SelfAttention.q.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 0, dd); }
+      if (r == "SelfAttention.k.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, di, dd); }
+      if (r == "SelfAttention.v.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 2 * di, dd); }
+      if (r == "SelfAttention.o.weight") { RC(expect(dd)); return put_lin(&L.wo, d, di, 0, dd); }
       if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln0, d); }
     } else if (sub == 1) {
-      if (r == "EncDecAttention.q.weight") { RC(expect(dd)); return put_bf16(&L.cq, dd, 0, dd); }
-      if (r == "EncDecAttention.k.weight") { RC(expect(dd)); return put_bf16(&L.ckv, 2 * dd, 0, dd); }
-      if (r == "EncDecAttention.v.weight") { RC(expect(dd)); return put_bf16(&L.ckv, 2 * dd, dd, dd); }
-      if (r == "EncDecAttention.o.weight") { RC(expect(dd)); return put_bf16(&L.co, dd, 0, dd); }
+      if (r == "EncDecAttention.q.weight") { RC(expect(dd)); return put_lin(&L.cq, di, d, 0, dd); }
+      if (r == "EncDecAttention.k.weight") { RC(expect(dd)); return put_lin(&L.ckv, 2 * di, d, 0, dd); }
+      if (r == "EncDecAttention.v.weight") { RC(expect(dd)); return put_lin(&L.ckv, 2 * di, d, di, dd); }
+      if (r == "EncDecAttention.o.weight") { RC(expect(dd)); return put_lin(&L.co, d, di, 0, dd); }
       if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln1, d); }
     } else if (sub == 2) {
-      if (r == "DenseReluDense.wi.weight") { RC(expect((int64_t)ff * d)); return put_bf16(&L.wi, (size_t)ff * d, 0, (int64_t)ff * d); }
-      if (r == "DenseReluDense.wo.weight") { RC(expect((int64_t)ff * d)); return put_bf16(&L.wo2, (size_t)ff * d, 0, (int64_t)ff * d); }
+      if (r == "DenseReluDense.wi.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wi, ff, d, 0, (int64_t)ff * d); }
+      if (r == "DenseReluDense.wo.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wo2, d, ff, 0, (int64_t)ff * d); }
       if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln2, d); }
     }
   }
@@ -372,6 +423,7 @@ extern "C" int pn_t5_finalize(PnT5* m, void* stream) {
   if (!m->dec_bias) RC(dev_alloc(m, &m->dec_bias, db.size()));
   PN_CUDA(cudaMemcpy(m->enc_bias, eb.data(), eb.size() * 4, cudaMemcpyHostToDevice));
   PN_CUDA(cudaMemcpy(m->dec_bias, db.data(), db.size() * 4, cudaMemcpyHostToDevice));
+  RC(pack_all(m, st));
   m->finalized = true;
   return PN_OK;
 }

@@ -18,16 +18,19 @@ constexpr int BLOCK_K = 64;   // one 128-byte swizzle atom of bf16
 constexpr int UMMA_K = 16;
 constexpr int kGemmThreads = 256;
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
+constexpr int EPI_BUF_BYTES = 32 * 128;               // one epilogue warp's 32 rows x 128 B staging tile
+constexpr int EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;      // 4 epilogue warps, double-buffered: 32 KB
 
 template <int kCtaGroup, int BLOCK_N>
 struct GemmCfg {
   static constexpr int B_ROWS = BLOCK_N / kCtaGroup;        // B rows this CTA loads
   static constexpr int B_STAGE_BYTES = B_ROWS * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int kStages = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int kAvail = 227 * 1024 - EPI_BYTES - 1024 /*align slack*/ - 512 /*barriers*/;
+  static constexpr int kStages = kAvail / STAGE_BYTES > 8 ? 8 : kAvail / STAGE_BYTES;
   static constexpr int kAccStages = 2;
   static constexpr int TMEM_COLS = kAccStages * BLOCK_N;    // 512 or 256 (power of two)
-  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
   static constexpr uint32_t IDESC = make_idesc_bf16(BLOCK_M * kCtaGroup, BLOCK_N, 0, 0);
 };
 
@@ -37,18 +40,29 @@ struct GemmArgs {
   int ldc;
   int mode;                // PN_EPI_*
   int relu;
-  const float* row_scale;  // nullable: out = acc * row_scale[row] (fused RMSNorm scale)
+  const float* row_scale;  // nullable: out = acc * row_scale[row]
+  // fused T5 RMSNorm of the A operand (HF:55-69): A holds the un-normalised bf16 residual stream, the norm weight is
+  // folded into B, and acc is scaled by rsqrt(sum_p sumsq_in[p*M + row] / norm_dim + eps)
+  const float* sumsq_in;
+  int sumsq_parts;
+  int norm_dim;
+  float eps;
+  // residual mode extras: bf16 copy of the updated residual stream and per-n-tile row sums of squares of it
+  __nv_bfloat16* copy_out;  // nullable, [M, ld_copy]
+  int ld_copy;
+  float* sumsq_out;         // nullable, [N / BLOCK_N][M]
 };
 
 template <int kCtaGroup, int BLOCK_N>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const GemmArgs args) {
+                 const __grid_constant__ CUtensorMap tmC, const GemmArgs args) {
   using Cfg = GemmCfg<kCtaGroup, BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + kStages * Cfg::STAGE_BYTES;
+  const uint32_t epi_smem = smem_base + kStages * Cfg::STAGE_BYTES;   // 1024-aligned
+  const uint32_t bar_base = epi_smem + EPI_BYTES;
   // barrier layout: full[kStages] empty[kStages] tmem_full[2] tmem_empty[2] | tmem ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
@@ -73,6 +87,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -148,64 +163,146 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       umma_commit<kCtaGroup>(tfull_bar(as));   // accumulator ready (signalled in both CTAs)
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: TMEM -> registers -> global =====================
-    const int ew = warp - 4;  // TMEM lane quarter this warp may access (= warp % 4)
+    // ===================== epilogue: TMEM -> registers -> swizzled smem tile -> global =====================
+    // Each warp owns 32 accumulator rows (TMEM lane quarter = warp % 4) and a private double-buffered 4 KB
+    // staging tile [32 rows x 128 B] in the 128-byte-swizzle layout: thread r writes row r conflict-free.
+    //   bf16 modes : the tile is a 32 x 64 bf16 box, written back by one TMA store (coalesced, asynchronous)
+    //   fp32 modes : the tile is a 32 x 32 fp32 box; the warp re-reads it row-contiguously (8 lanes = one 128 B
+    //                row) so the residual read-modify-write, the bf16 copy and the fp32 store are all coalesced;
+    //                the residual rows are prefetched into registers one chunk ahead
+    const int ew = warp - 4;
+    const uint32_t stage0 = epi_smem + ew * (2 * EPI_BUF_BYTES);
+    uint8_t* stage_gen = smem_raw + (stage0 - smem_u32(smem_raw));
+    const uint32_t swz = (uint32_t)(lane & 7);
+    const int rrow = lane >> 3, rj = lane & 7;        // read-back mapping: iteration i -> row 4*i + rrow, chunk rj
     int it = 0;
+    uint32_t cc = 0;                                  // chunks staged so far (buffer = cc & 1)
     for (int tile = group_id; tile < num_tiles; tile += num_groups, ++it) {
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
-      const int row = m_blk * tile_m + (int)cta_rank * BLOCK_M + ew * 32 + lane;
+      const int row0 = m_blk * tile_m + (int)cta_rank * BLOCK_M + ew * 32;   // first row of this warp
+      const int row = row0 + lane;
       const int col0 = n_blk * BLOCK_N;
-      mbar_wait(tfull_bar(as), aph);
-      tc_fence_after();
       const bool live = row < args.M;
       float rs = 1.0f;
-      if (args.row_scale && live) rs = args.row_scale[row];
+      if (live) {
+        if (args.row_scale) rs = args.row_scale[row];
+        if (args.sumsq_in) {
+          float ss = 0.0f;
+          for (int p = 0; p < args.sumsq_parts; ++p) ss += args.sumsq_in[(size_t)p * args.M + row];
+          rs *= rsqrtf(ss / (float)args.norm_dim + args.eps);
+        }
+      }
+      const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N;
+      if (args.mode == PN_EPI_BF16) {
+        mbar_wait(tfull_bar(as), aph);
+        tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N + c * 32, v);
-        tmem_ld_wait();
-        if (live) {
-          if (args.mode == PN_EPI_BF16) {
-            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(args.out) +
-                               (size_t)row * args.ldc + col0 + c * 32;
+        for (int c = 0; c < BLOCK_N / 64; ++c, ++cc) {
+          const uint32_t buf = stage0 + (cc & 1) * EPI_BUF_BYTES;
+          uint32_t v0[32], v1[32];
+          tmem_ld_32x32(t_row + c * 64, v0);
+          tmem_ld_32x32(t_row + c * 64 + 32, v1);
+          if (lane == 0) tma_store_wait_read<1>();   // the store that used this buffer two chunks ago has drained
+          __syncwarp();
+          tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint32_t pk[4];
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t(&v)[32] = j < 4 ? v0 : v1;
+            uint32_t pk[4];
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                float a = __uint_as_float(v[j * 8 + 2 * e]) * rs;
-                float b = __uint_as_float(v[j * 8 + 2 * e + 1]) * rs;
-                if (args.relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
-                __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-                pk[e] = *reinterpret_cast<uint32_t*>(&h);
+            for (int e = 0; e < 4; ++e) {
+              float x0 = __uint_as_float(v[(j & 3) * 8 + 2 * e]) * rs;
+              float x1 = __uint_as_float(v[(j & 3) * 8 + 2 * e + 1]) * rs;
+              if (args.relu) { x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
+              __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+              pk[e] = *reinterpret_cast<uint32_t*>(&h);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * 128 + ((j ^ swz) << 4)),
+                         "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                         : "memory");
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC, buf, col0 + c * 64, row0);   // rows beyond M are clipped by the tensor map
+            tma_store_commit();
+          }
+        }
+      } else {
+        const bool resid = args.mode == PN_EPI_RESID_F32;
+        float* outf = reinterpret_cast<float*>(args.out);
+        float ssq[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ssq[i] = 0.0f;
+        float4 pre[2][8];                              // residual rows of the next two chunks (register prefetch)
+        auto prefetch = [&](float4(&dst)[8], int c) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = row0 + 4 * i + rrow;
+            dst[i] = (resid && r < args.M && c < BLOCK_N / 32)
+                         ? *reinterpret_cast<const float4*>(outf + (size_t)r * args.ldc + col0 + c * 32 + rj * 4)
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        };
+        prefetch(pre[0], 0);                           // issued before the accumulator is even ready
+        prefetch(pre[1], 1);
+        mbar_wait(tfull_bar(as), aph);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c2 = 0; c2 < BLOCK_N / 32; c2 += 2) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u, ++cc) {
+            const int c = c2 + u;
+            uint8_t* bufg = stage_gen + (cc & 1) * EPI_BUF_BYTES;
+            uint32_t v[32];
+            tmem_ld_32x32(t_row + c * 32, v);
+            tmem_ld_wait();
+            __syncwarp();                              // every lane finished reading this buffer two chunks ago
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float4 f;
+              f.x = __uint_as_float(v[j * 4 + 0]) * rs;
+              f.y = __uint_as_float(v[j * 4 + 1]) * rs;
+              f.z = __uint_as_float(v[j * 4 + 2]) * rs;
+              f.w = __uint_as_float(v[j * 4 + 3]) * rs;
+              *reinterpret_cast<float4*>(bufg + lane * 128 + ((j ^ swz) << 4)) = f;
+            }
+            __syncwarp();
+            float4 cur[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) cur[i] = pre[u][i];
+            prefetch(pre[u], c + 2);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int rr = 4 * i + rrow;
+              const int r = row0 + rr;
+              const float4 acc = *reinterpret_cast<const float4*>(bufg + rr * 128 + ((rj ^ (rr & 7)) << 4));
+              float4 h = cur[i];
+              h.x += acc.x; h.y += acc.y; h.z += acc.z; h.w += acc.w;
+              if (r < args.M) {
+                const size_t off = (size_t)r * args.ldc + col0 + c * 32 + rj * 4;
+                *reinterpret_cast<float4*>(outf + off) = h;
+                if (args.copy_out) {
+                  __nv_bfloat162 lo = __floats2bfloat162_rn(h.x, h.y), hi = __floats2bfloat162_rn(h.z, h.w);
+                  uint2 uu = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+                  *reinterpret_cast<uint2*>(args.copy_out + (size_t)r * args.ld_copy + col0 + c * 32 + rj * 4) = uu;
+                }
               }
-              *reinterpret_cast<uint4*>(o + j * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              ssq[i] += h.x * h.x + h.y * h.y + h.z * h.z + h.w * h.w;
             }
-          } else if (args.mode == PN_EPI_F32) {  // fp32 store
-            float* o = reinterpret_cast<float*>(args.out) + (size_t)row * args.ldc + col0 + c * 32;
+          }
+        }
+        if (args.sumsq_out) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float4 r;
-              r.x = __uint_as_float(v[j * 4 + 0]) * rs;
-              r.y = __uint_as_float(v[j * 4 + 1]) * rs;
-              r.z = __uint_as_float(v[j * 4 + 2]) * rs;
-              r.w = __uint_as_float(v[j * 4 + 3]) * rs;
-              *reinterpret_cast<float4*>(o + j * 4) = r;
-            }
-          } else {  // PN_EPI_RESID_F32: out += acc
-            float* o = reinterpret_cast<float*>(args.out) + (size_t)row * args.ldc + col0 + c * 32;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float4 r = *reinterpret_cast<float4*>(o + j * 4);
-              r.x += __uint_as_float(v[j * 4 + 0]) * rs;
-              r.y += __uint_as_float(v[j * 4 + 1]) * rs;
-              r.z += __uint_as_float(v[j * 4 + 2]) * rs;
-              r.w += __uint_as_float(v[j * 4 + 3]) * rs;
-              *reinterpret_cast<float4*>(o + j * 4) = r;
-            }
+          for (int i = 0; i < 8; ++i) {
+            float t = ssq[i];
+            t += __shfl_xor_sync(0xffffffffu, t, 1);
+            t += __shfl_xor_sync(0xffffffffu, t, 2);
+            t += __shfl_xor_sync(0xffffffffu, t, 4);
+            const int r = row0 + 4 * i + rrow;
+            if (rj == 0 && r < args.M) args.sumsq_out[(size_t)n_blk * args.M + r] = t;
           }
         }
       }
@@ -216,6 +313,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         else mbar_arrive_remote(tempty_bar(as), 0);  // the leader's MMA warp owns the wait
       }
     }
+    if (lane == 0) tma_store_wait_all<0>();            // smem must outlive the last bulk stores
   }
 
   // ---- teardown (single-lane role loops rejoin their warps before the aligned barrier)
@@ -272,6 +370,11 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, const Gem
   if (rc) return rc;
   rc = pn_make_tmap_bf16_2d(&tmB, B, args.N, args.K, ldb, Cfg::B_ROWS, BLOCK_K);
   if (rc) return rc;
+  CUtensorMap tmC = tmA;   // only the bf16 epilogue stores through a tensor map (32-row x 64-column boxes)
+  if (args.mode == PN_EPI_BF16) {
+    rc = pn_make_tmap_bf16_2d(&tmC, args.out, args.M, args.N, args.ldc, 32, 64);
+    if (rc) return rc;
+  }
   auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -295,14 +398,13 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, const Gem
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   PnProfScope prof(PN_PROF_GEMM, 2.0 * args.M * args.N * args.K, st);
-  PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, args));
+  PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, args));
   g_pn_launches.fetch_add(1, std::memory_order_relaxed);
   return PN_OK;
 }
 
-int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M,
-                          int N, int K, int mode, int relu, const float* row_scale, int cta_group,
-                          cudaStream_t st) {
+int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
+                    int mode, int relu, const PnGemmExtra* ex, int cta_group, cudaStream_t st) {
   if (M <= 0 || N <= 0 || K <= 0) return pn_fail(PN_E_BADARG, "pn_gemm: empty problem");
   if (K % BLOCK_K) return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: K=%d must be a multiple of 64", K);
   if (N % 128) return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: N=%d must be a multiple of 128", N);
@@ -313,7 +415,18 @@ int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* 
     return pn_fail(PN_E_BADARG, "pn_gemm: mode");
   GemmArgs a;
   a.M = M; a.N = N; a.K = K; a.out = out; a.ldc = ldc; a.mode = mode; a.relu = relu;
-  a.row_scale = row_scale;
+  a.row_scale = ex ? ex->row_scale : nullptr;
+  a.sumsq_in = ex ? ex->sumsq_in : nullptr;
+  a.sumsq_parts = ex ? ex->sumsq_parts : 0;
+  a.norm_dim = ex ? ex->norm_dim : 1;
+  a.eps = ex ? ex->eps : 0.0f;
+  a.copy_out = ex ? ex->copy_out : nullptr;
+  a.ld_copy = ex ? ex->ld_copy : 0;
+  a.sumsq_out = ex ? ex->sumsq_out : nullptr;
+  if (a.copy_out && ((a.ld_copy % 4) || ((uintptr_t)a.copy_out & 7)))
+    return pn_fail(PN_E_BADARG, "pn_gemm: bf16 copy must be 8-byte aligned with ld %% 4 == 0");
+  if ((a.copy_out || a.sumsq_out) && mode == PN_EPI_BF16)
+    return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
   const bool n256 = (N % 256) == 0;
   if (cta_group == 2) {
     return n256 ? launch_gemm<2, 256>(A, lda, B, ldb, a, st) : launch_gemm<2, 128>(A, lda, B, ldb, a, st);
@@ -321,6 +434,17 @@ int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* 
     return n256 ? launch_gemm<1, 256>(A, lda, B, ldb, a, st) : launch_gemm<1, 128>(A, lda, B, ldb, a, st);
   }
   return pn_fail(PN_E_BADARG, "pn_gemm: cta_group must be 1 or 2");
+}
+
+// number of per-n-tile partial sums the residual epilogue writes per row for an N-wide output
+int pn_gemm_sumsq_parts(int N) { return (N % 256) == 0 ? N / 256 : N / 128; }
+
+int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M,
+                          int N, int K, int mode, int relu, const float* row_scale, int cta_group,
+                          cudaStream_t st) {
+  PnGemmExtra ex = {};
+  ex.row_scale = row_scale;
+  return pn_gemm_bf16_ex(A, lda, B, ldb, out, ldc, M, N, K, mode, relu, &ex, cta_group, st);
 }
 
 extern "C" int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* out,

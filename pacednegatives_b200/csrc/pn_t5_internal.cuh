@@ -12,6 +12,22 @@ int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* 
                           int N, int K, int mode, int relu, const float* row_scale, int cta_group,
                           cudaStream_t st);
 
+#include <cuda_bf16.h>
+// optional epilogue extras of the tcgen05 GEMM (all nullable)
+struct PnGemmExtra {
+  const float* row_scale;     // acc *= row_scale[row]
+  const float* sumsq_in;      // fused RMSNorm of A: acc *= rsqrt(sum_p sumsq_in[p*M+row] / norm_dim + eps)
+  int sumsq_parts;
+  int norm_dim;
+  float eps;
+  __nv_bfloat16* copy_out;    // fp32 modes: bf16 copy of the stored values, [M, ld_copy]
+  int ld_copy;
+  float* sumsq_out;           // fp32 modes: [pn_gemm_sumsq_parts(N)][M] row sums of squares per n-tile
+};
+int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
+                    int mode, int relu, const PnGemmExtra* ex, int cta_group, cudaStream_t st);
+int pn_gemm_sumsq_parts(int N);
+
 int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                          uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols);
 

@@ -7,10 +7,12 @@ namespace {
 
 constexpr int kThreads = 256;
 
-// hidden[row, :] = table[ids[row], :]   (fp32 table -> fp32 residual stream), one warp per row
+// hidden[row, :] = table[ids[row], :]   (fp32 table -> fp32 residual stream), one warp per row; optionally also
+// the bf16 copy of the row and its sum of squares (inputs of the RMSNorm fused into the next GEMM)
 __global__ void __launch_bounds__(kThreads)
 embed_kernel(const int32_t* __restrict__ ids, const float* __restrict__ table, int64_t rows, int d,
-             int vocab, float* __restrict__ hidden) {
+             int vocab, float* __restrict__ hidden, __nv_bfloat16* __restrict__ copy,
+             float* __restrict__ sumsq) {
   const int lane = threadIdx.x & 31;
   const int64_t w = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
@@ -19,7 +21,33 @@ embed_kernel(const int32_t* __restrict__ ids, const float* __restrict__ table, i
     id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
     const float4* src = reinterpret_cast<const float4*>(table + (size_t)id * d);
     float4* dst = reinterpret_cast<float4*>(hidden + (size_t)r * d);
-    for (int i = lane; i < d / 4; i += 32) dst[i] = src[i];
+    float ss = 0.0f;
+    for (int i = lane; i < d / 4; i += 32) {
+      const float4 v = src[i];
+      dst[i] = v;
+      ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+      if (copy) {
+        __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+        reinterpret_cast<uint2*>(copy + (size_t)r * d)[i] =
+            make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+      }
+    }
+    if (sumsq) {
+      ss = pn_warp_sum(ss);
+      if (lane == 0) sumsq[r] = ss;
+    }
+  }
+}
+
+// packed[r, c] = bf16( master[r, c] * (colscale ? colscale[c] : 1) ): folds an RMSNorm weight into the
+// [out, in] matrix of the linear that consumes the normalised activations
+__global__ void __launch_bounds__(kThreads)
+pack_weight_kernel(const float* __restrict__ master, const float* __restrict__ colscale, int64_t rows,
+                   int cols, __nv_bfloat16* __restrict__ packed) {
+  const int64_t n = rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
+    const float g = colscale ? colscale[i % cols] : 1.0f;
+    packed[i] = __float2bfloat16_rn(master[i] * g);
   }
 }
 
@@ -119,11 +147,20 @@ head_prep_kernel(const float* __restrict__ x, const float* __restrict__ w, int64
 }  // namespace
 
 int pn_t5_embed(const int32_t* ids, const float* table, int64_t rows, int d, int vocab, float* hidden,
-                cudaStream_t st) {
+                __nv_bfloat16* copy, float* sumsq, cudaStream_t st) {
   if (rows == 0) return PN_OK;
   if (d % 4) return pn_fail(PN_E_UNSUPPORTED, "embed: d_model %% 4 != 0");
   embed_kernel<<<pn_grid(rows * 32, kThreads, 1, 8), kThreads, 0, st>>>(ids, table, rows, d, vocab,
-                                                                        hidden);
+                                                                        hidden, copy, sumsq);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_pack_weight(const float* master, const float* colscale, int64_t rows, int cols,
+                      __nv_bfloat16* packed, cudaStream_t st) {
+  if (rows * cols == 0) return PN_OK;
+  pack_weight_kernel<<<pn_grid(rows * cols, kThreads, 4, 8), kThreads, 0, st>>>(master, colscale, rows, cols,
+                                                                              packed);
   PN_LAUNCHED();
   return PN_OK;
 }
