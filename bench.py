@@ -300,6 +300,98 @@ def bench_rerank(args):
         dist.destroy_process_group()
 
 
+# workload: paced selection + weighting bandwidth kernels (BASELINE.json configs[4])
+def bench_select(args):
+    from pacednegatives_b200 import _lib
+    from pacednegatives_b200 import weights as W, loss as L, metrics as M
+    from pacednegatives_b200.dataloader import CandidateMatrix, ROW, RANK as RANKM
+    _lib.require_gpu()
+    torch.cuda.set_device(LOCAL_RANK)
+    dist = dist_setup(True)
+    dev = torch.device("cuda", LOCAL_RANK)
+    Q, C, k = args.select_queries, 1000, 15
+    peaks = measured_peaks()
+    # cand[q, r] = (q*7919 + r*104729) mod 8841823, built on the device in slabs
+    cand = torch.empty(Q, C, dtype=torch.int32, device=dev)
+    r = torch.arange(C, device=dev, dtype=torch.int64) * 104729
+    for lo in range(0, Q, 1 << 16):
+        hi = min(Q, lo + (1 << 16))
+        q = torch.arange(lo + RANK * Q, hi + RANK * Q, device=dev, dtype=torch.int64) * 7919
+        cand[lo:hi] = ((q[:, None] + r[None, :]) % 8841823).to(torch.int32)
+    cm_row = CandidateMatrix(cand, ROW)
+    cm_rank = cm_row.rank_major()
+    g = torch.Generator(device=dev).manual_seed(5678 + RANK)
+    Mw = args.select_elems
+    losses = torch.empty(Mw, device=dev).exponential_(1 / 0.7, generator=g)
+    eta = torch.tensor([0.3466], device=dev)
+    wq = torch.rand(Q, device=dev, generator=g)
+    table, _ = cm_row.binomial_table(0.3466, 0.01)
+    G = 16
+    z2 = torch.randn(Q * G, 2, device=dev, generator=g)
+    gq = torch.ones(Q, device=dev)
+    Qm = min(Q, 200000)
+    scores = torch.randn(Qm, C, device=dev, generator=g)
+    rels = (torch.rand(Qm, C, device=dev, generator=g) > 0.95).to(torch.uint8)
+    docids = cand[:Qm]
+    row_tab = torch.ones(1 << 24, device=dev)
+    ce_p = torch.rand(1 << 24, device=dev, generator=g)
+    ce_n = torch.rand(1 << 24, device=dev, generator=g)
+    lib = _lib.lib()
+
+    def k_weights():
+        W.spl_weights(losses, eta, 0.0, 0, want_keep=True, want_stats=True)
+
+    def k_table():
+        _lib.check(lib.pn_weights_table_update(_lib.ptr(row_tab), _lib.ptr(ce_p), _lib.ptr(ce_n), row_tab.numel(),
+                                               1.0 / 16, 0.1, _lib.stream()))
+
+    kernels = [
+        ("spl_weights (eta threshold, keep mask, stats)", k_weights, Mw * 9.0),
+        ("weight table update", k_table, row_tab.numel() * 16.0),
+        ("level select, scalar level, rank-major", lambda: cm_rank.select_level(0.5, check=False), Q * 8.0),
+        ("level select, per-query weight, row-major gather", lambda: cm_row.select_items(wq, check=False), Q * 16.0),
+        ("binomial select k=15 (Philox stream)", lambda: cm_row.select_binomial(table, k, seed=7),
+         Q * k * 12.0 + 4.0 * Q),
+        ("restricted LCE fwd (G=16)", lambda: L.lce_restricted(z2, G), Q * (G * 8.0 + 4.0 + G * 4.0)),
+        ("top-k + nDCG@10/RR (C=1000)", lambda: M.topk_metrics(scores, docids, rels, 10), Qm * (C * 9.0 + 10 * 8 + 16)),
+    ]
+    res = []
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    l0 = _lib.launch_count()
+    tot_ms = 0.0
+    for name, fn, nbytes in kernels:
+        for _ in range(max(args.warmup, 3)):
+            fn()
+        ts = []
+        for _ in range(args.steps):
+            flush.zero_()     # inputs that fit the 126 MB L2 would otherwise be read from cache
+            e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ms = sum(ts) / len(ts)
+        tot_ms += ms
+        gbs = nbytes / (ms / 1e3) / 1e9
+        res.append({"kernel": name, "ms": ms, "algorithmic_bytes": nbytes, "achieved_gbs": gbs,
+                    "frac_of_hbm_peak": gbs / peaks["hbm_gbs"]})
+    launches = _lib.launch_count() - l0
+    top = res[0]
+    line = {"metric": "paced selection + weighting kernels, queries/s through one pass of all kernels",
+            "value": Q * WORLD / (tot_ms / 1e3), "unit": "queries/s", "n_gpus": WORLD, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": tot_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32/i32/f64", "data": "synthetic (SURVEY cfg5 generators)",
+            "config": {"workload": "paced negative sampling + weighting kernel sweep (BASELINE configs[4])",
+                       "queries": Q, "candidates": C, "k": k, "weight_elems": Mw, "l2": "256 MB flush between iterations"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peaks["hbm_gbs"],
+                         "unit": "GB/s", "frac": top["frac_of_hbm_peak"], "peak_source": peaks["src"], "traffic": None},
+            "kernels": res}
+    if RANK == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def bench_rerank_reference(args):
     """`--impl reference`: the reference's CPU code path for the same metric, on rank 0's host cores."""
     if RANK != 0:
@@ -371,6 +463,8 @@ def main():
     ap.add_argument("--cpu-sample-docs", type=int, default=32)
     ap.add_argument("--ref-docs-per-step", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--select-queries", type=int, default=1000000)
+    ap.add_argument("--select-elems", type=int, default=1 << 28)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3   # timing rule: at least 3 warm-up steps
@@ -385,6 +479,8 @@ def main():
         raise SystemExit("reference arm: workload not implemented")
     if args.workload == "rerank":
         return bench_rerank(args)
+    if args.workload == "select":
+        return bench_select(args)
     raise SystemExit(f"workload {args.workload} not implemented yet")
 
 

@@ -159,31 +159,39 @@ __device__ __forceinline__ float rel_score(float zt, float zf) {
   return d > 0.0f ? -(d + log1pf(expf(-d))) : -log1pf(expf(d));
 }
 
-// one warp per query
+// LANES (a power of two >= min(G, 32)) lanes per query: groups of up to 16 documents share a warp, so
+// no lane idles and the reduction is log2(LANES) shuffle rounds
+template <int LANES>
 __global__ void __launch_bounds__(kThreads)
 lce_restricted_fwd_kernel(const float* __restrict__ z2, int64_t Q, int32_t G,
                           float* __restrict__ loss_out, float* __restrict__ score_out) {
   const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * kThreads) >> 5;
-  for (int64_t q = warp; q < Q; q += nwarps) {
-    const float2* zz = reinterpret_cast<const float2*>(z2) + q * G;
+  const int sub = lane % LANES;
+  const int64_t slot = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5) * (32 / LANES) + lane / LANES;
+  const int64_t nslots = (((int64_t)gridDim.x * kThreads) >> 5) * (32 / LANES);
+  const int64_t iters = (Q + nslots - 1) / nslots;       // uniform trip count: shuffles stay convergent
+  for (int64_t itq = 0; itq < iters; ++itq) {
+    const int64_t q = slot + itq * nslots;
+    const bool live = q < Q;
     float m = -INFINITY, s = 0.0f, s0 = 0.0f;
-    for (int j = lane; j < G; j += 32) {
-      const float2 z = zz[j];
-      const float sc = rel_score(z.x, z.y);
-      if (score_out) score_out[q * G + j] = sc;
-      if (j == 0) s0 = sc;
-      online_add(m, s, sc);
+    if (live) {
+      const float2* zz = reinterpret_cast<const float2*>(z2) + q * G;
+      for (int j = sub; j < G; j += LANES) {
+        const float2 z = zz[j];
+        const float sc = rel_score(z.x, z.y);
+        if (score_out) score_out[q * G + j] = sc;
+        if (j == 0) s0 = sc;
+        online_add(m, s, sc);
+      }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
+    for (int o = LANES / 2; o > 0; o >>= 1) {
       const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
       const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
       online_merge(m, s, m2, s2);
     }
-    s0 = __shfl_sync(0xffffffffu, s0, 0);
-    if (lane == 0) loss_out[q] = (m + logf(s)) - s0;
+    s0 = __shfl_sync(0xffffffffu, s0, lane - sub);
+    if (live && sub == 0) loss_out[q] = (m + logf(s)) - s0;
   }
 }
 
@@ -292,8 +300,15 @@ extern "C" int pn_lce_restricted_fwd(const float* z2, int64_t Q, int32_t G, floa
   PN_CHECK_ARG(Q >= 0 && G > 0);
   if (Q == 0) return PN_OK;
   PN_CHECK_ARG(z2 && loss_out);
-  lce_restricted_fwd_kernel<<<pn_grid(Q * 32, kThreads, 1, 8), kThreads, 0,
-                              (cudaStream_t)stream>>>(z2, Q, G, loss_out, score_out);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (G <= 4)
+    lce_restricted_fwd_kernel<4><<<pn_grid(Q * 4, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
+  else if (G <= 8)
+    lce_restricted_fwd_kernel<8><<<pn_grid(Q * 8, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
+  else if (G <= 16)
+    lce_restricted_fwd_kernel<16><<<pn_grid(Q * 16, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
+  else
+    lce_restricted_fwd_kernel<32><<<pn_grid(Q * 32, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
   PN_LAUNCHED();
   return PN_OK;
 }

@@ -10,32 +10,34 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kUnroll = 4;  // float4 loads in flight per thread
 
-struct WStats {
-  double sw, swl, dswl, nlt, sl, nkeep;
+// Raw per-thread sums: everything the six statistics need, as plain sums of l and l^2 split by the keep mask,
+// so the per-element work is one IEEE divide, two compares and four fp32 adds; fp32 partials are flushed to
+// fp64 every 16 elements.  The statistics are assembled from the raw sums by the last CTA to finish:
+//   kept (l <= eta):  w = l/eta (LCE) | 1 - l/eta (ETA)      over:  w = l*mask*eta
+//   sum w, sum w*l and d(sum w*l)/d eta are linear in  A1 = sum_kept l, A2 = sum_kept l^2, B1 = sum_over l,
+//   B2 = sum_over l^2  (they differ from the sums of the ROUNDED fp32 weights by ~1e-7 relative).
+struct Raw {
+  float a1, a2, b1, b2;
+  int nkeep, nlt;
 };
 
 template <int VARIANT>
-__device__ __forceinline__ float weight_one(float l, float eta, float mask, WStats& s) {
+__device__ __forceinline__ float weight_one(float l, float eta, float mask, Raw& r) {
   const bool over = l > eta;  // the reference's `if loss[i] > self.eta`
+  const float l2 = l * l;
   float w;
   if (over) {
     w = __fmul_rn(__fmul_rn(l, mask), eta);
+    r.b1 += l;
+    r.b2 += l2;
   } else {
     const float q = __fdiv_rn(l, eta);
     w = (VARIANT == PN_W_LCE) ? q : __fadd_rn(-q, 1.0f);
+    r.a1 += l;
+    r.a2 += l2;
+    r.nkeep += 1;
   }
-  const double ld = (double)l, ed = (double)eta;
-  s.sw += (double)w;
-  s.swl += (double)w * ld;
-  if (over) {
-    s.dswl += (double)mask * ld * ld;
-  } else {
-    const double t = ld * ld / (ed * ed);
-    s.dswl += (VARIANT == PN_W_LCE) ? -t : t;
-    s.nkeep += 1.0;
-  }
-  if (l < eta) s.nlt += 1.0;
-  s.sl += ld;
+  r.nlt += (l < eta) ? 1 : 0;
   return w;
 }
 
@@ -45,7 +47,13 @@ weights_fwd_kernel(const float* __restrict__ loss, int64_t n, const float* __res
                    float mask, float* __restrict__ w_out, uint8_t* __restrict__ keep_out,
                    double* __restrict__ stats) {
   const float eta = __ldg(eta_p);
-  WStats s = {0, 0, 0, 0, 0, 0};
+  double acc[6] = {0, 0, 0, 0, 0, 0};   // A1 A2 B1 B2 nkeep nlt
+  auto flush = [&](Raw& r) {
+    acc[0] += (double)r.a1; acc[1] += (double)r.a2; acc[2] += (double)r.b1; acc[3] += (double)r.b2;
+    acc[4] += (double)r.nkeep; acc[5] += (double)r.nlt;
+    r = Raw{0.f, 0.f, 0.f, 0.f, 0, 0};
+  };
+  Raw r = {0.f, 0.f, 0.f, 0.f, 0, 0};
   const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x;
   const int64_t nthreads = (int64_t)gridDim.x * kThreads;
 
@@ -65,10 +73,10 @@ weights_fwd_kernel(const float* __restrict__ loss, int64_t n, const float* __res
         const int64_t i = base + (int64_t)u * nthreads;
         if (i < n4) {
           float4 w;
-          w.x = weight_one<VARIANT>(v[u].x, eta, mask, s);
-          w.y = weight_one<VARIANT>(v[u].y, eta, mask, s);
-          w.z = weight_one<VARIANT>(v[u].z, eta, mask, s);
-          w.w = weight_one<VARIANT>(v[u].w, eta, mask, s);
+          w.x = weight_one<VARIANT>(v[u].x, eta, mask, r);
+          w.y = weight_one<VARIANT>(v[u].y, eta, mask, r);
+          w.z = weight_one<VARIANT>(v[u].z, eta, mask, r);
+          w.w = weight_one<VARIANT>(v[u].w, eta, mask, r);
           pn_stg_stream(out4 + i, w);
           if (keep_out) {
             uchar4 k;
@@ -80,36 +88,63 @@ weights_fwd_kernel(const float* __restrict__ loss, int64_t n, const float* __res
           }
         }
       }
+      flush(r);
     }
     // scalar tail
     for (int64_t i = (n4 << 2) + tid; i < n; i += nthreads) {
       const float l = loss[i];
-      w_out[i] = weight_one<VARIANT>(l, eta, mask, s);
+      w_out[i] = weight_one<VARIANT>(l, eta, mask, r);
       if (keep_out) keep_out[i] = !(l > eta);
     }
+    flush(r);
   } else {
+    int cnt = 0;
     for (int64_t i = tid; i < n; i += nthreads) {
       const float l = loss[i];
-      w_out[i] = weight_one<VARIANT>(l, eta, mask, s);
+      w_out[i] = weight_one<VARIANT>(l, eta, mask, r);
       if (keep_out) keep_out[i] = !(l > eta);
+      if (++cnt == 16) { flush(r); cnt = 0; }
     }
+    flush(r);
   }
 
   if (stats == nullptr) return;
   __shared__ double red[6][kThreads / 32];
-  double vals[6] = {s.sw, s.swl, s.dswl, s.nlt, s.sl, s.nkeep};
+  __shared__ bool last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < 6; ++k) {
-    const double r = pn_warp_sum(vals[k]);
-    if (lane == 0) red[k][warp] = r;
+    const double t = pn_warp_sum(acc[k]);
+    if (lane == 0) red[k][warp] = t;
   }
   __syncthreads();
   if (threadIdx.x < 6) {
-    double r = 0;
+    double t = 0;
 #pragma unroll
-    for (int w = 0; w < kThreads / 32; ++w) r += red[threadIdx.x][w];
-    atomicAdd(stats + threadIdx.x, r);
+    for (int w = 0; w < kThreads / 32; ++w) t += red[threadIdx.x][w];
+    atomicAdd(stats + 6 + threadIdx.x, t);   // raw sums live in stats[6..11] until the last CTA folds them
+    __threadfence();
+  }
+  __syncthreads();
+  unsigned int* done = reinterpret_cast<unsigned int*>(stats + 12);   // zeroed with the scratch by the host
+  if (threadIdx.x == 0) last = atomicAdd(done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    __threadfence();
+    volatile double* raw = stats + 6;
+    const double A1 = raw[0], A2 = raw[1], B1 = raw[2], B2 = raw[3], nkeep = raw[4], nlt = raw[5];
+    const double e = (double)eta, mk = (double)mask;
+    double sw, swl, dswl;
+    if (VARIANT == PN_W_LCE) {
+      sw = A1 / e + mk * e * B1;
+      swl = A2 / e + mk * e * B2;
+      dswl = -A2 / (e * e) + mk * B2;
+    } else {
+      sw = nkeep - A1 / e + mk * e * B1;
+      swl = A1 - A2 / e + mk * e * B2;
+      dswl = A2 / (e * e) + mk * B2;
+    }
+    stats[0] = sw; stats[1] = swl; stats[2] = dswl; stats[3] = nlt; stats[4] = A1 + B1; stats[5] = nkeep;
   }
 }
 
@@ -190,7 +225,18 @@ extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, fl
   PN_CHECK_ARG(variant == PN_W_LCE || variant == PN_W_ETA);
   PN_CHECK_ARG(eta != nullptr);
   cudaStream_t st = (cudaStream_t)stream;
-  if (stats_out) PN_CUDA(cudaMemsetAsync(stats_out, 0, 6 * sizeof(double), st));
+  // the kernel accumulates raw sums in a 13-double scratch (per device, per stream use is serialised by
+  // the stream) and the last CTA writes the six statistics into its first half
+  static double* scratch[64] = {nullptr};
+  double* stats_dev = nullptr;
+  if (stats_out) {
+    int dev = 0;
+    PN_CUDA(cudaGetDevice(&dev));
+    if (!scratch[dev & 63]) PN_CUDA(cudaMalloc(&scratch[dev & 63], 13 * sizeof(double)));
+    stats_dev = scratch[dev & 63];
+    PN_CUDA(cudaMemsetAsync(stats_dev, 0, 13 * sizeof(double), st));
+    if (n == 0) PN_CUDA(cudaMemsetAsync(stats_out, 0, 6 * sizeof(double), st));
+  }
   if (n == 0) return PN_OK;
   PN_CHECK_ARG(loss != nullptr && w_out != nullptr);
   const bool vec = (((uintptr_t)loss | (uintptr_t)w_out) & 15) == 0 &&
@@ -198,7 +244,7 @@ extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, fl
   const int grid = pn_grid(n, kThreads, vec ? 4 * kUnroll : 4, 8);
 #define LAUNCH(V, VEC)                                                                       \
   weights_fwd_kernel<V, VEC><<<grid, kThreads, 0, st>>>(loss, n, eta, mask, w_out, keep_out, \
-                                                        stats_out)
+                                                        stats_dev)
   if (variant == PN_W_LCE) {
     if (vec) LAUNCH(PN_W_LCE, true); else LAUNCH(PN_W_LCE, false);
   } else {
@@ -206,6 +252,8 @@ extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, fl
   }
 #undef LAUNCH
   PN_LAUNCHED();
+  if (stats_out)
+    PN_CUDA(cudaMemcpyAsync(stats_out, stats_dev, 6 * sizeof(double), cudaMemcpyDeviceToDevice, st));
   return PN_OK;
 }
 

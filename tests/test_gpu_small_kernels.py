@@ -37,7 +37,8 @@ def test_weights_golden_bit_exact(pn, golden_dir):
         np.testing.assert_array_equal(keep.cpu().numpy().astype(bool), ~(g["loss"] > eta))
         st = stats.cpu().numpy()
         np.testing.assert_allclose(st[2] / len(g["loss"]), g[f"lce_dmean_deta_{ei}"][0], rtol=1e-5)
-        np.testing.assert_allclose(st, ow.spl_stats(g["loss"], eta, 0.0, ow.LCE), rtol=1e-9)
+        # statistics: assembled from fp64 raw sums of l and l^2 (DESIGN: 1e-5 relative), not from rounded w
+        np.testing.assert_allclose(st, ow.spl_stats(g["loss"], eta, 0.0, ow.LCE), rtol=1e-5)
         for mask in (0.0, 0.25):
             for name, var in (("eta", pn.w.ETA), ("lce", pn.w.LCE)):
                 w, _, _ = pn.w.spl_weights(loss, eta_t, mask, var)
@@ -60,7 +61,7 @@ def test_weights_sizes_and_alignment(pn, n, variant):
             if n:
                 np.testing.assert_allclose(stats.cpu().numpy(),
                                            ow.spl_stats(loss[off:off + n], eta, 0.5, variant),
-                                           rtol=1e-9, atol=1e-9)
+                                           rtol=1e-5, atol=1e-6 * max(1, n))
 
 
 def test_weights_modules_autograd(pn):
