@@ -8,80 +8,12 @@
 //   ctx     bf16 [rows, d_inner]  attention output
 //   big     bf16 [rows, max(3*d_inner, d_ff)]   fused q|k|v, FFN hidden, or cross k|v
 //   decoder buffers are the same at rows = docs*T.
-#include "pn_common.cuh"
-#include "pn_t5_internal.cuh"
+#include "pn_t5_model.cuh"
 
-#include <map>
-#include <string>
-#include <vector>
 #include <math.h>
 #include <string.h>
 
-int pn_t5_embed(const int32_t* ids, const float* table, int64_t rows, int d, int vocab, float* hidden,
-                __nv_bfloat16* copy, float* sumsq, cudaStream_t st);
-int pn_t5_pack_weight(const float* master, const float* colscale, int64_t rows, int cols,
-                      __nv_bfloat16* packed, cudaStream_t st);
-int pn_t5_rmsnorm(const float* x, const float* w, int64_t rows, int d, float eps, __nv_bfloat16* out,
-                  cudaStream_t st);
-int pn_t5_f32_to_bf16(const float* src, __nv_bfloat16* dst, int64_t n, cudaStream_t st);
-int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, int d, float eps,
-                int rel_id, int nrel_id, float* score, float* z2, cudaStream_t st);
-int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float eps,
-                    __nv_bfloat16* out, cudaStream_t st);
-
-#define RC(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
-
 namespace {
-
-// One linear: the fp32 master in HF's [out, in] layout (what the optimiser updates) and the packed bf16 copy
-// the tcgen05 GEMM reads, with the RMSNorm weight of its input folded into the columns (pn_t5_finalize).
-struct Lin {
-  float* master = nullptr;
-  __nv_bfloat16* packed = nullptr;
-  int64_t rows = 0;
-  int cols = 0;
-};
-struct EncLayer {
-  Lin wqkv, wo, wi, wo2;
-  float *ln0 = nullptr, *ln1 = nullptr;
-};
-struct DecLayer {
-  Lin wqkv, wo, cq, ckv, co, wi, wo2;
-  float *ln0 = nullptr, *ln1 = nullptr, *ln2 = nullptr;
-};
-
-}  // namespace
-
-struct PnT5 {
-  PnT5Config cfg;
-  int d_inner;
-  std::vector<void*> allocs;
-  float* emb = nullptr;              // fp32 [vocab, d]
-  __nv_bfloat16* emb_bf16 = nullptr; // bf16 [vocab_pad, d] for the full-vocabulary head
-  int vocab_pad = 0;
-  std::vector<EncLayer> enc;
-  std::vector<DecLayer> dec;
-  float *enc_final = nullptr, *dec_final = nullptr;
-  float *enc_rel = nullptr, *dec_rel = nullptr;  // [buckets, heads] as in HF
-  float *enc_bias = nullptr;                     // [heads, 1023] expanded by (j - i + 511)
-  float *dec_bias = nullptr;                     // [heads, 2, 2] for T <= 2
-  std::map<std::string, int> loaded;
-  bool finalized = false;
-  int cta_group = 2;
-};
-
-namespace {
-
-template <typename T>
-int dev_alloc(PnT5* m, T** p, size_t n) {
-  void* q = nullptr;
-  cudaError_t e = cudaMalloc(&q, n * sizeof(T));
-  if (e != cudaSuccess) return pn_fail(PN_E_OOM, "pn_t5: cudaMalloc(%zu) failed: %s", n * sizeof(T),
-                                       cudaGetErrorString(e));
-  m->allocs.push_back(q);
-  *p = (T*)q;
-  return PN_OK;
-}
 
 // HF:188-234 for the bidirectional (encoder) case in exact integer arithmetic; equals HF's fp32
 // expression for every |rel| <= 700 (tests/test_oracle_golden.py::test_relative_bucket_vs_hf).
@@ -108,7 +40,7 @@ int rel_bucket_bidir(int rel, int num_buckets, int max_distance) {
 
 // y = RMSNorm(h) . W^T with the norm fused: A = bf16 copy of h, W has the norm weight folded in, and the
 // epilogue scales each row by rsqrt(mean(h^2) + eps) from the partial sums of squares `ss` ([parts][M])
-int gemm_normed(const PnT5* m, const __nv_bfloat16* hb, const float* ss, int parts, const Lin& W, void* out,
+int gemm_normed(const PnT5* m, const __nv_bfloat16* hb, const float* ss, int parts, const PnLin& W, void* out,
                 int ldc, int M, int relu, cudaStream_t st) {
   PnGemmExtra ex = {};
   ex.sumsq_in = ss; ex.sumsq_parts = parts; ex.norm_dim = m->cfg.d_model; ex.eps = m->cfg.eps;
@@ -116,26 +48,12 @@ int gemm_normed(const PnT5* m, const __nv_bfloat16* hb, const float* ss, int par
                          m->cta_group, st);
 }
 // h += x . W^T, also refreshing the bf16 copy of h and its per-n-tile sums of squares for the next fused norm
-int gemm_resid(const PnT5* m, const __nv_bfloat16* x, const Lin& W, float* h, __nv_bfloat16* hb, float* ss,
+int gemm_resid(const PnT5* m, const __nv_bfloat16* x, const PnLin& W, float* h, __nv_bfloat16* hb, float* ss,
                int M, cudaStream_t st) {
   PnGemmExtra ex = {};
   ex.copy_out = hb; ex.ld_copy = (int)W.rows; ex.sumsq_out = ss;
   return pn_gemm_bf16_ex(x, W.cols, W.packed, W.cols, h, (int)W.rows, M, (int)W.rows, W.cols, PN_EPI_RESID_F32, 0,
                          &ex, m->cta_group, st);
-}
-
-// bf16 GEMM operands from the fp32 masters, with each RMSNorm weight folded into the linear that consumes the
-// normalised activations (encoder final norm -> every decoder layer's cross K/V projection)
-int pack_all(PnT5* m, cudaStream_t st) {
-  auto pk = [&](const Lin& L, const float* ln) { return pn_t5_pack_weight(L.master, ln, L.rows, L.cols, L.packed, st); };
-  for (auto& L : m->enc) {
-    RC(pk(L.wqkv, L.ln0)); RC(pk(L.wo, nullptr)); RC(pk(L.wi, L.ln1)); RC(pk(L.wo2, nullptr));
-  }
-  for (auto& L : m->dec) {
-    RC(pk(L.wqkv, L.ln0)); RC(pk(L.wo, nullptr)); RC(pk(L.cq, L.ln1)); RC(pk(L.ckv, m->enc_final));
-    RC(pk(L.co, nullptr)); RC(pk(L.wi, L.ln2)); RC(pk(L.wo2, nullptr));
-  }
-  return PN_OK;
 }
 
 struct Workspace {
@@ -182,7 +100,7 @@ int encoder_forward(const PnT5* m, const int32_t* ids, int64_t docs, int S, cons
   RC(pn_t5_embed(ids, m->emb, rows, d, m->cfg.vocab, w.hidden, w.xn, w.ss, st));
   int cur_parts = 1;
   for (size_t l = 0; l < m->enc.size(); ++l) {
-    const EncLayer& L = m->enc[l];
+    const PnEncLayer& L = m->enc[l];
     RC(gemm_normed(m, w.xn, w.ss, cur_parts, L.wqkv, w.big, 3 * di, rows, 0, st));
     RC(pn_t5_self_attn(w.big, 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx, di, st));
     RC(gemm_resid(m, w.ctx, L.wo, w.hidden, w.xn, w.ss, rows, st));
@@ -202,7 +120,7 @@ int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& 
   RC(pn_t5_embed(w.dec_ids, m->emb, drows, d, m->cfg.vocab, w.dh, w.dxn, w.dss, st));
   int cur_parts = 1;
   for (size_t l = 0; l < m->dec.size(); ++l) {
-    const DecLayer& L = m->dec[l];
+    const PnDecLayer& L = m->dec[l];
     // self-attention over the <= T decoder tokens (causal + decoder bias)
     RC(gemm_normed(m, w.dxn, w.dss, cur_parts, L.wqkv, w.dbig, 3 * di, drows, 0, st));
     RC(pn_t5_dec_attn(w.dbig, 3 * di, 0, w.dbig, w.dbig, 3 * di, di, 2 * di, (int)docs, T, T, H, 1,
@@ -239,22 +157,148 @@ __global__ void shift_right_kernel(const int64_t* labels, int64_t docs, int T, i
   }
 }
 
+// (re)build every packed bf16 operand from the flat fp32 parameters, with each RMSNorm weight folded into the
+// linear that consumes the normalised activations (encoder final norm -> every decoder cross K/V projection),
+// and re-expand the relative-position bias tables
+__global__ void expand_bias_kernel(const float* __restrict__ enc_rel, const float* __restrict__ dec_rel,
+                                   const int* __restrict__ bucket_of, int H, float* __restrict__ enc_bias,
+                                   float* __restrict__ dec_bias) {
+  const int W = 1023;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < H * W; i += gridDim.x * blockDim.x) {
+    const int h = i / W, k = i % W;
+    enc_bias[i] = enc_rel[bucket_of[k] * H + h];
+  }
+  // decoder (unidirectional): bucket = distance for distance < 16; T <= 2 here
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < H * 4; i += gridDim.x * blockDim.x) {
+    const int h = i / 4, t = (i / 2) & 1, j = i & 1;
+    const int dist = t - j > 0 ? t - j : 0;
+    dec_bias[i] = dec_rel[dist * H + h];
+  }
+}
+
 }  // namespace
+
+int pn_t5_repack(PnT5* m, cudaStream_t st) {
+  auto pk = [&](const PnLin& L) {
+    return pn_t5_pack_weight(L.master, L.fold, L.rows, L.cols, L.packed, L.packedT, (int)L.rows, st);
+  };
+  for (auto& L : m->enc) { RC(pk(L.wqkv)); RC(pk(L.wo)); RC(pk(L.wi)); RC(pk(L.wo2)); }
+  for (auto& L : m->dec) {
+    RC(pk(L.wqkv)); RC(pk(L.wo)); RC(pk(L.cq)); RC(pk(L.ckv)); RC(pk(L.co)); RC(pk(L.wi)); RC(pk(L.wo2));
+  }
+  RC(pn_t5_pack_weight(m->emb, nullptr, m->cfg.vocab, m->cfg.d_model, m->emb_bf16, m->embT_bf16, m->vocab_pad, st));
+  expand_bias_kernel<<<8, 256, 0, st>>>(m->enc_rel, m->dec_rel, (const int*)m->allocs[0], m->cfg.n_heads,
+                                        m->enc_bias, m->dec_bias);
+  PN_LAUNCHED();
+  return PN_OK;
+}
 
 extern "C" int pn_t5_create(const PnT5Config* cfg, PnT5** out) {
   PN_CHECK_ARG(cfg && out);
   PN_CHECK_ARG(cfg->d_kv == 64);
-  PN_CHECK_ARG(cfg->d_model % 64 == 0 && cfg->d_ff % 128 == 0);
+  PN_CHECK_ARG(cfg->d_model % 128 == 0 && cfg->d_ff % 128 == 0);
   PN_CHECK_ARG((cfg->n_heads * cfg->d_kv) % 128 == 0);
   PN_CHECK_ARG(cfg->n_layers > 0 && cfg->n_dec_layers > 0 && cfg->vocab > 0);
   PN_CHECK_ARG(cfg->rel_buckets > 0 && cfg->rel_buckets <= 64);
   PnT5* m = new PnT5();
   m->cfg = *cfg;
-  m->d_inner = cfg->n_heads * cfg->d_kv;
+  const int d = cfg->d_model, di = cfg->n_heads * cfg->d_kv, ff = cfg->d_ff, H = cfg->n_heads;
+  m->d_inner = di;
   m->vocab_pad = (cfg->vocab + 127) / 128 * 128;
   m->enc.resize(cfg->n_layers);
   m->dec.resize(cfg->n_dec_layers);
+  // ---- parameter table in HuggingFace state_dict order
+  int64_t off = 0;
+  auto add = [&](const std::string& name, int64_t numel) {
+    m->index[name] = (int)m->params.size();
+    m->params.push_back({name, off, numel});
+    const int64_t o = off;
+    off += numel;
+    return o;
+  };
+  char b[160];
+  m->emb_off = add("shared.weight", (int64_t)cfg->vocab * d);
+  const int64_t dd = (int64_t)di * d;
+  for (int i = 0; i < cfg->n_layers; ++i) {
+    PnEncLayer& L = m->enc[i];
+    auto nm = [&](const char* s) { snprintf(b, sizeof(b), "encoder.block.%d.layer.%s.weight", i, s); return std::string(b); };
+    L.wqkv.off = add(nm("0.SelfAttention.q"), dd); add(nm("0.SelfAttention.k"), dd); add(nm("0.SelfAttention.v"), dd);
+    L.wqkv.rows = 3 * di; L.wqkv.cols = d;
+    L.wo.off = add(nm("0.SelfAttention.o"), dd); L.wo.rows = d; L.wo.cols = di;
+    if (i == 0) m->enc_rel_off = add(nm("0.SelfAttention.relative_attention_bias"), (int64_t)cfg->rel_buckets * H);
+    L.ln0_off = add(nm("0.layer_norm"), d);
+    L.wi.off = add(nm("1.DenseReluDense.wi"), (int64_t)ff * d); L.wi.rows = ff; L.wi.cols = d;
+    L.wo2.off = add(nm("1.DenseReluDense.wo"), (int64_t)ff * d); L.wo2.rows = d; L.wo2.cols = ff;
+    L.ln1_off = add(nm("1.layer_norm"), d);
+    L.wqkv.fold_off = L.ln0_off; L.wi.fold_off = L.ln1_off;
+  }
+  m->enc_final_off = add("encoder.final_layer_norm.weight", d);
+  for (int i = 0; i < cfg->n_dec_layers; ++i) {
+    PnDecLayer& L = m->dec[i];
+    auto nm = [&](const char* s) { snprintf(b, sizeof(b), "decoder.block.%d.layer.%s.weight", i, s); return std::string(b); };
+    L.wqkv.off = add(nm("0.SelfAttention.q"), dd); add(nm("0.SelfAttention.k"), dd); add(nm("0.SelfAttention.v"), dd);
+    L.wqkv.rows = 3 * di; L.wqkv.cols = d;
+    L.wo.off = add(nm("0.SelfAttention.o"), dd); L.wo.rows = d; L.wo.cols = di;
+    if (i == 0) m->dec_rel_off = add(nm("0.SelfAttention.relative_attention_bias"), (int64_t)cfg->rel_buckets * H);
+    L.ln0_off = add(nm("0.layer_norm"), d);
+    L.cq.off = add(nm("1.EncDecAttention.q"), dd); L.cq.rows = di; L.cq.cols = d;
+    L.ckv.off = add(nm("1.EncDecAttention.k"), dd); add(nm("1.EncDecAttention.v"), dd);
+    L.ckv.rows = 2 * di; L.ckv.cols = d;
+    L.co.off = add(nm("1.EncDecAttention.o"), dd); L.co.rows = d; L.co.cols = di;
+    L.ln1_off = add(nm("1.layer_norm"), d);
+    L.wi.off = add(nm("2.DenseReluDense.wi"), (int64_t)ff * d); L.wi.rows = ff; L.wi.cols = d;
+    L.wo2.off = add(nm("2.DenseReluDense.wo"), (int64_t)ff * d); L.wo2.rows = d; L.wo2.cols = ff;
+    L.ln2_off = add(nm("2.layer_norm"), d);
+    L.wqkv.fold_off = L.ln0_off; L.cq.fold_off = L.ln1_off; L.wi.fold_off = L.ln2_off;
+    L.ckv.fold_off = m->enc_final_off;
+  }
+  m->dec_final_off = add("decoder.final_layer_norm.weight", d);
+  for (const char* alias : {"encoder.embed_tokens.weight", "decoder.embed_tokens.weight", "lm_head.weight"})
+    m->index[alias] = 0;   // tied to shared.weight
+  m->n_params = off;
+  m->loaded.assign(m->params.size(), 0);
   *out = m;
+  return PN_OK;
+}
+
+// device storage: the bucket-of-relative-position table (allocs[0]), the flat parameters, the packed operands
+static int t5_allocate(PnT5* m) {
+  if (m->flat) return PN_OK;
+  const int H = m->cfg.n_heads, nb = m->cfg.rel_buckets;
+  int* bucket_of = nullptr;
+  RC(pn_dev_alloc(m, &bucket_of, 1023));   // must stay allocs[0]
+  std::vector<int> bo(1023);
+  for (int k = 0; k < 1023; ++k) bo[k] = rel_bucket_bidir(k - 511, nb, m->cfg.rel_max_dist);
+  PN_CUDA(cudaMemcpy(bucket_of, bo.data(), 1023 * sizeof(int), cudaMemcpyHostToDevice));
+  RC(pn_dev_alloc(m, &m->flat, (size_t)m->n_params));
+  float* f = m->flat;
+  auto bind = [&](PnLin& L) -> int {
+    L.master = f + L.off;
+    L.fold = L.fold_off >= 0 ? f + L.fold_off : nullptr;
+    RC(pn_dev_alloc(m, &L.packed, (size_t)L.rows * L.cols));
+    if (m->want_train) RC(pn_dev_alloc(m, &L.packedT, (size_t)L.rows * L.cols));
+    return PN_OK;
+  };
+  for (auto& L : m->enc) {
+    RC(bind(L.wqkv)); RC(bind(L.wo)); RC(bind(L.wi)); RC(bind(L.wo2));
+    L.ln0 = f + L.ln0_off; L.ln1 = f + L.ln1_off;
+  }
+  for (auto& L : m->dec) {
+    RC(bind(L.wqkv)); RC(bind(L.wo)); RC(bind(L.cq)); RC(bind(L.ckv)); RC(bind(L.co)); RC(bind(L.wi)); RC(bind(L.wo2));
+    L.ln0 = f + L.ln0_off; L.ln1 = f + L.ln1_off; L.ln2 = f + L.ln2_off;
+  }
+  m->emb = f + m->emb_off;
+  m->enc_final = f + m->enc_final_off; m->dec_final = f + m->dec_final_off;
+  m->enc_rel = f + m->enc_rel_off; m->dec_rel = f + m->dec_rel_off;
+  const size_t ve = (size_t)m->vocab_pad * m->cfg.d_model;
+  RC(pn_dev_alloc(m, &m->emb_bf16, ve));
+  PN_CUDA(cudaMemset(m->emb_bf16, 0, ve * 2));
+  if (m->want_train) {
+    RC(pn_dev_alloc(m, &m->embT_bf16, ve));
+    PN_CUDA(cudaMemset(m->embT_bf16, 0, ve * 2));
+  }
+  RC(pn_dev_alloc(m, &m->enc_bias, (size_t)H * 1023));
+  RC(pn_dev_alloc(m, &m->dec_bias, (size_t)H * 4));
   return PN_OK;
 }
 
@@ -272,6 +316,11 @@ extern "C" int pn_t5_set_option(PnT5* m, const char* name, int64_t value) {
     m->cta_group = (int)value;
     return PN_OK;
   }
+  if (!strcmp(name, "train")) {   // must precede the first pn_t5_load_weight: also keeps transposed operands
+    if (m->flat) return pn_fail(PN_E_BADARG, "pn_t5_set_option: \"train\" must be set before weights are loaded");
+    m->want_train = value != 0;
+    return PN_OK;
+  }
   return pn_fail(PN_E_BADARG, "pn_t5_set_option: unknown option %s", name);
 }
 
@@ -279,153 +328,47 @@ extern "C" int pn_t5_set_option(PnT5* m, const char* name, int64_t value) {
 extern "C" int pn_t5_load_weight(PnT5* m, const char* name, const float* src, int64_t numel,
                                  void* stream) {
   PN_CHECK_ARG(m && name && src);
-  cudaStream_t st = (cudaStream_t)stream;
-  const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
-  std::string n(name);
-  auto expect = [&](int64_t want) -> int {
-    if (numel != want)
-      return pn_fail(PN_E_BADARG, "pn_t5_load_weight: %s has %lld elements, expected %lld", name,
-                     (long long)numel, (long long)want);
-    return PN_OK;
-  };
-  // fp32 master [rows_total, cols]; this parameter fills rows [row_off, row_off + cnt / cols)
-  auto put_lin = [&](Lin* L, int64_t rows_total, int cols, int64_t row_off, int64_t cnt) -> int {
-    if (!L->master) {
-      RC(dev_alloc(m, &L->master, (size_t)rows_total * cols));
-      RC(dev_alloc(m, &L->packed, (size_t)rows_total * cols));
-      L->rows = rows_total;
-      L->cols = cols;
-    }
-    PN_CUDA(cudaMemcpyAsync(L->master + row_off * cols, src, cnt * sizeof(float), cudaMemcpyDeviceToDevice, st));
-    m->finalized = false;
-    return PN_OK;
-  };
-  auto put_f32 = [&](float** slot, int64_t cnt) -> int {
-    if (!*slot) RC(dev_alloc(m, slot, (size_t)cnt));
-    PN_CUDA(cudaMemcpyAsync(*slot, src, cnt * sizeof(float), cudaMemcpyDeviceToDevice, st));
-    return PN_OK;
-  };
-  m->loaded[n] = 1;
-  if (n == "shared.weight" || n == "encoder.embed_tokens.weight" ||
-      n == "decoder.embed_tokens.weight" || n == "lm_head.weight") {
-    RC(expect((int64_t)m->cfg.vocab * d));
-    if (m->emb && n != "shared.weight") return PN_OK;  // tied copies
-    RC(put_f32(&m->emb, numel));
-    if (!m->emb_bf16) {
-      RC(dev_alloc(m, &m->emb_bf16, (size_t)m->vocab_pad * d));
-      PN_CUDA(cudaMemsetAsync(m->emb_bf16, 0, (size_t)m->vocab_pad * d * 2, st));
-    }
-    m->loaded["shared.weight"] = 1;
-    return pn_t5_f32_to_bf16(src, m->emb_bf16, numel, st);
-  }
-  if (n == "encoder.final_layer_norm.weight") { RC(expect(d)); return put_f32(&m->enc_final, d); }
-  if (n == "decoder.final_layer_norm.weight") { RC(expect(d)); return put_f32(&m->dec_final, d); }
-  char stack[16], rest[96];
-  int blk = -1, sub = -1;
-  if (sscanf(name, "%7[a-z].block.%d.layer.%d.%95s", stack, &blk, &sub, rest) != 4)
+  auto it = m->index.find(name);
+  if (it == m->index.end())
     return pn_fail(PN_E_BADARG, "pn_t5_load_weight: unrecognised parameter name %s", name);
-  const bool is_dec = !strcmp(stack, "decoder");
-  if (!is_dec && strcmp(stack, "encoder"))
-    return pn_fail(PN_E_BADARG, "pn_t5_load_weight: unrecognised parameter name %s", name);
-  if (blk < 0 || blk >= (int)(is_dec ? m->dec.size() : m->enc.size()))
-    return pn_fail(PN_E_BADARG, "pn_t5_load_weight: block index out of range in %s", name);
-  std::string r(rest);
-  const int64_t dd = (int64_t)di * d;
-  if (r == "SelfAttention.relative_attention_bias.weight") {
-    RC(expect((int64_t)m->cfg.rel_buckets * H));
-    return put_f32(is_dec ? &m->dec_rel : &m->enc_rel, numel);
-  }
-  if (!is_dec) {
-    EncLayer& L = m->enc[blk];
-    if (sub == 0) {
-      if (r == "SelfAttention.q.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 0, dd); }
-      if (r == "SelfAttention.k.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, di, dd); }
-      if (r == "SelfAttention.v.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 2 * di, dd); }
-      if (r == "SelfAttention.o.weight") { RC(expect(dd)); return put_lin(&L.wo, d, di, 0, dd); }
-      if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln0, d); }
-    } else if (sub == 1) {
-      if (r == "DenseReluDense.wi.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wi, ff, d, 0, (int64_t)ff * d); }
-      if (r == "DenseReluDense.wo.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wo2, d, ff, 0, (int64_t)ff * d); }
-      if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln1, d); }
-    }
-  } else {
-    DecLayer& L = m->dec[blk];
-    if (sub == 0) {
-      if (r == "SelfAttention.q.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 0, dd); }
-      if (r == "SelfAttention.k.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, di, dd); }
-      if (r == "SelfAttention.v.weight") { RC(expect(dd)); return put_lin(&L.wqkv, 3 * di, d, 2 * di, dd); }
-      if (r == "SelfAttention.o.weight") { RC(expect(dd)); return put_lin(&L.wo, d, di, 0, dd); }
-      if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln0, d); }
-    } else if (sub == 1) {
-      if (r == "EncDecAttention.q.weight") { RC(expect(dd)); return put_lin(&L.cq, di, d, 0, dd); }
-      if (r == "EncDecAttention.k.weight") { RC(expect(dd)); return put_lin(&L.ckv, 2 * di, d, 0, dd); }
-      if (r == "EncDecAttention.v.weight") { RC(expect(dd)); return put_lin(&L.ckv, 2 * di, d, di, dd); }
-      if (r == "EncDecAttention.o.weight") { RC(expect(dd)); return put_lin(&L.co, d, di, 0, dd); }
-      if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln1, d); }
-    } else if (sub == 2) {
-      if (r == "DenseReluDense.wi.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wi, ff, d, 0, (int64_t)ff * d); }
-      if (r == "DenseReluDense.wo.weight") { RC(expect((int64_t)ff * d)); return put_lin(&L.wo2, d, ff, 0, (int64_t)ff * d); }
-      if (r == "layer_norm.weight") { RC(expect(d)); return put_f32(&L.ln2, d); }
-    }
-  }
-  return pn_fail(PN_E_BADARG, "pn_t5_load_weight: unrecognised parameter name %s", name);
+  const PnParam& p = m->params[it->second];
+  if (numel != p.numel)
+    return pn_fail(PN_E_BADARG, "pn_t5_load_weight: %s has %lld elements, expected %lld", name,
+                   (long long)numel, (long long)p.numel);
+  RC(t5_allocate(m));
+  if (it->second == 0 && m->loaded[0] && strcmp(name, "shared.weight")) return PN_OK;  // tied copies
+  PN_CUDA(cudaMemcpyAsync(m->flat + p.off, src, numel * sizeof(float), cudaMemcpyDeviceToDevice,
+                          (cudaStream_t)stream));
+  m->loaded[it->second] = 1;
+  m->finalized = false;
+  return PN_OK;
 }
 
 extern "C" int pn_t5_finalize(PnT5* m, void* stream) {
   PN_CHECK_ARG(m);
-  cudaStream_t st = (cudaStream_t)stream;
   // every parameter of a tied-embedding T5 must have been supplied
-  std::vector<std::string> need = {"shared.weight", "encoder.final_layer_norm.weight",
-                                   "decoder.final_layer_norm.weight",
-                                   "encoder.block.0.layer.0.SelfAttention.relative_attention_bias.weight",
-                                   "decoder.block.0.layer.0.SelfAttention.relative_attention_bias.weight"};
-  char buf[128];
-  for (size_t i = 0; i < m->enc.size(); ++i) {
-    for (const char* s : {"0.SelfAttention.q", "0.SelfAttention.k", "0.SelfAttention.v",
-                          "0.SelfAttention.o", "0.layer_norm", "1.DenseReluDense.wi",
-                          "1.DenseReluDense.wo", "1.layer_norm"}) {
-      snprintf(buf, sizeof(buf), "encoder.block.%zu.layer.%s.weight", i, s);
-      need.push_back(buf);
-    }
-  }
-  for (size_t i = 0; i < m->dec.size(); ++i) {
-    for (const char* s : {"0.SelfAttention.q", "0.SelfAttention.k", "0.SelfAttention.v",
-                          "0.SelfAttention.o", "0.layer_norm", "1.EncDecAttention.q",
-                          "1.EncDecAttention.k", "1.EncDecAttention.v", "1.EncDecAttention.o",
-                          "1.layer_norm", "2.DenseReluDense.wi", "2.DenseReluDense.wo", "2.layer_norm"}) {
-      snprintf(buf, sizeof(buf), "decoder.block.%zu.layer.%s.weight", i, s);
-      need.push_back(buf);
-    }
-  }
-  for (const auto& s : need)
-    if (!m->loaded.count(s)) return pn_fail(PN_E_BADARG, "pn_t5_finalize: missing weight %s", s.c_str());
-  // expand the bias tables on the host (tiny) from the [buckets, heads] embeddings
-  const int H = m->cfg.n_heads, nb = m->cfg.rel_buckets;
-  std::vector<float> rel((size_t)nb * H), drel((size_t)nb * H);
-  PN_CUDA(cudaStreamSynchronize(st));
-  PN_CUDA(cudaMemcpy(rel.data(), m->enc_rel, rel.size() * 4, cudaMemcpyDeviceToHost));
-  PN_CUDA(cudaMemcpy(drel.data(), m->dec_rel, drel.size() * 4, cudaMemcpyDeviceToHost));
-  const int W = 1023;
-  std::vector<float> eb((size_t)H * W), db((size_t)H * 4);
-  for (int h = 0; h < H; ++h) {
-    for (int i = 0; i < W; ++i) {
-      const int relpos = i - 511;  // j - i
-      eb[(size_t)h * W + i] = rel[(size_t)rel_bucket_bidir(relpos, nb, m->cfg.rel_max_dist) * H + h];
-    }
-    // decoder (unidirectional): bucket = min(i - j, ...) = distance for distance < 16; T <= 2 here
-    for (int t = 0; t < 2; ++t)
-      for (int j = 0; j < 2; ++j) {
-        const int dist = t - j > 0 ? t - j : 0;
-        db[((size_t)h * 2 + t) * 2 + j] = drel[(size_t)dist * H + h];
-      }
-  }
-  if (!m->enc_bias) RC(dev_alloc(m, &m->enc_bias, eb.size()));
-  if (!m->dec_bias) RC(dev_alloc(m, &m->dec_bias, db.size()));
-  PN_CUDA(cudaMemcpy(m->enc_bias, eb.data(), eb.size() * 4, cudaMemcpyHostToDevice));
-  PN_CUDA(cudaMemcpy(m->dec_bias, db.data(), db.size() * 4, cudaMemcpyHostToDevice));
-  RC(pack_all(m, st));
+  for (size_t i = 0; i < m->params.size(); ++i)
+    if (!m->loaded[i]) return pn_fail(PN_E_BADARG, "pn_t5_finalize: missing weight %s", m->params[i].name.c_str());
+  RC(pn_t5_repack(m, (cudaStream_t)stream));
   m->finalized = true;
   return PN_OK;
+}
+
+/* flat parameter access (training, checkpoint export): HF order, one contiguous fp32 buffer */
+extern "C" int64_t pn_t5_num_params(const PnT5* m) { return m ? m->n_params : -1; }
+extern "C" int32_t pn_t5_num_tensors(const PnT5* m) { return m ? (int32_t)m->params.size() : -1; }
+extern "C" int pn_t5_tensor_info(const PnT5* m, int32_t i, char* name_out, int32_t name_cap,
+                                 int64_t* offset_out, int64_t* numel_out) {
+  PN_CHECK_ARG(m && i >= 0 && i < (int32_t)m->params.size());
+  const PnParam& p = m->params[i];
+  if (name_out && name_cap > 0) snprintf(name_out, name_cap, "%s", p.name.c_str());
+  if (offset_out) *offset_out = p.off;
+  if (numel_out) *numel_out = p.numel;
+  return PN_OK;
+}
+extern "C" float* pn_t5_params(PnT5* m) {
+  if (!m || t5_allocate(m)) return nullptr;
+  return m->flat;
 }
 
 extern "C" int64_t pn_t5_workspace_bytes(const PnT5* m, int64_t docs, int32_t S, int32_t T,

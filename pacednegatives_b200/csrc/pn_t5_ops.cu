@@ -40,14 +40,39 @@ embed_kernel(const int32_t* __restrict__ ids, const float* __restrict__ table, i
 }
 
 // packed[r, c] = bf16( master[r, c] * (colscale ? colscale[c] : 1) ): folds an RMSNorm weight into the
-// [out, in] matrix of the linear that consumes the normalised activations
-__global__ void __launch_bounds__(kThreads)
+// [out, in] matrix of the linear that consumes the normalised activations; packedT[c, r] (ld = ldT) is the
+// transposed copy the data-gradient GEMM reads.  32x32 tiles through shared memory: both stores coalesced.
+__global__ void __launch_bounds__(256)
 pack_weight_kernel(const float* __restrict__ master, const float* __restrict__ colscale, int64_t rows,
-                   int cols, __nv_bfloat16* __restrict__ packed) {
-  const int64_t n = rows * cols;
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
-    const float g = colscale ? colscale[i % cols] : 1.0f;
-    packed[i] = __float2bfloat16_rn(master[i] * g);
+                   int cols, __nv_bfloat16* __restrict__ packed, __nv_bfloat16* __restrict__ packedT, int ldT) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  const int64_t tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
+  for (int64_t t = blockIdx.x; t < tiles_c * tiles_r; t += gridDim.x) {
+    const int64_t r0 = (t / tiles_c) * 32;
+    const int c0 = (int)(t % tiles_c) * 32;
+    const int c = c0 + tx;
+    const float g = (colscale && c < cols) ? colscale[c] : 1.0f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t r = r0 + ty + 8 * k;
+      float v = 0.0f;
+      if (r < rows && c < cols) {
+        v = master[r * cols + c] * g;
+        packed[r * cols + c] = __float2bfloat16_rn(v);
+      }
+      tile[ty + 8 * k][tx] = v;
+    }
+    __syncthreads();
+    if (packedT) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int cc = c0 + ty + 8 * k;
+        const int64_t rr = r0 + tx;
+        if (cc < cols && rr < rows) packedT[(int64_t)cc * ldT + rr] = __float2bfloat16_rn(tile[tx][ty + 8 * k]);
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -157,10 +182,11 @@ int pn_t5_embed(const int32_t* ids, const float* table, int64_t rows, int d, int
 }
 
 int pn_t5_pack_weight(const float* master, const float* colscale, int64_t rows, int cols,
-                      __nv_bfloat16* packed, cudaStream_t st) {
+                      __nv_bfloat16* packed, __nv_bfloat16* packedT, int ldT, cudaStream_t st) {
   if (rows * cols == 0) return PN_OK;
-  pack_weight_kernel<<<pn_grid(rows * cols, kThreads, 4, 8), kThreads, 0, st>>>(master, colscale, rows, cols,
-                                                                              packed);
+  const int64_t tiles = ((rows + 31) / 32) * ((cols + 31) / 32);
+  const int grid = (int)(tiles < (int64_t)PN_SM_COUNT * 16 ? tiles : (int64_t)PN_SM_COUNT * 16);
+  pack_weight_kernel<<<grid, 256, 0, st>>>(master, colscale, rows, cols, packed, packedT, ldT);
   PN_LAUNCHED();
   return PN_OK;
 }
