@@ -177,6 +177,14 @@ int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* o
                  int64_t M, int64_t N, int64_t K, int mode, int relu, const float* row_scale,
                  int cta_group, void* stream);
 
+/* Weight gradient of a linear layer (autograd of HF modeling_t5.py:277,298-299,338,92-103 under
+ * lceT5.py:155 manual_backward): C[M,N] (fp32, ldc) += A[K,M]^T . B[K,N] with A = dY and B = X, both bf16 row-major
+ * with K rows (documents x positions).  Both operands are consumed MN-major straight from their row-major
+ * tensors; the K range is split across SMs and accumulated with fp32 vector atomics (order non-deterministic).
+ * N % 128 == 0, M % 8 == 0; any K (TMA zero-fills the tail). */
+int pn_gemm_bf16_wgrad(const void* A, int64_t lda, const void* B, int64_t ldb, float* out, int64_t ldc,
+                       int64_t M, int64_t N, int64_t K, int cta_group, void* stream);
+
 /* T5 encoder self-attention (HF modeling_t5.py:308-336): out = softmax(Q K^T + bias[h, j-i]) V per
  * (document, head), no 1/sqrt(d) scaling, d_kv = 64, S <= 512, no mask.  qkv bf16 [docs*S, 3*H*64] holds
  * q | k | v column blocks; bias fp32 [H, 1023] indexed by (j - i + 511); out bf16 [docs*S, H*64]. */
@@ -199,7 +207,8 @@ typedef struct PnT5Config {
 
 int pn_t5_create(const PnT5Config* cfg, PnT5** out);
 int pn_t5_destroy(PnT5* m);
-/* options: "cta_group" = 1 | 2 (tcgen05 tile mode of the linears) */
+/* options: "cta_group" = 1 | 2 (tcgen05 tile mode of the linears); "train" = 1 (before loading weights):
+ * also keep the transposed bf16 operands the data-gradient GEMMs read */
 int pn_t5_set_option(PnT5* m, const char* name, int64_t value);
 /* One parameter by its HuggingFace state_dict name (e.g. "encoder.block.3.layer.0.SelfAttention.q.weight"),
  * fp32 contiguous DEVICE tensor in HF's layout; converted into the handle's packed bf16 buffers. */
@@ -207,6 +216,15 @@ int pn_t5_load_weight(PnT5* m, const char* hf_name, const float* src, int64_t nu
 /* checks every parameter arrived, expands the relative-position bias tables (syncs the stream) */
 int pn_t5_finalize(PnT5* m, void* stream);
 int64_t pn_t5_workspace_bytes(const PnT5* m, int64_t docs, int32_t S, int32_t T, int want_logits);
+/* Flat parameter storage: every parameter lives in one contiguous fp32 DEVICE buffer in state_dict order
+ * (what the gradient all-reduce of lceT5.py:155 under DDP, AdamW and save_pretrained export walk).
+ * pn_t5_tensor_info gives tensor i's HF name, element offset and size; pn_t5_params the buffer (owned by the
+ * handle; after writing into it call pn_t5_finalize again to refresh the packed bf16 operands). */
+int64_t pn_t5_num_params(const PnT5* m);
+int32_t pn_t5_num_tensors(const PnT5* m);
+int pn_t5_tensor_info(const PnT5* m, int32_t i, char* name_out, int32_t name_cap, int64_t* offset_out,
+                      int64_t* numel_out);
+float* pn_t5_params(PnT5* m);
 int32_t pn_t5_vocab_pad(const PnT5* m);
 /* Re-rank scores for `docs` prompts of S token ids (int32 [docs,S]): encoder, one decoder step from the
  * start token, two-row head: z2_out[d] = (z_true, z_false), score_out[d] = log_softmax(z2)[0]. */

@@ -39,7 +39,12 @@ SIGNATURES = {
                                    c_u64, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pn_gemm_bf16": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_int,
                              c_vp, c_int, c_vp]),
+    "pn_gemm_bf16_wgrad": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_vp]),
     "pn_t5_self_attention": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "pn_t5_num_params": (c_i64, [c_vp]),
+    "pn_t5_num_tensors": (c_i32, [c_vp]),
+    "pn_t5_tensor_info": (c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_vp]),
+    "pn_t5_params": (c_vp, [c_vp]),
     "pn_t5_create": (c_int, [c_vp, c_vp]),
     "pn_t5_destroy": (c_int, [c_vp]),
     "pn_t5_set_option": (c_int, [c_vp, C.c_char_p, c_i64]),

@@ -39,6 +39,7 @@ struct GemmArgs {
   void* out;               // bf16 [M, ldc] (mode 0) or fp32 [M, ldc] (mode 1, accumulated in place)
   int ldc;
   int mode;                // PN_EPI_*
+  int splits;              // k-splits per output tile (> 1 only with PN_EPI_ATOMIC_F32)
   int relu;
   const float* row_scale;  // nullable: out = acc * row_scale[row]
   // fused T5 RMSNorm of the A operand (HF:55-69): A holds the un-normalised bf16 residual stream, the norm weight is
@@ -53,7 +54,10 @@ struct GemmArgs {
   float* sumsq_out;         // nullable, [N / BLOCK_N][M]
 };
 
-template <int kCtaGroup, int BLOCK_N>
+// kTN = false: C[M,N] = A[M,K] . B[N,K]^T   (both operands K-major: forward and data-gradient GEMMs)
+// kTN = true : C[M,N] += A[K,M]^T . B[K,N]   (both operands MN-major: weight gradients dW = dY^T X, K = rows);
+//              the K range is split over args.splits work items per tile, accumulated with fp32 atomics
+template <int kCtaGroup, int BLOCK_N, bool kTN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const GemmArgs args) {
@@ -81,8 +85,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int tile_m = BLOCK_M * kCtaGroup;
   const int m_tiles = (args.M + tile_m - 1) / tile_m;
   const int n_tiles = args.N / BLOCK_N;
-  const int num_tiles = m_tiles * n_tiles;
-  const int num_kb = args.K / BLOCK_K;
+  const int num_out_tiles = m_tiles * n_tiles;
+  const int num_tiles = num_out_tiles * args.splits;            // work items: (k-split, output tile)
+  const int total_kb = (args.K + BLOCK_K - 1) / BLOCK_K;
+  const int kb_per_split = (total_kb + args.splits - 1) / args.splits;
+  auto kb_range = [&](int item, int& kb0, int& kb1) {
+    const int sp = item / num_out_tiles;
+    kb0 = sp * kb_per_split;
+    kb1 = kb0 + kb_per_split < total_kb ? kb0 + kb_per_split : total_kb;
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -113,23 +124,39 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== TMA producer =====================
     int s = 0;
     uint32_t ph = 0;
-    for (int tile = group_id; tile < num_tiles; tile += num_groups) {
+    for (int item = group_id; item < num_tiles; item += num_groups) {
+      const int tile = item % num_out_tiles;
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
       const int m0 = m_blk * tile_m + (int)cta_rank * BLOCK_M;
       const int n0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      int kb0, kb1;
+      kb_range(item, kb0, kb1);
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(empty_bar(s), ph ^ 1);
         const uint32_t sa = smem_base + s * Cfg::STAGE_BYTES;
         const uint32_t sb = sa + A_STAGE_BYTES;
-        if (kCtaGroup == 1) {
-          mbar_arrive_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
-          tma_load_2d(sa, &tmA, full_bar(s), kb * BLOCK_K, m0);
-          tma_load_2d(sb, &tmB, full_bar(s), kb * BLOCK_K, n0);
+        if (kCtaGroup == 1) mbar_arrive_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
+        else if (leader) mbar_arrive_expect_tx(full_bar(s), 2 * Cfg::STAGE_BYTES);  // both CTAs' halves
+        if (!kTN) {
+          if (kCtaGroup == 1) {
+            tma_load_2d(sa, &tmA, full_bar(s), kb * BLOCK_K, m0);
+            tma_load_2d(sb, &tmB, full_bar(s), kb * BLOCK_K, n0);
+          } else {
+            tma_load_2d_2sm(sa, &tmA, full_bar(s), kb * BLOCK_K, m0);
+            tma_load_2d_2sm(sb, &tmB, full_bar(s), kb * BLOCK_K, n0);
+          }
         } else {
-          // both CTAs' loads complete on the leader's barrier, which expects both halves
-          if (leader) mbar_arrive_expect_tx(full_bar(s), 2 * Cfg::STAGE_BYTES);
-          tma_load_2d_2sm(sa, &tmA, full_bar(s), kb * BLOCK_K, m0);
-          tma_load_2d_2sm(sb, &tmB, full_bar(s), kb * BLOCK_K, n0);
+          // MN-major tiles: boxes of 64 k-rows x 64 columns (8 KB), one per 64-wide block of M / N
+#pragma unroll
+          for (int j = 0; j < BLOCK_M / 64; ++j) {
+            if (kCtaGroup == 1) tma_load_2d(sa + j * 8192, &tmA, full_bar(s), m0 + j * 64, kb * BLOCK_K);
+            else tma_load_2d_2sm(sa + j * 8192, &tmA, full_bar(s), m0 + j * 64, kb * BLOCK_K);
+          }
+#pragma unroll
+          for (int j = 0; j < Cfg::B_ROWS / 64; ++j) {
+            if (kCtaGroup == 1) tma_load_2d(sb + j * 8192, &tmB, full_bar(s), n0 + j * 64, kb * BLOCK_K);
+            else tma_load_2d_2sm(sb + j * 8192, &tmB, full_bar(s), n0 + j * 64, kb * BLOCK_K);
+          }
         }
         if (++s == kStages) { s = 0; ph ^= 1; }
       }
@@ -139,23 +166,33 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int s = 0;
     uint32_t ph = 0;
     int it = 0;
-    for (int tile = group_id; tile < num_tiles; tile += num_groups, ++it) {
+    constexpr uint32_t IDESC = kTN ? make_idesc_bf16(BLOCK_M * kCtaGroup, BLOCK_N, 1, 1) : Cfg::IDESC;
+    for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
+      int kb0, kb1;
+      kb_range(item, kb0, kb1);
       mbar_wait_cluster(tempty_bar(as), aph ^ 1);  // epilogues of both CTAs drained this stage
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BLOCK_N;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(full_bar(s), ph);
         tc_fence_after();
         const uint32_t sa = smem_base + s * Cfg::STAGE_BYTES;
-        const uint64_t adesc = make_desc_kmajor_sw128(sa);
-        const uint64_t bdesc = make_desc_kmajor_sw128(sa + A_STAGE_BYTES);
+        const uint32_t sb = sa + A_STAGE_BYTES;
 #pragma unroll
         for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-          // advance 32 bytes (16 bf16) inside the swizzle atom: +2 in the 16-byte address field
-          umma_bf16<kCtaGroup>(d_tmem, adesc + 2u * k, bdesc + 2u * k, Cfg::IDESC,
-                               (kb | k) ? 1u : 0u);
+          uint64_t adesc, bdesc;
+          if (!kTN) {
+            // advance 32 bytes (16 bf16) inside the swizzle atom: +2 in the 16-byte address field
+            adesc = make_desc_kmajor_sw128(sa) + 2u * k;
+            bdesc = make_desc_kmajor_sw128(sb) + 2u * k;
+          } else {
+            // 16 k-rows of 128 B further down; 64-wide MN blocks are 8 KB apart (LBO), 8-row groups 1 KB (SBO)
+            adesc = make_desc_mnmajor_sw128(sa + k * 2048, 8192);
+            bdesc = make_desc_mnmajor_sw128(sb + k * 2048, 8192);
+          }
+          umma_bf16<kCtaGroup>(d_tmem, adesc, bdesc, IDESC, ((kb - kb0) | k) ? 1u : 0u);
         }
         umma_commit<kCtaGroup>(empty_bar(s));  // frees the smem slot (in both CTAs) when MMAs retire
         if (++s == kStages) { s = 0; ph ^= 1; }
@@ -177,7 +214,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int rrow = lane >> 3, rj = lane & 7;        // read-back mapping: iteration i -> row 4*i + rrow, chunk rj
     int it = 0;
     uint32_t cc = 0;                                  // chunks staged so far (buffer = cc & 1)
-    for (int tile = group_id; tile < num_tiles; tile += num_groups, ++it) {
+    for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
+      const int tile = item % num_out_tiles;
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
@@ -232,6 +270,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       } else {
         const bool resid = args.mode == PN_EPI_RESID_F32;
+        const bool atomic = args.mode == PN_EPI_ATOMIC_F32;
         float* outf = reinterpret_cast<float*>(args.out);
         float ssq[8];
 #pragma unroll
@@ -283,7 +322,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               h.x += acc.x; h.y += acc.y; h.z += acc.z; h.w += acc.w;
               if (r < args.M) {
                 const size_t off = (size_t)r * args.ldc + col0 + c * 32 + rj * 4;
-                *reinterpret_cast<float4*>(outf + off) = h;
+                if (atomic) atomicAdd(reinterpret_cast<float4*>(outf + off), h);   // red.global.add.v4.f32
+                else *reinterpret_cast<float4*>(outf + off) = h;
                 if (args.copy_out) {
                   __nv_bfloat162 lo = __floats2bfloat162_rn(h.x, h.y), hi = __floats2bfloat162_rn(h.z, h.w);
                   uint2 uu = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
@@ -361,21 +401,28 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
   return PN_OK;
 }
 
-template <int kCtaGroup, int BLOCK_N>
-static int launch_gemm(const void* A, int lda, const void* B, int ldb, const GemmArgs& args,
-                       cudaStream_t st) {
+template <int kCtaGroup, int BLOCK_N, bool kTN>
+static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs args, cudaStream_t st) {
   using Cfg = GemmCfg<kCtaGroup, BLOCK_N>;
   CUtensorMap tmA, tmB;
-  int rc = pn_make_tmap_bf16_2d(&tmA, A, args.M, args.K, lda, BLOCK_M, BLOCK_K);
-  if (rc) return rc;
-  rc = pn_make_tmap_bf16_2d(&tmB, B, args.N, args.K, ldb, Cfg::B_ROWS, BLOCK_K);
-  if (rc) return rc;
+  int rc;
+  if (!kTN) {
+    rc = pn_make_tmap_bf16_2d(&tmA, A, args.M, args.K, lda, BLOCK_M, BLOCK_K);
+    if (rc) return rc;
+    rc = pn_make_tmap_bf16_2d(&tmB, B, args.N, args.K, ldb, Cfg::B_ROWS, BLOCK_K);
+    if (rc) return rc;
+  } else {   // operands are [K rows, M | N columns] row-major: 64 x 64 boxes
+    rc = pn_make_tmap_bf16_2d(&tmA, A, args.K, args.M, lda, BLOCK_K, 64);
+    if (rc) return rc;
+    rc = pn_make_tmap_bf16_2d(&tmB, B, args.K, args.N, ldb, BLOCK_K, 64);
+    if (rc) return rc;
+  }
   CUtensorMap tmC = tmA;   // only the bf16 epilogue stores through a tensor map (32-row x 64-column boxes)
   if (args.mode == PN_EPI_BF16) {
     rc = pn_make_tmap_bf16_2d(&tmC, args.out, args.M, args.N, args.ldc, 32, 64);
     if (rc) return rc;
   }
-  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N>;
+  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N, kTN>;
   static bool attr_done = false;
   if (!attr_done) {
     PN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -383,8 +430,19 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, const Gem
   }
   const int tile_m = BLOCK_M * kCtaGroup;
   const int tiles = ((args.M + tile_m - 1) / tile_m) * (args.N / BLOCK_N);
-  int groups = PN_SM_COUNT / kCtaGroup;
-  if (tiles < groups) groups = tiles;
+  const int max_groups = PN_SM_COUNT / kCtaGroup;
+  args.splits = 1;
+  if (kTN) {
+    // enough k-splits to give every SM (pair) a few work items, each at least 8 k-blocks deep
+    const int total_kb = (args.K + BLOCK_K - 1) / BLOCK_K;
+    int want = (2 * max_groups + tiles - 1) / tiles;
+    if (want > total_kb / 8) want = total_kb / 8;
+    if (want < 1) want = 1;
+    const int per = (total_kb + want - 1) / want;
+    args.splits = (total_kb + per - 1) / per;          // no empty split
+  }
+  int groups = max_groups;
+  if (tiles * args.splits < groups) groups = tiles * args.splits;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(groups * kCtaGroup);
   cfg.blockDim = dim3(kGemmThreads);
@@ -397,10 +455,34 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, const Gem
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  PnProfScope prof(PN_PROF_GEMM, 2.0 * args.M * args.N * args.K, st);
+  PnProfScope prof(kTN ? PN_PROF_WGRAD : PN_PROF_GEMM, 2.0 * args.M * args.N * args.K, st);
   PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, args));
   g_pn_launches.fetch_add(1, std::memory_order_relaxed);
   return PN_OK;
+}
+
+int pn_gemm_wgrad(const void* A, int lda, const void* B, int ldb, float* out, int ldc, int M, int N, int K,
+                  int cta_group, cudaStream_t st) {
+  if (M <= 0 || N <= 0 || K <= 0) return pn_fail(PN_E_BADARG, "pn_gemm_wgrad: empty problem");
+  if (N % 128) return pn_fail(PN_E_UNSUPPORTED, "pn_gemm_wgrad: N=%d must be a multiple of 128", N);
+  if (M % 8) return pn_fail(PN_E_UNSUPPORTED, "pn_gemm_wgrad: M=%d must be a multiple of 8", M);
+  if ((lda % 8) || (ldb % 8) || (ldc % 4) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) || ((uintptr_t)out & 15))
+    return pn_fail(PN_E_BADARG, "pn_gemm_wgrad: operands must be 16-byte aligned");
+  GemmArgs a = {};
+  a.M = M; a.N = N; a.K = K; a.out = out; a.ldc = ldc; a.mode = PN_EPI_ATOMIC_F32; a.norm_dim = 1;
+  const bool n256 = (N % 256) == 0;
+  if (cta_group == 2)
+    return n256 ? launch_gemm<2, 256, true>(A, lda, B, ldb, a, st) : launch_gemm<2, 128, true>(A, lda, B, ldb, a, st);
+  if (cta_group == 1)
+    return n256 ? launch_gemm<1, 256, true>(A, lda, B, ldb, a, st) : launch_gemm<1, 128, true>(A, lda, B, ldb, a, st);
+  return pn_fail(PN_E_BADARG, "pn_gemm_wgrad: cta_group must be 1 or 2");
+}
+
+extern "C" int pn_gemm_bf16_wgrad(const void* A, int64_t lda, const void* B, int64_t ldb, float* out, int64_t ldc,
+                                  int64_t M, int64_t N, int64_t K, int cta_group, void* stream) {
+  PN_CHECK_ARG(A && B && out);
+  return pn_gemm_wgrad(A, (int)lda, B, (int)ldb, out, (int)ldc, (int)M, (int)N, (int)K, cta_group,
+                       (cudaStream_t)stream);
 }
 
 int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
@@ -413,8 +495,8 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
     return pn_fail(PN_E_BADARG, "pn_gemm: operands must be 16-byte aligned with ld %% 8 == 0");
   if (mode != PN_EPI_BF16 && mode != PN_EPI_RESID_F32 && mode != PN_EPI_F32)
     return pn_fail(PN_E_BADARG, "pn_gemm: mode");
-  GemmArgs a;
-  a.M = M; a.N = N; a.K = K; a.out = out; a.ldc = ldc; a.mode = mode; a.relu = relu;
+  GemmArgs a = {};
+  a.M = M; a.N = N; a.K = K; a.out = out; a.ldc = ldc; a.mode = mode; a.relu = relu; a.splits = 1;
   a.row_scale = ex ? ex->row_scale : nullptr;
   a.sumsq_in = ex ? ex->sumsq_in : nullptr;
   a.sumsq_parts = ex ? ex->sumsq_parts : 0;
@@ -429,9 +511,9 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
     return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
   const bool n256 = (N % 256) == 0;
   if (cta_group == 2) {
-    return n256 ? launch_gemm<2, 256>(A, lda, B, ldb, a, st) : launch_gemm<2, 128>(A, lda, B, ldb, a, st);
+    return n256 ? launch_gemm<2, 256, false>(A, lda, B, ldb, a, st) : launch_gemm<2, 128, false>(A, lda, B, ldb, a, st);
   } else if (cta_group == 1) {
-    return n256 ? launch_gemm<1, 256>(A, lda, B, ldb, a, st) : launch_gemm<1, 128>(A, lda, B, ldb, a, st);
+    return n256 ? launch_gemm<1, 256, false>(A, lda, B, ldb, a, st) : launch_gemm<1, 128, false>(A, lda, B, ldb, a, st);
   }
   return pn_fail(PN_E_BADARG, "pn_gemm: cta_group must be 1 or 2");
 }

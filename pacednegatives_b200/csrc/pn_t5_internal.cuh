@@ -4,7 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-enum { PN_EPI_BF16 = 0, PN_EPI_RESID_F32 = 1, PN_EPI_F32 = 2 };
+enum { PN_EPI_BF16 = 0, PN_EPI_RESID_F32 = 1, PN_EPI_F32 = 2, PN_EPI_ATOMIC_F32 = 3 };
 
 // C = A[M,K] . B[N,K]^T on the tcgen05 path (pn_t5_gemm.cu).  mode PN_EPI_BF16: bf16 out (optional
 // ReLU, optional per-row scale); PN_EPI_RESID_F32: fp32 out += acc.
@@ -27,6 +27,10 @@ struct PnGemmExtra {
 int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
                     int mode, int relu, const PnGemmExtra* ex, int cta_group, cudaStream_t st);
 int pn_gemm_sumsq_parts(int N);
+// weight gradient on the tcgen05 path: C[M,N] (fp32, ldc) += A[K,M]^T . B[K,N], A and B bf16 row-major with K rows
+// (dW = dY^T X); the K range is split across work items and accumulated with fp32 vector atomics
+int pn_gemm_wgrad(const void* A, int lda, const void* B, int ldb, float* out, int ldc, int M, int N, int K,
+                  int cta_group, cudaStream_t st);
 
 int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                          uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols);

@@ -73,3 +73,23 @@ def test_gemm_rejects_bad_shapes():
     out = torch.zeros(64, 128, device="cuda", dtype=torch.bfloat16)
     with pytest.raises(RuntimeError):
         run_gemm(A, B, out)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cta_group", [1, 2])
+@pytest.mark.parametrize("K,M,N", [(4096, 768, 768), (1000, 2304, 768), (520, 3000, 256), (64, 128, 128),
+                                   (20000, 768, 3072)])
+def test_wgrad_gemm_vs_torch(cta_group, K, M, N):
+    """dW[M,N] += dY[K,M]^T X[K,N] on the MN-major tcgen05 path with split-K fp32 atomics."""
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    torch.manual_seed(K + M + N)
+    dY = (torch.randn(K, M, device="cuda") * 0.5).bfloat16()
+    X = (torch.randn(K, N, device="cuda") * 0.5).bfloat16()
+    out = torch.randn(M, N, device="cuda")
+    ref = out + dY.float().t() @ X.float()
+    _lib.check(_lib.lib().pn_gemm_bf16_wgrad(_lib.ptr(dY), M, _lib.ptr(X), N, _lib.ptr(out), N, M, N, K, cta_group,
+                                             _lib.stream()))
+    err = (out - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    assert err <= 2e-5 * scale + 1e-3, f"K={K} M={M} N={N}: max err {err} (scale {scale})"
