@@ -191,6 +191,20 @@ int pn_gemm_bf16_wgrad(const void* A, int64_t lda, const void* B, int64_t ldb, f
 int pn_t5_self_attention(const void* qkv, int32_t docs, int32_t S, int32_t n_heads, const float* bias,
                          void* out, void* stream);
 
+/* Same, also returning the base-2 row logsumexp lse2 fp32 [docs*S, H] = log2(sum_j 2^((s_ij + bias) * log2 e))
+ * that the backward pass recomputes the probabilities from. */
+int pn_t5_self_attention_lse(const void* qkv, int32_t docs, int32_t S, int32_t n_heads, const float* bias,
+                             void* out, float* lse2, void* stream);
+
+/* Backward of pn_t5_self_attention (autograd of HF modeling_t5.py:308-336 under lceT5.py:155 manual_backward).
+ * Inputs: qkv and bias as in the forward, ctx = the forward's out, dctx = its gradient (bf16 [docs*S, H*64]),
+ * lse2 from pn_t5_self_attention_lse.  Outputs: dqkv bf16 [docs*S, 3*H*64] = dq | dk | dv, each row multiplied
+ * by row_scale[row] when row_scale is not NULL; dbias_diag fp32 [H, 1023] += sum over documents of dS along
+ * the diagonal (j - i + 511) (caller zeroes it); dvec_ws is a [docs*S, H] fp32 workspace. */
+int pn_t5_self_attention_bwd(const void* qkv, int32_t docs, int32_t S, int32_t n_heads, const float* bias,
+                             const void* ctx, const void* dctx, const float* lse2, const float* row_scale,
+                             void* dqkv, float* dbias_diag, float* dvec_ws, void* stream);
+
 /* ------------------------------------------------------------------ a1 / a9 / a12: monoT5 scorer
  * Replaces transformers.T5ForConditionalGeneration as the reference calls it (lceT5.py:106,132-133,
  * 149-150; pairwrapper.py:223-247; the re-rank formula distill/wrapper.py:34-38).  ReLU FFN, RMSNorm,
@@ -235,6 +249,32 @@ int pn_t5_score(PnT5* m, const int32_t* ids, int64_t docs, int32_t S, int32_t re
 int pn_t5_logits(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S, int32_t T,
                  int32_t rel_id, int32_t nrel_id, float* logits_out, float* z2_out, void* workspace,
                  int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ a10 / a13: the training step
+ * Replaces, for LCEModel.training_step (lceT5.py:124-167), the gradient-tracking model calls
+ * `self.model(**p).logits`, `self.model(**n).logits` (lceT5.py:149-150), the autograd of
+ * `self.manual_backward(main_loss.mean())` (lceT5.py:154-155) and `opt.step()` of the transformers.AdamW built
+ * in configure_optimizers (lceT5.py:171-172).  The handle must have been created with option "train" = 1.
+ *
+ * pn_t5_set_train_buffers: caller-owned fp32 device buffers of pn_t5_num_params() elements, laid out like
+ *   pn_t5_params() (HF state_dict order): gradients (accumulated into), Adam first / second moments (zeroed by
+ *   the caller once).  One contiguous gradient buffer = one all-reduce per step in data-parallel runs.
+ * pn_t5_train_forward: logits_out fp32 [docs*T, vocab_pad]; every activation the backward needs stays in
+ *   `workspace` (pn_t5_train_workspace_bytes), which must be left untouched until pn_t5_train_backward.
+ * pn_t5_train_backward: dlogits fp32 [docs*T, vocab_pad] = d loss / d logits; gradients += .  vocab % 8 == 0.
+ * pn_t5_adamw_step: p -= lr*sqrt(1-b2^t)/(1-b1^t) * m/(sqrt(v)+eps) (+ decoupled weight decay) on gscale*grad,
+ *   then the packed bf16 operands are rebuilt.  pn_adamw: the same update on any fp32 tensor (eta). */
+int64_t pn_t5_train_workspace_bytes(const PnT5* m, int64_t docs, int32_t S, int32_t T);
+int pn_t5_set_train_buffers(PnT5* m, float* grads, float* adam_m, float* adam_v);
+int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S, int32_t T,
+                        float* logits_out, void* workspace, int64_t workspace_bytes, void* stream);
+int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S, int32_t T,
+                         void* workspace, int64_t workspace_bytes, void* stream);
+int pn_t5_zero_grad(PnT5* m, void* stream);
+int pn_t5_adamw_step(PnT5* m, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                     float gscale, void* stream);
+int pn_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+             float eps, float weight_decay, int64_t step, float gscale, void* stream);
 
 #ifdef __cplusplus
 }

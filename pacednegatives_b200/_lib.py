@@ -41,6 +41,16 @@ SIGNATURES = {
                              c_vp, c_int, c_vp]),
     "pn_gemm_bf16_wgrad": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_vp]),
     "pn_t5_self_attention": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "pn_t5_self_attention_lse": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "pn_t5_self_attention_bwd": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                         c_vp, c_vp]),
+    "pn_t5_train_workspace_bytes": (c_i64, [c_vp, c_i64, c_i32, c_i32]),
+    "pn_t5_set_train_buffers": (c_int, [c_vp, c_vp, c_vp, c_vp]),
+    "pn_t5_train_forward": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_i64, c_vp]),
+    "pn_t5_train_backward": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
+    "pn_t5_zero_grad": (c_int, [c_vp, c_vp]),
+    "pn_t5_adamw_step": (c_int, [c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_i64, c_f32, c_vp]),
+    "pn_adamw": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_f32, c_f32, c_f32, c_f32, c_f32, c_i64, c_f32, c_vp]),
     "pn_t5_num_params": (c_i64, [c_vp]),
     "pn_t5_num_tensors": (c_i32, [c_vp]),
     "pn_t5_tensor_info": (c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_vp]),

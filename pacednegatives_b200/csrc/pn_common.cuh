@@ -35,6 +35,7 @@ static inline int pn_fail(int code, const char* fmt, ...) {
   } while (0)
 
 // after a <<<>>> launch
+static inline void pn_count_launch() { g_pn_launches.fetch_add(1, std::memory_order_relaxed); }
 #define PN_LAUNCHED()                                                                         \
   do {                                                                                        \
     g_pn_launches.fetch_add(1, std::memory_order_relaxed);                                    \

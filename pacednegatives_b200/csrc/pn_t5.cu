@@ -102,7 +102,7 @@ int encoder_forward(const PnT5* m, const int32_t* ids, int64_t docs, int S, cons
   for (size_t l = 0; l < m->enc.size(); ++l) {
     const PnEncLayer& L = m->enc[l];
     RC(gemm_normed(m, w.xn, w.ss, cur_parts, L.wqkv, w.big, 3 * di, rows, 0, st));
-    RC(pn_t5_self_attn(w.big, 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx, di, st));
+    RC(pn_t5_self_attn(w.big, 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx, di, nullptr, st));
     RC(gemm_resid(m, w.ctx, L.wo, w.hidden, w.xn, w.ss, rows, st));
     cur_parts = parts;
     RC(gemm_normed(m, w.xn, w.ss, cur_parts, L.wi, w.big, ff, rows, 1, st));
@@ -435,11 +435,20 @@ extern "C" int pn_t5_logits(PnT5* m, const int32_t* ids, const int64_t* labels, 
 
 extern "C" int32_t pn_t5_vocab_pad(const PnT5* m) { return m ? m->vocab_pad : -1; }
 
+extern "C" int pn_t5_self_attention_lse(const void* qkv, int32_t docs, int32_t S, int32_t n_heads,
+                                        const float* bias, void* out, float* lse2, void* stream) {
+  PN_CHECK_ARG(qkv && bias && out && lse2 && docs >= 0 && n_heads > 0);
+  if (docs == 0) return PN_OK;
+  const int di = n_heads * 64;
+  return pn_t5_self_attn((const __nv_bfloat16*)qkv, 3 * di, 0, di, 2 * di, docs, S, n_heads, bias,
+                         (__nv_bfloat16*)out, di, lse2, (cudaStream_t)stream);
+}
+
 extern "C" int pn_t5_self_attention(const void* qkv, int32_t docs, int32_t S, int32_t n_heads,
                                     const float* bias, void* out, void* stream) {
   PN_CHECK_ARG(qkv && bias && out && docs >= 0 && n_heads > 0);
   if (docs == 0) return PN_OK;
   const int di = n_heads * 64;
   return pn_t5_self_attn((const __nv_bfloat16*)qkv, 3 * di, 0, di, 2 * di, docs, S, n_heads, bias,
-                         (__nv_bfloat16*)out, di, (cudaStream_t)stream);
+                         (__nv_bfloat16*)out, di, nullptr, (cudaStream_t)stream);
 }

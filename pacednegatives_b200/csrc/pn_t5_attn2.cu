@@ -58,6 +58,7 @@ struct Attn2Args {
   const float* bias;              // [n_heads, 1023] additive bias by (j - i + 511)
   __nv_bfloat16* out;
   int ld_out;
+  float* lse;                     // optional [docs*S, n_heads]: log2-domain logsumexp of each row (training)
   long long* dbg;                 // optional [2][64][8] clock64 stamps of CTA 0 (PN_ATTN_DBG)
 };
 
@@ -396,6 +397,8 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
           // rows -> bf16, transposed through a 2 KB per-warp staging tile so that every store instruction writes
           // 8 rows x 64 contiguous bytes instead of 32 rows x 16 bytes
           const float inv = 1.0f / l;
+          if (a.lse && qi < S)
+            a.lse[(size_t)((doc0 + it * a.cph) * S + qi) * a.n_heads + head] = m_used + log2f(l);
           uint8_t* stage = gbase + SM_STAGE + warp * 2048;
           const int doc_row0 = (doc0 + it * a.cph) * S + qb * QB + w4 * 32;
 #pragma unroll
@@ -456,9 +459,9 @@ static int attn_impl() {
 }
 
 int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
-                    int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out,
+                    int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
                     cudaStream_t st) {
-  if (attn_impl() == 1)
+  if (attn_impl() == 1 && !lse_out)
     return pn_t5_self_attn_v1(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, out, ld_out, st);
   if (S < 1 || S > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "self-attention: S=%d not in [1,512]", S);
   if (docs <= 0) return PN_OK;
@@ -472,6 +475,7 @@ int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, 
   if (a.cph > docs) a.cph = docs;
   a.q_col = q_col; a.k_col = k_col; a.v_col = v_col;
   a.bias = bias; a.out = out; a.ld_out = ld_out;
+  a.lse = lse_out;
   a.dbg = nullptr;
   if (getenv("PN_ATTN_DBG")) {
     static long long* dbg = nullptr;

@@ -1,0 +1,511 @@
+// Backward of the T5 encoder self-attention (autograd of HF modeling_t5.py:308-336 under lceT5.py:155):
+//   P = softmax(Q K^T + bias),  O = P V
+//   dV = P^T dO,   dP = dO V^T,   dS = P (.) (dP - D),  D_i = sum_d dO_id O_id,
+//   dQ = dS K,     dK = dS^T Q,   dbias[h, j - i] += dS_ij        (no 1/sqrt(d) scale in T5)
+// Flash-style on tcgen05, P recomputed from the forward's log2-domain row logsumexp; nothing [S,S]-sized
+// ever reaches HBM.  One templated kernel, two launches:
+//   MODE 0 (dK, dV, dbias): a work item is (doc, 128-key block); K, V stay resident, the query blocks stream
+//   MODE 1 (dQ)           : a work item is (doc, 128-query block); Q, dO stay resident, the key blocks stream
+// Per inner step both modes form S = Q K^T and dP = dO V^T as 128x128 UMMAs into TMEM (rows = queries), 256
+// threads (two per query row, 64 key columns each) turn them into P and dS (bf16, swizzled shared-memory
+// tiles), and the accumulating UMMAs consume those tiles MN-major (P^T dO, dS^T Q) or K-major (dS K).
+// A CTA serves one head for its whole life, so the per-diagonal bias gradient accumulates in shared memory
+// (warp-skewed shuffle reduction: one shared atomic per diagonal per warp) and is flushed once.
+// Warp roles: 0..7 compute, 8 = TMA producer, 9 = TMEM allocator + MMA issuer, 10..13 (MODE 0) = bias-gradient
+// diagonal sums read back from the dS tile.
+#include "pn_common.cuh"
+#include "pn_tc.cuh"
+#include "pn_t5_internal.cuh"
+
+using namespace pntc;
+
+namespace {
+
+constexpr int kThreadsKV = 512;   // MODE 0: + 4 diagonal warps (+ 2 idle: setmaxnreg works on whole warpgroups)
+constexpr int kThreadsQ = 320;
+constexpr int DK = 64;
+constexpr int BLK = 128;                       // rows per query / key block
+constexpr int TILE_BYTES = BLK * DK * 2;       // 16 KB: [128 x 64] bf16, 128-byte swizzle
+constexpr int PT_BYTES = 2 * TILE_BYTES;       // [128 q x 128 k] bf16 as two 64-column sub-tiles
+constexpr int MAX_S = 512;
+constexpr int BIAS_W = 2 * MAX_S - 1;
+constexpr int BIAS_STRIDE = 1032;
+constexpr float kLog2e = 1.4426950408889634f;
+
+// smem: resident pair | streamed pair x2 | P tile | dS tile | bias copies | diag accumulators | barriers
+constexpr int SM_RES = 0;                              // [0] = Q or K, [1] = dO or V
+constexpr int SM_STR = 2 * TILE_BYTES;                 // 2 buffers x (2 tiles)
+constexpr int SM_P = SM_STR + 4 * TILE_BYTES;
+constexpr int SM_DS = SM_P + PT_BYTES;
+constexpr int SM_BIAS = SM_DS + PT_BYTES;
+constexpr int SM_DIAG = SM_BIAS + 4 * BIAS_STRIDE * 4;
+constexpr int SM_BAR = SM_DIAG + 1024 * 4;
+enum { B_RES_FULL = 0, B_RES_FREE, B_STR_FULL0, B_STR_FULL1, B_STR_EMPTY0, B_STR_EMPTY1, B_SP_FULL, B_SP_FREE,
+       B_PD_READY, B_PD_FREE, B_ACC_FULL, B_ACC_FREE, NUM_BARS };
+constexpr int BWD_SMEM = SM_BAR + NUM_BARS * 8 + 16 + 1024;
+
+constexpr uint32_t TM_S = 0, TM_DP = 128, TM_ACC0 = 256, TM_ACC1 = 320, TM_COLS = 512;
+
+struct BwdArgs {
+  int S, n_heads, docs, cph;
+  int q_col, k_col, v_col;          // column blocks of qkv / dqkv
+  const float* bias;                // [H, 1023]
+  const float* lse2;                // [rows, H] log2-domain logsumexp from the forward
+  const float* dvec;                // [rows, H] D_i = sum_d dO O
+  const float* row_scale;           // nullable [rows]: dq/dk/dv rows are scaled (fused-norm backward)
+  __nv_bfloat16* dqkv;              // [rows, ld] gradients, same layout as qkv
+  int ld;
+  float* dbias_diag;                // [H, 1023] += per-diagonal sums (MODE 0 only)
+};
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+template <int MODE>
+__global__ void __maxnreg__(MODE == 0 ? 120 : 168)
+t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                   const BwdArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  float* sbias = reinterpret_cast<float*>(gbase + SM_BIAS);
+  float* sdiag = reinterpret_cast<float*>(gbase + SM_DIAG);
+  const uint32_t bar0 = base + SM_BAR;
+  auto bar = [&](int i) { return bar0 + 8u * i; };
+  const uint32_t tmem_slot = bar0 + 8u * NUM_BARS;
+  uint32_t* tmem_slot_gen = reinterpret_cast<uint32_t*>(gbase + SM_BAR + 8 * NUM_BARS);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int head = blockIdx.x / a.cph, c_in_head = blockIdx.x % a.cph;
+  const int S = a.S;
+  const int nb = (S + BLK - 1) / BLK;                 // blocks per document (queries and keys alike)
+  const int items_total = a.docs * nb;
+  const int n_items = c_in_head < items_total ? (items_total - c_in_head + a.cph - 1) / a.cph : 0;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+    mbar_init(bar(B_RES_FULL), 1);
+    mbar_init(bar(B_RES_FREE), 1);
+    mbar_init(bar(B_STR_FULL0), 1);
+    mbar_init(bar(B_STR_FULL1), 1);
+    mbar_init(bar(B_STR_EMPTY0), 1);
+    mbar_init(bar(B_STR_EMPTY1), 1);
+    mbar_init(bar(B_SP_FULL), 1);
+    mbar_init(bar(B_SP_FREE), 8);
+    mbar_init(bar(B_PD_READY), 8);
+    mbar_init(bar(B_PD_FREE), MODE == 0 ? 5 : 1);   // tcgen05.commit (+ the 4 diagonal warps)
+    mbar_init(bar(B_ACC_FULL), 1);
+    mbar_init(bar(B_ACC_FREE), 8);
+    fence_mbar_init();
+  }
+  if (warp == 9) {
+    tmem_alloc<1>(tmem_slot, TM_COLS);
+    tmem_relinquish<1>();
+  }
+  for (int i = threadIdx.x; i < 4 * BIAS_STRIDE; i += blockDim.x) {
+    const int sh = i / BIAS_STRIDE, k = i % BIAS_STRIDE;
+    const int src = k + sh;
+    sbias[i] = src < BIAS_W ? a.bias[(size_t)head * BIAS_W + src] * kLog2e : 0.0f;
+  }
+  for (int i = threadIdx.x; i < 1024; i += blockDim.x) sdiag[i] = 0.0f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot_gen;
+
+  // item i of this CTA -> (doc, outer block); inner step t -> inner block
+  auto item_doc = [&](int i) { return (c_in_head + i * a.cph) / nb; };
+  auto item_ob = [&](int i) { return (c_in_head + i * a.cph) % nb; };
+  // tile sources: MODE 0 resident = (K, V) of key block ob, streamed = (Q, dO) of query block t
+  //               MODE 1 resident = (Q, dO) of query block ob, streamed = (K, V) of key block t
+  const int col_q = a.q_col + head * DK, col_k = a.k_col + head * DK, col_v = a.v_col + head * DK;
+  const int col_do = head * DK;
+
+  // MODE 0 registers: the 8 compute warps take what the other two warpgroups give up
+  if (warp == 8) {
+    if (MODE == 0) reg_dealloc<72>();
+    if (lane == 0) {
+      // ===================== TMA producer =====================
+      int g = 0;
+      for (int it = 0; it < n_items; ++it) {
+        const int row0 = item_doc(it) * S, ob = item_ob(it);
+        mbar_wait(bar(B_RES_FREE), (it & 1) ^ 1);
+        mbar_arrive_expect_tx(bar(B_RES_FULL), 2 * TILE_BYTES);
+        if (MODE == 0) {
+          tma_load_2d(base + SM_RES, &tmQKV, bar(B_RES_FULL), col_k, row0 + ob * BLK);
+          tma_load_2d(base + SM_RES + TILE_BYTES, &tmQKV, bar(B_RES_FULL), col_v, row0 + ob * BLK);
+        } else {
+          tma_load_2d(base + SM_RES, &tmQKV, bar(B_RES_FULL), col_q, row0 + ob * BLK);
+          tma_load_2d(base + SM_RES + TILE_BYTES, &tmDO, bar(B_RES_FULL), col_do, row0 + ob * BLK);
+        }
+        for (int t = 0; t < nb; ++t, ++g) {
+          const int b = g & 1;
+          mbar_wait(bar(B_STR_EMPTY0 + b), ((g >> 1) & 1) ^ 1);
+          mbar_arrive_expect_tx(bar(B_STR_FULL0 + b), 2 * TILE_BYTES);
+          const uint32_t dst = base + SM_STR + b * 2 * TILE_BYTES;
+          if (MODE == 0) {
+            tma_load_2d(dst, &tmQKV, bar(B_STR_FULL0 + b), col_q, row0 + t * BLK);
+            tma_load_2d(dst + TILE_BYTES, &tmDO, bar(B_STR_FULL0 + b), col_do, row0 + t * BLK);
+          } else {
+            tma_load_2d(dst, &tmQKV, bar(B_STR_FULL0 + b), col_k, row0 + t * BLK);
+            tma_load_2d(dst + TILE_BYTES, &tmQKV, bar(B_STR_FULL0 + b), col_v, row0 + t * BLK);
+          }
+        }
+      }
+    }
+  } else if (warp == 9) {
+    if (MODE == 0) reg_dealloc<72>();
+    if (lane == 0) {
+      // ===================== MMA issuer =====================
+      constexpr uint32_t IDESC_SP = make_idesc_bf16(128, BLK, 0, 0);
+      constexpr uint32_t IDESC_TN = make_idesc_bf16(128, DK, 1, 1);    // A = P^T / dS^T (MN-major), B MN-major
+      constexpr uint32_t IDESC_NN = make_idesc_bf16(128, DK, 0, 1);    // A = dS (K-major), B = K MN-major
+      const int total = n_items * nb;
+      auto tiles = [&](int g, uint32_t& tq, uint32_t& tk, uint32_t& tdo, uint32_t& tv) {
+        const uint32_t str = base + SM_STR + (g & 1) * 2 * TILE_BYTES, res = base + SM_RES;
+        if (MODE == 0) { tq = str; tdo = str + TILE_BYTES; tk = res; tv = res + TILE_BYTES; }
+        else { tq = res; tdo = res + TILE_BYTES; tk = str; tv = str + TILE_BYTES; }
+      };
+      auto issue_sp = [&](int g) {
+        const int it = g / nb, t = g % nb;
+        uint32_t tq, tk, tdo, tv;
+        tiles(g, tq, tk, tdo, tv);
+        mbar_wait(bar(B_STR_FULL0 + (g & 1)), (g >> 1) & 1);
+        if (t == 0) mbar_wait(bar(B_RES_FULL), it & 1);
+        if (g > 0) mbar_wait(bar(B_SP_FREE), (g - 1) & 1);   // compute threads hold S, dP of the previous step
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < DK / 16; ++k)
+          umma_bf16<1>(tmem + TM_S, make_desc_kmajor_sw128(tq) + 2u * k, make_desc_kmajor_sw128(tk) + 2u * k,
+                       IDESC_SP, k ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < DK / 16; ++k)
+          umma_bf16<1>(tmem + TM_DP, make_desc_kmajor_sw128(tdo) + 2u * k, make_desc_kmajor_sw128(tv) + 2u * k,
+                       IDESC_SP, k ? 1u : 0u);
+        umma_commit<1>(bar(B_SP_FULL));
+      };
+      auto issue_acc = [&](int g) {
+        const int it = g / nb, t = g % nb;
+        uint32_t tq, tk, tdo, tv;
+        tiles(g, tq, tk, tdo, tv);
+        mbar_wait(bar(B_PD_READY), g & 1);
+        if (t == 0 && it > 0) mbar_wait(bar(B_ACC_FREE), (it - 1) & 1);
+        tc_fence_after();
+        const uint32_t tp = base + SM_P, tds = base + SM_DS;
+#pragma unroll
+        for (int kk = 0; kk < BLK / 16; ++kk) {
+          const uint32_t acc = (t | kk) ? 1u : 0u;
+          if (MODE == 0) {
+            // dV[k, :] += sum_q P[q, k] dO[q, :]      dK[k, :] += sum_q dS[q, k] Q[q, :]
+            umma_bf16<1>(tmem + TM_ACC0, make_desc_mnmajor_sw128(tp + kk * 2048, TILE_BYTES),
+                         make_desc_mnmajor_sw128(tdo + kk * 2048, TILE_BYTES), IDESC_TN, acc);
+            umma_bf16<1>(tmem + TM_ACC1, make_desc_mnmajor_sw128(tds + kk * 2048, TILE_BYTES),
+                         make_desc_mnmajor_sw128(tq + kk * 2048, TILE_BYTES), IDESC_TN, acc);
+          } else {
+            // dQ[q, :] += sum_k dS[q, k] K[k, :]
+            umma_bf16<1>(tmem + TM_ACC0, make_desc_kmajor_sw128(tds + (kk >> 2) * TILE_BYTES) + 2u * (kk & 3),
+                         make_desc_mnmajor_sw128(tk + kk * 2048, TILE_BYTES), IDESC_NN, acc);
+          }
+        }
+        umma_commit<1>(bar(B_PD_FREE));
+        umma_commit<1>(bar(B_STR_EMPTY0 + (g & 1)));
+        if (t == nb - 1) {
+          umma_commit<1>(bar(B_ACC_FULL));
+          umma_commit<1>(bar(B_RES_FREE));
+        }
+      };
+      if (total > 0) issue_sp(0);
+      for (int g = 0; g < total; ++g) {
+        const bool last_of_item = (g % nb) == nb - 1;
+        // S / dP of the next step are formed while the compute warps work on this one; across an item boundary
+        // the resident tiles are only released by this step's accumulating MMAs, so those go first
+        if (!last_of_item) issue_sp(g + 1);
+        issue_acc(g);
+        if (last_of_item && g + 1 < total) issue_sp(g + 1);
+      }
+    }
+  } else if (warp < 8) {
+    // ===================== compute warps: thread = (query row r, 64-key half) =====================
+    if (MODE == 0) reg_alloc<168>();
+    const int w4 = warp & 3, half = warp >> 2;
+    const int r = w4 * 32 + lane;                   // query row inside the block = TMEM lane
+    const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
+    const int sh = 3 - (r & 3);                     // shifted bias copy that keeps this row 16-byte aligned
+    const float* bcopy = sbias + sh * BIAS_STRIDE;
+    uint8_t* prow = gbase + SM_P + half * TILE_BYTES + r * 128;
+    uint8_t* dsrow = gbase + SM_DS + half * TILE_BYTES + r * 128;
+    int g = 0;
+    for (int it = 0; it < n_items; ++it) {
+      const int row0 = item_doc(it) * S, ob = item_ob(it);
+      for (int t = 0; t < nb; ++t, ++g) {
+        const int qb = MODE == 0 ? t : ob, kb = MODE == 0 ? ob : t;
+        const int qi = qb * BLK + r;
+        const int k0 = kb * BLK + half * 64;
+        float nlse = 0.0f, dv = 0.0f;
+        int kvalid = 0;                             // keys of this half that exist (0 for a padding query row)
+        if (qi < S) {
+          const size_t o = (size_t)(row0 + qi) * a.n_heads + head;
+          nlse = -a.lse2[o];
+          dv = a.dvec[o];
+          kvalid = min(64, S - k0);
+        }
+        mbar_wait(bar(B_SP_FULL), g & 1);
+        tc_fence_after();
+        uint32_t pp[32], pd[32];                    // P and dS of this thread's 64 columns, packed bf16
+#pragma unroll
+        for (int c2 = 0; c2 < 2; ++c2) {
+          uint32_t s[32], dp[32];
+          tmem_ld_32x32(tmem + lane_addr + TM_S + half * 64 + c2 * 32, s);
+          tmem_ld_32x32(tmem + lane_addr + TM_DP + half * 64 + c2 * 32, dp);
+          tmem_ld_wait();
+          const float4* bp = reinterpret_cast<const float4*>(bcopy + (k0 + c2 * 32 - qi + (MAX_S - 1) - sh));
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b = bp[j >> 2];
+            const float bb[4] = {b.x, b.y, b.z, b.w};
+            float p[4], d[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float x = fmaf(__uint_as_float(s[j + e]), kLog2e, bb[e]) + nlse;
+              p[e] = (c2 * 32 + j + e < kvalid) ? ex2_approx(x) : 0.0f;
+              d[e] = p[e] * (__uint_as_float(dp[j + e]) - dv);
+            }
+            pp[c2 * 16 + (j >> 1)] = pack2(p[0], p[1]);
+            pp[c2 * 16 + (j >> 1) + 1] = pack2(p[2], p[3]);
+            pd[c2 * 16 + (j >> 1)] = pack2(d[0], d[1]);
+            pd[c2 * 16 + (j >> 1) + 1] = pack2(d[2], d[3]);
+          }
+        }
+        // S, dP are in registers: the tensor core may form the next step's
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_SP_FREE));
+        if (g > 0) mbar_wait(bar(B_PD_FREE), (g - 1) & 1);   // previous step's accumulating MMAs read P, dS
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int ch = (j ^ (r & 7)) << 4;        // 128-byte swizzle: 16-byte chunk j of row r
+          if (MODE == 0)
+            *reinterpret_cast<uint4*>(prow + ch) = make_uint4(pp[4 * j], pp[4 * j + 1], pp[4 * j + 2], pp[4 * j + 3]);
+          *reinterpret_cast<uint4*>(dsrow + ch) = make_uint4(pd[4 * j], pd[4 * j + 1], pd[4 * j + 2], pd[4 * j + 3]);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_PD_READY));
+
+        if (t == nb - 1) {
+          // ---- item epilogue: dV, dK of key block ob (MODE 0) or dQ of query block ob (MODE 1)
+          mbar_wait(bar(B_ACC_FULL), it & 1);
+          tc_fence_after();
+          uint32_t a0[32], a1[32];
+          tmem_ld_32x32(tmem + lane_addr + TM_ACC0 + half * 32, a0);
+          if (MODE == 0) tmem_ld_32x32(tmem + lane_addr + TM_ACC1 + half * 32, a1);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(B_ACC_FREE));
+          const int oi = ob * BLK + r;
+          if (oi < S) {
+            const size_t grow = (size_t)(row0 + oi);
+            const float sc = a.row_scale ? a.row_scale[grow] : 1.0f;
+            __nv_bfloat16* dst0 = a.dqkv + grow * a.ld + (MODE == 0 ? a.v_col : a.q_col) + head * DK + half * 32;
+            __nv_bfloat16* dst1 = a.dqkv + grow * a.ld + a.k_col + head * DK + half * 32;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 u;
+              u.x = pack2(__uint_as_float(a0[8 * j + 0]) * sc, __uint_as_float(a0[8 * j + 1]) * sc);
+              u.y = pack2(__uint_as_float(a0[8 * j + 2]) * sc, __uint_as_float(a0[8 * j + 3]) * sc);
+              u.z = pack2(__uint_as_float(a0[8 * j + 4]) * sc, __uint_as_float(a0[8 * j + 5]) * sc);
+              u.w = pack2(__uint_as_float(a0[8 * j + 6]) * sc, __uint_as_float(a0[8 * j + 7]) * sc);
+              reinterpret_cast<uint4*>(dst0)[j] = u;
+              if (MODE == 0) {
+                u.x = pack2(__uint_as_float(a1[8 * j + 0]) * sc, __uint_as_float(a1[8 * j + 1]) * sc);
+                u.y = pack2(__uint_as_float(a1[8 * j + 2]) * sc, __uint_as_float(a1[8 * j + 3]) * sc);
+                u.z = pack2(__uint_as_float(a1[8 * j + 4]) * sc, __uint_as_float(a1[8 * j + 5]) * sc);
+                u.w = pack2(__uint_as_float(a1[8 * j + 6]) * sc, __uint_as_float(a1[8 * j + 7]) * sc);
+                reinterpret_cast<uint4*>(dst1)[j] = u;
+              }
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== diagonal warps (MODE 0): dbias[j - i] += dS_ij =====================
+    // The dS tile [128 q x 128 k] is cut into 8x8 blocks (a, b); block-diagonal delta = b - a holds the 15
+    // diagonals 8*delta-7 .. 8*delta+7.  Thread (c, sub) takes the blocks a = sub and sub + 8 of the wrapped
+    // block-diagonal b = (a + c) mod 16: one conflict-free 16-byte load per block row, statically indexed
+    // accumulators, then one shared-memory atomic per diagonal.
+    if (MODE == 0) reg_dealloc<72>();
+    if (MODE == 0 && warp < 14) {
+      const int u = threadIdx.x - 320;
+      const int c = u >> 3, sub = u & 7;
+      const uint8_t* ds = gbase + SM_DS;
+      int g = 0;
+      for (int it = 0; it < n_items; ++it) {
+        const int ob = item_ob(it);
+        for (int t = 0; t < nb; ++t, ++g) {
+          mbar_wait(bar(B_PD_READY), g & 1);
+          const int dbase = (ob - t) * BLK + (MAX_S - 1);      // (key block - query block) * 128 + 511
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int ab = sub + 8 * i;
+            const int b = (ab + c) & 15;
+            const int delta = (ab + c) >= 16 ? c - 16 : c;
+            float acc[15];
+#pragma unroll
+            for (int j = 0; j < 15; ++j) acc[j] = 0.0f;
+            const uint8_t* blk = ds + (b >> 3) * TILE_BYTES + ab * 8 * 128;
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr) {
+              const uint4 v = *reinterpret_cast<const uint4*>(blk + rr * 128 + (((b & 7) ^ rr) << 4));
+              const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                acc[2 * e - rr + 7] += __uint_as_float(w[e] << 16);
+                acc[2 * e + 1 - rr + 7] += __uint_as_float(w[e] & 0xffff0000u);
+              }
+            }
+            float* dst = sdiag + dbase + 8 * delta - 7;
+#pragma unroll
+            for (int j = 0; j < 15; ++j) {
+              const int idx = dbase + 8 * delta - 7 + j;
+              if (idx >= 0 && idx < BIAS_W && acc[j] != 0.0f) atomicAdd(dst + j, acc[j]);
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(B_PD_FREE));
+        }
+      }
+    }
+  }
+
+  // ---- teardown
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) tmem_dealloc<1>(tmem, TM_COLS);
+  if (MODE == 0) {
+    for (int i = threadIdx.x; i < BIAS_W; i += blockDim.x) {
+      const float v = sdiag[i];
+      if (v != 0.0f) atomicAdd(a.dbias_diag + (size_t)head * BIAS_W + i, v);
+    }
+  }
+}
+
+// D[row, h] = sum_d dO[row, h*64 + d] * O[row, h*64 + d]: eight lanes per (row, head)
+__global__ void attn_dvec_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                 int ld, int64_t rows, int H, float* __restrict__ dvec) {
+  const int64_t gi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t grp = gi >> 3;
+  const int l8 = (int)(gi & 7);
+  float acc = 0.0f;
+  if (grp < rows * H) {
+    const int64_t row = grp / H;
+    const int h = (int)(grp % H);
+    const size_t off = (size_t)row * ld + h * DK + l8 * 8;
+    const uint4 x = *reinterpret_cast<const uint4*>(o + off);
+    const uint4 y = *reinterpret_cast<const uint4*>(d_o + off);
+    const uint32_t xs[4] = {x.x, x.y, x.z, x.w}, ys[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      acc = fmaf(__uint_as_float(xs[e] << 16), __uint_as_float(ys[e] << 16), acc);
+      acc = fmaf(__uint_as_float(xs[e] & 0xffff0000u), __uint_as_float(ys[e] & 0xffff0000u), acc);
+    }
+  }
+  acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+  if (l8 == 0 && grp < rows * H) dvec[grp] = acc;
+}
+
+// grad of relative_attention_bias.weight [buckets, H] += per-diagonal sums folded by bucket(j - i)
+__global__ void rel_bias_grad_kernel(const float* __restrict__ diag, const int* __restrict__ bucket_of, int H,
+                                     int buckets, float* __restrict__ grad) {
+  __shared__ float sb[64];
+  const int h = blockIdx.x;
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) sb[i] = 0.0f;
+  __syncthreads();
+  for (int i = threadIdx.x; i < BIAS_W; i += blockDim.x) {
+    const float v = diag[(size_t)h * BIAS_W + i];
+    if (v != 0.0f) atomicAdd(&sb[bucket_of[i]], v);
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < buckets; b += blockDim.x) grad[(size_t)b * H + h] += sb[b];
+}
+
+}  // namespace
+
+int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, int v_col, int docs, int S,
+                        int n_heads, const float* bias, const __nv_bfloat16* ctx, const __nv_bfloat16* dctx,
+                        int ld_ctx, const float* lse2, float* dvec, const float* row_scale,
+                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st) {
+  if (S < 1 || S > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "self-attention backward: S=%d not in [1,512]", S);
+  if (docs <= 0) return PN_OK;
+  const int64_t rows = (int64_t)docs * S;
+  CUtensorMap tmQKV, tmDO;
+  int rc = pn_make_tmap_bf16_2d(&tmQKV, qkv, (uint64_t)rows, (uint64_t)ld, ld, BLK, DK);
+  if (rc) return rc;
+  rc = pn_make_tmap_bf16_2d(&tmDO, dctx, (uint64_t)rows, (uint64_t)ld_ctx, ld_ctx, BLK, DK);
+  if (rc) return rc;
+  static bool attr_done = false;
+  if (!attr_done) {
+    PN_CUDA(cudaFuncSetAttribute(t5_attn_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    PN_CUDA(cudaFuncSetAttribute(t5_attn_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    attr_done = true;
+  }
+  {
+    const int64_t threads = rows * n_heads * 8;
+    attn_dvec_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(ctx, dctx, ld_ctx, rows, n_heads, dvec);
+    PN_LAUNCHED();
+  }
+  const int nb = (S + BLK - 1) / BLK;
+  BwdArgs a;
+  a.S = S; a.n_heads = n_heads; a.docs = docs;
+  a.cph = PN_SM_COUNT / n_heads;
+  if (a.cph < 1) a.cph = 1;
+  if (a.cph > docs * nb) a.cph = docs * nb;
+  a.q_col = q_col; a.k_col = k_col; a.v_col = v_col;
+  a.bias = bias; a.lse2 = lse2; a.dvec = dvec; a.row_scale = row_scale;
+  a.dqkv = dqkv; a.ld = ld; a.dbias_diag = dbias_diag;
+  // five [128 x 128 x 64] products per (query block, key block) pair, S and dP formed twice
+  PnProfScope prof(PN_PROF_ATTN_BWD, 14.0 * docs * n_heads * (double)S * S * DK, st);
+  auto launched = [&](const void* fn, const char* which) -> int {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) return PN_OK;
+    cudaFuncAttributes fa = {};
+    cudaFuncGetAttributes(&fa, fn);
+    return pn_fail(PN_E_LAUNCH, "pn_t5_self_attn_bwd: %s launch failed: %s (regs %d, max threads %d, static smem %zu, "
+                   "max dynamic smem %d, requested %d)", which, cudaGetErrorString(e), fa.numRegs,
+                   fa.maxThreadsPerBlock, fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes, BWD_SMEM);
+  };
+  t5_attn_bwd_kernel<0><<<n_heads * a.cph, kThreadsKV, BWD_SMEM, st>>>(tmQKV, tmDO, a);
+  pn_count_launch();
+  if (int rc2 = launched((const void*)t5_attn_bwd_kernel<0>, "dK/dV")) return rc2;
+  t5_attn_bwd_kernel<1><<<n_heads * a.cph, kThreadsQ, BWD_SMEM, st>>>(tmQKV, tmDO, a);
+  pn_count_launch();
+  if (int rc2 = launched((const void*)t5_attn_bwd_kernel<1>, "dQ")) return rc2;
+  return PN_OK;
+}
+
+int pn_t5_rel_bias_grad(const float* dbias_diag, const int* bucket_of, int n_heads, int buckets, float* grad,
+                        cudaStream_t st) {
+  if (buckets > 64) return pn_fail(PN_E_UNSUPPORTED, "relative bias gradient: %d buckets > 64", buckets);
+  rel_bias_grad_kernel<<<n_heads, 256, 0, st>>>(dbias_diag, bucket_of, n_heads, buckets, grad);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+/* test entry: see include/pn_b200.h */
+extern "C" int pn_t5_self_attention_bwd(const void* qkv, int32_t docs, int32_t S, int32_t n_heads,
+                                        const float* bias, const void* ctx, const void* dctx,
+                                        const float* lse2, const float* row_scale, void* dqkv,
+                                        float* dbias_diag, float* dvec_ws, void* stream) {
+  PN_CHECK_ARG(qkv && bias && ctx && dctx && lse2 && dqkv && dbias_diag && dvec_ws && docs >= 0 && n_heads > 0);
+  const int di = n_heads * DK;
+  return pn_t5_self_attn_bwd((const __nv_bfloat16*)qkv, 3 * di, 0, di, 2 * di, docs, S, n_heads, bias,
+                             (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, di, lse2, dvec_ws,
+                             row_scale, (__nv_bfloat16*)dqkv, dbias_diag, (cudaStream_t)stream);
+}

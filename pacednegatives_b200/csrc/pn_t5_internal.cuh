@@ -38,10 +38,28 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
 #include <cuda_bf16.h>
 // T5 encoder self-attention on tcgen05 (pn_t5_attn.cu).  qkv rows are doc*S + position.
 int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
-                    int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out,
+                    int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
                     cudaStream_t st);
+// Backward of pn_t5_self_attn (pn_t5_attn_bwd.cu): dqkv <- (dq | dk | dv) (each row optionally scaled by
+// row_scale), dbias_diag [H, 1023] += per-diagonal sums of dS; lse2 is the forward's lse_out, dvec a [rows, H]
+// workspace.  pn_t5_rel_bias_grad folds the diagonals into the gradient of relative_attention_bias.weight.
+int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, int v_col, int docs, int S,
+                        int n_heads, const float* bias, const __nv_bfloat16* ctx, const __nv_bfloat16* dctx,
+                        int ld_ctx, const float* lse2, float* dvec, const float* row_scale,
+                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st);
+int pn_t5_rel_bias_grad(const float* dbias_diag, const int* bucket_of, int n_heads, int buckets, float* grad,
+                        cudaStream_t st);
 // decoder self / cross attention for T <= 2 query tokens per document
 int pn_t5_dec_attn(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_bfloat16* k,
                    const __nv_bfloat16* v, int ld_kv, int k_col, int v_col, int docs, int T, int Sk,
                    int n_heads, int causal, const float* bias, __nv_bfloat16* out, int ld_out,
                    cudaStream_t st);
+
+// Backward of pn_t5_dec_attn (pn_t5_dec_attn_bwd.cu).  dq rows are scaled by rs_q, dk / dv rows by rs_kv (both
+// nullable); grad_rel (nullable) accumulates the decoder relative_attention_bias gradient [buckets, H].
+int pn_t5_dec_attn_bwd(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_bfloat16* k,
+                       const __nv_bfloat16* v, int ld_kv, int k_col, int v_col, const __nv_bfloat16* dout,
+                       int ld_do, int docs, int T, int Sk, int n_heads, int causal, const float* bias,
+                       const float* rs_q, const float* rs_kv, __nv_bfloat16* dq, int ld_dq, int dq_col,
+                       __nv_bfloat16* dkv, int ld_dkv, int dk_col, int dv_col, float* grad_rel,
+                       cudaStream_t st);

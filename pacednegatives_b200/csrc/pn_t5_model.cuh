@@ -97,3 +97,19 @@ int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float e
 
 // pn_t5.cu: (re)build every packed bf16 operand and the expanded bias tables from the flat fp32 parameters
 int pn_t5_repack(PnT5* m, cudaStream_t st);
+
+// pn_t5_train_ops.cu
+int pn_t5_rs(const float* ss, int parts, int64_t rows, int d, float eps, float* rs, cudaStream_t st);
+int pn_t5_relu_mask_scale(__nv_bfloat16* y, const __nv_bfloat16* act, const float* rs, int64_t rows, int cols,
+                          cudaStream_t st);
+int pn_t5_row_scale(__nv_bfloat16* y, int ld, const float* rs, int64_t rows, int cols, cudaStream_t st);
+int pn_t5_norm_bwd(const float* G, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d, int accumulate,
+                   float* dh, __nv_bfloat16* dhb, cudaStream_t st);
+int pn_t5_unfold(const float* dWp, const float* W, const float* g, int64_t rows, int cols, float* gradW,
+                 float* gradg, cudaStream_t st);
+int pn_t5_embed_bwd(const int32_t* ids, const float* dh, int64_t rows, int d, int vocab, float* grad_table,
+                    cudaStream_t st);
+int pn_t5_final_norm_bwd(const float* dy, const float* x, const float* w, int64_t rows, int d, float eps,
+                         float* dx, __nv_bfloat16* dxb, float* dw, cudaStream_t st);
+int pn_t5_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                float wd, int64_t step, float gscale, cudaStream_t st);

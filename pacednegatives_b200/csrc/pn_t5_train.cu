@@ -1,0 +1,344 @@
+// Training pass of the monoT5 model (LCEModel.training_step, lceT5.py:124-167): the
+// gradient-tracking forward `self.model(**p).logits` / `self.model(**n).logits` (lceT5.py:149-150), the
+// autograd of `self.manual_backward(main_loss.mean())` (lceT5.py:154-155) and `opt.step()` (lceT5.py:156) with
+// the optimiser of configure_optimizers (transformers.AdamW, lceT5.py:171-172).
+//
+// Same kernels and fused-norm formulation as the scorer (pn_t5.cu); what differs is that every GEMM input the
+// backward pass needs is kept.  Saved per encoder layer, rows = docs*S:
+//   hb[2l], hb[2l+1] bf16 [rows, d]  residual stream entering the attention / FFN sub-layer
+//   rs[2l], rs[2l+1] fp32 [rows]     its RMSNorm scale rsqrt(mean(h^2) + eps)
+//   qkv[l] bf16 [rows, 3*di],  lse[l] fp32 [rows, H] (base-2 logsumexp),  ctx[l] bf16 [rows, di],
+//   act[l] bf16 [rows, ff] (post-ReLU)
+// plus hb[2L], rs[2L] (encoder output before its final norm, which is folded into the cross K/V projections) and,
+// per decoder layer, ckv[l] bf16 [rows, 2*di] and the decoder-row (docs*T) analogues.  Nothing [S, S]-sized is
+// kept: the attention backward recomputes the probabilities from lse.
+//
+// Backward per linear y = rs * (hb W'^T) (see pn_t5_train_ops.cu for the algebra): one weight-gradient GEMM
+// (MN-major tcgen05, split-K fp32 atomics), one data-gradient GEMM against the transposed packed weight, and a
+// single bandwidth pass (norm_bwd) that folds the RMSNorm Jacobian into the residual-stream gradient.
+#include "pn_t5_model.cuh"
+
+#include <string.h>
+
+namespace {
+
+size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct TrainWs {
+  // encoder rows
+  float* hidden;                       // residual stream (forward); sum of cross K/V data gradients (backward)
+  std::vector<__nv_bfloat16*> hb;      // 2L+1
+  std::vector<float*> rs;              // 2L+1
+  float* ss;
+  std::vector<__nv_bfloat16*> qkv, ctx, act, ckv;
+  std::vector<float*> lse;
+  float *dH, *gbuf, *dvec;
+  __nv_bfloat16 *dHb, *dbig, *dctx;
+  float *dWtmp, *diag;
+  // decoder rows
+  float* dec_hidden;
+  std::vector<__nv_bfloat16*> dhb;     // 3Ld+1
+  std::vector<float*> drs;
+  float* dss;
+  std::vector<__nv_bfloat16*> dqkv, dctx_s, cq, dctx_c, dact;
+  int32_t* dec_ids;
+  __nv_bfloat16* head_in;
+  float *ddH, *dgbuf;
+  __nv_bfloat16 *ddHb, *ddbig, *ddctx, *dlb;
+  // header kept at the start of the workspace so that backward can check it belongs to the forward
+  int64_t* header;
+};
+
+size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, TrainWs* w) {
+  const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
+  const size_t L = m->enc.size(), Ld = m->dec.size();
+  const size_t rows = (size_t)docs * S, drows = (size_t)docs * T;
+  const size_t bigc = (size_t)(3 * di > ff ? 3 * di : ff);
+  const size_t parts = (size_t)pn_gemm_sumsq_parts(d);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes); return base ? base + o : nullptr; };
+  w->header = (int64_t*)take(64);
+  w->hidden = (float*)take(rows * d * 4);
+  w->hb.resize(2 * L + 1); w->rs.resize(2 * L + 1);
+  for (auto& p : w->hb) p = (__nv_bfloat16*)take(rows * d * 2);
+  for (auto& p : w->rs) p = (float*)take(rows * 4);
+  w->ss = (float*)take(rows * parts * 4);
+  w->qkv.resize(L); w->ctx.resize(L); w->act.resize(L); w->lse.resize(L); w->ckv.resize(Ld);
+  for (auto& p : w->qkv) p = (__nv_bfloat16*)take(rows * 3 * di * 2);
+  for (auto& p : w->ctx) p = (__nv_bfloat16*)take(rows * di * 2);
+  for (auto& p : w->act) p = (__nv_bfloat16*)take(rows * ff * 2);
+  for (auto& p : w->lse) p = (float*)take(rows * H * 4);
+  for (auto& p : w->ckv) p = (__nv_bfloat16*)take(rows * 2 * di * 2);
+  w->dH = (float*)take(rows * d * 4);
+  w->gbuf = (float*)take(rows * d * 4);
+  w->dvec = (float*)take(rows * H * 4);
+  w->dHb = (__nv_bfloat16*)take(rows * d * 2);
+  w->dbig = (__nv_bfloat16*)take(rows * bigc * 2);
+  w->dctx = (__nv_bfloat16*)take(rows * di * 2);
+  w->dWtmp = (float*)take(bigc * d * 4);
+  w->diag = (float*)take((size_t)H * 1023 * 4);
+  w->dec_hidden = (float*)take(drows * d * 4);
+  w->dhb.resize(3 * Ld + 1); w->drs.resize(3 * Ld + 1);
+  for (auto& p : w->dhb) p = (__nv_bfloat16*)take(drows * d * 2);
+  for (auto& p : w->drs) p = (float*)take(drows * 4);
+  w->dss = (float*)take(drows * parts * 4);
+  w->dqkv.resize(Ld); w->dctx_s.resize(Ld); w->cq.resize(Ld); w->dctx_c.resize(Ld); w->dact.resize(Ld);
+  for (auto& p : w->dqkv) p = (__nv_bfloat16*)take(drows * 3 * di * 2);
+  for (auto& p : w->dctx_s) p = (__nv_bfloat16*)take(drows * di * 2);
+  for (auto& p : w->cq) p = (__nv_bfloat16*)take(drows * di * 2);
+  for (auto& p : w->dctx_c) p = (__nv_bfloat16*)take(drows * di * 2);
+  for (auto& p : w->dact) p = (__nv_bfloat16*)take(drows * ff * 2);
+  w->dec_ids = (int32_t*)take(drows * 4);
+  w->head_in = (__nv_bfloat16*)take(drows * d * 2);
+  w->ddH = (float*)take(drows * d * 4);
+  w->dgbuf = (float*)take(drows * d * 4);
+  w->ddHb = (__nv_bfloat16*)take(drows * d * 2);
+  w->ddbig = (__nv_bfloat16*)take(drows * bigc * 2);
+  w->ddctx = (__nv_bfloat16*)take(drows * di * 2);
+  w->dlb = (__nv_bfloat16*)take(drows * (size_t)m->vocab_pad * 2);
+  return off;
+}
+
+// decoder_input_ids = shift_right(labels): [start, labels[:, :-1]] with -100 -> pad (HF:595-614)
+__global__ void shift_right_train_kernel(const int64_t* labels, int64_t docs, int T, int32_t start, int32_t pad,
+                                         int32_t* out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < docs * T;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int t = (int)(i % T);
+    int64_t v = t == 0 ? start : labels[i - 1];
+    if (v == -100) v = pad;
+    out[i] = (int32_t)v;
+  }
+}
+
+// y = rs (.) (hb W'^T), bf16 out
+int lin_fwd(const PnT5* m, const __nv_bfloat16* hb, const float* rs, const PnLin& W, __nv_bfloat16* out, int M,
+            int relu, cudaStream_t st) {
+  PnGemmExtra ex = {};
+  ex.row_scale = rs;
+  return pn_gemm_bf16_ex(hb, W.cols, W.packed, W.cols, out, (int)W.rows, M, (int)W.rows, W.cols, PN_EPI_BF16, relu,
+                         &ex, m->cta_group, st);
+}
+// h += x W^T; hb_next = bf16(h); rs_next from the epilogue's row sums of squares
+int lin_resid(const PnT5* m, const __nv_bfloat16* x, const PnLin& W, float* h, __nv_bfloat16* hb_next, float* ss,
+              float* rs_next, int M, cudaStream_t st) {
+  PnGemmExtra ex = {};
+  ex.copy_out = hb_next; ex.ld_copy = (int)W.rows; ex.sumsq_out = ss;
+  RC(pn_gemm_bf16_ex(x, W.cols, W.packed, W.cols, h, (int)W.rows, M, (int)W.rows, W.cols, PN_EPI_RESID_F32, 0, &ex,
+                     m->cta_group, st));
+  return pn_t5_rs(ss, pn_gemm_sumsq_parts((int)W.rows), M, (int)W.rows, m->cfg.eps, rs_next, st);
+}
+
+// data gradient: out[M, in] = dY[M, out] . W  (B operand = the transposed packed weight [in, out])
+int dgrad(const PnT5* m, const __nv_bfloat16* dY, int ld_dy, const PnLin& W, void* out, int mode, int M,
+          cudaStream_t st) {
+  return pn_gemm_bf16_ex(dY, ld_dy, W.packedT, (int)W.rows, out, W.cols, M, W.cols, (int)W.rows, mode, 0, nullptr,
+                         m->cta_group, st);
+}
+// weight gradient of an un-normed linear: grads[W] += dY^T X
+int wgrad_plain(const PnT5* m, const __nv_bfloat16* dY, int ld_dy, const __nv_bfloat16* X, const PnLin& W, int K,
+                cudaStream_t st) {
+  return pn_gemm_wgrad(dY, ld_dy, X, W.cols, m->grads + W.off, W.cols, (int)W.rows, W.cols, K, m->cta_group, st);
+}
+// weight gradient of a linear behind a fused RMSNorm: dW' = Ys^T hb, then unfold into grads[W] and grads[g]
+int wgrad_folded(const PnT5* m, const __nv_bfloat16* Ys, int ld_ys, const __nv_bfloat16* hb, const PnLin& W,
+                 float* tmp, int K, cudaStream_t st) {
+  PN_CUDA(cudaMemsetAsync(tmp, 0, (size_t)W.rows * W.cols * 4, st));
+  RC(pn_gemm_wgrad(Ys, ld_ys, hb, W.cols, tmp, W.cols, (int)W.rows, W.cols, K, m->cta_group, st));
+  return pn_t5_unfold(tmp, W.master, W.fold, W.rows, W.cols, m->grads + W.off, m->grads + W.fold_off, st);
+}
+
+}  // namespace
+
+extern "C" int64_t pn_t5_train_workspace_bytes(const PnT5* m, int64_t docs, int32_t S, int32_t T) {
+  if (!m || docs < 0 || S < 1 || T < 1) return -1;
+  TrainWs w;
+  return (int64_t)carve_train(m, docs, S, T, nullptr, &w);
+}
+
+extern "C" int pn_t5_set_train_buffers(PnT5* m, float* grads, float* adam_m, float* adam_v) {
+  PN_CHECK_ARG(m && grads);
+  if (!m->want_train) return pn_fail(PN_E_BADARG, "pn_t5_set_train_buffers: model was not created with option \"train\"");
+  m->grads = grads; m->adam_m = adam_m; m->adam_v = adam_v;
+  return PN_OK;
+}
+
+// logits_out fp32 [docs*T, vocab_pad] = self.model(input_ids=ids, labels=labels).logits with every activation the
+// backward needs left in `workspace`
+extern "C" int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S,
+                                   int32_t T, float* logits_out, void* workspace, int64_t workspace_bytes,
+                                   void* stream) {
+  PN_CHECK_ARG(m && m->finalized);
+  if (!m->want_train) return pn_fail(PN_E_BADARG, "pn_t5_train_forward: model was not created with option \"train\"");
+  PN_CHECK_ARG(docs >= 0 && S >= 1 && S <= 512 && (T == 1 || T == 2));
+  if (docs == 0) return PN_OK;
+  PN_CHECK_ARG(ids && labels && logits_out && workspace);
+  PN_CHECK_ARG(docs * (int64_t)S < (1ll << 31));
+  TrainWs w;
+  const size_t need = carve_train(m, docs, S, T, (uint8_t*)workspace, &w);
+  if ((int64_t)need > workspace_bytes)
+    return pn_fail(PN_E_BADARG, "pn_t5_train_forward: workspace %lld < %zu bytes", (long long)workspace_bytes, need);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int d = m->cfg.d_model, di = m->d_inner, H = m->cfg.n_heads;
+  const int rows = (int)(docs * S), drows = (int)(docs * T);
+  const size_t L = m->enc.size(), Ld = m->dec.size();
+  const int64_t hdr[4] = {docs, S, T, 0x706e7472};
+  PN_CUDA(cudaMemcpyAsync(w.header, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
+
+  // ---- encoder
+  RC(pn_t5_embed(ids, m->emb, rows, d, m->cfg.vocab, w.hidden, w.hb[0], w.ss, st));
+  RC(pn_t5_rs(w.ss, 1, rows, d, m->cfg.eps, w.rs[0], st));
+  for (size_t l = 0; l < L; ++l) {
+    const PnEncLayer& E = m->enc[l];
+    RC(lin_fwd(m, w.hb[2 * l], w.rs[2 * l], E.wqkv, w.qkv[l], rows, 0, st));
+    RC(pn_t5_self_attn(w.qkv[l], 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx[l], di, w.lse[l], st));
+    RC(lin_resid(m, w.ctx[l], E.wo, w.hidden, w.hb[2 * l + 1], w.ss, w.rs[2 * l + 1], rows, st));
+    RC(lin_fwd(m, w.hb[2 * l + 1], w.rs[2 * l + 1], E.wi, w.act[l], rows, 1, st));
+    RC(lin_resid(m, w.act[l], E.wo2, w.hidden, w.hb[2 * l + 2], w.ss, w.rs[2 * l + 2], rows, st));
+  }
+  // ---- decoder over shift_right(labels)
+  shift_right_train_kernel<<<pn_grid(docs * T, 256, 1, 4), 256, 0, st>>>(labels, docs, T, m->cfg.pad_id,
+                                                                        m->cfg.pad_id, w.dec_ids);
+  PN_LAUNCHED();
+  RC(pn_t5_embed(w.dec_ids, m->emb, drows, d, m->cfg.vocab, w.dec_hidden, w.dhb[0], w.dss, st));
+  RC(pn_t5_rs(w.dss, 1, drows, d, m->cfg.eps, w.drs[0], st));
+  for (size_t l = 0; l < Ld; ++l) {
+    const PnDecLayer& D = m->dec[l];
+    RC(lin_fwd(m, w.dhb[3 * l], w.drs[3 * l], D.wqkv, w.dqkv[l], drows, 0, st));
+    RC(pn_t5_dec_attn(w.dqkv[l], 3 * di, 0, w.dqkv[l], w.dqkv[l], 3 * di, di, 2 * di, (int)docs, T, T, H, 1,
+                      m->dec_bias, w.dctx_s[l], di, st));
+    RC(lin_resid(m, w.dctx_s[l], D.wo, w.dec_hidden, w.dhb[3 * l + 1], w.dss, w.drs[3 * l + 1], drows, st));
+    RC(lin_fwd(m, w.dhb[3 * l + 1], w.drs[3 * l + 1], D.cq, w.cq[l], drows, 0, st));
+    RC(lin_fwd(m, w.hb[2 * L], w.rs[2 * L], D.ckv, w.ckv[l], rows, 0, st));
+    RC(pn_t5_dec_attn(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
+                      w.dctx_c[l], di, st));
+    RC(lin_resid(m, w.dctx_c[l], D.co, w.dec_hidden, w.dhb[3 * l + 2], w.dss, w.drs[3 * l + 2], drows, st));
+    RC(lin_fwd(m, w.dhb[3 * l + 2], w.drs[3 * l + 2], D.wi, w.dact[l], drows, 1, st));
+    RC(lin_resid(m, w.dact[l], D.wo2, w.dec_hidden, w.dhb[3 * l + 3], w.dss, w.drs[3 * l + 3], drows, st));
+  }
+  // ---- tied head: logits = (RMSNorm(h) * d^-0.5) E^T  (HF:1107-1110)
+  RC(pn_t5_head_prep(w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.head_in, st));
+  RC(pn_gemm_bf16_internal(w.head_in, d, m->emb_bf16, d, logits_out, m->vocab_pad, drows, m->vocab_pad, d,
+                           PN_EPI_F32, 0, nullptr, m->cta_group, st));
+  return PN_OK;
+}
+
+// Accumulates d loss / d parameters into the gradient buffer, given dlogits = d loss / d logits (fp32
+// [docs*T, vocab_pad]) for the forward pass whose activations `workspace` holds.
+extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S,
+                                    int32_t T, void* workspace, int64_t workspace_bytes, void* stream) {
+  PN_CHECK_ARG(m && m->finalized && m->want_train);
+  if (!m->grads) return pn_fail(PN_E_BADARG, "pn_t5_train_backward: no gradient buffer (pn_t5_set_train_buffers)");
+  PN_CHECK_ARG(docs >= 0 && S >= 1 && S <= 512 && (T == 1 || T == 2));
+  if (docs == 0) return PN_OK;
+  PN_CHECK_ARG(ids && dlogits && workspace);
+  if (m->cfg.vocab % 8)
+    return pn_fail(PN_E_UNSUPPORTED, "pn_t5_train_backward: vocab=%d must be a multiple of 8", m->cfg.vocab);
+  TrainWs w;
+  const size_t need = carve_train(m, docs, S, T, (uint8_t*)workspace, &w);
+  if ((int64_t)need > workspace_bytes)
+    return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace %lld < %zu bytes", (long long)workspace_bytes, need);
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t hdr[4];
+  PN_CUDA(cudaMemcpyAsync(hdr, w.header, sizeof(hdr), cudaMemcpyDeviceToHost, st));
+  PN_CUDA(cudaStreamSynchronize(st));
+  if (hdr[0] != docs || hdr[1] != S || hdr[2] != T || hdr[3] != 0x706e7472)
+    return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace does not hold a forward pass of this shape");
+  const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
+  const int rows = (int)(docs * S), drows = (int)(docs * T);
+  const int L = (int)m->enc.size(), Ld = (int)m->dec.size();
+  const int Vp = m->vocab_pad;
+  float* G = m->grads;
+  const int* bucket_of = (const int*)m->allocs[0];
+
+  // ---- head: d head_in = dlogits E,  dE += dlogits^T head_in,  then the final decoder norm
+  RC(pn_t5_f32_to_bf16(dlogits, w.dlb, (int64_t)drows * Vp, st));
+  RC(pn_gemm_wgrad(w.dlb, Vp, w.head_in, d, G + m->emb_off, d, m->cfg.vocab, d, drows, m->cta_group, st));
+  RC(pn_gemm_bf16_internal(w.dlb, Vp, m->embT_bf16, Vp, w.dgbuf, d, drows, d, Vp, PN_EPI_F32, 0, nullptr,
+                           m->cta_group, st));
+  RC(pn_t5_final_norm_bwd(w.dgbuf, w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.ddH, w.ddHb,
+                          G + m->dec_final_off, st));
+
+  // ---- decoder layers, last to first.  ddH / ddHb = gradient of the decoder residual stream
+  for (int l = Ld - 1; l >= 0; --l) {
+    const PnDecLayer& D = m->dec[l];
+    const __nv_bfloat16 *hb0 = w.dhb[3 * l], *hb1 = w.dhb[3 * l + 1], *hb2 = w.dhb[3 * l + 2];
+    const float *rs0 = w.drs[3 * l], *rs1 = w.drs[3 * l + 1], *rs2 = w.drs[3 * l + 2];
+    // FFN: h3 = h2 + relu(norm(h2) Wi^T) Wo^T
+    RC(wgrad_plain(m, w.ddHb, d, w.dact[l], D.wo2, drows, st));
+    RC(dgrad(m, w.ddHb, d, D.wo2, w.ddbig, PN_EPI_BF16, drows, st));
+    RC(pn_t5_relu_mask_scale(w.ddbig, w.dact[l], rs2, drows, ff, st));
+    RC(wgrad_folded(m, w.ddbig, ff, hb2, D.wi, w.dWtmp, drows, st));
+    RC(dgrad(m, w.ddbig, ff, D.wi, w.dgbuf, PN_EPI_F32, drows, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, hb2, rs2, drows, d, 1, w.ddH, w.ddHb, st));
+    // cross-attention: h2 = h1 + attn(norm(h1) Cq^T, norm_f(enc) Ckv^T) Co^T
+    RC(wgrad_plain(m, w.ddHb, d, w.dctx_c[l], D.co, drows, st));
+    RC(dgrad(m, w.ddHb, d, D.co, w.ddctx, PN_EPI_BF16, drows, st));
+    RC(pn_t5_dec_attn_bwd(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, w.ddctx, di, (int)docs, T, S, H, 0,
+                          nullptr, rs1, w.rs[2 * L], w.ddbig, di, 0, w.dbig, 2 * di, 0, di, nullptr, st));
+    RC(wgrad_folded(m, w.ddbig, di, hb1, D.cq, w.dWtmp, drows, st));
+    RC(dgrad(m, w.ddbig, di, D.cq, w.dgbuf, PN_EPI_F32, drows, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, hb1, rs1, drows, d, 1, w.ddH, w.ddHb, st));
+    RC(wgrad_folded(m, w.dbig, 2 * di, w.hb[2 * L], D.ckv, w.dWtmp, rows, st));
+    // every decoder layer reads the same normalised encoder output: their data gradients add up in `hidden`
+    RC(dgrad(m, w.dbig, 2 * di, D.ckv, w.hidden, l == Ld - 1 ? PN_EPI_F32 : PN_EPI_RESID_F32, rows, st));
+    // self-attention: h1 = h0 + attn(norm(h0) Wqkv^T) Wo^T
+    RC(wgrad_plain(m, w.ddHb, d, w.dctx_s[l], D.wo, drows, st));
+    RC(dgrad(m, w.ddHb, d, D.wo, w.ddctx, PN_EPI_BF16, drows, st));
+    RC(pn_t5_dec_attn_bwd(w.dqkv[l], 3 * di, 0, w.dqkv[l], w.dqkv[l], 3 * di, di, 2 * di, w.ddctx, di, (int)docs, T,
+                          T, H, 1, m->dec_bias, rs0, rs0, w.ddbig, 3 * di, 0, w.ddbig, 3 * di, di, 2 * di,
+                          G + m->dec_rel_off, st));
+    RC(wgrad_folded(m, w.ddbig, 3 * di, hb0, D.wqkv, w.dWtmp, drows, st));
+    RC(dgrad(m, w.ddbig, 3 * di, D.wqkv, w.dgbuf, PN_EPI_F32, drows, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st));
+  }
+  RC(pn_t5_embed_bwd(w.dec_ids, w.ddH, drows, d, m->cfg.vocab, G + m->emb_off, st));
+
+  // ---- encoder: the final norm (folded into every Ckv), then the layers last to first
+  RC(pn_t5_norm_bwd(w.hidden, w.hb[2 * L], w.rs[2 * L], rows, d, 0, w.dH, w.dHb, st));
+  PN_CUDA(cudaMemsetAsync(w.diag, 0, (size_t)H * 1023 * 4, st));
+  for (int l = L - 1; l >= 0; --l) {
+    const PnEncLayer& E = m->enc[l];
+    const __nv_bfloat16 *hb0 = w.hb[2 * l], *hb1 = w.hb[2 * l + 1];
+    const float *rs0 = w.rs[2 * l], *rs1 = w.rs[2 * l + 1];
+    RC(wgrad_plain(m, w.dHb, d, w.act[l], E.wo2, rows, st));
+    RC(dgrad(m, w.dHb, d, E.wo2, w.dbig, PN_EPI_BF16, rows, st));
+    RC(pn_t5_relu_mask_scale(w.dbig, w.act[l], rs1, rows, ff, st));
+    RC(wgrad_folded(m, w.dbig, ff, hb1, E.wi, w.dWtmp, rows, st));
+    RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, PN_EPI_F32, rows, st));
+    RC(pn_t5_norm_bwd(w.gbuf, hb1, rs1, rows, d, 1, w.dH, w.dHb, st));
+    RC(wgrad_plain(m, w.dHb, d, w.ctx[l], E.wo, rows, st));
+    RC(dgrad(m, w.dHb, d, E.wo, w.dctx, PN_EPI_BF16, rows, st));
+    RC(pn_t5_self_attn_bwd(w.qkv[l], 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx[l], w.dctx, di,
+                           w.lse[l], w.dvec, rs0, w.dbig, w.diag, st));
+    RC(wgrad_folded(m, w.dbig, 3 * di, hb0, E.wqkv, w.dWtmp, rows, st));
+    RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, PN_EPI_F32, rows, st));
+    RC(pn_t5_norm_bwd(w.gbuf, hb0, rs0, rows, d, 1, w.dH, w.dHb, st));
+  }
+  RC(pn_t5_embed_bwd(ids, w.dH, rows, d, m->cfg.vocab, G + m->emb_off, st));
+  RC(pn_t5_rel_bias_grad(w.diag, bucket_of, H, m->cfg.rel_buckets, G + m->enc_rel_off, st));
+  return PN_OK;
+}
+
+extern "C" int pn_t5_zero_grad(PnT5* m, void* stream) {
+  PN_CHECK_ARG(m && m->grads);
+  PN_CUDA(cudaMemsetAsync(m->grads, 0, (size_t)m->n_params * 4, (cudaStream_t)stream));
+  return PN_OK;
+}
+
+// transformers.AdamW step over the flat parameter buffer (gradients multiplied by gscale first, e.g. 1/world for
+// a summed all-reduce), then the bf16 operands are rebuilt from the updated masters
+extern "C" int pn_t5_adamw_step(PnT5* m, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                int64_t step, float gscale, void* stream) {
+  PN_CHECK_ARG(m && m->finalized && m->grads && m->adam_m && m->adam_v && step >= 1);
+  cudaStream_t st = (cudaStream_t)stream;
+  RC(pn_t5_adamw(m->flat, m->grads, m->adam_m, m->adam_v, m->n_params, lr, beta1, beta2, eps, weight_decay, step,
+                 gscale, st));
+  return pn_t5_repack(m, st);
+}
+
+extern "C" int pn_adamw(float* p, const float* g, float* mom, float* var, int64_t n, float lr, float beta1,
+                        float beta2, float eps, float weight_decay, int64_t step, float gscale, void* stream) {
+  PN_CHECK_ARG(p && g && mom && var && n >= 0 && step >= 1);
+  return pn_t5_adamw(p, g, mom, var, n, lr, beta1, beta2, eps, weight_decay, step, gscale, (cudaStream_t)stream);
+}

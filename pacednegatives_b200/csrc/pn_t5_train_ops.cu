@@ -1,0 +1,286 @@
+// Bandwidth-bound pieces of the T5 backward pass (autograd of HF modeling_t5.py under lceT5.py:154-157):
+// RMSNorm backward in the "fused norm" formulation, ReLU mask, folded-weight gradient unfold, embedding
+// scatter, final-norm/head backward, AdamW.  All one pass over their operands, 128-bit accesses.
+//
+// Fused-norm algebra (forward: y = rs * (hb @ W'^T), rs = rsqrt(mean(h^2)+eps), W' = W diag(g), hb = bf16(h)):
+//   Ys = rs (.) dY  (row-scaled upstream gradient, what the producers of dY write)
+//   dW' = Ys^T hb            (weight-gradient GEMM on the saved bf16 residual copy)
+//   G   = Ys W'              (data-gradient GEMM)      = rs * d x_hat
+//   dh  = G - rs^2 * hb * mean_k(G_k hb_k)             (the rs of x_hat and of d x_hat cancel inside the mean)
+//   dW  = dW' diag(g),  dg_k = sum_n dW'[n,k] W[n,k]
+#include "pn_t5_model.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// rs[row] = rsqrt(sum_p ss[p*rows + row] / d + eps)
+__global__ void __launch_bounds__(kThreads)
+rs_kernel(const float* __restrict__ ss, int parts, int64_t rows, int d, float eps, float* __restrict__ rs) {
+  for (int64_t r = (int64_t)blockIdx.x * kThreads + threadIdx.x; r < rows; r += (int64_t)gridDim.x * kThreads) {
+    float s = 0.0f;
+    for (int p = 0; p < parts; ++p) s += ss[(size_t)p * rows + r];
+    rs[r] = rsqrtf(s / (float)d + eps);
+  }
+}
+
+// y[r, c] = (act[r, c] > 0 ? y[r, c] : 0) * rs[r]   in place, bf16 [rows, cols]
+__global__ void __launch_bounds__(kThreads)
+relu_mask_scale_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ act,
+                       const float* __restrict__ rs, int64_t rows, int cols) {
+  const int64_t n8 = rows * cols / 8;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n8; i += (int64_t)gridDim.x * kThreads) {
+    const int64_t r = (i * 8) / cols;
+    const float s = rs ? rs[r] : 1.0f;
+    uint4 yv = reinterpret_cast<const uint4*>(y)[i];
+    const uint4 av = reinterpret_cast<const uint4*>(act)[i];
+    __nv_bfloat162* yh = reinterpret_cast<__nv_bfloat162*>(&yv);
+    const __nv_bfloat162* ah = reinterpret_cast<const __nv_bfloat162*>(&av);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float2 f = __bfloat1622float2(yh[e]);
+      const float2 a = __bfloat1622float2(ah[e]);
+      f.x = a.x > 0.0f ? f.x * s : 0.0f;
+      f.y = a.y > 0.0f ? f.y * s : 0.0f;
+      yh[e] = __floats2bfloat162_rn(f.x, f.y);
+    }
+    reinterpret_cast<uint4*>(y)[i] = yv;
+  }
+}
+
+// y[r, :] *= rs[r]   in place, bf16 [rows, cols] with row stride ld (a column block of a wider matrix)
+__global__ void __launch_bounds__(kThreads)
+row_scale_kernel(__nv_bfloat16* __restrict__ y, int ld, const float* __restrict__ rs, int64_t rows, int cols) {
+  const int c8 = cols / 8;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < rows * c8; i += (int64_t)gridDim.x * kThreads) {
+    const int64_t r = i / c8;
+    const int c = (int)(i % c8);
+    const float s = rs[r];
+    uint4* p = reinterpret_cast<uint4*>(y + (size_t)r * ld) + c;
+    uint4 v = *p;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float2 f = __bfloat1622float2(h[e]);
+      h[e] = __floats2bfloat162_rn(f.x * s, f.y * s);
+    }
+    *p = v;
+  }
+}
+
+// Fused-norm backward, one warp per row:  dh[r,:] (+)= G[r,:] - rs[r]^2 * hb[r,:] * mean_k(G[r,k] hb[r,k]);
+// also refreshes the bf16 copy of dh that the next GEMMs read.  accumulate = 0 overwrites dh.
+template <int MAXV>
+__global__ void __launch_bounds__(kThreads)
+norm_bwd_kernel(const float* __restrict__ G, const __nv_bfloat16* __restrict__ hb, const float* __restrict__ rs,
+                int64_t rows, int d, int accumulate, float* __restrict__ dh, __nv_bfloat16* __restrict__ dhb) {
+  const int lane = threadIdx.x & 31;
+  const int64_t wid = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
+  const int nv = d / 4;
+  for (int64_t r = wid; r < rows; r += nw) {
+    float4 g[MAXV], h[MAXV];
+    float dot = 0.0f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        g[i] = reinterpret_cast<const float4*>(G + (size_t)r * d)[c];
+        const uint2 raw = reinterpret_cast<const uint2*>(hb + (size_t)r * d)[c];
+        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+        h[i] = make_float4(a.x, a.y, b.x, b.y);
+        dot += g[i].x * h[i].x + g[i].y * h[i].y + g[i].z * h[i].z + g[i].w * h[i].w;
+      }
+    }
+    dot = pn_warp_sum(dot);
+    const float s = rs[r];
+    const float k = s * s * dot / (float)d;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        float4 o;
+        o.x = g[i].x - k * h[i].x; o.y = g[i].y - k * h[i].y; o.z = g[i].z - k * h[i].z; o.w = g[i].w - k * h[i].w;
+        float4* dst = reinterpret_cast<float4*>(dh + (size_t)r * d) + c;
+        if (accumulate) {
+          const float4 p = *dst;
+          o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+        }
+        *dst = o;
+        if (dhb) {
+          __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+          reinterpret_cast<uint2*>(dhb + (size_t)r * d)[c] =
+              make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+        }
+      }
+    }
+  }
+}
+
+// gradW[n,k] += dWp[n,k] * g[k];  gradg[k] += sum_n dWp[n,k] * W[n,k]   (W = fp32 master, dWp = d W')
+// grid.x tiles the columns (32 per CTA), each CTA walks a slab of rows; one atomic per column per CTA.
+__global__ void __launch_bounds__(kThreads)
+unfold_kernel(const float* __restrict__ dWp, const float* __restrict__ W, const float* __restrict__ g,
+              int64_t rows, int cols, float* __restrict__ gradW, float* __restrict__ gradg) {
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  const int64_t r0 = (int64_t)blockIdx.y * 256;
+  float acc = 0.0f;
+  if (c < cols) {
+    const float gc = g[c];
+    for (int64_t r = r0 + ty; r < rows && r < r0 + 256; r += 8) {
+      const float v = dWp[r * cols + c];
+      gradW[r * cols + c] += v * gc;
+      acc += v * W[r * cols + c];
+    }
+  }
+  red[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && c < cols) {
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][tx];
+    atomicAdd(gradg + c, t);
+  }
+}
+
+// grad_table[ids[r], :] += dh[r, :]  (tied input embeddings), one warp per row, vector atomics
+__global__ void __launch_bounds__(kThreads)
+embed_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ dh, int64_t rows, int d, int vocab,
+                 float* __restrict__ grad_table) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
+  for (int64_t r = w; r < rows; r += nw) {
+    int id = ids[r];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    const float4* src = reinterpret_cast<const float4*>(dh + (size_t)r * d);
+    float4* dst = reinterpret_cast<float4*>(grad_table + (size_t)id * d);
+    for (int i = lane; i < d / 4; i += 32) atomicAdd(dst + i, src[i]);
+  }
+}
+
+// Final decoder norm + head scale, y = x * rsqrt(mean(x^2)+eps) * w * d^-0.5 (HF:55-69,1107-1108):
+//   dx = k * (w (.) dy - x_hat * mean(x_hat (.) w (.) dy)),  dw += k' * sum_rows dy (.) x_hat,   k = rs * d^-0.5
+__global__ void __launch_bounds__(kThreads)
+final_norm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ w,
+                      int64_t rows, int d, float eps, float* __restrict__ dx, __nv_bfloat16* __restrict__ dxb,
+                      float* __restrict__ dw) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  if (r >= rows) return;
+  const float* xr = x + (size_t)r * d;
+  const float* gr = dy + (size_t)r * d;
+  float ss = 0.0f, dot = 0.0f;
+  for (int i = lane; i < d; i += 32) {
+    ss += xr[i] * xr[i];
+    dot += xr[i] * w[i] * gr[i];
+  }
+  ss = pn_warp_sum(ss);
+  dot = pn_warp_sum(dot);
+  const float rs = rsqrtf(ss / (float)d + eps);
+  const float sc = rsqrtf((float)d);
+  const float m = dot * rs * rs / (float)d;     // mean(x_hat w dy) * rs, folded for the x (not x_hat) product
+  for (int i = lane; i < d; i += 32) {
+    const float v = sc * rs * (w[i] * gr[i] - xr[i] * m);
+    dx[(size_t)r * d + i] = v;
+    if (dxb) dxb[(size_t)r * d + i] = __float2bfloat16_rn(v);
+    atomicAdd(dw + i, sc * gr[i] * xr[i] * rs);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+             int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2, float gscale) {
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
+    const float gi = g[i] * gscale;
+    const float mi = b1 * m[i] + (1.0f - b1) * gi;
+    const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    // transformers.AdamW (the class the reference constructs, lceT5.py:171-175): step_size = lr*sqrt(bc2)/bc1,
+    // p -= step_size * m / (sqrt(v) + eps); decoupled decay p -= lr * wd * p
+    float x = p[i];
+    x -= (lr * sqrtf(bc2) / bc1) * (mi / (sqrtf(vi) + eps));
+    if (wd != 0.0f) x -= lr * wd * x;
+    p[i] = x;
+  }
+}
+
+}  // namespace
+
+int pn_t5_rs(const float* ss, int parts, int64_t rows, int d, float eps, float* rs, cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  rs_kernel<<<pn_grid(rows, kThreads, 1, 8), kThreads, 0, st>>>(ss, parts, rows, d, eps, rs);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_relu_mask_scale(__nv_bfloat16* y, const __nv_bfloat16* act, const float* rs, int64_t rows, int cols,
+                          cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  if (cols % 8) return pn_fail(PN_E_UNSUPPORTED, "relu_mask_scale: cols %% 8 != 0");
+  relu_mask_scale_kernel<<<pn_grid(rows * cols / 8, kThreads, 2, 8), kThreads, 0, st>>>(y, act, rs, rows, cols);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_row_scale(__nv_bfloat16* y, int ld, const float* rs, int64_t rows, int cols, cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  if ((cols % 8) || (ld % 8)) return pn_fail(PN_E_UNSUPPORTED, "row_scale: cols/ld %% 8 != 0");
+  row_scale_kernel<<<pn_grid(rows * (cols / 8), kThreads, 2, 8), kThreads, 0, st>>>(y, ld, rs, rows, cols);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_norm_bwd(const float* G, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d, int accumulate,
+                   float* dh, __nv_bfloat16* dhb, cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  if (d % 4 || d > 32 * 4 * 16) return pn_fail(PN_E_UNSUPPORTED, "norm_bwd: d_model=%d unsupported", d);
+  const int grid = pn_grid(rows * 32, kThreads, 1, 8);
+  if (d <= 32 * 4 * 4)
+    norm_bwd_kernel<4><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb);
+  else if (d <= 32 * 4 * 8)
+    norm_bwd_kernel<8><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb);
+  else
+    norm_bwd_kernel<16><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_unfold(const float* dWp, const float* W, const float* g, int64_t rows, int cols, float* gradW,
+                 float* gradg, cudaStream_t st) {
+  if (rows * cols == 0) return PN_OK;
+  dim3 grid((cols + 31) / 32, (unsigned)((rows + 255) / 256));
+  unfold_kernel<<<grid, kThreads, 0, st>>>(dWp, W, g, rows, cols, gradW, gradg);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_embed_bwd(const int32_t* ids, const float* dh, int64_t rows, int d, int vocab, float* grad_table,
+                    cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  embed_bwd_kernel<<<pn_grid(rows * 32, kThreads, 1, 8), kThreads, 0, st>>>(ids, dh, rows, d, vocab, grad_table);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_final_norm_bwd(const float* dy, const float* x, const float* w, int64_t rows, int d, float eps,
+                         float* dx, __nv_bfloat16* dxb, float* dw, cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  final_norm_bwd_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(dy, x, w, rows, d,
+                                                                                               eps, dx, dxb, dw);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                float wd, int64_t step, float gscale, cudaStream_t st) {
+  if (n == 0) return PN_OK;
+  const float bc1 = 1.0f - powf(b1, (float)step), bc2 = 1.0f - powf(b2, (float)step);
+  adamw_kernel<<<pn_grid(n, kThreads, 4, 8), kThreads, 0, st>>>(p, g, m, v, n, lr, b1, b2, eps, wd, bc1, bc2, gscale);
+  PN_LAUNCHED();
+  return PN_OK;
+}

@@ -1,0 +1,222 @@
+"""The LCE training step on the B200 — host-side mirror of ``pacednegatives/lceT5.py``.
+
+``LCEModel`` keeps the reference's interface for the hot path (``pair_loss`` lceT5.py:116-123,
+``training_step`` lceT5.py:124-167, ``configure_optimizers`` lceT5.py:170-183) with the same hparams names;
+the model is ``MonoT5Model`` (libpn_b200.so: tcgen05 forward + backward, flat fp32 parameters, AdamW kernel)
+instead of ``transformers.T5ForConditionalGeneration`` + autograd + ``transformers.AdamW``.  Lightning, the
+tokenizer and ir_datasets (lceT5.py:13-75) are out of scope: a batch is the ``(p, n)`` pair of
+``{'input_ids', 'labels'}`` dicts that LCEDataModule.collate returns (lceT5.py:38-53).
+
+Data parallel (Lightning DDP in the reference): every rank runs the same step on its own queries; the flat
+gradient buffer and eta's gradient are all-reduced (mean) once per step over ``torch.distributed``.
+"""
+from collections import OrderedDict
+from types import SimpleNamespace
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .loss import pair_loss as _pair_loss
+from .scorer import MonoT5Scorer
+from .weights import LCEWeights
+
+
+def linear_schedule_with_warmup(step, warmup_steps, total_steps):
+    """lr multiplier of transformers.get_linear_schedule_with_warmup after `step` scheduler steps."""
+    if step < warmup_steps:
+        return float(step) / float(max(1, warmup_steps))
+    return max(0.0, float(total_steps - step) / float(max(1, total_steps - warmup_steps)))
+
+
+class _ModelFn(torch.autograd.Function):
+    """logits = model(input_ids=, labels=).logits with the backward pass wired to pn_t5_train_backward."""
+
+    @staticmethod
+    def forward(ctx, anchor, model, ids, labels):
+        N, S = ids.shape
+        T = labels.shape[1]
+        lib = _lib.lib()
+        need = int(lib.pn_t5_train_workspace_bytes(model._h, N, S, T))
+        ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+        logits = torch.empty(N * T, model.vocab_pad, dtype=torch.float32, device="cuda")
+        _lib.check(lib.pn_t5_train_forward(model._h, _lib.ptr(ids), _lib.ptr(labels), N, S, T, _lib.ptr(logits),
+                                           _lib.ptr(ws), need, _lib.stream()))
+        ctx.model, ctx.ws, ctx.ids, ctx.shape = model, ws, ids, (N, S, T)
+        return logits.view(N, T, model.vocab_pad)
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        N, S, T = ctx.shape
+        model = ctx.model
+        d = dlogits.contiguous().float()
+        _lib.check(_lib.lib().pn_t5_train_backward(model._h, _lib.ptr(ctx.ids), _lib.ptr(d), N, S, T,
+                                                   _lib.ptr(ctx.ws), ctx.ws.numel(), _lib.stream()))
+        ctx.ws = None
+        return torch.zeros_like(model._anchor), None, None, None
+
+
+class MonoT5Model(MonoT5Scorer):
+    """Trainable monoT5: ``model(input_ids, labels)`` returns logits [N, T, vocab] that backpropagate into the
+    flat gradient buffer ``grads`` (HF state_dict order, see ``named_offsets``)."""
+
+    def __init__(self, dims, state_dict, **kw):
+        super().__init__(dims, state_dict, train=True, **kw)
+        lib = _lib.lib()
+        n = int(lib.pn_t5_num_params(self._h))
+        self.grads = torch.zeros(n, dtype=torch.float32, device="cuda")
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device="cuda")
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device="cuda")
+        _lib.check(lib.pn_t5_set_train_buffers(self._h, _lib.ptr(self.grads), _lib.ptr(self.exp_avg),
+                                               _lib.ptr(self.exp_avg_sq)))
+        self._anchor = torch.zeros(1, device="cuda", requires_grad=True)
+        self.opt_steps = 0
+
+    def __call__(self, input_ids, labels, attention_mask=None):
+        if attention_mask is not None and not bool(torch.as_tensor(attention_mask).all()):
+            raise NotImplementedError("padded batches are not supported: every prompt must fill its S tokens")
+        ids = self._ids(input_ids)
+        lab = torch.as_tensor(labels).to(device="cuda", dtype=torch.int64).contiguous()
+        out = _ModelFn.apply(self._anchor, self, ids, lab)
+        return out[:, :, :self.dims.vocab]
+
+    def named_offsets(self):
+        """[(hf_name, offset, numel)] of the flat parameter / gradient buffers."""
+        import ctypes as C
+        lib = _lib.lib()
+        out = []
+        name = C.create_string_buffer(256)
+        off, numel = C.c_int64(), C.c_int64()
+        for i in range(int(lib.pn_t5_num_tensors(self._h))):
+            _lib.check(lib.pn_t5_tensor_info(self._h, i, name, 256, C.byref(off), C.byref(numel)))
+            out.append((name.value.decode(), off.value, numel.value))
+        return out
+
+    def named_grads(self):
+        return {n: self.grads[o:o + k] for n, o, k in self.named_offsets()}
+
+    def zero_grad(self):
+        _lib.check(_lib.lib().pn_t5_zero_grad(self._h, _lib.stream()))
+
+    def all_reduce_grads(self, group=None):
+        """DDP's gradient mean: one all-reduce over the flat buffer; returns the scale still to apply."""
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=group)
+            return 1.0 / dist.get_world_size(group)
+        return 1.0
+
+    def step(self, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, gscale=1.0):
+        """transformers.AdamW defaults (the optimiser of lceT5.py:172)."""
+        self.opt_steps += 1
+        _lib.check(_lib.lib().pn_t5_adamw_step(self._h, float(lr), betas[0], betas[1], eps, weight_decay,
+                                               self.opt_steps, float(gscale), _lib.stream()))
+
+
+class _AdamWTensor:
+    """transformers.AdamW on one small device tensor (the eta parameter, lceT5.py:171)."""
+
+    def __init__(self, param, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0):
+        self.param, self.lr, self.betas, self.eps, self.wd = param, float(lr), betas, eps, weight_decay
+        self.m = torch.zeros_like(param.data)
+        self.v = torch.zeros_like(param.data)
+        self.steps = 0
+
+    def zero_grad(self):
+        self.param.grad = None
+
+    def step(self, lr=None):
+        if self.param.grad is None:
+            return
+        self.steps += 1
+        g = self.param.grad.contiguous().float()
+        _lib.check(_lib.lib().pn_adamw(_lib.ptr(self.param.data), _lib.ptr(g), _lib.ptr(self.m), _lib.ptr(self.v),
+                                       self.param.numel(), self.lr if lr is None else float(lr), self.betas[0],
+                                       self.betas[1], self.eps, self.wd, self.steps, 1.0, _lib.stream()))
+
+
+class LCEModel:
+    """hparams: dict or namespace with the reference's keys — n, use_mean, ignore_index, lr, meta_lr,
+    warmup_steps, total_steps, eta — plus `dims` / `state_dict` in place of `model_name` (no hub access).
+    `elide_no_grad_forward` (default True) reuses the gradient-tracking forward's logits for the meta step: with
+    dropout 0 the reference's no-grad forward (lceT5.py:131-133) computes exactly the same numbers."""
+
+    def __init__(self, hparams, dims=None, state_dict=None, model=None, elide_no_grad_forward=True, **model_kw):
+        if isinstance(hparams, dict):
+            hparams = SimpleNamespace(**hparams)
+        self.hparams = hparams
+        self.model = model if model is not None else MonoT5Model(dims, state_dict, **model_kw)
+        self.weights = LCEWeights(hparams)
+        self.elide = bool(elide_no_grad_forward)
+        self.difficulty = self.weights.eta.item()
+        self.global_step = 0
+        self.logged = {}
+        self._opts = None
+
+    def log(self, name, value):
+        self.logged[name] = value
+
+    def pair_loss(self, p, n, op, on):
+        return _pair_loss(p, n, op, on, use_mean=bool(self.hparams.use_mean),
+                          ignore_index=int(getattr(self.hparams, "ignore_index", -100)))
+
+    def configure_optimizers(self):
+        meta_opt = _AdamWTensor(self.weights.eta, lr=self.hparams.meta_lr)
+        return [meta_opt, self.model], [None, None]
+
+    def _lr_scale(self):
+        return linear_schedule_with_warmup(self.global_step, int(self.hparams.warmup_steps),
+                                           int(self.hparams.total_steps))
+
+    def training_step(self, batch, batch_nb=0):
+        p, n = batch
+        if self._opts is None:
+            self._opts = self.configure_optimizers()[0]
+        meta_opt, opt = self._opts
+        k, V = int(self.hparams.n), self.model.dims.vocab
+        scale = self._lr_scale()
+
+        if self.elide:
+            plogits = self.model(p["input_ids"], p["labels"])
+            nlogits = self.model(n["input_ids"], n["labels"]).view(-1, k, V)
+            p0, n0 = plogits.detach(), nlogits.detach()
+        else:
+            with torch.no_grad():
+                p0, _ = self.model.logits(p["input_ids"], p["labels"])
+                n0, _ = self.model.logits(n["input_ids"], n["labels"])
+                n0 = n0.reshape(-1, k, V)
+        op = torch.as_tensor(p["labels"]).cuda()
+        on = torch.as_tensor(n["labels"]).cuda()
+        with torch.no_grad():
+            loss = self.pair_loss(p0.contiguous(), n0.contiguous(), op, on)
+
+        weights = self.weights(loss)
+        meta_loss = weights * loss
+        meta_opt.zero_grad()
+        meta_loss.mean().backward()
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1 and \
+                self.weights.eta.grad is not None:
+            dist.all_reduce(self.weights.eta.grad, op=dist.ReduceOp.SUM)
+            self.weights.eta.grad /= dist.get_world_size()
+        meta_opt.step(lr=self.hparams.meta_lr * scale)
+
+        self.log("avg_weight", weights.mean())
+        self.log("meta_loss", meta_loss.mean())
+        self.log("eta", self.weights.eta.item())
+
+        if not self.elide:
+            plogits = self.model(p["input_ids"], p["labels"])
+            nlogits = self.model(n["input_ids"], n["labels"]).view(-1, k, V)
+        main_loss = self.pair_loss(plogits.contiguous(), nlogits.contiguous(), op, on)
+
+        opt.zero_grad()
+        main_loss.mean().backward()
+        gscale = opt.all_reduce_grads()
+        opt.step(lr=self.hparams.lr * scale, gscale=gscale)
+        self.global_step += 1
+
+        tqdm_dict = {"meta_loss": loss.mean(), "avg_weight": weights.mean(), "main_loss": loss.mean()}
+        output = OrderedDict({"main_loss": main_loss.mean(), "meta_loss": meta_loss.mean(),
+                              "progress_bar": tqdm_dict, "log": tqdm_dict})
+        self.log("main_loss", loss.mean())
+        self.difficulty = self.weights.eta.item()
+        return output

@@ -304,6 +304,105 @@ def gold_t5(rt, out):
         pair_loss=ce.numpy(), rel_ids=np.array([rel_id, nrel_id]), k=np.array(k))
 
 
+class LegacyAdamW(torch.optim.Optimizer):
+    """Restatement of transformers.AdamW.step (transformers <= 4.x optimization.py, the class lceT5.py:5,171-172
+    constructs; removed from the transformers 5.x in this image): defaults betas (0.9, 0.999), eps 1e-6,
+    weight_decay 0, correct_bias True."""
+
+    def __init__(self, params, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0):
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+
+    @torch.no_grad()
+    def step(self):
+        for g in self.param_groups:
+            for p in g["params"]:
+                if p.grad is None:
+                    continue
+                st = self.state[p]
+                if not st:
+                    st["step"] = 0
+                    st["exp_avg"] = torch.zeros_like(p)
+                    st["exp_avg_sq"] = torch.zeros_like(p)
+                b1, b2 = g["betas"]
+                st["step"] += 1
+                st["exp_avg"].mul_(b1).add_(p.grad, alpha=1.0 - b1)
+                st["exp_avg_sq"].mul_(b2).addcmul_(p.grad, p.grad, value=1.0 - b2)
+                denom = st["exp_avg_sq"].sqrt().add_(g["eps"])
+                step_size = g["lr"] * (1.0 - b2 ** st["step"]) ** 0.5 / (1.0 - b1 ** st["step"])
+                p.addcdiv_(st["exp_avg"], denom, value=-step_size)
+                if g["weight_decay"] > 0.0:
+                    p.add_(p, alpha=-g["lr"] * g["weight_decay"])
+
+
+def gold_train(rt, out):
+    """The reference's own LCEModel.training_step (lceT5.py:124-167) executed unmodified on a tiny random-init
+    HF T5 (fp32, CPU) for two steps: losses, eta, every parameter's gradient (norm + leading slice) of step 1."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    from transformers import T5Config, T5ForConditionalGeneration, get_linear_schedule_with_warmup
+    dims = ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
+    w = ot.init_weights(dims, seed=23)
+    cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
+                   num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
+                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   pad_token_id=0, eos_token_id=1, feed_forward_proj="relu", tie_word_embeddings=True)
+    m = T5ForConditionalGeneration(cfg).train()
+    sd = {k_: torch.tensor(v) for k_, v in w.items()}
+    sd["encoder.embed_tokens.weight"] = sd["decoder.embed_tokens.weight"] = sd["shared.weight"]
+    sd["lm_head.weight"] = sd["shared.weight"]
+    missing = m.load_state_dict(sd, strict=False)
+    assert not missing.missing_keys and not missing.unexpected_keys, missing
+    hp = types.SimpleNamespace(n=3, use_mean=True, ignore_index=-100, lr=1e-3, meta_lr=1e-2, warmup_steps=0,
+                               total_steps=10, eta=20.0)
+    rng = np.random.RandomState(4321)
+    Q, k, S = 2, hp.n, 128
+    rel_id, nrel_id = 117, 213
+    pids = rng.randint(2, dims.vocab, size=(Q, S)).astype(np.int64)
+    nids = rng.randint(2, dims.vocab, size=(Q * k, S)).astype(np.int64)
+    pids[:, -1] = 1
+    nids[:, -1] = 1
+    plab = np.tile([[rel_id, 1]], (Q, 1)).astype(np.int64)
+    nlab = np.tile([[nrel_id, 1]], (Q * k, 1)).astype(np.int64)
+    batch = ({"input_ids": torch.tensor(pids), "labels": torch.tensor(plab)},
+             {"input_ids": torch.tensor(nids), "labels": torch.tensor(nlab)})
+
+    self = types.SimpleNamespace()
+    self.hparams = hp
+    self.model = m
+    self.weights = rt.LCEWeights(hp)
+    self.loss_fn = torch.nn.CrossEntropyLoss(ignore_index=hp.ignore_index, reduction="none")
+    self.pair_loss = lambda p, n, op, on: rt.LCEModel.pair_loss(self, p, n, op, on)
+    meta_opt = LegacyAdamW(self.weights.parameters(), lr=hp.meta_lr)
+    opt = LegacyAdamW(m.parameters(), lr=hp.lr)
+    scheds = [get_linear_schedule_with_warmup(o, num_warmup_steps=hp.warmup_steps,
+                                              num_training_steps=hp.total_steps) for o in (meta_opt, opt)]
+    self.optimizers = lambda: (meta_opt, opt)
+    self.lr_schedulers = lambda: scheds
+    self.manual_backward = lambda loss: loss.backward()
+    logged = {}
+    self.log = lambda name, v: logged.__setitem__(name, float(v))
+    names = [n_ for n_, _ in m.named_parameters()]
+    res = {}
+    for step in range(2):
+        before = {n_: p.detach().clone() for n_, p in m.named_parameters()}
+        o = rt.LCEModel.training_step(self, batch, step)
+        res[f"main_loss{step}"] = float(o["main_loss"])
+        res[f"meta_loss{step}"] = float(o["meta_loss"])
+        res[f"eta{step}"] = float(self.weights.eta.item())
+        res[f"avg_weight{step}"] = logged["avg_weight"]
+        if step == 0:
+            for n_, p in m.named_parameters():
+                g = p.grad.detach().reshape(-1)
+                res["gnorm/" + n_] = float(g.norm())
+                res["ghead/" + n_] = g[:64].numpy().copy()
+                res["dnorm/" + n_] = float((p.detach() - before[n_]).norm())
+    np.savez_compressed(
+        out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
+                            dims.n_heads]), seed=np.array(23), pids=pids, nids=nids, plab=plab, nlab=nlab,
+        hp=np.array([hp.n, int(hp.use_mean), hp.lr, hp.meta_lr, hp.warmup_steps, hp.total_steps, hp.eta]),
+        names=np.array(names), **{k_: np.asarray(v) for k_, v in res.items()})
+
+
 def main():
     rw, rd, rl, rt, rp = import_reference()
     gold_weights(rw, rt, os.path.join(HERE, "weights_golden.npz"))
@@ -311,6 +410,7 @@ def main():
     gold_select(rd, os.path.join(HERE, "select_golden.npz"))
     gold_table_update(rp, rw, os.path.join(HERE, "table_update_golden.npz"))
     gold_t5(rt, os.path.join(HERE, "t5_tiny_golden.npz"))
+    gold_train(rt, os.path.join(HERE, "train_golden.npz"))
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -1,0 +1,64 @@
+"""GPU parity: backward of the encoder self-attention (flash-style tcgen05 kernel) vs torch autograd of
+softmax(QK^T + bias) V in fp32 on the same bf16 inputs.  The kernel recomputes P from the forward's base-2
+logsumexp and rounds P / dS to bf16 before the accumulating MMAs, hence the bf16-level tolerances."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def run_case(docs, S, H, with_scale, seed):
+    from pacednegatives_b200 import _lib
+    lib = _lib.lib()
+    torch.manual_seed(seed)
+    di = H * 64
+    rows = docs * S
+    qkv = (torch.randn(rows, 3 * di, device="cuda") * 0.5).bfloat16()
+    bias = torch.randn(H, 1023, device="cuda")
+    dctx = (torch.randn(rows, di, device="cuda") * 0.5).bfloat16()
+    rs = (torch.rand(rows, device="cuda") + 0.5) if with_scale else None
+    ctx = torch.zeros(rows, di, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(rows, H, device="cuda")
+    _lib.check(lib.pn_t5_self_attention_lse(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(ctx),
+                                            _lib.ptr(lse), _lib.stream()))
+    dqkv = torch.full((rows, 3 * di), float("nan"), device="cuda").bfloat16()
+    diag = torch.zeros(H, 1023, device="cuda")
+    dvec = torch.zeros(rows, H, device="cuda")
+    _lib.check(lib.pn_t5_self_attention_bwd(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(ctx),
+                                            _lib.ptr(dctx), _lib.ptr(lse), _lib.ptr(rs) if with_scale else None,
+                                            _lib.ptr(dqkv), _lib.ptr(diag), _lib.ptr(dvec), _lib.stream()))
+    torch.cuda.synchronize()
+
+    x = qkv.float().requires_grad_(True)
+    bp = bias.clone().requires_grad_(True)
+    q, k, v = [t.view(docs, S, H, 64).transpose(1, 2) for t in x.split(di, dim=1)]
+    pos = torch.arange(S, device="cuda")
+    b = bp[:, (pos[None, :] - pos[:, None]) + 511]
+    s = q @ k.transpose(2, 3) + b[None]
+    p = torch.softmax(s, dim=-1)
+    ref_ctx = (p @ v).transpose(1, 2).reshape(rows, di)
+    ref_lse2 = torch.logsumexp(s, dim=-1).transpose(1, 2).reshape(rows, H) * 1.4426950408889634
+    ref_ctx.backward(dctx.float())
+    gx = x.grad
+    if with_scale:
+        gx = gx * rs[:, None]
+    assert (lse - ref_lse2).abs().max().item() < 2e-2
+    got = dqkv.float()
+    assert torch.isfinite(got).all(), "unwritten or non-finite gradient rows"
+    scale = gx.abs().max().item()
+    for name, sl in (("dq", slice(0, di)), ("dk", slice(di, 2 * di)), ("dv", slice(2 * di, 3 * di))):
+        err = (got[:, sl] - gx[:, sl]).abs().max().item()
+        assert err < 2e-2 * max(1.0, scale), f"{name}: docs={docs} S={S} H={H}: err {err} (scale {scale})"
+    gb = bp.grad
+    err = (diag - gb).abs().max().item()
+    assert err < 2e-2 * max(1.0, gb.abs().max().item()), f"dbias: docs={docs} S={S} H={H}: err {err}"
+
+
+@pytest.mark.parametrize("docs,S,H,with_scale", [
+    (1, 128, 1, False), (2, 128, 2, False), (1, 256, 1, False), (3, 512, 2, True), (2, 384, 4, False),
+    (1, 200, 2, True), (2, 77, 2, False), (5, 512, 12, True),
+])
+def test_self_attention_backward_vs_autograd(docs, S, H, with_scale):
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    run_case(docs, S, H, with_scale, seed=docs * 1000 + S + H)
