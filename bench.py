@@ -450,6 +450,167 @@ def bench_rerank_reference(args):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------
+# workload: the LCE training step (BASELINE.json configs[2])
+def hf_train_sample(n_docs, S, steps, warmup, threads=None):
+    """The reference's CPU path for one training step's model work on a bounded sample: HF
+    T5ForConditionalGeneration fp32 forward + backward + AdamW over n_docs prompts with 2 label tokens and the
+    reference's loss (lceT5.py:149-156).  Returns (docs/s, description, seconds)."""
+    if threads:
+        torch.set_num_threads(threads)
+    from transformers import T5Config, T5ForConditionalGeneration
+    cfg = T5Config(vocab_size=32128, d_model=768, d_kv=64, d_ff=3072, num_layers=12, num_decoder_layers=12,
+                   num_heads=12, dropout_rate=0.0, decoder_start_token_id=0, pad_token_id=0, eos_token_id=1)
+    torch.manual_seed(0)
+    model = T5ForConditionalGeneration(cfg).train()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3, eps=1e-6, weight_decay=0.0)
+    ids = torch.from_numpy(synth_ids(n_docs, S, 4567).astype(np.int64))
+    labels = torch.tensor([[1176, 1]] + [[6136, 1]] * (n_docs - 1))
+    loss_fn = torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none")
+
+    def run():
+        logits = model(input_ids=ids, labels=labels).logits
+        ce = loss_fn(logits.view(-1, logits.size(-1)), labels.view(-1))
+        opt.zero_grad()
+        ce.mean().backward()
+        opt.step()
+        return float(ce.mean())
+    for _ in range(warmup):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run()
+    dt = time.perf_counter() - t0
+    return n_docs * steps / dt, "transformers T5ForConditionalGeneration fp32 eager CPU fwd+bwd+AdamW", dt
+
+
+def bench_train(args):
+    from pacednegatives_b200 import _lib
+    from pacednegatives_b200.lceT5 import LCEModel
+    from pacednegatives_b200.scorer import T5_BASE, random_state_dict, flops_per_doc
+    _lib.require_gpu()
+    torch.cuda.set_device(LOCAL_RANK)
+    dist = dist_setup(True)
+    lib = _lib.lib()
+    S, T, k = 512, 2, 15
+    Q = args.train_queries
+    dims = T5_BASE
+    hp = dict(n=k, use_mean=True, ignore_index=-100, lr=1e-3, meta_lr=1e-3, warmup_steps=0,
+              total_steps=1000000, eta=0.3466)
+    m = LCEModel(hp, dims=dims, state_dict=random_state_dict(dims, seed=0), cta_group=args.cta_group)
+    total = args.steps + args.warmup
+    nbuf = min(total, 4)
+    plab = torch.tensor([[1176, 1]] * Q, dtype=torch.int64)
+    nlab = torch.tensor([[6136, 1]] * (Q * k), dtype=torch.int64)
+    host = []
+    for i in range(nbuf):
+        ids = torch.from_numpy(synth_ids(Q * (1 + k), S, 4567 + 1000 * RANK + i))
+        host.append(({"input_ids": ids[:Q].contiguous().pin_memory(), "labels": plab.pin_memory()},
+                     {"input_ids": ids[Q:].contiguous().pin_memory(), "labels": nlab.pin_memory()}))
+    dev = [tuple({kk: v.cuda() for kk, v in part.items()} for part in b) for b in host]
+    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+
+    def step_dev(i):
+        m.training_step(dev[i % nbuf], i)
+
+    def step_e2e(i):
+        b = tuple({kk: v.cuda(non_blocking=True) for kk, v in part.items()} for part in host[i % nbuf])
+        out = m.training_step(b, i)
+        loss_host[0].copy_(out["main_loss"].detach(), non_blocking=True)
+        loss_host[1].copy_(out["meta_loss"].detach(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # the caller logs the step's losses
+
+    for i in range(args.warmup):
+        step_dev(i)
+    clocks = ClockSampler(LOCAL_RANK)
+    clocks.start()
+    lib.pn_prof_enable(1)
+    l0 = _lib.launch_count()
+    ms = timed_region(dist, step_dev, args.steps)
+    launches = _lib.launch_count() - l0
+    lib.pn_prof_enable(0)
+    clk = clocks.stop()
+    prof = {name: prof_read(kind) for name, kind in (("gemm", 0), ("attn", 1), ("wgrad", 3), ("attn_bwd", 4))}
+    for i in range(2):
+        step_e2e(i)
+    e2e_ms = timed_region(dist, step_e2e, args.steps)
+
+    queries = Q * args.steps * WORLD
+    value = queries / (ms / 1e3)
+    e2e_value = queries / (e2e_ms / 1e3)
+    peaks = measured_peaks()
+    # forward + backward (2x forward) with the redundant no-grad forward elided: 3x the forward count
+    step_flops = Q * (1 + k) * flops_per_doc(dims, S, T, True) * 3.0
+    g_ms, g_n, g_flops = prof["gemm"]
+    gemm_tflops = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
+
+    def tf(name):
+        t_ms, n, work = prof[name]
+        return {"tflops": work / (t_ms / 1e3) / 1e12 if t_ms else 0.0, "launches": int(n),
+                "share_of_step": t_ms / ms if ms else None}
+    line = {
+        "metric": "LCE training queries/s (1+15 docs per query)", "value": value, "unit": "queries/s",
+        "n_gpus": WORLD, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic (random-init t5-base dims, ids U{2..32099}, labels true/false + </s>)",
+        "config": {"workload": "LCE training step, monoT5-base, 1+15 docs per query, seq 512 (BASELINE configs[2])",
+                   "queries_per_step_per_gpu": Q, "negatives": k, "seq_len": S, "label_tokens": T,
+                   "no_grad_forward": "elided (identical arithmetic at dropout 0); FLOP count uses 3x forward",
+                   "optimizer": "AdamW (transformers rule) on flat fp32 masters + eta meta step",
+                   "l2": "activations per step (tens of GB) exceed the 126 MB L2; no flush needed",
+                   "parallelism": f"dp{WORLD}: one all-reduce of the flat fp32 gradient buffer per step"},
+        "gpu_launches": int(launches),
+        "model_tflops": step_flops / (ms / args.steps / 1e3) / 1e12,
+        "model_frac_of_sustained_peak": step_flops / (ms / args.steps / 1e3) / 1e12 / peaks["bf16_sustained"],
+        "e2e": {"value": e2e_value, "unit": "queries/s",
+                "h2d_bytes_per_step": int(Q * (1 + k) * S * 4 + Q * (1 + k) * T * 8),
+                "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / args.steps},
+        "roofline": {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05: forward linears + data gradients)",
+                     "achieved": gemm_tflops, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                     "frac": gemm_tflops / peaks["bf16_sustained"], "peak_source": peaks["src"] + " sustained",
+                     "launches": int(g_n), "avg_launch_ms": g_ms / max(g_n, 1),
+                     "share_of_step": g_ms / ms if ms else None,
+                     "wgrad": tf("wgrad"), "attention": tf("attn"), "attention_bwd": tf("attn_bwd"),
+                     "traffic": None},
+        "clocks": clk,
+    }
+    if RANK == 0:
+        if WORLD == 1 and not args.no_cpu_baseline:
+            try:
+                v, how, dt = hf_train_sample(4, S, 1, 1)
+                line["cpu_baseline"] = {"value": v / (1 + k), "unit": "queries/s", "cores": torch.get_num_threads(),
+                                        "host_cpus": os.cpu_count(), "kind": "port",
+                                        "sample": f"4 docs x seq {S} x 1 step ({dt:.1f} s), {how}; docs/s / {1 + k}"}
+            except Exception as e:   # transformers missing: say so rather than invent a number
+                line["cpu_baseline"] = {"value": None, "unit": "queries/s", "kind": "port", "sample": f"failed: {e}"}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def bench_train_reference(args):
+    """`--impl reference --workload train`: HF fp32 forward+backward+AdamW on the host cores, rank 0 only."""
+    if RANK != 0:
+        return
+    S, k = 512, 15
+    n = args.ref_train_docs
+    torch.set_num_threads(os.cpu_count() or 1)
+    v, how, dt = hf_train_sample(n, S, args.steps, args.warmup)
+    qs = v / (1 + k)
+    line = {"impl": "reference", "metric": "LCE training queries/s (1+15 docs per query)", "value": qs,
+            "unit": "queries/s", "n_gpus": WORLD, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "LCE training step, monoT5-base, 1+15 docs per query, seq 512 (BASELINE configs[2])",
+                       "sample_docs_per_step": n, "seq_len": S},
+            "gpu_launches": 0,
+            "cpu_baseline": {"value": qs, "unit": "queries/s", "cores": torch.get_num_threads(),
+                             "host_cpus": os.cpu_count(), "kind": "port",
+                             "sample": f"{n} docs x seq {S} per step, {how}; docs/s / {1 + k}"},
+            "e2e": {"value": qs, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -465,6 +626,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--select-queries", type=int, default=1000000)
     ap.add_argument("--select-elems", type=int, default=1 << 28)
+    ap.add_argument("--train-queries", type=int, default=16)
+    ap.add_argument("--ref-train-docs", type=int, default=4)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3   # timing rule: at least 3 warm-up steps
@@ -476,11 +639,15 @@ def main():
     if args.impl == "reference":
         if args.workload == "rerank":
             return bench_rerank_reference(args)
+        if args.workload == "train":
+            return bench_train_reference(args)
         raise SystemExit("reference arm: workload not implemented")
     if args.workload == "rerank":
         return bench_rerank(args)
     if args.workload == "select":
         return bench_select(args)
+    if args.workload == "train":
+        return bench_train(args)
     raise SystemExit(f"workload {args.workload} not implemented yet")
 
 

@@ -1,0 +1,83 @@
+"""GPU parity of the training step: LCEModel.training_step on the B200 kernels vs the golden
+vectors written by the REFERENCE's own training_step (tests/golden/make_golden.py::gold_train: unmodified
+lceT5.LCEModel.training_step driving HF T5ForConditionalGeneration in fp32 with transformers.AdamW's update rule).
+Tolerances: north_star's 2e-2 absolute on losses (bf16 tensor-core arithmetic against fp32), each gradient tensor's
+norm within 3 % and its leading entries within 10 % of their scale (bf16 operands in every GEMM of the backward)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import t5 as ot
+
+pytestmark = pytest.mark.gpu
+
+
+def load_case(golden_dir):
+    g = np.load(os.path.join(golden_dir, "train_golden.npz"))
+    v, d, kv, ff, L, Ld, H = [int(x) for x in g["dims"]]
+    dims = ot.T5Dims(vocab=v, d_model=d, d_kv=kv, d_ff=ff, n_layers=L, n_dec_layers=Ld, n_heads=H)
+    n, use_mean, lr, meta_lr, warm, total, eta = [float(x) for x in g["hp"]]
+    hp = dict(n=int(n), use_mean=bool(use_mean), ignore_index=-100, lr=lr, meta_lr=meta_lr, warmup_steps=int(warm),
+              total_steps=int(total), eta=eta)
+    batch = ({"input_ids": torch.tensor(g["pids"]), "labels": torch.tensor(g["plab"])},
+             {"input_ids": torch.tensor(g["nids"]), "labels": torch.tensor(g["nlab"])})
+    return g, dims, hp, batch
+
+
+@pytest.mark.parametrize("elide", [True, False])
+def test_training_step_vs_reference_golden(golden_dir, elide):
+    from pacednegatives_b200.lceT5 import LCEModel
+    from pacednegatives_b200.scorer import T5Dims
+    g, dims, hp, batch = load_case(golden_dir)
+    w = ot.init_weights(dims, seed=int(g["seed"]))
+    m = LCEModel(hp, dims=T5Dims(**dims.__dict__), state_dict={k: torch.as_tensor(v) for k, v in w.items()},
+                 elide_no_grad_forward=elide)
+    out = m.training_step(batch, 0)
+    assert abs(float(out["main_loss"].detach()) - float(g["main_loss0"])) < 2e-2
+    assert abs(float(out["meta_loss"]) - float(g["meta_loss0"])) < 2e-2
+    assert abs(m.weights.eta.item() - float(g["eta0"])) < 1e-4
+    assert abs(float(m.logged["avg_weight"]) - float(g["avg_weight0"])) < 2e-3
+    grads = m.model.named_grads()
+    names = [str(n) for n in g["names"]]
+    assert sorted(names) == sorted(grads.keys())
+    worst = 0.0
+    for n in names:
+        ref_norm = float(g["gnorm/" + n])
+        got = grads[n]
+        head = torch.tensor(g["ghead/" + n]).cuda()
+        rel_norm = abs(got.norm().item() - ref_norm) / max(ref_norm, 1e-6)
+        err = (got[:head.numel()] - head).abs().max().item()
+        scale = max(head.abs().max().item(), ref_norm / got.numel() ** 0.5)
+        worst = max(worst, rel_norm)
+        assert rel_norm < 3e-2, f"{n}: |grad| {got.norm().item()} vs {ref_norm}"
+        assert err < 1e-1 * scale + 1e-5, f"{n}: leading gradient entries off by {err} (scale {scale})"
+    out1 = m.training_step(batch, 1)
+    # the second step runs on the AdamW-updated weights and eta
+    assert abs(float(out1["main_loss"]) - float(g["main_loss1"])) < 5e-2
+    assert abs(float(out1["meta_loss"]) - float(g["meta_loss1"])) < 5e-2
+    assert abs(m.weights.eta.item() - float(g["eta1"])) < 2e-4
+
+
+def test_adamw_kernel_vs_transformers_rule():
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    lib = _lib.lib()
+    torch.manual_seed(3)
+    n = 100003
+    p = torch.randn(n, device="cuda")
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    rp, rm, rv = p.double().clone(), m.double().clone(), v.double().clone()
+    lr, b1, b2, eps, wd = 1e-3, 0.9, 0.999, 1e-6, 0.01
+    for step in range(1, 4):
+        gr = torch.randn(n, device="cuda") * 0.1
+        _lib.check(lib.pn_adamw(_lib.ptr(p), _lib.ptr(gr), _lib.ptr(m), _lib.ptr(v), n, lr, b1, b2, eps, wd, step,
+                                0.5, _lib.stream()))
+        gd = gr.double() * 0.5
+        rm = b1 * rm + (1 - b1) * gd
+        rv = b2 * rv + (1 - b2) * gd * gd
+        rp = rp - lr * (1 - b2 ** step) ** 0.5 / (1 - b1 ** step) * rm / (rv.sqrt() + eps)
+        rp = rp - lr * wd * rp
+    assert (p.double() - rp).abs().max().item() < 1e-5
