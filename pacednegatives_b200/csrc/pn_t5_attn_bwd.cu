@@ -14,6 +14,7 @@
 // Warp roles: 0..7 compute, 8 = TMA producer, 9 = TMEM allocator + MMA issuer, 10..13 (MODE 0) = bias-gradient
 // diagonal sums read back from the dS tile.
 #include "pn_common.cuh"
+#include <stdlib.h>
 #include "pn_tc.cuh"
 #include "pn_t5_internal.cuh"
 
@@ -334,10 +335,12 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     }
   } else {
     // ===================== diagonal warps (MODE 0): dbias[j - i] += dS_ij =====================
-    // The dS tile [128 q x 128 k] is cut into 8x8 blocks (a, b); block-diagonal delta = b - a holds the 15
-    // diagonals 8*delta-7 .. 8*delta+7.  Thread (c, sub) takes the blocks a = sub and sub + 8 of the wrapped
-    // block-diagonal b = (a + c) mod 16: one conflict-free 16-byte load per block row, statically indexed
-    // accumulators, then one shared-memory atomic per diagonal.
+    // The dS tile [128 q x 128 k] is cut into 8-row x 8-diagonal parallelograms: thread (c, sub) owns the wrapped
+    // diagonals (k - q) mod 128 in [8c, 8c + 8) of the row blocks a = sub and sub + 8.  Row 8a + rr reads them
+    // from the two 16-byte chunks (a + c) mod 16 (elements rr..7) and (a + c + 1) mod 16 (elements 0..rr-1),
+    // conflict-free, with compile-time register indices; a chunk that wrapped past column 127 belongs to the
+    // diagonal 128 below.  The eight threads of a class then reduce-scatter by shuffles, so every diagonal of
+    // the tile has exactly one owner: no atomics.
     if (MODE == 0) reg_dealloc<72>();
     if (MODE == 0 && warp < 14) {
       const int u = threadIdx.x - 320;
@@ -348,35 +351,71 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const int ob = item_ob(it);
         for (int t = 0; t < nb; ++t, ++g) {
           mbar_wait(bar(B_PD_READY), g & 1);
-          const int dbase = (ob - t) * BLK + (MAX_S - 1);      // (key block - query block) * 128 + 511
+          float accn[8], accw[8];        // diagonals 8c + i, and 8c + i - 128 (wrapped chunks)
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            const int ab = sub + 8 * i;
-            const int b = (ab + c) & 15;
-            const int delta = (ab + c) >= 16 ? c - 16 : c;
-            float acc[15];
+          for (int i = 0; i < 8; ++i) accn[i] = accw[i] = 0.0f;
 #pragma unroll
-            for (int j = 0; j < 15; ++j) acc[j] = 0.0f;
-            const uint8_t* blk = ds + (b >> 3) * TILE_BYTES + ab * 8 * 128;
+          for (int blk = 0; blk < 2; ++blk) {
+            const int ab = sub + 8 * blk;
+            const int b0 = (ab + c) & 15, b1 = (ab + c + 1) & 15;
+            const bool wrap0 = ab + c >= 16, wrap1 = ab + c + 1 >= 16;
+            float lo[8], hi[8];          // sums from the first / second chunk
+#pragma unroll
+            for (int i = 0; i < 8; ++i) lo[i] = hi[i] = 0.0f;
+            const uint8_t* rowp = ds + ab * 8 * 128;
 #pragma unroll
             for (int rr = 0; rr < 8; ++rr) {
-              const uint4 v = *reinterpret_cast<const uint4*>(blk + rr * 128 + (((b & 7) ^ rr) << 4));
-              const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+              const uint4 v0 = *reinterpret_cast<const uint4*>(rowp + (b0 >> 3) * TILE_BYTES + rr * 128 +
+                                                               (((b0 & 7) ^ rr) << 4));
+              const uint32_t w0[4] = {v0.x, v0.y, v0.z, v0.w};
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                acc[2 * e - rr + 7] += __uint_as_float(w[e] << 16);
-                acc[2 * e + 1 - rr + 7] += __uint_as_float(w[e] & 0xffff0000u);
+              for (int e = rr; e < 8; ++e)
+                lo[e - rr] += __uint_as_float((e & 1) ? (w0[e >> 1] & 0xffff0000u) : (w0[e >> 1] << 16));
+              if (rr > 0) {
+                const uint4 v1 = *reinterpret_cast<const uint4*>(rowp + (b1 >> 3) * TILE_BYTES + rr * 128 +
+                                                                 (((b1 & 7) ^ rr) << 4));
+                const uint32_t w1[4] = {v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+                for (int e = 0; e < rr; ++e)
+                  hi[e + 8 - rr] += __uint_as_float((e & 1) ? (w1[e >> 1] & 0xffff0000u) : (w1[e >> 1] << 16));
               }
             }
-            float* dst = sdiag + dbase + 8 * delta - 7;
 #pragma unroll
-            for (int j = 0; j < 15; ++j) {
-              const int idx = dbase + 8 * delta - 7 + j;
-              if (idx >= 0 && idx < BIAS_W && acc[j] != 0.0f) atomicAdd(dst + j, acc[j]);
+            for (int i = 0; i < 8; ++i) {
+              accn[i] += (wrap0 ? 0.0f : lo[i]) + (wrap1 ? 0.0f : hi[i]);
+              accw[i] += (wrap0 ? lo[i] : 0.0f) + (wrap1 ? hi[i] : 0.0f);
             }
           }
+          // the tile is consumed: let the compute warps overwrite it while the partial sums are combined
           __syncwarp();
           if (lane == 0) mbar_arrive(bar(B_PD_FREE));
+          // reduce-scatter over the 8 threads of the class: thread `sub` ends up with diagonal i = sub
+          float n4[4], w4[4];
+          {
+            const bool up = sub & 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float sn = up ? accn[j] : accn[4 + j], sw = up ? accw[j] : accw[4 + j];
+              n4[j] = (up ? accn[4 + j] : accn[j]) + __shfl_xor_sync(0xffffffffu, sn, 4);
+              w4[j] = (up ? accw[4 + j] : accw[j]) + __shfl_xor_sync(0xffffffffu, sw, 4);
+            }
+          }
+          float n2[2], w2[2];
+          {
+            const bool up = sub & 2;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const float sn = up ? n4[j] : n4[2 + j], sw = up ? w4[j] : w4[2 + j];
+              n2[j] = (up ? n4[2 + j] : n4[j]) + __shfl_xor_sync(0xffffffffu, sn, 2);
+              w2[j] = (up ? w4[2 + j] : w4[j]) + __shfl_xor_sync(0xffffffffu, sw, 2);
+            }
+          }
+          const bool up = sub & 1;
+          const float vn = (up ? n2[1] : n2[0]) + __shfl_xor_sync(0xffffffffu, up ? n2[0] : n2[1], 1);
+          const float vw = (up ? w2[1] : w2[0]) + __shfl_xor_sync(0xffffffffu, up ? w2[0] : w2[1], 1);
+          const int idx = (ob - t) * BLK + (MAX_S - 1) + 8 * c + sub;   // (key block - query block) * 128 + 511 + d
+          if (idx >= 0 && idx < BIAS_W) sdiag[idx] += vn;
+          if (idx - BLK >= 0 && idx - BLK < BIAS_W) sdiag[idx - BLK] += vw;
         }
       }
     }
@@ -481,12 +520,21 @@ int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, 
                    "max dynamic smem %d, requested %d)", which, cudaGetErrorString(e), fa.numRegs,
                    fa.maxThreadsPerBlock, fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes, BWD_SMEM);
   };
-  t5_attn_bwd_kernel<0><<<n_heads * a.cph, kThreadsKV, BWD_SMEM, st>>>(tmQKV, tmDO, a);
-  pn_count_launch();
-  if (int rc2 = launched((const void*)t5_attn_bwd_kernel<0>, "dK/dV")) return rc2;
-  t5_attn_bwd_kernel<1><<<n_heads * a.cph, kThreadsQ, BWD_SMEM, st>>>(tmQKV, tmDO, a);
-  pn_count_launch();
-  if (int rc2 = launched((const void*)t5_attn_bwd_kernel<1>, "dQ")) return rc2;
+  static int only = -2;   // PN_ATTN_BWD_ONLY=0|1 runs a single pass (timing tools only)
+  if (only == -2) {
+    const char* e = getenv("PN_ATTN_BWD_ONLY");
+    only = e ? atoi(e) : -1;
+  }
+  if (only != 1) {
+    t5_attn_bwd_kernel<0><<<n_heads * a.cph, kThreadsKV, BWD_SMEM, st>>>(tmQKV, tmDO, a);
+    pn_count_launch();
+    if (int rc2 = launched((const void*)t5_attn_bwd_kernel<0>, "dK/dV")) return rc2;
+  }
+  if (only != 0) {
+    t5_attn_bwd_kernel<1><<<n_heads * a.cph, kThreadsQ, BWD_SMEM, st>>>(tmQKV, tmDO, a);
+    pn_count_launch();
+    if (int rc2 = launched((const void*)t5_attn_bwd_kernel<1>, "dQ")) return rc2;
+  }
   return PN_OK;
 }
 

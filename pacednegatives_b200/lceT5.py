@@ -29,6 +29,15 @@ def linear_schedule_with_warmup(step, warmup_steps, total_steps):
     return max(0.0, float(total_steps - step) / float(max(1, total_steps - warmup_steps)))
 
 
+def all_reduce_mean_scale(t, group=None):
+    """DDP's gradient averaging on a flat buffer: SUM all-reduce in place, returns the 1/world factor the
+    optimiser kernel still has to apply (so the mean costs no extra pass)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        return 1.0 / dist.get_world_size(group)
+    return 1.0
+
+
 class _ModelFn(torch.autograd.Function):
     """logits = model(input_ids=, labels=).logits with the backward pass wired to pn_t5_train_backward."""
 
@@ -100,10 +109,7 @@ class MonoT5Model(MonoT5Scorer):
 
     def all_reduce_grads(self, group=None):
         """DDP's gradient mean: one all-reduce over the flat buffer; returns the scale still to apply."""
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=group)
-            return 1.0 / dist.get_world_size(group)
-        return 1.0
+        return all_reduce_mean_scale(self.grads, group)
 
     def step(self, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, gscale=1.0):
         """transformers.AdamW defaults (the optimiser of lceT5.py:172)."""
@@ -193,10 +199,8 @@ class LCEModel:
         meta_loss = weights * loss
         meta_opt.zero_grad()
         meta_loss.mean().backward()
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1 and \
-                self.weights.eta.grad is not None:
-            dist.all_reduce(self.weights.eta.grad, op=dist.ReduceOp.SUM)
-            self.weights.eta.grad /= dist.get_world_size()
+        if self.weights.eta.grad is not None:
+            self.weights.eta.grad *= all_reduce_mean_scale(self.weights.eta.grad)
         meta_opt.step(lr=self.hparams.meta_lr * scale)
 
         self.log("avg_weight", weights.mean())
