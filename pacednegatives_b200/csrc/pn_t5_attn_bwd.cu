@@ -238,6 +238,22 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const float* bcopy = sbias + sh * BIAS_STRIDE;
     uint8_t* prow = gbase + SM_P + half * TILE_BYTES + r * 128;
     uint8_t* dsrow = gbase + SM_DS + half * TILE_BYTES + r * 128;
+    // row statistics (-lse2, D) of step g2's query row; fetched one step ahead so the loads never stall a step
+    const int total = n_items * nb;
+    auto row_stats = [&](int g2, float& nl, float& dd) {
+      nl = 0.0f; dd = 0.0f;
+      if (g2 < total) {
+        const int it2 = g2 / nb;
+        const int qi2 = (MODE == 0 ? g2 % nb : item_ob(it2)) * BLK + r;
+        if (qi2 < S) {
+          const size_t o = (size_t)(item_doc(it2) * S + qi2) * a.n_heads + head;
+          nl = -a.lse2[o];
+          dd = a.dvec[o];
+        }
+      }
+    };
+    float nlse, dv, nlse_nx, dv_nx;
+    row_stats(0, nlse, dv);
     int g = 0;
     for (int it = 0; it < n_items; ++it) {
       const int row0 = item_doc(it) * S, ob = item_ob(it);
@@ -245,14 +261,8 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const int qb = MODE == 0 ? t : ob, kb = MODE == 0 ? ob : t;
         const int qi = qb * BLK + r;
         const int k0 = kb * BLK + half * 64;
-        float nlse = 0.0f, dv = 0.0f;
-        int kvalid = 0;                             // keys of this half that exist (0 for a padding query row)
-        if (qi < S) {
-          const size_t o = (size_t)(row0 + qi) * a.n_heads + head;
-          nlse = -a.lse2[o];
-          dv = a.dvec[o];
-          kvalid = min(64, S - k0);
-        }
+        const int kvalid = qi < S ? min(64, S - k0) : 0;   // keys of this half that exist (0 for a padding row)
+        row_stats(g + 1, nlse_nx, dv_nx);
         mbar_wait(bar(B_SP_FULL), g & 1);
         tc_fence_after();
         uint32_t pp[32], pd[32];                    // P and dS of this thread's 64 columns, packed bf16
@@ -295,6 +305,8 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_PD_READY));
+        nlse = nlse_nx;
+        dv = dv_nx;
 
         if (t == nb - 1) {
           // ---- item epilogue: dV, dK of key block ob (MODE 0) or dQ of query block ob (MODE 1)

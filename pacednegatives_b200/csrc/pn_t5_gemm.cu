@@ -52,6 +52,9 @@ struct GemmArgs {
   __nv_bfloat16* copy_out;  // nullable, [M, ld_copy]
   int ld_copy;
   float* sumsq_out;         // nullable, [N / BLOCK_N][M]
+  // bf16 mode, nullable: ReLU backward fused into a data-gradient GEMM, out = mask[row, col] > 0 ? acc : 0
+  const __nv_bfloat16* mask;
+  int ld_mask;
 };
 
 // kTN = false: C[M,N] = A[M,K] . B[N,K]^T   (both operands K-major: forward and data-gradient GEMMs)
@@ -242,6 +245,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           uint32_t v0[32], v1[32];
           tmem_ld_32x32(t_row + c * 64, v0);
           tmem_ld_32x32(t_row + c * 64 + 32, v1);
+          uint4 mk[8];                               // this row's 64 mask entries (one 128-byte line)
+          if (args.mask) {
+            const uint4* mp = reinterpret_cast<const uint4*>(args.mask + (size_t)row * args.ld_mask + col0 + c * 64);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) mk[j] = live ? __ldg(mp + j) : make_uint4(0u, 0u, 0u, 0u);
+          }
           if (lane == 0) tma_store_wait_read<1>();   // the store that used this buffer two chunks ago has drained
           __syncwarp();
           tmem_ld_wait();
@@ -254,6 +263,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               float x0 = __uint_as_float(v[(j & 3) * 8 + 2 * e]) * rs;
               float x1 = __uint_as_float(v[(j & 3) * 8 + 2 * e + 1]) * rs;
               if (args.relu) { x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
+              if (args.mask) {   // the mask holds ReLU outputs (>= 0): positive <=> any magnitude bit set
+                const uint32_t mw = e == 0 ? mk[j].x : (e == 1 ? mk[j].y : (e == 2 ? mk[j].z : mk[j].w));
+                x0 = (mw & 0x00007fffu) ? x0 : 0.0f;
+                x1 = (mw & 0x7fff0000u) ? x1 : 0.0f;
+              }
               __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
               pk[e] = *reinterpret_cast<uint32_t*>(&h);
             }
@@ -505,6 +519,10 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   a.copy_out = ex ? ex->copy_out : nullptr;
   a.ld_copy = ex ? ex->ld_copy : 0;
   a.sumsq_out = ex ? ex->sumsq_out : nullptr;
+  a.mask = ex ? ex->relu_mask : nullptr;
+  a.ld_mask = ex ? ex->ld_mask : 0;
+  if (a.mask && (mode != PN_EPI_BF16 || (a.ld_mask % 8) || ((uintptr_t)a.mask & 15)))
+    return pn_fail(PN_E_BADARG, "pn_gemm: relu mask needs the bf16 epilogue, 16-byte alignment and ld %% 8 == 0");
   if (a.copy_out && ((a.ld_copy % 4) || ((uintptr_t)a.copy_out & 7)))
     return pn_fail(PN_E_BADARG, "pn_gemm: bf16 copy must be 8-byte aligned with ld %% 4 == 0");
   if ((a.copy_out || a.sumsq_out) && mode == PN_EPI_BF16)

@@ -23,6 +23,8 @@ struct PnGemmExtra {
   __nv_bfloat16* copy_out;    // fp32 modes: bf16 copy of the stored values, [M, ld_copy]
   int ld_copy;
   float* sumsq_out;           // fp32 modes: [pn_gemm_sumsq_parts(N)][M] row sums of squares per n-tile
+  const __nv_bfloat16* relu_mask;   // bf16 mode: out = relu_mask[row, col] > 0 ? acc : 0 (ReLU backward), [M, ld_mask]
+  int ld_mask;
 };
 int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
                     int mode, int relu, const PnGemmExtra* ex, int cta_group, cudaStream_t st);

@@ -135,6 +135,15 @@ int dgrad(const PnT5* m, const __nv_bfloat16* dY, int ld_dy, const PnLin& W, voi
   return pn_gemm_bf16_ex(dY, ld_dy, W.packedT, (int)W.rows, out, W.cols, M, W.cols, (int)W.rows, mode, 0, nullptr,
                          m->cta_group, st);
 }
+// data gradient through Wo of the FFN with the ReLU backward and the fused-norm row scale in the epilogue:
+// Ys = rs (.) (dY Wo (.) [act > 0])
+int dgrad_relu(const PnT5* m, const __nv_bfloat16* dY, const PnLin& W, const __nv_bfloat16* act, const float* rs,
+               __nv_bfloat16* out, int M, cudaStream_t st) {
+  PnGemmExtra ex = {};
+  ex.row_scale = rs; ex.relu_mask = act; ex.ld_mask = W.cols;
+  return pn_gemm_bf16_ex(dY, (int)W.rows, W.packedT, (int)W.rows, out, W.cols, M, W.cols, (int)W.rows, PN_EPI_BF16, 0,
+                         &ex, m->cta_group, st);
+}
 // weight gradient of an un-normed linear: grads[W] += dY^T X
 int wgrad_plain(const PnT5* m, const __nv_bfloat16* dY, int ld_dy, const __nv_bfloat16* X, const PnLin& W, int K,
                 cudaStream_t st) {
@@ -266,8 +275,7 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     const float *rs0 = w.drs[3 * l], *rs1 = w.drs[3 * l + 1], *rs2 = w.drs[3 * l + 2];
     // FFN: h3 = h2 + relu(norm(h2) Wi^T) Wo^T
     RC(wgrad_plain(m, w.ddHb, d, w.dact[l], D.wo2, drows, st));
-    RC(dgrad(m, w.ddHb, d, D.wo2, w.ddbig, PN_EPI_BF16, drows, st));
-    RC(pn_t5_relu_mask_scale(w.ddbig, w.dact[l], rs2, drows, ff, st));
+    RC(dgrad_relu(m, w.ddHb, D.wo2, w.dact[l], rs2, w.ddbig, drows, st));
     RC(wgrad_folded(m, w.ddbig, ff, hb2, D.wi, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, ff, D.wi, w.dgbuf, PN_EPI_F32, drows, st));
     RC(pn_t5_norm_bwd(w.dgbuf, hb2, rs2, drows, d, 1, w.ddH, w.ddHb, st));
@@ -302,8 +310,7 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     const __nv_bfloat16 *hb0 = w.hb[2 * l], *hb1 = w.hb[2 * l + 1];
     const float *rs0 = w.rs[2 * l], *rs1 = w.rs[2 * l + 1];
     RC(wgrad_plain(m, w.dHb, d, w.act[l], E.wo2, rows, st));
-    RC(dgrad(m, w.dHb, d, E.wo2, w.dbig, PN_EPI_BF16, rows, st));
-    RC(pn_t5_relu_mask_scale(w.dbig, w.act[l], rs1, rows, ff, st));
+    RC(dgrad_relu(m, w.dHb, E.wo2, w.act[l], rs1, w.dbig, rows, st));
     RC(wgrad_folded(m, w.dbig, ff, hb1, E.wi, w.dWtmp, rows, st));
     RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, PN_EPI_F32, rows, st));
     RC(pn_t5_norm_bwd(w.gbuf, hb1, rs1, rows, d, 1, w.dH, w.dHb, st));
