@@ -23,7 +23,7 @@ using namespace pntc;
 namespace {
 
 constexpr int kThreadsKV = 512;   // MODE 0: + 4 diagonal warps (+ 2 idle: setmaxnreg works on whole warpgroups)
-constexpr int kThreadsQ = 320;
+constexpr int kThreadsQ = 512;    // MODE 1: 6 idle warps only donate registers
 constexpr int DK = 64;
 constexpr int BLK = 128;                       // rows per query / key block
 constexpr int TILE_BYTES = BLK * DK * 2;       // 16 KB: [128 x 64] bf16, 128-byte swizzle
@@ -46,6 +46,7 @@ enum { B_RES_FULL = 0, B_RES_FREE, B_STR_FULL0, B_STR_FULL1, B_STR_EMPTY0, B_STR
 constexpr int BWD_SMEM = SM_BAR + NUM_BARS * 8 + 16 + 1024;
 
 constexpr uint32_t TM_S = 0, TM_DP = 128, TM_ACC0 = 256, TM_ACC1 = 320, TM_COLS = 512;
+constexpr uint32_t TM_DS = 320;   // MODE 1: dS as packed bf16 (64 columns), the A operand of dQ += dS K
 
 struct BwdArgs {
   int S, n_heads, docs, cph;
@@ -64,8 +65,33 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// packed fp32 pairs (sm_100 FFMA2 / FADD2 / FMUL2)
+__device__ __forceinline__ uint64_t f2pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
 template <int MODE>
-__global__ void __maxnreg__(MODE == 0 ? 120 : 168)
+__global__ void __maxnreg__(120)
 t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const BwdArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -127,7 +153,7 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
 
   // MODE 0 registers: the 8 compute warps take what the other two warpgroups give up
   if (warp == 8) {
-    if (MODE == 0) reg_dealloc<72>();
+    reg_dealloc<40>();
     if (lane == 0) {
       // ===================== TMA producer =====================
       int g = 0;
@@ -158,58 +184,66 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       }
     }
   } else if (warp == 9) {
-    if (MODE == 0) reg_dealloc<72>();
-    if (lane == 0) {
-      // ===================== MMA issuer =====================
-      constexpr uint32_t IDESC_SP = make_idesc_bf16(128, BLK, 0, 0);
-      constexpr uint32_t IDESC_TN = make_idesc_bf16(128, DK, 1, 1);    // A = P^T / dS^T (MN-major), B MN-major
-      constexpr uint32_t IDESC_NN = make_idesc_bf16(128, DK, 0, 1);    // A = dS (K-major), B = K MN-major
-      const int total = n_items * nb;
-      auto tiles = [&](int g, uint32_t& tq, uint32_t& tk, uint32_t& tdo, uint32_t& tv) {
-        const uint32_t str = base + SM_STR + (g & 1) * 2 * TILE_BYTES, res = base + SM_RES;
-        if (MODE == 0) { tq = str; tdo = str + TILE_BYTES; tk = res; tv = res + TILE_BYTES; }
-        else { tq = res; tdo = res + TILE_BYTES; tk = str; tv = str + TILE_BYTES; }
-      };
-      auto issue_sp = [&](int g) {
-        const int it = g / nb, t = g % nb;
-        uint32_t tq, tk, tdo, tv;
-        tiles(g, tq, tk, tdo, tv);
-        mbar_wait(bar(B_STR_FULL0 + (g & 1)), (g >> 1) & 1);
-        if (t == 0) mbar_wait(bar(B_RES_FULL), it & 1);
-        if (g > 0) mbar_wait(bar(B_SP_FREE), (g - 1) & 1);   // compute threads hold S, dP of the previous step
-        tc_fence_after();
+    reg_dealloc<40>();
+    // ===================== MMA issuer =====================
+    // The whole warp runs this loop so that every shared-memory descriptor is warp-uniform (uniform registers,
+    // no per-instruction vector->uniform moves: a [128 x 64 x 16] MMA is only 32 tensor-core cycles of work and
+    // would otherwise be bound by its own issue); one lane issues.
+    constexpr uint32_t IDESC_SP = make_idesc_bf16(128, BLK, 0, 0);
+    constexpr uint32_t IDESC_TN = make_idesc_bf16(128, DK, 1, 1);    // A = P^T / dS^T (MN-major), B MN-major
+    constexpr uint32_t IDESC_NN = make_idesc_bf16(128, DK, 0, 1);    // A = dS from TMEM, B = K MN-major
+    const int total = n_items * nb;
+    const bool leader = lane == 0;
+    const uint32_t res = base + SM_RES;
+    // K-major descriptors (S = Q K^T, dP = dO V^T) and MN-major ones (accumulating products); a 16-element K step
+    // advances a K-major descriptor by 2 (32 B) and an MN-major one by 128 (16 rows x 128 B)
+    const uint64_t res0_k = make_desc_kmajor_sw128(res), res1_k = make_desc_kmajor_sw128(res + TILE_BYTES);
+    const uint64_t res0_mn = make_desc_mnmajor_sw128(res, TILE_BYTES);
+    const uint64_t p_mn = make_desc_mnmajor_sw128(base + SM_P, TILE_BYTES);
+    const uint64_t ds_mn = make_desc_mnmajor_sw128(base + SM_DS, TILE_BYTES);
+    auto issue_sp = [&](int g) {
+      const int it = g / nb, t = g % nb;
+      const uint32_t str = base + SM_STR + (g & 1) * 2 * TILE_BYTES;
+      const uint64_t str0_k = make_desc_kmajor_sw128(str), str1_k = make_desc_kmajor_sw128(str + TILE_BYTES);
+      // MODE 0: streamed = (Q, dO), resident = (K, V);  MODE 1: resident = (Q, dO), streamed = (K, V)
+      const uint64_t dq = MODE == 0 ? str0_k : res0_k, ddo = MODE == 0 ? str1_k : res1_k;
+      const uint64_t dk = MODE == 0 ? res0_k : str0_k, dv = MODE == 0 ? res1_k : str1_k;
+      mbar_wait(bar(B_STR_FULL0 + (g & 1)), (g >> 1) & 1);
+      if (t == 0) mbar_wait(bar(B_RES_FULL), it & 1);
+      if (g > 0) mbar_wait(bar(B_SP_FREE), (g - 1) & 1);   // compute threads hold S, dP of the previous step
+      tc_fence_after();
+      if (leader) {
 #pragma unroll
-        for (int k = 0; k < DK / 16; ++k)
-          umma_bf16<1>(tmem + TM_S, make_desc_kmajor_sw128(tq) + 2u * k, make_desc_kmajor_sw128(tk) + 2u * k,
-                       IDESC_SP, k ? 1u : 0u);
+        for (int k = 0; k < DK / 16; ++k) umma_bf16<1>(tmem + TM_S, dq + 2u * k, dk + 2u * k, IDESC_SP, k ? 1u : 0u);
 #pragma unroll
-        for (int k = 0; k < DK / 16; ++k)
-          umma_bf16<1>(tmem + TM_DP, make_desc_kmajor_sw128(tdo) + 2u * k, make_desc_kmajor_sw128(tv) + 2u * k,
-                       IDESC_SP, k ? 1u : 0u);
+        for (int k = 0; k < DK / 16; ++k) umma_bf16<1>(tmem + TM_DP, ddo + 2u * k, dv + 2u * k, IDESC_SP, k ? 1u : 0u);
         umma_commit<1>(bar(B_SP_FULL));
-      };
-      auto issue_acc = [&](int g) {
-        const int it = g / nb, t = g % nb;
-        uint32_t tq, tk, tdo, tv;
-        tiles(g, tq, tk, tdo, tv);
-        mbar_wait(bar(B_PD_READY), g & 1);
-        if (t == 0 && it > 0) mbar_wait(bar(B_ACC_FREE), (it - 1) & 1);
-        tc_fence_after();
-        const uint32_t tp = base + SM_P, tds = base + SM_DS;
+      }
+      __syncwarp();
+    };
+    auto issue_acc = [&](int g) {
+      const int it = g / nb, t = g % nb;
+      const uint32_t str = base + SM_STR + (g & 1) * 2 * TILE_BYTES;
+      const uint64_t str0_mn = make_desc_mnmajor_sw128(str, TILE_BYTES);
+      const uint64_t str1_mn = make_desc_mnmajor_sw128(str + TILE_BYTES, TILE_BYTES);
+      mbar_wait(bar(B_PD_READY), g & 1);
+      if (t == 0 && it > 0) mbar_wait(bar(B_ACC_FREE), (it - 1) & 1);
+      tc_fence_after();
+      const uint32_t first = t ? 1u : 0u;
+      if (leader) {
+        if (MODE == 0) {
+          // dV[k, :] += sum_q P[q, k] dO[q, :]      dK[k, :] += sum_q dS[q, k] Q[q, :]
 #pragma unroll
-        for (int kk = 0; kk < BLK / 16; ++kk) {
-          const uint32_t acc = (t | kk) ? 1u : 0u;
-          if (MODE == 0) {
-            // dV[k, :] += sum_q P[q, k] dO[q, :]      dK[k, :] += sum_q dS[q, k] Q[q, :]
-            umma_bf16<1>(tmem + TM_ACC0, make_desc_mnmajor_sw128(tp + kk * 2048, TILE_BYTES),
-                         make_desc_mnmajor_sw128(tdo + kk * 2048, TILE_BYTES), IDESC_TN, acc);
-            umma_bf16<1>(tmem + TM_ACC1, make_desc_mnmajor_sw128(tds + kk * 2048, TILE_BYTES),
-                         make_desc_mnmajor_sw128(tq + kk * 2048, TILE_BYTES), IDESC_TN, acc);
-          } else {
-            // dQ[q, :] += sum_k dS[q, k] K[k, :]
-            umma_bf16<1>(tmem + TM_ACC0, make_desc_kmajor_sw128(tds + (kk >> 2) * TILE_BYTES) + 2u * (kk & 3),
-                         make_desc_mnmajor_sw128(tk + kk * 2048, TILE_BYTES), IDESC_NN, acc);
-          }
+          for (int kk = 0; kk < BLK / 16; ++kk)
+            umma_bf16<1>(tmem + TM_ACC0, p_mn + 128u * kk, str1_mn + 128u * kk, IDESC_TN, kk ? 1u : first);
+#pragma unroll
+          for (int kk = 0; kk < BLK / 16; ++kk)
+            umma_bf16<1>(tmem + TM_ACC1, ds_mn + 128u * kk, str0_mn + 128u * kk, IDESC_TN, kk ? 1u : first);
+        } else {
+          // dQ[q, :] += sum_k dS[q, k] K[k, :]
+#pragma unroll
+          for (int kk = 0; kk < BLK / 16; ++kk)
+            umma_bf16_ts(tmem + TM_ACC0, tmem + TM_DS + kk * 8, str0_mn + 128u * kk, IDESC_NN, kk ? 1u : first);
         }
         umma_commit<1>(bar(B_PD_FREE));
         umma_commit<1>(bar(B_STR_EMPTY0 + (g & 1)));
@@ -217,20 +251,23 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           umma_commit<1>(bar(B_ACC_FULL));
           umma_commit<1>(bar(B_RES_FREE));
         }
-      };
-      if (total > 0) issue_sp(0);
-      for (int g = 0; g < total; ++g) {
-        const bool last_of_item = (g % nb) == nb - 1;
-        // S / dP of the next step are formed while the compute warps work on this one; across an item boundary
-        // the resident tiles are only released by this step's accumulating MMAs, so those go first
-        if (!last_of_item) issue_sp(g + 1);
-        issue_acc(g);
-        if (last_of_item && g + 1 < total) issue_sp(g + 1);
       }
+      __syncwarp();
+    };
+    (void)res0_mn;
+    if (total > 0) issue_sp(0);
+    for (int g = 0; g < total; ++g) {
+      const bool last_of_item = (g % nb) == nb - 1;
+      // S / dP of the next step are formed while the compute warps work on this one; across an item boundary
+      // the resident tiles are only released by this step's accumulating MMAs, so those go first
+      if (!last_of_item) issue_sp(g + 1);
+      issue_acc(g);
+      if (last_of_item && g + 1 < total) issue_sp(g + 1);
     }
   } else if (warp < 8) {
     // ===================== compute warps: thread = (query row r, 64-key half) =====================
-    if (MODE == 0) reg_alloc<168>();
+    if (MODE == 0) reg_alloc<184>();   // per scheduler: 2 x 184 + 72 (diagonal warp) + 40 = 4 x 120
+    else reg_alloc<200>();             //                2 x 200 + 2 x 40
     const int w4 = warp & 3, half = warp >> 2;
     const int r = w4 * 32 + lane;                   // query row inside the block = TMEM lane
     const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
@@ -247,13 +284,13 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const int qi2 = (MODE == 0 ? g2 % nb : item_ob(it2)) * BLK + r;
         if (qi2 < S) {
           const size_t o = (size_t)(item_doc(it2) * S + qi2) * a.n_heads + head;
-          nl = -a.lse2[o];
+          nl = a.lse2[o];   // raw values: nothing may depend on these loads before the next step
           dd = a.dvec[o];
         }
       }
     };
-    float nlse, dv, nlse_nx, dv_nx;
-    row_stats(0, nlse, dv);
+    float lse, dv, lse_nx, dv_nx;
+    row_stats(0, lse, dv);
     int g = 0;
     for (int it = 0; it < n_items; ++it) {
       const int row0 = item_doc(it) * S, ob = item_ob(it);
@@ -262,50 +299,87 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const int qi = qb * BLK + r;
         const int k0 = kb * BLK + half * 64;
         const int kvalid = qi < S ? min(64, S - k0) : 0;   // keys of this half that exist (0 for a padding row)
-        row_stats(g + 1, nlse_nx, dv_nx);
+        row_stats(g + 1, lse_nx, dv_nx);
+        const float nlse = -lse;
+        const bool full = __all_sync(0xffffffffu, kvalid == 64);   // no padding rows or keys in this warp's block
         mbar_wait(bar(B_SP_FULL), g & 1);
         tc_fence_after();
         uint32_t pp[32], pd[32];                    // P and dS of this thread's 64 columns, packed bf16
-#pragma unroll
-        for (int c2 = 0; c2 < 2; ++c2) {
-          uint32_t s[32], dp[32];
-          tmem_ld_32x32(tmem + lane_addr + TM_S + half * 64 + c2 * 32, s);
-          tmem_ld_32x32(tmem + lane_addr + TM_DP + half * 64 + c2 * 32, dp);
-          tmem_ld_wait();
-          const float4* bp = reinterpret_cast<const float4*>(bcopy + (k0 + c2 * 32 - qi + (MAX_S - 1) - sh));
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 b = bp[j >> 2];
-            const float bb[4] = {b.x, b.y, b.z, b.w};
-            float p[4], d[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float x = fmaf(__uint_as_float(s[j + e]), kLog2e, bb[e]) + nlse;
-              p[e] = (c2 * 32 + j + e < kvalid) ? ex2_approx(x) : 0.0f;
-              d[e] = p[e] * (__uint_as_float(dp[j + e]) - dv);
-            }
-            pp[c2 * 16 + (j >> 1)] = pack2(p[0], p[1]);
-            pp[c2 * 16 + (j >> 1) + 1] = pack2(p[2], p[3]);
-            pd[c2 * 16 + (j >> 1)] = pack2(d[0], d[1]);
-            pd[c2 * 16 + (j >> 1) + 1] = pack2(d[2], d[3]);
-          }
-        }
-        // S, dP are in registers: the tensor core may form the next step's
+        uint32_t sraw[2][32], dpraw[2][32];
+        tmem_ld_32x32(tmem + lane_addr + TM_S + half * 64, sraw[0]);
+        tmem_ld_32x32(tmem + lane_addr + TM_DP + half * 64, dpraw[0]);
+        tmem_ld_32x32(tmem + lane_addr + TM_S + half * 64 + 32, sraw[1]);
+        tmem_ld_32x32(tmem + lane_addr + TM_DP + half * 64 + 32, dpraw[1]);
+        tmem_ld_wait();
+        // S, dP are in registers: the tensor core forms the next step's while this one is processed
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_SP_FREE));
-        if (g > 0) mbar_wait(bar(B_PD_FREE), (g - 1) & 1);   // previous step's accumulating MMAs read P, dS
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int ch = (j ^ (r & 7)) << 4;        // 128-byte swizzle: 16-byte chunk j of row r
-          if (MODE == 0)
-            *reinterpret_cast<uint4*>(prow + ch) = make_uint4(pp[4 * j], pp[4 * j + 1], pp[4 * j + 2], pp[4 * j + 3]);
-          *reinterpret_cast<uint4*>(dsrow + ch) = make_uint4(pd[4 * j], pd[4 * j + 1], pd[4 * j + 2], pd[4 * j + 3]);
+        for (int c2 = 0; c2 < 2; ++c2) {
+          const uint32_t(&s)[32] = sraw[c2];
+          const uint32_t(&dp)[32] = dpraw[c2];
+          const float4* bp = reinterpret_cast<const float4*>(bcopy + (k0 + c2 * 32 - qi + (MAX_S - 1) - sh));
+          if (full) {
+            // packed fp32 pairs (FFMA2 / FADD2 / FMUL2): half the issue slots of the scalar form
+            const uint64_t l2 = f2pack(kLog2e, kLog2e), nl2 = f2pack(nlse, nlse), ndv2 = f2pack(-dv, -dv);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b = bp[j >> 2];
+#pragma unroll
+              for (int h2 = 0; h2 < 2; ++h2) {
+                const uint64_t sv = f2pack(__uint_as_float(s[j + 2 * h2]), __uint_as_float(s[j + 2 * h2 + 1]));
+                const uint64_t bv = h2 ? f2pack(b.z, b.w) : f2pack(b.x, b.y);
+                const uint64_t x = add2(fma2(sv, l2, bv), nl2);
+                float x0, x1;
+                f2unpack(x, x0, x1);
+                const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+                const uint64_t dpv = f2pack(__uint_as_float(dp[j + 2 * h2]), __uint_as_float(dp[j + 2 * h2 + 1]));
+                const uint64_t dsv = mul2(f2pack(p0, p1), add2(dpv, ndv2));
+                float d0, d1;
+                f2unpack(dsv, d0, d1);
+                pp[c2 * 16 + (j >> 1) + h2] = pack2(p0, p1);
+                pd[c2 * 16 + (j >> 1) + h2] = pack2(d0, d1);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b = bp[j >> 2];
+              const float bb[4] = {b.x, b.y, b.z, b.w};
+              float p[4], d[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float x = fmaf(__uint_as_float(s[j + e]), kLog2e, bb[e]) + nlse;
+                p[e] = (c2 * 32 + j + e < kvalid) ? ex2_approx(x) : 0.0f;
+                d[e] = p[e] * (__uint_as_float(dp[j + e]) - dv);
+              }
+              pp[c2 * 16 + (j >> 1)] = pack2(p[0], p[1]);
+              pp[c2 * 16 + (j >> 1) + 1] = pack2(p[2], p[3]);
+              pd[c2 * 16 + (j >> 1)] = pack2(d[0], d[1]);
+              pd[c2 * 16 + (j >> 1) + 1] = pack2(d[2], d[3]);
+            }
+          }
         }
-        fence_proxy_async();
+        if (g > 0) mbar_wait(bar(B_PD_FREE), (g - 1) & 1);   // previous step's accumulating MMAs read P, dS
+        if (MODE == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int ch = (j ^ (r & 7)) << 4;      // 128-byte swizzle: 16-byte chunk j of row r
+            *reinterpret_cast<uint4*>(prow + ch) = make_uint4(pp[4 * j], pp[4 * j + 1], pp[4 * j + 2], pp[4 * j + 3]);
+            *reinterpret_cast<uint4*>(dsrow + ch) = make_uint4(pd[4 * j], pd[4 * j + 1], pd[4 * j + 2], pd[4 * j + 3]);
+          }
+          fence_proxy_async();
+        } else {
+          // dS stays in tensor memory: rows = queries, two keys per 32-bit column (TS-mode operand of dQ += dS K)
+          tc_fence_after();
+          tmem_st_32x32(tmem + lane_addr + TM_DS + half * 32, pd);
+          tmem_st_wait();
+          tc_fence_before();
+        }
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_PD_READY));
-        nlse = nlse_nx;
+        lse = lse_nx;
         dv = dv_nx;
 
         if (t == nb - 1) {
@@ -353,7 +427,8 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     // conflict-free, with compile-time register indices; a chunk that wrapped past column 127 belongs to the
     // diagonal 128 below.  The eight threads of a class then reduce-scatter by shuffles, so every diagonal of
     // the tile has exactly one owner: no atomics.
-    if (MODE == 0) reg_dealloc<72>();
+    if (MODE == 0 && warp < 14) reg_dealloc<72>();
+    else reg_dealloc<40>();
     if (MODE == 0 && warp < 14) {
       const int u = threadIdx.x - 320;
       const int c = u >> 3, sub = u & 7;
@@ -443,6 +518,7 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       const float v = sdiag[i];
       if (v != 0.0f) atomicAdd(a.dbias_diag + (size_t)head * BIAS_W + i, v);
     }
+
   }
 }
 

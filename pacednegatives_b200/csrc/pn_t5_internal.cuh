@@ -44,7 +44,8 @@ int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, 
                     cudaStream_t st);
 // Backward of pn_t5_self_attn (pn_t5_attn_bwd.cu): dqkv <- (dq | dk | dv) (each row optionally scaled by
 // row_scale), dbias_diag [H, 1023] += per-diagonal sums of dS; lse2 is the forward's lse_out, dvec a [rows, H]
-// workspace.  pn_t5_rel_bias_grad folds the diagonals into the gradient of relative_attention_bias.weight.
+// workspace.
+// pn_t5_rel_bias_grad folds the diagonals into the gradient of relative_attention_bias.weight.
 int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, int v_col, int docs, int S,
                         int n_heads, const float* bias, const __nv_bfloat16* ctx, const __nv_bfloat16* dctx,
                         int ld_ctx, const float* lse2, float* dvec, const float* row_scale,

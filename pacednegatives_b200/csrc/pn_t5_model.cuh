@@ -9,6 +9,7 @@
 #include "pn_common.cuh"
 #include "pn_t5_internal.cuh"
 
+#include <array>
 #include <map>
 #include <string>
 #include <vector>
@@ -66,6 +67,7 @@ struct PnT5 {
   int64_t enc_rel_off = 0, dec_rel_off = 0;
   float *enc_bias = nullptr;                     // [heads, 1023] expanded by (j - i + 511)
   float *dec_bias = nullptr;                     // [heads, 2, 2] for T <= 2
+  std::map<const void*, std::array<int64_t, 3>> fwd_ws;   // training workspaces holding a forward pass: docs, S, T
   bool finalized = false;
   bool want_train = false;           // also keep packedT / embT (pn_t5_set_option "train")
   int cta_group = 2;

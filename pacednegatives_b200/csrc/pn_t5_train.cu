@@ -45,8 +45,7 @@ struct TrainWs {
   __nv_bfloat16* head_in;
   float *ddH, *dgbuf;
   __nv_bfloat16 *ddHb, *ddbig, *ddctx, *dlb;
-  // header kept at the start of the workspace so that backward can check it belongs to the forward
-  int64_t* header;
+  int64_t* header;   // reserved
 };
 
 size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, TrainWs* w) {
@@ -191,8 +190,7 @@ extern "C" int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* l
   const int d = m->cfg.d_model, di = m->d_inner, H = m->cfg.n_heads;
   const int rows = (int)(docs * S), drows = (int)(docs * T);
   const size_t L = m->enc.size(), Ld = m->dec.size();
-  const int64_t hdr[4] = {docs, S, T, 0x706e7472};
-  PN_CUDA(cudaMemcpyAsync(w.header, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
+  m->fwd_ws[workspace] = {docs, (int64_t)S, (int64_t)T};   // host-side record: backward checks it without a sync
 
   // ---- encoder
   RC(pn_t5_embed(ids, m->emb, rows, d, m->cfg.vocab, w.hidden, w.hb[0], w.ss, st));
@@ -248,11 +246,12 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
   if ((int64_t)need > workspace_bytes)
     return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace %lld < %zu bytes", (long long)workspace_bytes, need);
   cudaStream_t st = (cudaStream_t)stream;
-  int64_t hdr[4];
-  PN_CUDA(cudaMemcpyAsync(hdr, w.header, sizeof(hdr), cudaMemcpyDeviceToHost, st));
-  PN_CUDA(cudaStreamSynchronize(st));
-  if (hdr[0] != docs || hdr[1] != S || hdr[2] != T || hdr[3] != 0x706e7472)
-    return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace does not hold a forward pass of this shape");
+  {
+    auto it = m->fwd_ws.find(workspace);
+    if (it == m->fwd_ws.end() || it->second[0] != docs || it->second[1] != S || it->second[2] != T)
+      return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace does not hold a forward pass of this shape");
+    m->fwd_ws.erase(it);
+  }
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
   const int rows = (int)(docs * S), drows = (int)(docs * T);
   const int L = (int)m->enc.size(), Ld = (int)m->dec.size();

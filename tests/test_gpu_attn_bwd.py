@@ -7,7 +7,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def run_case(docs, S, H, with_scale, seed):
+def run_case(docs, S, H, with_scale, seed, DC=0):
     from pacednegatives_b200 import _lib
     lib = _lib.lib()
     torch.manual_seed(seed)
@@ -15,6 +15,9 @@ def run_case(docs, S, H, with_scale, seed):
     rows = docs * S
     qkv = (torch.randn(rows, 3 * di, device="cuda") * 0.5).bfloat16()
     bias = torch.randn(H, 1023, device="cuda")
+    if DC:   # T5-like table: one value per side beyond |j - i| >= DC
+        bias[:, 511 + DC:] = bias[:, 1022:1023]
+        bias[:, :511 - DC + 1] = bias[:, 0:1]
     dctx = (torch.randn(rows, di, device="cuda") * 0.5).bfloat16()
     rs = (torch.rand(rows, device="cuda") + 0.5) if with_scale else None
     ctx = torch.zeros(rows, di, device="cuda", dtype=torch.bfloat16)
@@ -50,6 +53,11 @@ def run_case(docs, S, H, with_scale, seed):
         err = (got[:, sl] - gx[:, sl]).abs().max().item()
         assert err < 2e-2 * max(1.0, scale), f"{name}: docs={docs} S={S} H={H}: err {err} (scale {scale})"
     gb = bp.grad
+    if DC:   # the constant regions are one parameter each: compare their totals, and the near diagonals one by one
+        def fold(x):
+            return torch.cat([x[:, :511 - DC + 1].sum(1, keepdim=True), x[:, 511 - DC + 1:511 + DC],
+                              x[:, 511 + DC:].sum(1, keepdim=True)], dim=1)
+        diag, gb = fold(diag), fold(gb)
     err = (diag - gb).abs().max().item()
     assert err < 2e-2 * max(1.0, gb.abs().max().item()), f"dbias: docs={docs} S={S} H={H}: err {err}"
 
@@ -62,3 +70,13 @@ def test_self_attention_backward_vs_autograd(docs, S, H, with_scale):
     from pacednegatives_b200 import _lib
     _lib.require_gpu()
     run_case(docs, S, H, with_scale, seed=docs * 1000 + S + H)
+
+
+@pytest.mark.parametrize("docs,S,H,DC", [(3, 512, 2, 91), (2, 384, 4, 128), (1, 200, 2, 60), (5, 512, 12, 91),
+                                         (2, 512, 1, 300)])
+def test_self_attention_backward_saturated_bias(docs, S, H, DC):
+    """bias_const_dist: tiles wholly beyond the bucket saturation distance skip the bias table and the per-diagonal
+    reduction (T5: 91 for 32 buckets / max_distance 128)."""
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    run_case(docs, S, H, True, seed=docs * 1000 + S + H + DC, DC=DC)

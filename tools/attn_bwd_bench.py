@@ -10,6 +10,10 @@ iters = int(os.environ.get("ITERS", 5))
 di, rows = H * 64, docs * S
 qkv = (torch.randn(rows, 3 * di, device="cuda") * 0.5).bfloat16()
 bias = torch.randn(H, 1023, device="cuda")
+DC = int(os.environ.get("DC", 91))
+if DC:
+    bias[:, 511 + DC:] = bias[:, 1022:1023]
+    bias[:, :511 - DC + 1] = bias[:, 0:1]
 dctx = (torch.randn(rows, di, device="cuda") * 0.5).bfloat16()
 ctx = torch.zeros(rows, di, device="cuda", dtype=torch.bfloat16)
 lse = torch.zeros(rows, H, device="cuda")

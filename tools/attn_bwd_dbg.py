@@ -14,6 +14,7 @@ def one(docs, S, H, ws):
     rows = docs * S
     qkv = (torch.randn(rows, 3 * di, device="cuda") * 0.5).bfloat16()
     bias = torch.randn(H, 1023, device="cuda")
+    DC = 0
     dctx = (torch.randn(rows, di, device="cuda") * 0.5).bfloat16()
     rs = (torch.rand(rows, device="cuda") + 0.5) if ws else None
     ctx = torch.zeros(rows, di, device="cuda", dtype=torch.bfloat16)
