@@ -173,6 +173,19 @@ class LCEModel:
         return linear_schedule_with_warmup(self.global_step, int(self.hparams.warmup_steps),
                                            int(self.hparams.total_steps))
 
+    def _forward_pn(self, p, n, k, V):
+        """`self.model(**p).logits`, `self.model(**n).logits` (lceT5.py:149-150).  Documents are independent, so
+        when both batches have the same sequence and label lengths they go through the model as ONE batch (half
+        the kernel launches, fuller GEMM tiles); the logits are the same numbers either way."""
+        pi, ni = torch.as_tensor(p["input_ids"]), torch.as_tensor(n["input_ids"])
+        pl, nl = torch.as_tensor(p["labels"]), torch.as_tensor(n["labels"])
+        if pi.shape[1] == ni.shape[1] and pl.shape[1] == nl.shape[1]:
+            dev = "cuda"
+            logits = self.model(torch.cat([pi.to(dev), ni.to(dev)]), torch.cat([pl.to(dev), nl.to(dev)]))
+            Q = pi.shape[0]
+            return logits[:Q], logits[Q:].reshape(-1, k, V)
+        return self.model(pi, pl), self.model(ni, nl).view(-1, k, V)
+
     def training_step(self, batch, batch_nb=0):
         p, n = batch
         if self._opts is None:
@@ -182,8 +195,7 @@ class LCEModel:
         scale = self._lr_scale()
 
         if self.elide:
-            plogits = self.model(p["input_ids"], p["labels"])
-            nlogits = self.model(n["input_ids"], n["labels"]).view(-1, k, V)
+            plogits, nlogits = self._forward_pn(p, n, k, V)
             p0, n0 = plogits.detach(), nlogits.detach()
         else:
             with torch.no_grad():
@@ -208,8 +220,7 @@ class LCEModel:
         self.log("eta", self.weights.eta.item())
 
         if not self.elide:
-            plogits = self.model(p["input_ids"], p["labels"])
-            nlogits = self.model(n["input_ids"], n["labels"]).view(-1, k, V)
+            plogits, nlogits = self._forward_pn(p, n, k, V)
         main_loss = self.pair_loss(plogits.contiguous(), nlogits.contiguous(), op, on)
 
         opt.zero_grad()
