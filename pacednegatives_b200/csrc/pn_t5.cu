@@ -11,6 +11,7 @@
 #include "pn_t5_model.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace {
@@ -61,6 +62,9 @@ struct Workspace {
   float* dh; __nv_bfloat16 *dxn, *dctx, *dbig; float* dss;
   int32_t* dec_ids;
   __nv_bfloat16* head_in; float* logits;
+  // cross-attention without the K/V projection (see pn_t5_ops.cu): R = docs * Mp rows, Mp = T*H rounded up to 8
+  float *rs_enc, *scores, *cprime;
+  __nv_bfloat16 *qexp, *qk, *P, *cprime_b, *ctxfull;
 };
 
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -85,6 +89,15 @@ size_t carve(const PnT5* m, int64_t docs, int S, int T, int want_logits, uint8_t
   w->dec_ids = (int32_t*)take(drows * 4);
   w->head_in = (__nv_bfloat16*)take(drows * d * 2);
   w->logits = (float*)take(want_logits ? drows * (size_t)m->vocab_pad * 4 : 0);
+  const size_t Mp = (size_t)((T * m->cfg.n_heads + 7) & ~7), R = (size_t)docs * Mp;
+  w->rs_enc = (float*)take(rows * 4);
+  w->scores = (float*)take(rows * 128 * 4);
+  w->cprime = (float*)take(R * d * 4);
+  w->qexp = (__nv_bfloat16*)take(R * di * 2);
+  w->qk = (__nv_bfloat16*)take(R * d * 2);
+  w->P = (__nv_bfloat16*)take(rows * Mp * 2);
+  w->cprime_b = (__nv_bfloat16*)take(R * d * 2);
+  w->ctxfull = (__nv_bfloat16*)take(R * di * 2);
   return off;
 }
 
@@ -118,6 +131,13 @@ int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& 
   const int parts = pn_gemm_sumsq_parts(d);
   const int enc_parts = m->enc.empty() ? 1 : parts;
   RC(pn_t5_embed(w.dec_ids, m->emb, drows, d, m->cfg.vocab, w.dh, w.dxn, w.dss, st));
+  // Cross-attention: with T <= 2 decoder tokens the K/V projection of all S encoder rows is replaced by
+  // scores = X (Wk^T q) and out = Wv (P^T X) (pn_t5_ops.cu); needs whole GEMM tiles per document.
+  const int TH = T * H, Mp = (TH + 7) & ~7;
+  static const bool xattn_off = getenv("PN_XATTN_OFF") != nullptr;
+  const bool xattn = !xattn_off && (S % 128) == 0 && Mp <= 32;
+  const int R = (int)docs * Mp;
+  if (xattn) RC(pn_t5_rs(w.ss, enc_parts, rows, d, m->cfg.eps, w.rs_enc, st));
   int cur_parts = 1;
   for (size_t l = 0; l < m->dec.size(); ++l) {
     const PnDecLayer& L = m->dec[l];
@@ -130,9 +150,29 @@ int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& 
     // cross-attention: K/V projection of all S encoder states (the 13% of FLOPs), no bias; the encoder's
     // final RMSNorm is fused into this GEMM
     RC(gemm_normed(m, w.dxn, w.dss, cur_parts, L.cq, w.dbig, di, drows, 0, st));
-    RC(gemm_normed(m, w.xn, w.ss, enc_parts, L.ckv, w.big, 2 * di, rows, 0, st));
-    RC(pn_t5_dec_attn(w.dbig, di, 0, w.big, w.big, 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
-                      w.dctx, di, st));
+    if (xattn) {
+      // QK[doc, (t,h), :] = Wk_h^T q[doc, t, h]  (B = the K half of the transposed packed weight, [d, d_inner])
+      RC(pn_t5_cross_expand_q(w.dbig, di, docs, T, H, Mp, w.qexp, st));
+      RC(pn_gemm_bf16_internal(w.qexp, di, L.ckv.packedT, 2 * di, w.qk, d, R, d, di, PN_EPI_BF16, 0, nullptr,
+                               m->cta_group, st));
+      // scores[row, (t,h)] = rs[row] * (x_row . QK[doc(row), (t,h)]): block-diagonal B, one QK per document
+      PnGemmExtra ex = {};
+      ex.row_scale = w.rs_enc; ex.group_rows = S; ex.group_b_rows = Mp;
+      RC(pn_gemm_bf16_ex(w.xn, d, w.qk, d, w.scores, 128, rows, 128, d, PN_EPI_F32, 0, &ex, (S % 256) == 0 ? 2 : 1,
+                         st));
+      RC(pn_t5_cross_softmax(w.scores, 128, w.rs_enc, docs, S, TH, Mp, w.P, st));
+      // C'[doc] = P[doc]^T . X[doc]  (batched MN-major GEMM), then out = C' . Wv^T and the per-head diagonal blocks
+      PN_CUDA(cudaMemsetAsync(w.cprime, 0, (size_t)R * d * 4, st));
+      RC(pn_gemm_tn_batched(w.P, Mp, w.xn, d, w.cprime, d, Mp, d, S, (int)docs, st));
+      RC(pn_t5_f32_to_bf16(w.cprime, w.cprime_b, (int64_t)R * d, st));
+      RC(pn_gemm_bf16_internal(w.cprime_b, d, L.ckv.packed + (size_t)di * d, d, w.ctxfull, di, R, di, d, PN_EPI_BF16,
+                               0, nullptr, m->cta_group, st));
+      RC(pn_t5_cross_gather(w.ctxfull, Mp, docs, T, H, w.dctx, di, st));
+    } else {
+      RC(gemm_normed(m, w.xn, w.ss, enc_parts, L.ckv, w.big, 2 * di, rows, 0, st));
+      RC(pn_t5_dec_attn(w.dbig, di, 0, w.big, w.big, 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
+                        w.dctx, di, st));
+    }
     RC(gemm_resid(m, w.dctx, L.co, w.dh, w.dxn, w.dss, drows, st));
     // FFN
     RC(gemm_normed(m, w.dxn, w.dss, cur_parts, L.wi, w.dbig, ff, drows, 1, st));
@@ -272,11 +312,11 @@ static int t5_allocate(PnT5* m) {
   PN_CUDA(cudaMemcpy(bucket_of, bo.data(), 1023 * sizeof(int), cudaMemcpyHostToDevice));
   RC(pn_dev_alloc(m, &m->flat, (size_t)m->n_params));
   float* f = m->flat;
-  auto bind = [&](PnLin& L) -> int {
+  auto bind = [&](PnLin& L, bool needT = false) -> int {
     L.master = f + L.off;
     L.fold = L.fold_off >= 0 ? f + L.fold_off : nullptr;
     RC(pn_dev_alloc(m, &L.packed, (size_t)L.rows * L.cols));
-    if (m->want_train) RC(pn_dev_alloc(m, &L.packedT, (size_t)L.rows * L.cols));
+    if (m->want_train || needT) RC(pn_dev_alloc(m, &L.packedT, (size_t)L.rows * L.cols));
     return PN_OK;
   };
   for (auto& L : m->enc) {
@@ -284,7 +324,7 @@ static int t5_allocate(PnT5* m) {
     L.ln0 = f + L.ln0_off; L.ln1 = f + L.ln1_off;
   }
   for (auto& L : m->dec) {
-    RC(bind(L.wqkv)); RC(bind(L.wo)); RC(bind(L.cq)); RC(bind(L.ckv)); RC(bind(L.co)); RC(bind(L.wi)); RC(bind(L.wo2));
+    RC(bind(L.wqkv)); RC(bind(L.wo)); RC(bind(L.cq)); RC(bind(L.ckv, true)); RC(bind(L.co)); RC(bind(L.wi)); RC(bind(L.wo2));
     L.ln0 = f + L.ln0_off; L.ln1 = f + L.ln1_off; L.ln2 = f + L.ln2_off;
   }
   m->emb = f + m->emb_off;

@@ -55,6 +55,12 @@ struct GemmArgs {
   // bf16 mode, nullable: ReLU backward fused into a data-gradient GEMM, out = mask[row, col] > 0 ? acc : 0
   const __nv_bfloat16* mask;
   int ld_mask;
+  // block-diagonal B (kTN = false): rows [g*group_rows, (g+1)*group_rows) of A multiply the B rows starting at
+  // g*group_b_rows (one small B per document); group_rows is a multiple of the M tile.  0 = one B for all rows.
+  int group_rows, group_b_rows;
+  // batched kTN: split s covers the K rows of batch s and writes its own output at out + s*batch_stride
+  long long batch_stride;
+  int batches;
 };
 
 // kTN = false: C[M,N] = A[M,K] . B[N,K]^T   (both operands K-major: forward and data-gradient GEMMs)
@@ -131,7 +137,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int tile = item % num_out_tiles;
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
       const int m0 = m_blk * tile_m + (int)cta_rank * BLOCK_M;
-      const int n0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;
+      int n0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;
+      if (!kTN && args.group_rows > 0) n0 += (m_blk * tile_m / args.group_rows) * args.group_b_rows;
       int kb0, kb1;
       kb_range(item, kb0, kb1);
       for (int kb = kb0; kb < kb1; ++kb) {
@@ -285,7 +292,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       } else {
         const bool resid = args.mode == PN_EPI_RESID_F32;
         const bool atomic = args.mode == PN_EPI_ATOMIC_F32;
-        float* outf = reinterpret_cast<float*>(args.out);
+        float* outf = reinterpret_cast<float*>(args.out) + (size_t)(item / num_out_tiles) * args.batch_stride;
         float ssq[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) ssq[i] = 0.0f;
@@ -423,7 +430,13 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
   if (!kTN) {
     rc = pn_make_tmap_bf16_2d(&tmA, A, args.M, args.K, lda, BLOCK_M, BLOCK_K);
     if (rc) return rc;
-    rc = pn_make_tmap_bf16_2d(&tmB, B, args.N, args.K, ldb, Cfg::B_ROWS, BLOCK_K);
+    const uint64_t b_rows = args.group_rows > 0
+                                ? (uint64_t)((args.M + args.group_rows - 1) / args.group_rows) * args.group_b_rows
+                                : (uint64_t)args.N;   // block-diagonal B: reads past the last group are zero-filled
+    if (args.group_rows > 0 && (args.group_rows % (BLOCK_M * kCtaGroup)))
+      return pn_fail(PN_E_BADARG, "pn_gemm: group_rows=%d must be a multiple of the %d-row tile", args.group_rows,
+                     BLOCK_M * kCtaGroup);
+    rc = pn_make_tmap_bf16_2d(&tmB, B, b_rows, args.K, ldb, Cfg::B_ROWS, BLOCK_K);
     if (rc) return rc;
   } else {   // operands are [K rows, M | N columns] row-major: 64 x 64 boxes
     rc = pn_make_tmap_bf16_2d(&tmA, A, args.K, args.M, lda, BLOCK_K, 64);
@@ -446,7 +459,9 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
   const int tiles = ((args.M + tile_m - 1) / tile_m) * (args.N / BLOCK_N);
   const int max_groups = PN_SM_COUNT / kCtaGroup;
   args.splits = 1;
-  if (kTN) {
+  if (kTN && args.batches > 0) {
+    args.splits = args.batches;   // one work item per (batch, output tile); K rows of batch s = split s
+  } else if (kTN) {
     // enough k-splits to give every SM (pair) a few work items, each at least 8 k-blocks deep
     const int total_kb = (args.K + BLOCK_K - 1) / BLOCK_K;
     int want = (2 * max_groups + tiles - 1) / tiles;
@@ -473,6 +488,23 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
   PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, args));
   g_pn_launches.fetch_add(1, std::memory_order_relaxed);
   return PN_OK;
+}
+
+// Batched C_b[M,N] (fp32, += into zeroed memory) = A_b[Kper,M]^T . B_b[Kper,N]: batch b owns rows
+// [b*Kper, (b+1)*Kper) of A and B and the output block out + b*M*ldc.  Kper % 64 == 0.
+int pn_gemm_tn_batched(const void* A, int lda, const void* B, int ldb, float* out, int ldc, int M, int N, int Kper,
+                       int batches, cudaStream_t st) {
+  if (M <= 0 || N <= 0 || Kper <= 0 || batches <= 0) return pn_fail(PN_E_BADARG, "pn_gemm_tn_batched: empty problem");
+  if ((N % 128) || (M % 8) || (Kper % 64))
+    return pn_fail(PN_E_UNSUPPORTED, "pn_gemm_tn_batched: need N %% 128 == 0, M %% 8 == 0, Kper %% 64 == 0");
+  if (M > 128) return pn_fail(PN_E_UNSUPPORTED, "pn_gemm_tn_batched: M=%d > 128", M);
+  if ((lda % 8) || (ldb % 8) || (ldc % 4) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) || ((uintptr_t)out & 15))
+    return pn_fail(PN_E_BADARG, "pn_gemm_tn_batched: operands must be 16-byte aligned");
+  GemmArgs a = {};
+  a.M = M; a.N = N; a.K = Kper * batches; a.out = out; a.ldc = ldc; a.mode = PN_EPI_ATOMIC_F32; a.norm_dim = 1;
+  a.batches = batches; a.batch_stride = (long long)M * ldc;
+  return (N % 256) == 0 ? launch_gemm<1, 256, true>(A, lda, B, ldb, a, st)
+                        : launch_gemm<1, 128, true>(A, lda, B, ldb, a, st);
 }
 
 int pn_gemm_wgrad(const void* A, int lda, const void* B, int ldb, float* out, int ldc, int M, int N, int K,
@@ -519,6 +551,8 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   a.copy_out = ex ? ex->copy_out : nullptr;
   a.ld_copy = ex ? ex->ld_copy : 0;
   a.sumsq_out = ex ? ex->sumsq_out : nullptr;
+  a.group_rows = ex ? ex->group_rows : 0;
+  a.group_b_rows = ex ? ex->group_b_rows : 0;
   a.mask = ex ? ex->relu_mask : nullptr;
   a.ld_mask = ex ? ex->ld_mask : 0;
   if (a.mask && (mode != PN_EPI_BF16 || (a.ld_mask % 8) || ((uintptr_t)a.mask & 15)))

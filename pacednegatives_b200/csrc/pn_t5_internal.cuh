@@ -25,6 +25,7 @@ struct PnGemmExtra {
   float* sumsq_out;           // fp32 modes: [pn_gemm_sumsq_parts(N)][M] row sums of squares per n-tile
   const __nv_bfloat16* relu_mask;   // bf16 mode: out = relu_mask[row, col] > 0 ? acc : 0 (ReLU backward), [M, ld_mask]
   int ld_mask;
+  int group_rows, group_b_rows;     // block-diagonal B: A rows [g*group_rows, ..) use the B rows from g*group_b_rows
 };
 int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
                     int mode, int relu, const PnGemmExtra* ex, int cta_group, cudaStream_t st);
@@ -33,6 +34,11 @@ int pn_gemm_sumsq_parts(int N);
 // (dW = dY^T X); the K range is split across work items and accumulated with fp32 vector atomics
 int pn_gemm_wgrad(const void* A, int lda, const void* B, int ldb, float* out, int ldc, int M, int N, int K,
                   int cta_group, cudaStream_t st);
+
+// batched C_b[M,N] (fp32, accumulated into zeroed memory) = A_b[Kper,M]^T . B_b[Kper,N], batch b = rows
+// [b*Kper, (b+1)*Kper) of A and B, output block out + b*M*ldc
+int pn_gemm_tn_batched(const void* A, int lda, const void* B, int ldb, float* out, int ldc, int M, int N, int Kper,
+                       int batches, cudaStream_t st);
 
 int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                          uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols);

@@ -97,6 +97,14 @@ int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, 
 int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float eps,
                     __nv_bfloat16* out, cudaStream_t st);
 
+// cross-attention without the K/V projection (pn_t5_ops.cu)
+int pn_t5_cross_expand_q(const __nv_bfloat16* q, int ld_q, int64_t docs, int T, int H, int Mp, __nv_bfloat16* qexp,
+                         cudaStream_t st);
+int pn_t5_cross_softmax(const float* scores, int lds, const float* rs, int64_t docs, int S, int TH, int Mp,
+                        __nv_bfloat16* P, cudaStream_t st);
+int pn_t5_cross_gather(const __nv_bfloat16* full, int Mp, int64_t docs, int T, int H, __nv_bfloat16* ctx, int ld_ctx,
+                       cudaStream_t st);
+
 // pn_t5.cu: (re)build every packed bf16 operand and the expanded bias tables from the flat fp32 parameters
 int pn_t5_repack(PnT5* m, cudaStream_t st);
 

@@ -230,3 +230,126 @@ int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float e
   PN_LAUNCHED();
   return PN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Cross-attention without the K/V projection of the encoder states (decoder has T <= 2 tokens per document):
+//   s[t,h,j] = q[t,h,:] . (Wk_h x_j) = x_j . (Wk_h^T q[t,h,:])            -> scores = X . QK^T, QK = Qexp . Wk
+//   o[t,h,:] = sum_j p[t,h,j] Wv_h x_j = Wv_h (sum_j p[t,h,j] x_j)        -> C' = P^T . X,     O = C' . Wv^T
+// which replaces a [rows, d] x [d, 2*d_inner] GEMM per decoder layer (13 % of the forward FLOPs) by two skinny
+// products over the same rows (T*H columns) and three tiny ones over docs*T*H rows.
+namespace {
+
+// Qexp[doc*Mp + t*H + h, :] = q[doc*T + t, head block h] placed at columns h*64.., zero elsewhere (and in pad rows)
+__global__ void __launch_bounds__(256)
+cross_expand_q_kernel(const __nv_bfloat16* __restrict__ q, int ld_q, int64_t docs, int T, int H, int Mp,
+                      __nv_bfloat16* __restrict__ qexp) {
+  const int c8n = H * 8;   // 16-byte chunks per row (d_inner / 8)
+  const int64_t n = docs * Mp * c8n;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+    const int c8 = (int)(i % c8n);
+    const int64_t row = i / c8n;
+    const int th = (int)(row % Mp);
+    const int64_t doc = row / Mp;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (th < T * H && (c8 >> 3) == th % H)
+      v = *reinterpret_cast<const uint4*>(q + (size_t)(doc * T + th / H) * ld_q + c8 * 8);
+    reinterpret_cast<uint4*>(qexp)[i] = v;
+  }
+}
+
+// P[row, th] = softmax over the document's S rows of scores[row, th], times rs[row] (the RMS scale of x_row, so that
+// P^T . X sums the normalised states); pad columns th >= TH are written as zero.  One CTA per document.
+__global__ void __launch_bounds__(256)
+cross_softmax_kernel(const float* __restrict__ scores, int lds, const float* __restrict__ rs, int S, int TH, int Mp,
+                     __nv_bfloat16* __restrict__ P) {
+  __shared__ float red[8][32];
+  __shared__ float stat[32];
+  const int64_t row0 = (int64_t)blockIdx.x * S;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // thread layout: th = tid % 32 (columns), row phase = tid / 32 (8 rows in flight per pass)
+  const int th = lane;
+  const bool act = th < TH;
+  float v[64];   // this lane's column, rows warp, warp + 8, ... (S <= 512)
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < 64; ++i) {
+    const int j = warp + 8 * i;
+    v[i] = (act && j < S) ? scores[(size_t)(row0 + j) * lds + th] : -INFINITY;
+    mx = fmaxf(mx, v[i]);
+  }
+  red[warp][lane] = mx;
+  __syncthreads();
+  if (warp == 0) {
+    float m = red[0][lane];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) m = fmaxf(m, red[k][lane]);
+    stat[lane] = m;
+  }
+  __syncthreads();
+  mx = stat[lane];
+  __syncthreads();
+  float sum = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 64; ++i) {
+    v[i] = act ? __expf(v[i] - mx) : 0.0f;   // exp(-inf) = 0 for rows beyond S
+    sum += v[i];
+  }
+  red[warp][lane] = sum;
+  __syncthreads();
+  if (warp == 0) {
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][lane];
+    stat[lane] = 1.0f / t;
+  }
+  __syncthreads();
+  const float inv = stat[lane];
+  if (th < Mp) {
+#pragma unroll
+    for (int i = 0; i < 64; ++i) {
+      const int j = warp + 8 * i;
+      if (j < S) P[(size_t)(row0 + j) * Mp + th] = __float2bfloat16_rn(act ? v[i] * inv * rs[row0 + j] : 0.0f);
+    }
+  }
+}
+
+// ctx[doc*T + t, h*64 + c] = full[doc*Mp + t*H + h, h*64 + c]
+__global__ void __launch_bounds__(256)
+cross_gather_kernel(const __nv_bfloat16* __restrict__ full, int Mp, int64_t docs, int T, int H,
+                    __nv_bfloat16* __restrict__ ctx, int ld_ctx) {
+  const int c8n = H * 8;
+  const int64_t n = docs * T * c8n;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+    const int c8 = (int)(i % c8n);
+    const int64_t dt = i / c8n;
+    const int64_t doc = dt / T;
+    const int t = (int)(dt % T), h = c8 >> 3;
+    const uint4 v = *reinterpret_cast<const uint4*>(full + (size_t)(doc * Mp + t * H + h) * (H * 64) + c8 * 8);
+    *reinterpret_cast<uint4*>(ctx + (size_t)dt * ld_ctx + c8 * 8) = v;
+  }
+}
+
+}  // namespace
+
+int pn_t5_cross_expand_q(const __nv_bfloat16* q, int ld_q, int64_t docs, int T, int H, int Mp, __nv_bfloat16* qexp,
+                         cudaStream_t st) {
+  if (docs == 0) return PN_OK;
+  cross_expand_q_kernel<<<pn_grid(docs * Mp * H * 8, 256, 1, 8), 256, 0, st>>>(q, ld_q, docs, T, H, Mp, qexp);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+int pn_t5_cross_softmax(const float* scores, int lds, const float* rs, int64_t docs, int S, int TH, int Mp,
+                        __nv_bfloat16* P, cudaStream_t st) {
+  if (docs == 0) return PN_OK;
+  if (Mp > 32 || TH > Mp) return pn_fail(PN_E_UNSUPPORTED, "cross softmax: T*H=%d > 32", TH);
+  cross_softmax_kernel<<<(unsigned)docs, 256, 0, st>>>(scores, lds, rs, S, TH, Mp, P);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+int pn_t5_cross_gather(const __nv_bfloat16* full, int Mp, int64_t docs, int T, int H, __nv_bfloat16* ctx, int ld_ctx,
+                       cudaStream_t st) {
+  if (docs == 0) return PN_OK;
+  cross_gather_kernel<<<pn_grid(docs * T * H * 8, 256, 1, 8), 256, 0, st>>>(full, Mp, docs, T, H, ctx, ld_ctx);
+  PN_LAUNCHED();
+  return PN_OK;
+}

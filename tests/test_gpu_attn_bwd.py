@@ -75,8 +75,8 @@ def test_self_attention_backward_vs_autograd(docs, S, H, with_scale):
 @pytest.mark.parametrize("docs,S,H,DC", [(3, 512, 2, 91), (2, 384, 4, 128), (1, 200, 2, 60), (5, 512, 12, 91),
                                          (2, 512, 1, 300)])
 def test_self_attention_backward_saturated_bias(docs, S, H, DC):
-    """bias_const_dist: tiles wholly beyond the bucket saturation distance skip the bias table and the per-diagonal
-    reduction (T5: 91 for 32 buckets / max_distance 128)."""
+    """T5-shaped bias tables (one value per side beyond the bucket saturation distance, 91 for 32 buckets /
+    max_distance 128): the saturated regions are a single parameter each, so their gradient is compared as a sum."""
     from pacednegatives_b200 import _lib
     _lib.require_gpu()
     run_case(docs, S, H, True, seed=docs * 1000 + S + H + DC, DC=DC)
