@@ -50,7 +50,7 @@ int64_t pn_launch_count(void);
 /* Per-kernel-class device timing for bench.py's roofline object: when enabled, every launch of a
  * class is bracketed by CUDA events on its own stream.  kind 0 = tcgen05 GEMM (work = 2MNK flops),
  * 1 = encoder self-attention (work = 4*S*S*64 flops per (doc, head)), 2 = elementwise, 3 = wgrad GEMM,
- * 4 = attention backward.  pn_prof_read waits for outstanding events and returns the sums since the last
+ * 4 = attention backward, 5 = HBM-bound GEMM launches (< 200 FLOP per byte of operands + output; work = those bytes).  pn_prof_read waits for outstanding events and returns the sums since the last
  * pn_prof_enable(1). */
 int pn_prof_enable(int on);
 int pn_prof_read(int kind, double* ms_sum, int64_t* launches, double* work_sum);

@@ -47,6 +47,7 @@ static inline void pn_count_launch() { g_pn_launches.fetch_add(1, std::memory_or
 // ---- per-kernel-class device timing (pn_prof_*, pn_api.cu): CUDA events recorded on the launching
 // stream around a launch when profiling is enabled; bench.py reads the sums for its roofline object.
 enum { PN_PROF_GEMM = 0, PN_PROF_ATTN = 1, PN_PROF_ELEMWISE = 2, PN_PROF_WGRAD = 3, PN_PROF_ATTN_BWD = 4,
+       PN_PROF_GEMM_HBM = 5,   // GEMM launches whose operands + output outweigh their FLOPs (work = bytes)
        PN_PROF_KINDS = 8 };
 extern std::atomic<int> g_pn_prof_on;
 void pn_prof_begin_impl(int kind, double work, cudaStream_t st);

@@ -134,8 +134,7 @@ int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& 
   // Cross-attention: with T <= 2 decoder tokens the K/V projection of all S encoder rows is replaced by
   // scores = X (Wk^T q) and out = Wv (P^T X) (pn_t5_ops.cu); needs whole GEMM tiles per document.
   const int TH = T * H, Mp = (TH + 7) & ~7;
-  static const bool xattn_off = getenv("PN_XATTN_OFF") != nullptr;
-  const bool xattn = !xattn_off && (S % 128) == 0 && Mp <= 32;
+  const bool xattn = m->xattn && (S % 128) == 0 && Mp <= 32;
   const int R = (int)docs * Mp;
   if (xattn) RC(pn_t5_rs(w.ss, enc_parts, rows, d, m->cfg.eps, w.rs_enc, st));
   int cur_parts = 1;
@@ -354,6 +353,10 @@ extern "C" int pn_t5_set_option(PnT5* m, const char* name, int64_t value) {
   if (!strcmp(name, "cta_group")) {
     PN_CHECK_ARG(value == 1 || value == 2);
     m->cta_group = (int)value;
+    return PN_OK;
+  }
+  if (!strcmp(name, "xattn")) {   // 0: always project the encoder states to K/V for the cross-attention
+    m->xattn = value != 0;
     return PN_OK;
   }
   if (!strcmp(name, "train")) {   // must precede the first pn_t5_load_weight: also keeps transposed operands

@@ -484,7 +484,15 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  PnProfScope prof(kTN ? PN_PROF_WGRAD : PN_PROF_GEMM, 2.0 * args.M * args.N * args.K, st);
+  // launches below ~200 FLOP per byte of compulsory traffic (skinny products, the fp32 residual read-modify-write
+  // of the narrow output projections) are HBM-bound: they are timed as their own class with bytes as the work
+  const double flops = 2.0 * args.M * args.N * args.K;
+  const double out_b = args.mode == PN_EPI_BF16 ? 2.0 : (args.mode == PN_EPI_RESID_F32 ? 8.0 : 4.0);
+  const double bytes = 2.0 * ((double)args.M * args.K + (double)(args.group_rows > 0 ? args.M / args.group_rows : 1) *
+                                                            args.N * args.K) +
+                       (double)args.M * args.N * (out_b + (args.copy_out ? 2.0 : 0.0) + (args.mask ? 2.0 : 0.0));
+  const bool hbm_bound = flops < 200.0 * bytes;
+  PnProfScope prof(hbm_bound ? PN_PROF_GEMM_HBM : (kTN ? PN_PROF_WGRAD : PN_PROF_GEMM), hbm_bound ? bytes : flops, st);
   PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, args));
   g_pn_launches.fetch_add(1, std::memory_order_relaxed);
   return PN_OK;

@@ -69,6 +69,7 @@ struct PnT5 {
   float *dec_bias = nullptr;                     // [heads, 2, 2] for T <= 2
   std::map<const void*, std::array<int64_t, 3>> fwd_ws;   // training workspaces holding a forward pass: docs, S, T
   bool finalized = false;
+  bool xattn = true;                 // projection-free cross-attention where the shapes allow ("xattn" option)
   bool want_train = false;           // also keep packedT / embT (pn_t5_set_option "train")
   int cta_group = 2;
 };
@@ -104,6 +105,11 @@ int pn_t5_cross_softmax(const float* scores, int lds, const float* rs, int64_t d
                         __nv_bfloat16* P, cudaStream_t st);
 int pn_t5_cross_gather(const __nv_bfloat16* full, int Mp, int64_t docs, int T, int H, __nv_bfloat16* ctx, int ld_ctx,
                        cudaStream_t st);
+
+int pn_t5_cross_softmax_bwd(const __nv_bfloat16* Pp, const float* dP, int ldd, const float* rs, int64_t docs, int S,
+                            int TH, int Mp, __nv_bfloat16* U, int ldu, int u_col, __nv_bfloat16* V2, cudaStream_t st);
+int pn_t5_cross_bt_pack(const __nv_bfloat16* dC, const __nv_bfloat16* QK, int64_t docs, int d, int Mp,
+                        __nv_bfloat16* BT, int ldb, int k_col, cudaStream_t st);
 
 // pn_t5.cu: (re)build every packed bf16 operand and the expanded bias tables from the flat fp32 parameters
 int pn_t5_repack(PnT5* m, cudaStream_t st);

@@ -353,3 +353,100 @@ int pn_t5_cross_gather(const __nv_bfloat16* full, int Mp, int64_t docs, int T, i
   PN_LAUNCHED();
   return PN_OK;
 }
+
+// ---- backward pieces of the projection-free cross-attention (training, pn_t5_train.cu)
+namespace {
+
+// Per document: P = Pp / rs (Pp is what cross_softmax_kernel stored), dSc = P (.) (dP - sum_j P dP).
+//   U[row, u_col + th]      = P     (value path:  d x_hat += P  . dC')
+//   U[row, u_col + Mp + th] = dSc   (score path:  d x_hat += dSc . QK),   columns up to 64 zero
+//   V2[row, th]             = rs * dSc            (d QK = V2^T X)
+__global__ void __launch_bounds__(256)
+cross_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ Pp, const float* __restrict__ dP, int ldd,
+                         const float* __restrict__ rs, int S, int TH, int Mp, __nv_bfloat16* __restrict__ U, int ldu,
+                         int u_col, __nv_bfloat16* __restrict__ V2) {
+  __shared__ float red[8][32];
+  __shared__ float stat[32];
+  const int64_t row0 = (int64_t)blockIdx.x * S;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int th = lane;
+  const bool act = th < TH;
+  float p[64], g[64];
+  float dot = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 64; ++i) {
+    const int j = warp + 8 * i;
+    p[i] = 0.0f; g[i] = 0.0f;
+    if (act && j < S) {
+      const float r = rs[row0 + j];
+      p[i] = __bfloat162float(Pp[(size_t)(row0 + j) * Mp + th]) / r;
+      g[i] = dP[(size_t)(row0 + j) * ldd + th];
+      dot += p[i] * g[i];
+    }
+  }
+  red[warp][lane] = dot;
+  __syncthreads();
+  if (warp == 0) {
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][lane];
+    stat[lane] = t;
+  }
+  __syncthreads();
+  dot = stat[lane];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) {
+    const int j = warp + 8 * i;
+    if (j < S) {
+      const float ds = p[i] * (g[i] - dot);
+      __nv_bfloat16* urow = U + (size_t)(row0 + j) * ldu + u_col;
+      if (th < Mp) {
+        urow[th] = __float2bfloat16_rn(p[i]);
+        urow[Mp + th] = __float2bfloat16_rn(ds);
+        V2[(size_t)(row0 + j) * Mp + th] = __float2bfloat16_rn(act ? ds * rs[row0 + j] : 0.0f);
+      }
+      for (int c = 2 * Mp + th; c < 64; c += 32) urow[c] = __float2bfloat16_rn(0.0f);
+    }
+  }
+}
+
+// BT[doc*d + n, k_col + k] = k < Mp ? dC[doc*Mp + k, n] : (k < 2*Mp ? QK[doc*Mp + k - Mp, n] : 0),  k in [0, 64)
+__global__ void __launch_bounds__(256)
+cross_bt_pack_kernel(const __nv_bfloat16* __restrict__ dC, const __nv_bfloat16* __restrict__ QK, int64_t docs, int d,
+                     int Mp, __nv_bfloat16* __restrict__ BT, int ldb, int k_col) {
+  const int64_t n_items = docs * d;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n_items; i += (int64_t)gridDim.x * 256) {
+    const int n = (int)(i % d);
+    const int64_t doc = i / d;
+    __nv_bfloat16 v[64];
+#pragma unroll
+    for (int k = 0; k < 64; ++k) {
+      __nv_bfloat16 x = __float2bfloat16_rn(0.0f);
+      if (k < Mp) x = dC[(size_t)(doc * Mp + k) * d + n];
+      else if (k < 2 * Mp) x = QK[(size_t)(doc * Mp + k - Mp) * d + n];
+      v[k] = x;
+    }
+    uint4* dst = reinterpret_cast<uint4*>(BT + (size_t)i * ldb + k_col);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) dst[c] = reinterpret_cast<const uint4*>(v)[c];
+  }
+}
+
+}  // namespace
+
+int pn_t5_cross_softmax_bwd(const __nv_bfloat16* Pp, const float* dP, int ldd, const float* rs, int64_t docs, int S,
+                            int TH, int Mp, __nv_bfloat16* U, int ldu, int u_col, __nv_bfloat16* V2, cudaStream_t st) {
+  if (docs == 0) return PN_OK;
+  if (2 * Mp > 64 || TH > Mp) return pn_fail(PN_E_UNSUPPORTED, "cross softmax backward: T*H=%d > 32", TH);
+  cross_softmax_bwd_kernel<<<(unsigned)docs, 256, 0, st>>>(Pp, dP, ldd, rs, S, TH, Mp, U, ldu, u_col, V2);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+int pn_t5_cross_bt_pack(const __nv_bfloat16* dC, const __nv_bfloat16* QK, int64_t docs, int d, int Mp,
+                        __nv_bfloat16* BT, int ldb, int k_col, cudaStream_t st) {
+  if (docs == 0) return PN_OK;
+  if ((ldb % 8) || (k_col % 8)) return pn_fail(PN_E_BADARG, "cross bt pack: ldb / k_col must be multiples of 8");
+  cross_bt_pack_kernel<<<pn_grid(docs * d, 256, 1, 8), 256, 0, st>>>(dC, QK, docs, d, Mp, BT, ldb, k_col);
+  PN_LAUNCHED();
+  return PN_OK;
+}

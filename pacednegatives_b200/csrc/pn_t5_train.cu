@@ -10,7 +10,8 @@
 //   qkv[l] bf16 [rows, 3*di],  lse[l] fp32 [rows, H] (base-2 logsumexp),  ctx[l] bf16 [rows, di],
 //   act[l] bf16 [rows, ff] (post-ReLU)
 // plus hb[2L], rs[2L] (encoder output before its final norm, which is folded into the cross K/V projections) and,
-// per decoder layer, ckv[l] bf16 [rows, 2*di] and the decoder-row (docs*T) analogues.  Nothing [S, S]-sized is
+// per decoder layer, the cross-attention operands (QK, P, C' of the projection-free form, or ckv[l] bf16
+// [rows, 2*di] when the shapes rule it out) and the decoder-row (docs*T) analogues.  Nothing [S, S]-sized is
 // kept: the attention backward recomputes the probabilities from lse.
 //
 // Backward per linear y = rs * (hb W'^T) (see pn_t5_train_ops.cu for the algebra): one weight-gradient GEMM
@@ -45,6 +46,12 @@ struct TrainWs {
   __nv_bfloat16* head_in;
   float *ddH, *dgbuf;
   __nv_bfloat16 *ddHb, *ddbig, *ddctx, *dlb;
+  // projection-free cross-attention (pn_t5_ops.cu): R = docs*Mp rows, Mp = T*H rounded up to 8
+  bool xattn;
+  int Mp;
+  std::vector<__nv_bfloat16*> qk, Pp, cpb;   // per decoder layer: QK [R, d], P*rs [rows, Mp], C' [R, d]
+  float *scores, *cprime;                   // [rows, 128], [R, d]
+  __nv_bfloat16 *qexp, *ctxfull, *dOfull, *dCp, *V2, *dQKb, *A_all, *B_all;
   int64_t* header;   // reserved
 };
 
@@ -67,7 +74,27 @@ size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, Tra
   for (auto& p : w->ctx) p = (__nv_bfloat16*)take(rows * di * 2);
   for (auto& p : w->act) p = (__nv_bfloat16*)take(rows * ff * 2);
   for (auto& p : w->lse) p = (float*)take(rows * H * 4);
-  for (auto& p : w->ckv) p = (__nv_bfloat16*)take(rows * 2 * di * 2);
+  w->Mp = (T * H + 7) & ~7;
+  w->xattn = m->xattn && (S % 128) == 0 && w->Mp <= 32;
+  const size_t Mp = (size_t)w->Mp, R = (size_t)docs * Mp;
+  if (!w->xattn) {
+    for (auto& p : w->ckv) p = (__nv_bfloat16*)take(rows * 2 * di * 2);
+  } else {
+    w->qk.resize(Ld); w->Pp.resize(Ld); w->cpb.resize(Ld);
+    for (auto& p : w->qk) p = (__nv_bfloat16*)take(R * d * 2);
+    for (auto& p : w->Pp) p = (__nv_bfloat16*)take(rows * Mp * 2);
+    for (auto& p : w->cpb) p = (__nv_bfloat16*)take(R * d * 2);
+    w->scores = (float*)take(rows * 128 * 4);
+    w->cprime = (float*)take(R * d * 4);
+    w->qexp = (__nv_bfloat16*)take(R * di * 2);
+    w->ctxfull = (__nv_bfloat16*)take(R * di * 2);
+    w->dOfull = (__nv_bfloat16*)take(R * di * 2);
+    w->dCp = (__nv_bfloat16*)take(R * d * 2);
+    w->V2 = (__nv_bfloat16*)take(rows * Mp * 2);
+    w->dQKb = (__nv_bfloat16*)take(R * d * 2);
+    w->A_all = (__nv_bfloat16*)take(rows * 64 * Ld * 2);
+    w->B_all = (__nv_bfloat16*)take((size_t)docs * d * 64 * Ld * 2);
+  }
   w->dH = (float*)take(rows * d * 4);
   w->gbuf = (float*)take(rows * d * 4);
   w->dvec = (float*)take(rows * H * 4);
@@ -216,9 +243,28 @@ extern "C" int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* l
                       m->dec_bias, w.dctx_s[l], di, st));
     RC(lin_resid(m, w.dctx_s[l], D.wo, w.dec_hidden, w.dhb[3 * l + 1], w.dss, w.drs[3 * l + 1], drows, st));
     RC(lin_fwd(m, w.dhb[3 * l + 1], w.drs[3 * l + 1], D.cq, w.cq[l], drows, 0, st));
-    RC(lin_fwd(m, w.hb[2 * L], w.rs[2 * L], D.ckv, w.ckv[l], rows, 0, st));
-    RC(pn_t5_dec_attn(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
-                      w.dctx_c[l], di, st));
+    if (w.xattn) {
+      // scores = X (Wk^T q), out = Wv (P^T X): no K/V projection of the encoder rows (pn_t5_ops.cu)
+      const int Mp = w.Mp, R = (int)docs * Mp;
+      RC(pn_t5_cross_expand_q(w.cq[l], di, docs, T, H, Mp, w.qexp, st));
+      RC(pn_gemm_bf16_internal(w.qexp, di, D.ckv.packedT, 2 * di, w.qk[l], d, R, d, di, PN_EPI_BF16, 0, nullptr,
+                               m->cta_group, st));
+      PnGemmExtra ex = {};
+      ex.row_scale = w.rs[2 * L]; ex.group_rows = S; ex.group_b_rows = Mp;
+      RC(pn_gemm_bf16_ex(w.hb[2 * L], d, w.qk[l], d, w.scores, 128, rows, 128, d, PN_EPI_F32, 0, &ex,
+                         (S % 256) == 0 ? 2 : 1, st));
+      RC(pn_t5_cross_softmax(w.scores, 128, w.rs[2 * L], docs, S, T * H, Mp, w.Pp[l], st));
+      PN_CUDA(cudaMemsetAsync(w.cprime, 0, (size_t)R * d * 4, st));
+      RC(pn_gemm_tn_batched(w.Pp[l], Mp, w.hb[2 * L], d, w.cprime, d, Mp, d, S, (int)docs, st));
+      RC(pn_t5_f32_to_bf16(w.cprime, w.cpb[l], (int64_t)R * d, st));
+      RC(pn_gemm_bf16_internal(w.cpb[l], d, D.ckv.packed + (size_t)di * d, d, w.ctxfull, di, R, di, d, PN_EPI_BF16, 0,
+                               nullptr, m->cta_group, st));
+      RC(pn_t5_cross_gather(w.ctxfull, Mp, docs, T, H, w.dctx_c[l], di, st));
+    } else {
+      RC(lin_fwd(m, w.hb[2 * L], w.rs[2 * L], D.ckv, w.ckv[l], rows, 0, st));
+      RC(pn_t5_dec_attn(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
+                        w.dctx_c[l], di, st));
+    }
     RC(lin_resid(m, w.dctx_c[l], D.co, w.dec_hidden, w.dhb[3 * l + 2], w.dss, w.drs[3 * l + 2], drows, st));
     RC(lin_fwd(m, w.dhb[3 * l + 2], w.drs[3 * l + 2], D.wi, w.dact[l], drows, 1, st));
     RC(lin_resid(m, w.dact[l], D.wo2, w.dec_hidden, w.dhb[3 * l + 3], w.dss, w.drs[3 * l + 3], drows, st));
@@ -281,14 +327,46 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     // cross-attention: h2 = h1 + attn(norm(h1) Cq^T, norm_f(enc) Ckv^T) Co^T
     RC(wgrad_plain(m, w.ddHb, d, w.dctx_c[l], D.co, drows, st));
     RC(dgrad(m, w.ddHb, d, D.co, w.ddctx, PN_EPI_BF16, drows, st));
-    RC(pn_t5_dec_attn_bwd(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, w.ddctx, di, (int)docs, T, S, H, 0,
-                          nullptr, rs1, w.rs[2 * L], w.ddbig, di, 0, w.dbig, 2 * di, 0, di, nullptr, st));
+    if (w.xattn) {
+      const int Mp = w.Mp, R = (int)docs * Mp, ldall = 64 * Ld;
+      const float* rsE = w.rs[2 * L];
+      const __nv_bfloat16* X = w.hb[2 * L];
+      // d out (head blocks back on the diagonal) -> dWv' = dO^T C',  dC' = dO Wv'
+      RC(pn_t5_cross_expand_q(w.ddctx, di, docs, T, H, Mp, w.dOfull, st));
+      PN_CUDA(cudaMemsetAsync(w.dWtmp, 0, (size_t)2 * di * d * 4, st));
+      RC(pn_gemm_wgrad(w.dOfull, di, w.cpb[l], d, w.dWtmp + (size_t)di * d, d, di, d, R, m->cta_group, st));
+      RC(pn_gemm_bf16_internal(w.dOfull, di, D.ckv.packedT + di, 2 * di, w.dCp, d, R, d, di, PN_EPI_BF16, 0, nullptr,
+                               m->cta_group, st));
+      // dP[row, (t,h)] = rs[row] * (x_row . dC'[doc, (t,h)])  (same block-diagonal product as the scores)
+      PnGemmExtra ex = {};
+      ex.row_scale = rsE; ex.group_rows = S; ex.group_b_rows = Mp;
+      RC(pn_gemm_bf16_ex(X, d, w.dCp, d, w.scores, 128, rows, 128, d, PN_EPI_F32, 0, &ex, (S % 256) == 0 ? 2 : 1, st));
+      // softmax backward; its outputs and [dC'; QK] become column block l of the operands of ONE product over
+      // all layers that yields the gradient of the normalised encoder states (after the loop)
+      RC(pn_t5_cross_softmax_bwd(w.Pp[l], w.scores, 128, rsE, docs, S, T * H, Mp, w.A_all, ldall, 64 * l, w.V2, st));
+      RC(pn_t5_cross_bt_pack(w.dCp, w.qk[l], docs, d, Mp, w.B_all, ldall, 64 * l, st));
+      // dQK = (rs dSc)^T X -> dWk' = Qexp^T dQK,  dQexp = dQK Wk'^T -> dq (head blocks), scaled for the fused norm
+      PN_CUDA(cudaMemsetAsync(w.cprime, 0, (size_t)R * d * 4, st));
+      RC(pn_gemm_tn_batched(w.V2, Mp, X, d, w.cprime, d, Mp, d, S, (int)docs, st));
+      RC(pn_t5_f32_to_bf16(w.cprime, w.dQKb, (int64_t)R * d, st));
+      RC(pn_t5_cross_expand_q(w.cq[l], di, docs, T, H, Mp, w.qexp, st));
+      RC(pn_gemm_wgrad(w.qexp, di, w.dQKb, d, w.dWtmp, d, di, d, R, m->cta_group, st));
+      RC(pn_t5_unfold(w.dWtmp, D.ckv.master, D.ckv.fold, D.ckv.rows, D.ckv.cols, G + D.ckv.off, G + D.ckv.fold_off,
+                      st));
+      RC(pn_gemm_bf16_internal(w.dQKb, d, D.ckv.packed, d, w.ctxfull, di, R, di, d, PN_EPI_BF16, 0, nullptr,
+                               m->cta_group, st));
+      RC(pn_t5_cross_gather(w.ctxfull, Mp, docs, T, H, w.ddbig, di, st));
+      RC(pn_t5_row_scale(w.ddbig, di, rs1, drows, di, st));
+    } else {
+      RC(pn_t5_dec_attn_bwd(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, w.ddctx, di, (int)docs, T, S, H, 0,
+                            nullptr, rs1, w.rs[2 * L], w.ddbig, di, 0, w.dbig, 2 * di, 0, di, nullptr, st));
+      RC(wgrad_folded(m, w.dbig, 2 * di, w.hb[2 * L], D.ckv, w.dWtmp, rows, st));
+      // every decoder layer reads the same normalised encoder output: their data gradients add up in `hidden`
+      RC(dgrad(m, w.dbig, 2 * di, D.ckv, w.hidden, l == Ld - 1 ? PN_EPI_F32 : PN_EPI_RESID_F32, rows, st));
+    }
     RC(wgrad_folded(m, w.ddbig, di, hb1, D.cq, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, di, D.cq, w.dgbuf, PN_EPI_F32, drows, st));
     RC(pn_t5_norm_bwd(w.dgbuf, hb1, rs1, drows, d, 1, w.ddH, w.ddHb, st));
-    RC(wgrad_folded(m, w.dbig, 2 * di, w.hb[2 * L], D.ckv, w.dWtmp, rows, st));
-    // every decoder layer reads the same normalised encoder output: their data gradients add up in `hidden`
-    RC(dgrad(m, w.dbig, 2 * di, D.ckv, w.hidden, l == Ld - 1 ? PN_EPI_F32 : PN_EPI_RESID_F32, rows, st));
     // self-attention: h1 = h0 + attn(norm(h0) Wqkv^T) Wo^T
     RC(wgrad_plain(m, w.ddHb, d, w.dctx_s[l], D.wo, drows, st));
     RC(dgrad(m, w.ddHb, d, D.wo, w.ddctx, PN_EPI_BF16, drows, st));
@@ -300,6 +378,14 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     RC(pn_t5_norm_bwd(w.dgbuf, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st));
   }
   RC(pn_t5_embed_bwd(w.dec_ids, w.ddH, drows, d, m->cfg.vocab, G + m->emb_off, st));
+  if (w.xattn) {
+    // G = rs (.) ([P | dSc]_all-layers . [dC'; QK]_all-layers): every layer's cross-attention gradient of the
+    // normalised encoder states in one block-diagonal GEMM (K = 64 per layer)
+    PnGemmExtra ex = {};
+    ex.row_scale = w.rs[2 * L]; ex.group_rows = S; ex.group_b_rows = d;
+    RC(pn_gemm_bf16_ex(w.A_all, 64 * Ld, w.B_all, 64 * Ld, w.hidden, d, rows, d, 64 * Ld, PN_EPI_F32, 0, &ex,
+                       (S % 256) == 0 ? 2 : 1, st));
+  }
 
   // ---- encoder: the final norm (folded into every Ckv), then the layers last to first
   RC(pn_t5_norm_bwd(w.hidden, w.hb[2 * L], w.rs[2 * L], rows, d, 0, w.dH, w.dHb, st));

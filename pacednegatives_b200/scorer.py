@@ -92,7 +92,7 @@ class MonoT5Scorer:
     """dims: T5Dims; state_dict: {hf_name: tensor} (any float dtype, CPU or CUDA)."""
 
     def __init__(self, dims, state_dict, rel_id=REL_ID, nrel_id=NREL_ID, chunk_docs=128, cta_group=2,
-                 train=False):
+                 train=False, xattn=True):
         _lib.require_gpu()
         self.dims, self.rel_id, self.nrel_id = dims, int(rel_id), int(nrel_id)
         self.chunk_docs = int(chunk_docs)
@@ -103,6 +103,8 @@ class MonoT5Scorer:
         _lib.check(lib.pn_t5_create(C.byref(cfg), C.byref(h)))
         self._h = h
         _lib.check(lib.pn_t5_set_option(self._h, b"cta_group", cta_group))
+        # xattn: cross-attention as X (Wk^T q) / Wv (P^T X) instead of projecting every encoder row to K and V
+        _lib.check(lib.pn_t5_set_option(self._h, b"xattn", int(bool(xattn))))
         if train:   # also keep the transposed operands of the data-gradient GEMMs (must precede the weights)
             _lib.check(lib.pn_t5_set_option(self._h, b"train", 1))
         for name, t in state_dict.items():

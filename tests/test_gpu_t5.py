@@ -71,9 +71,11 @@ def test_score_tiny_golden(golden_dir, cta_group):
 
 
 @pytest.mark.parametrize("S", [128, 200, 512])
-def test_score_small_vs_oracle(S):
+@pytest.mark.parametrize("xattn", [True, False])
+def test_score_small_vs_oracle(S, xattn):
+    """xattn: cross-attention as X (Wk^T q) / Wv (P^T X) (S % 128 == 0) vs the K/V projection of every encoder row."""
     dims = ot.T5Dims(vocab=1024, d_model=256, d_kv=64, d_ff=512, n_layers=3, n_dec_layers=3, n_heads=4)
-    w, m = make(dims, 3, rel_id=17, nrel_id=23, chunk_docs=4)
+    w, m = make(dims, 3, rel_id=17, nrel_id=23, chunk_docs=4, xattn=xattn)
     ids = rand_ids(np.random.RandomState(S), 6, S, dims.vocab)   # 6 docs, chunks of 4: ragged last chunk
     s, z2 = m.score(ids, return_z2=True)
     es, ez = ot.score(w, dims, ids, 17, 23)

@@ -26,14 +26,14 @@ def load_case(golden_dir):
     return g, dims, hp, batch
 
 
-@pytest.mark.parametrize("elide", [True, False])
-def test_training_step_vs_reference_golden(golden_dir, elide):
+@pytest.mark.parametrize("elide,xattn", [(True, True), (False, True), (True, False)])
+def test_training_step_vs_reference_golden(golden_dir, elide, xattn):
     from pacednegatives_b200.lceT5 import LCEModel
     from pacednegatives_b200.scorer import T5Dims
     g, dims, hp, batch = load_case(golden_dir)
     w = ot.init_weights(dims, seed=int(g["seed"]))
     m = LCEModel(hp, dims=T5Dims(**dims.__dict__), state_dict={k: torch.as_tensor(v) for k, v in w.items()},
-                 elide_no_grad_forward=elide)
+                 elide_no_grad_forward=elide, xattn=xattn)
     out = m.training_step(batch, 0)
     assert abs(float(out["main_loss"].detach()) - float(g["main_loss0"])) < 2e-2
     assert abs(float(out["meta_loss"]) - float(g["meta_loss0"])) < 2e-2
