@@ -631,7 +631,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="rerank", choices=["rerank", "train", "select"])
     ap.add_argument("--queries-per-step", type=int, default=4)
-    ap.add_argument("--chunk-docs", type=int, default=250)
+    ap.add_argument("--chunk-docs", type=int, default=1000)
     ap.add_argument("--cta-group", type=int, default=2)
     ap.add_argument("--cpu-sample-docs", type=int, default=32)
     ap.add_argument("--ref-docs-per-step", type=int, default=16)

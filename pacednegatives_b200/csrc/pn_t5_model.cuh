@@ -119,8 +119,8 @@ int pn_t5_rs(const float* ss, int parts, int64_t rows, int d, float eps, float* 
 int pn_t5_relu_mask_scale(__nv_bfloat16* y, const __nv_bfloat16* act, const float* rs, int64_t rows, int cols,
                           cudaStream_t st);
 int pn_t5_row_scale(__nv_bfloat16* y, int ld, const float* rs, int64_t rows, int cols, cudaStream_t st);
-int pn_t5_norm_bwd(const float* G, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d, int accumulate,
-                   float* dh, __nv_bfloat16* dhb, cudaStream_t st);
+int pn_t5_norm_bwd(const void* G, int g_bf16, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d,
+                   int accumulate, float* dh, __nv_bfloat16* dhb, cudaStream_t st);
 int pn_t5_unfold(const float* dWp, const float* W, const float* g, int64_t rows, int cols, float* gradW,
                  float* gradg, cudaStream_t st);
 int pn_t5_embed_bwd(const int32_t* ids, const float* dh, int64_t rows, int d, int vocab, float* grad_table,

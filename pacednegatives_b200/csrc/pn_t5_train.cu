@@ -323,7 +323,7 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     RC(dgrad_relu(m, w.ddHb, D.wo2, w.dact[l], rs2, w.ddbig, drows, st));
     RC(wgrad_folded(m, w.ddbig, ff, hb2, D.wi, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, ff, D.wi, w.dgbuf, PN_EPI_F32, drows, st));
-    RC(pn_t5_norm_bwd(w.dgbuf, hb2, rs2, drows, d, 1, w.ddH, w.ddHb, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb2, rs2, drows, d, 1, w.ddH, w.ddHb, st));
     // cross-attention: h2 = h1 + attn(norm(h1) Cq^T, norm_f(enc) Ckv^T) Co^T
     RC(wgrad_plain(m, w.ddHb, d, w.dctx_c[l], D.co, drows, st));
     RC(dgrad(m, w.ddHb, d, D.co, w.ddctx, PN_EPI_BF16, drows, st));
@@ -366,7 +366,7 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     }
     RC(wgrad_folded(m, w.ddbig, di, hb1, D.cq, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, di, D.cq, w.dgbuf, PN_EPI_F32, drows, st));
-    RC(pn_t5_norm_bwd(w.dgbuf, hb1, rs1, drows, d, 1, w.ddH, w.ddHb, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb1, rs1, drows, d, 1, w.ddH, w.ddHb, st));
     // self-attention: h1 = h0 + attn(norm(h0) Wqkv^T) Wo^T
     RC(wgrad_plain(m, w.ddHb, d, w.dctx_s[l], D.wo, drows, st));
     RC(dgrad(m, w.ddHb, d, D.wo, w.ddctx, PN_EPI_BF16, drows, st));
@@ -375,7 +375,7 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
                           G + m->dec_rel_off, st));
     RC(wgrad_folded(m, w.ddbig, 3 * di, hb0, D.wqkv, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, 3 * di, D.wqkv, w.dgbuf, PN_EPI_F32, drows, st));
-    RC(pn_t5_norm_bwd(w.dgbuf, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st));
   }
   RC(pn_t5_embed_bwd(w.dec_ids, w.ddH, drows, d, m->cfg.vocab, G + m->emb_off, st));
   if (w.xattn) {
@@ -388,7 +388,7 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
   }
 
   // ---- encoder: the final norm (folded into every Ckv), then the layers last to first
-  RC(pn_t5_norm_bwd(w.hidden, w.hb[2 * L], w.rs[2 * L], rows, d, 0, w.dH, w.dHb, st));
+  RC(pn_t5_norm_bwd(w.hidden, 0, w.hb[2 * L], w.rs[2 * L], rows, d, 0, w.dH, w.dHb, st));
   PN_CUDA(cudaMemsetAsync(w.diag, 0, (size_t)H * 1023 * 4, st));
   for (int l = L - 1; l >= 0; --l) {
     const PnEncLayer& E = m->enc[l];
@@ -398,14 +398,14 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     RC(dgrad_relu(m, w.dHb, E.wo2, w.act[l], rs1, w.dbig, rows, st));
     RC(wgrad_folded(m, w.dbig, ff, hb1, E.wi, w.dWtmp, rows, st));
     RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, PN_EPI_F32, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, hb1, rs1, rows, d, 1, w.dH, w.dHb, st));
+    RC(pn_t5_norm_bwd(w.gbuf, 0, hb1, rs1, rows, d, 1, w.dH, w.dHb, st));
     RC(wgrad_plain(m, w.dHb, d, w.ctx[l], E.wo, rows, st));
     RC(dgrad(m, w.dHb, d, E.wo, w.dctx, PN_EPI_BF16, rows, st));
     RC(pn_t5_self_attn_bwd(w.qkv[l], 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx[l], w.dctx, di,
                            w.lse[l], w.dvec, rs0, w.dbig, w.diag, st));
     RC(wgrad_folded(m, w.dbig, 3 * di, hb0, E.wqkv, w.dWtmp, rows, st));
     RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, PN_EPI_F32, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, hb0, rs0, rows, d, 1, w.dH, w.dHb, st));
+    RC(pn_t5_norm_bwd(w.gbuf, 0, hb0, rs0, rows, d, 1, w.dH, w.dHb, st));
   }
   RC(pn_t5_embed_bwd(ids, w.dH, rows, d, m->cfg.vocab, G + m->emb_off, st));
   RC(pn_t5_rel_bias_grad(w.diag, bucket_of, H, m->cfg.rel_buckets, G + m->enc_rel_off, st));

@@ -70,10 +70,12 @@ row_scale_kernel(__nv_bfloat16* __restrict__ y, int ld, const float* __restrict_
 
 // Fused-norm backward, one warp per row:  dh[r,:] (+)= G[r,:] - rs[r]^2 * hb[r,:] * mean_k(G[r,k] hb[r,k]);
 // also refreshes the bf16 copy of dh that the next GEMMs read.  accumulate = 0 overwrites dh.
-template <int MAXV>
+template <int MAXV, bool kG16>
 __global__ void __launch_bounds__(kThreads)
-norm_bwd_kernel(const float* __restrict__ G, const __nv_bfloat16* __restrict__ hb, const float* __restrict__ rs,
+norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ hb, const float* __restrict__ rs,
                 int64_t rows, int d, int accumulate, float* __restrict__ dh, __nv_bfloat16* __restrict__ dhb) {
+  const float* G = reinterpret_cast<const float*>(Gv);
+  const __nv_bfloat16* G16 = reinterpret_cast<const __nv_bfloat16*>(Gv);
   const int lane = threadIdx.x & 31;
   const int64_t wid = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
@@ -85,7 +87,14 @@ norm_bwd_kernel(const float* __restrict__ G, const __nv_bfloat16* __restrict__ h
     for (int i = 0; i < MAXV; ++i) {
       const int c = lane + i * 32;
       if (c < nv) {
-        g[i] = reinterpret_cast<const float4*>(G + (size_t)r * d)[c];
+        if (kG16) {
+          const uint2 gr = reinterpret_cast<const uint2*>(G16 + (size_t)r * d)[c];
+          const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gr.x));
+          const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gr.y));
+          g[i] = make_float4(ga.x, ga.y, gb.x, gb.y);
+        } else {
+          g[i] = reinterpret_cast<const float4*>(G + (size_t)r * d)[c];
+        }
         const uint2 raw = reinterpret_cast<const uint2*>(hb + (size_t)r * d)[c];
         const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
         const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
@@ -235,17 +244,16 @@ int pn_t5_row_scale(__nv_bfloat16* y, int ld, const float* rs, int64_t rows, int
   return PN_OK;
 }
 
-int pn_t5_norm_bwd(const float* G, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d, int accumulate,
-                   float* dh, __nv_bfloat16* dhb, cudaStream_t st) {
+int pn_t5_norm_bwd(const void* G, int g_bf16, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d,
+                   int accumulate, float* dh, __nv_bfloat16* dhb, cudaStream_t st) {
   if (rows == 0) return PN_OK;
   if (d % 4 || d > 32 * 4 * 16) return pn_fail(PN_E_UNSUPPORTED, "norm_bwd: d_model=%d unsupported", d);
   const int grid = pn_grid(rows * 32, kThreads, 1, 8);
-  if (d <= 32 * 4 * 4)
-    norm_bwd_kernel<4><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb);
-  else if (d <= 32 * 4 * 8)
-    norm_bwd_kernel<8><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb);
-  else
-    norm_bwd_kernel<16><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb);
+#define PN_NB(V, B) norm_bwd_kernel<V, B><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb)
+  if (d <= 32 * 4 * 4) { if (g_bf16) PN_NB(4, true); else PN_NB(4, false); }
+  else if (d <= 32 * 4 * 8) { if (g_bf16) PN_NB(8, true); else PN_NB(8, false); }
+  else { if (g_bf16) PN_NB(16, true); else PN_NB(16, false); }
+#undef PN_NB
   PN_LAUNCHED();
   return PN_OK;
 }
