@@ -361,52 +361,92 @@ namespace {
 //   U[row, u_col + th]      = P     (value path:  d x_hat += P  . dC')
 //   U[row, u_col + Mp + th] = dSc   (score path:  d x_hat += dSc . QK),   columns up to 64 zero
 //   V2[row, th]             = rs * dSc            (d QK = V2^T X)
-__global__ void __launch_bounds__(256)
+// One CTA per document, one thread per encoder row: the Mp values of a row are contiguous in Pp (bf16) and dP (fp32),
+// so every access is a 16-byte vector and a row's 128-byte slice of U is written by one thread.
+template <int MP8>
+__global__ void __launch_bounds__(512)
 cross_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ Pp, const float* __restrict__ dP, int ldd,
-                         const float* __restrict__ rs, int S, int TH, int Mp, __nv_bfloat16* __restrict__ U, int ldu,
+                         const float* __restrict__ rs, int S, int TH, __nv_bfloat16* __restrict__ U, int ldu,
                          int u_col, __nv_bfloat16* __restrict__ V2) {
-  __shared__ float red[8][32];
-  __shared__ float stat[32];
+  constexpr int Mp = MP8 * 8;
+  __shared__ float red[16][Mp];
+  __shared__ float stat[Mp];
   const int64_t row0 = (int64_t)blockIdx.x * S;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int th = lane;
-  const bool act = th < TH;
-  float p[64], g[64];
-  float dot = 0.0f;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float p[Mp], g[Mp], dot[Mp];
+  float r = 1.0f;
+  auto load = [&](int j) {
+    if (j < S) {
+      r = rs[row0 + j];
+      const float inv = 1.0f / r;
 #pragma unroll
-  for (int i = 0; i < 64; ++i) {
-    const int j = warp + 8 * i;
-    p[i] = 0.0f; g[i] = 0.0f;
-    if (act && j < S) {
-      const float r = rs[row0 + j];
-      p[i] = __bfloat162float(Pp[(size_t)(row0 + j) * Mp + th]) / r;
-      g[i] = dP[(size_t)(row0 + j) * ldd + th];
-      dot += p[i] * g[i];
+      for (int c = 0; c < MP8; ++c) {
+        const uint4 raw = reinterpret_cast<const uint4*>(Pp + (size_t)(row0 + j) * Mp)[c];
+        const uint32_t w4[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w4[k]));
+          p[c * 8 + 2 * k] = f.x * inv;
+          p[c * 8 + 2 * k + 1] = f.y * inv;
+        }
+        const float4 g0 = reinterpret_cast<const float4*>(dP + (size_t)(row0 + j) * ldd)[2 * c];
+        const float4 g1 = reinterpret_cast<const float4*>(dP + (size_t)(row0 + j) * ldd)[2 * c + 1];
+        g[c * 8 + 0] = g0.x; g[c * 8 + 1] = g0.y; g[c * 8 + 2] = g0.z; g[c * 8 + 3] = g0.w;
+        g[c * 8 + 4] = g1.x; g[c * 8 + 5] = g1.y; g[c * 8 + 6] = g1.z; g[c * 8 + 7] = g1.w;
+      }
+#pragma unroll
+      for (int c = 0; c < Mp; ++c)
+        if (c >= TH) { p[c] = 0.0f; g[c] = 0.0f; }
+    } else {
+#pragma unroll
+      for (int c = 0; c < Mp; ++c) { p[c] = 0.0f; g[c] = 0.0f; }
     }
+  };
+#pragma unroll
+  for (int c = 0; c < Mp; ++c) dot[c] = 0.0f;
+  for (int j0 = 0; j0 < S; j0 += 512) {
+    load(j0 + tid);
+#pragma unroll
+    for (int c = 0; c < Mp; ++c) dot[c] += p[c] * g[c];
   }
-  red[warp][lane] = dot;
+#pragma unroll
+  for (int c = 0; c < Mp; ++c) {
+    float t = pn_warp_sum(dot[c]);
+    if (lane == 0) red[warp][c] = t;
+  }
   __syncthreads();
-  if (warp == 0) {
+  if (tid < Mp) {
     float t = 0.0f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += red[k][lane];
-    stat[lane] = t;
+    for (int k = 0; k < 16; ++k) t += red[k][tid];
+    stat[tid] = t;
   }
   __syncthreads();
-  dot = stat[lane];
+  for (int j0 = 0; j0 < S; j0 += 512) {
+    const int j = j0 + tid;
+    if (S > 512) load(j);   // a document of at most 512 rows still holds its row in registers
+    if (j >= S) continue;
+    uint4* urow = reinterpret_cast<uint4*>(U + (size_t)(row0 + j) * ldu + u_col);
+    uint4* vrow = reinterpret_cast<uint4*>(V2 + (size_t)(row0 + j) * Mp);
+    uint32_t up[Mp / 2], ud[Mp / 2], uv[Mp / 2];
 #pragma unroll
-  for (int i = 0; i < 64; ++i) {
-    const int j = warp + 8 * i;
-    if (j < S) {
-      const float ds = p[i] * (g[i] - dot);
-      __nv_bfloat16* urow = U + (size_t)(row0 + j) * ldu + u_col;
-      if (th < Mp) {
-        urow[th] = __float2bfloat16_rn(p[i]);
-        urow[Mp + th] = __float2bfloat16_rn(ds);
-        V2[(size_t)(row0 + j) * Mp + th] = __float2bfloat16_rn(act ? ds * rs[row0 + j] : 0.0f);
-      }
-      for (int c = 2 * Mp + th; c < 64; c += 32) urow[c] = __float2bfloat16_rn(0.0f);
+    for (int c = 0; c < Mp; c += 2) {
+      const float d0 = p[c] * (g[c] - stat[c]), d1 = p[c + 1] * (g[c + 1] - stat[c + 1]);
+      __nv_bfloat162 a = __floats2bfloat162_rn(p[c], p[c + 1]);
+      __nv_bfloat162 b = __floats2bfloat162_rn(d0, d1);
+      __nv_bfloat162 e = __floats2bfloat162_rn(d0 * r, d1 * r);
+      up[c / 2] = *reinterpret_cast<uint32_t*>(&a);
+      ud[c / 2] = *reinterpret_cast<uint32_t*>(&b);
+      uv[c / 2] = *reinterpret_cast<uint32_t*>(&e);
     }
+#pragma unroll
+    for (int c = 0; c < MP8; ++c) {
+      urow[c] = make_uint4(up[4 * c], up[4 * c + 1], up[4 * c + 2], up[4 * c + 3]);
+      urow[MP8 + c] = make_uint4(ud[4 * c], ud[4 * c + 1], ud[4 * c + 2], ud[4 * c + 3]);
+      vrow[c] = make_uint4(uv[4 * c], uv[4 * c + 1], uv[4 * c + 2], uv[4 * c + 3]);
+    }
+#pragma unroll
+    for (int c = 2 * MP8; c < 8; ++c) urow[c] = make_uint4(0u, 0u, 0u, 0u);
   }
 }
 
@@ -437,8 +477,17 @@ cross_bt_pack_kernel(const __nv_bfloat16* __restrict__ dC, const __nv_bfloat16* 
 int pn_t5_cross_softmax_bwd(const __nv_bfloat16* Pp, const float* dP, int ldd, const float* rs, int64_t docs, int S,
                             int TH, int Mp, __nv_bfloat16* U, int ldu, int u_col, __nv_bfloat16* V2, cudaStream_t st) {
   if (docs == 0) return PN_OK;
-  if (2 * Mp > 64 || TH > Mp) return pn_fail(PN_E_UNSUPPORTED, "cross softmax backward: T*H=%d > 32", TH);
-  cross_softmax_bwd_kernel<<<(unsigned)docs, 256, 0, st>>>(Pp, dP, ldd, rs, S, TH, Mp, U, ldu, u_col, V2);
+  if (2 * Mp > 64 || TH > Mp || (Mp % 8)) return pn_fail(PN_E_UNSUPPORTED, "cross softmax backward: T*H=%d > 32", TH);
+  if ((ldd % 4) || (ldu % 8) || (u_col % 8))
+    return pn_fail(PN_E_BADARG, "cross softmax backward: ldd %% 4, ldu %% 8, u_col %% 8 must be 0");
+#define PN_CSB(N) cross_softmax_bwd_kernel<N><<<(unsigned)docs, 512, 0, st>>>(Pp, dP, ldd, rs, S, TH, U, ldu, u_col, V2)
+  switch (Mp / 8) {
+    case 1: PN_CSB(1); break;
+    case 2: PN_CSB(2); break;
+    case 3: PN_CSB(3); break;
+    default: PN_CSB(4); break;
+  }
+#undef PN_CSB
   PN_LAUNCHED();
   return PN_OK;
 }

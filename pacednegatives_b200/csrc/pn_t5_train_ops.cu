@@ -81,12 +81,13 @@ norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ h
   const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
   const int nv = d / 4;
   for (int64_t r = wid; r < rows; r += nw) {
-    float4 g[MAXV], h[MAXV];
+    float4 g[MAXV], h[MAXV], pv[MAXV];   // the read half of the dh update is issued with the other loads
     float dot = 0.0f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
       const int c = lane + i * 32;
       if (c < nv) {
+        pv[i] = accumulate ? reinterpret_cast<const float4*>(dh + (size_t)r * d)[c] : make_float4(0.f, 0.f, 0.f, 0.f);
         if (kG16) {
           const uint2 gr = reinterpret_cast<const uint2*>(G16 + (size_t)r * d)[c];
           const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gr.x));
@@ -112,10 +113,7 @@ norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ h
         float4 o;
         o.x = g[i].x - k * h[i].x; o.y = g[i].y - k * h[i].y; o.z = g[i].z - k * h[i].z; o.w = g[i].w - k * h[i].w;
         float4* dst = reinterpret_cast<float4*>(dh + (size_t)r * d) + c;
-        if (accumulate) {
-          const float4 p = *dst;
-          o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
-        }
+        o.x += pv[i].x; o.y += pv[i].y; o.z += pv[i].z; o.w += pv[i].w;
         *dst = o;
         if (dhb) {
           __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
@@ -128,30 +126,45 @@ norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ h
 }
 
 // gradW[n,k] += dWp[n,k] * g[k];  gradg[k] += sum_n dWp[n,k] * W[n,k]   (W = fp32 master, dWp = d W')
-// grid.x tiles the columns (32 per CTA), each CTA walks a slab of rows; one atomic per column per CTA.
+// A CTA owns 128 columns (one float4 per lane) x 32 rows; every load of a thread is independent and issued up front,
+// one atomic per column per CTA.
 __global__ void __launch_bounds__(kThreads)
 unfold_kernel(const float* __restrict__ dWp, const float* __restrict__ W, const float* __restrict__ g,
               int64_t rows, int cols, float* __restrict__ gradW, float* __restrict__ gradg) {
-  __shared__ float red[8][33];
+  __shared__ float4 red[8][32];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int c = blockIdx.x * 32 + tx;
-  const int64_t r0 = (int64_t)blockIdx.y * 256;
-  float acc = 0.0f;
+  const int c = (blockIdx.x * 32 + tx) * 4;
+  const int64_t r0 = (int64_t)blockIdx.y * 32 + ty;
+  float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
   if (c < cols) {
-    const float gc = g[c];
-    for (int64_t r = r0 + ty; r < rows && r < r0 + 256; r += 8) {
-      const float v = dWp[r * cols + c];
-      gradW[r * cols + c] += v * gc;
-      acc += v * W[r * cols + c];
+    const float4 gc = *reinterpret_cast<const float4*>(g + c);
+    float4 v[4], w[4], o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t r = r0 + 8 * i;
+      if (r < rows) {
+        v[i] = *reinterpret_cast<const float4*>(dWp + r * cols + c);
+        w[i] = *reinterpret_cast<const float4*>(W + r * cols + c);
+        o[i] = *reinterpret_cast<const float4*>(gradW + r * cols + c);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t r = r0 + 8 * i;
+      if (r < rows) {
+        o[i].x += v[i].x * gc.x; o[i].y += v[i].y * gc.y; o[i].z += v[i].z * gc.z; o[i].w += v[i].w * gc.w;
+        *reinterpret_cast<float4*>(gradW + r * cols + c) = o[i];
+        acc.x += v[i].x * w[i].x; acc.y += v[i].y * w[i].y; acc.z += v[i].z * w[i].z; acc.w += v[i].w * w[i].w;
+      }
     }
   }
   red[ty][tx] = acc;
   __syncthreads();
-  if (ty == 0 && c < cols) {
+  if (ty < 4 && c < cols) {   // warp ty sums component ty of the 8 partials
     float t = 0.0f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += red[k][tx];
-    atomicAdd(gradg + c, t);
+    for (int k = 0; k < 8; ++k) t += reinterpret_cast<const float*>(&red[k][tx])[ty];
+    atomicAdd(gradg + c + ty, t);
   }
 }
 
@@ -251,6 +264,7 @@ int pn_t5_norm_bwd(const void* G, int g_bf16, const __nv_bfloat16* hb, const flo
   const int grid = pn_grid(rows * 32, kThreads, 1, 8);
 #define PN_NB(V, B) norm_bwd_kernel<V, B><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb)
   if (d <= 32 * 4 * 4) { if (g_bf16) PN_NB(4, true); else PN_NB(4, false); }
+  else if (d <= 32 * 4 * 6) { if (g_bf16) PN_NB(6, true); else PN_NB(6, false); }
   else if (d <= 32 * 4 * 8) { if (g_bf16) PN_NB(8, true); else PN_NB(8, false); }
   else { if (g_bf16) PN_NB(16, true); else PN_NB(16, false); }
 #undef PN_NB
@@ -261,7 +275,10 @@ int pn_t5_norm_bwd(const void* G, int g_bf16, const __nv_bfloat16* hb, const flo
 int pn_t5_unfold(const float* dWp, const float* W, const float* g, int64_t rows, int cols, float* gradW,
                  float* gradg, cudaStream_t st) {
   if (rows * cols == 0) return PN_OK;
-  dim3 grid((cols + 31) / 32, (unsigned)((rows + 255) / 256));
+  if (cols % 4 || ((reinterpret_cast<uintptr_t>(dWp) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(g) |
+                    reinterpret_cast<uintptr_t>(gradW)) & 15))
+    return pn_fail(PN_E_UNSUPPORTED, "unfold: cols %% 4 != 0 or operands not 16-byte aligned");
+  dim3 grid((cols / 4 + 31) / 32, (unsigned)((rows + 31) / 32));
   unfold_kernel<<<grid, kThreads, 0, st>>>(dWp, W, g, rows, cols, gradW, gradg);
   PN_LAUNCHED();
   return PN_OK;
