@@ -89,18 +89,6 @@ class MonoT5Model(MonoT5Scorer):
         out = _ModelFn.apply(self._anchor, self, ids, lab)
         return out[:, :, :self.dims.vocab]
 
-    def named_offsets(self):
-        """[(hf_name, offset, numel)] of the flat parameter / gradient buffers."""
-        import ctypes as C
-        lib = _lib.lib()
-        out = []
-        name = C.create_string_buffer(256)
-        off, numel = C.c_int64(), C.c_int64()
-        for i in range(int(lib.pn_t5_num_tensors(self._h))):
-            _lib.check(lib.pn_t5_tensor_info(self._h, i, name, 256, C.byref(off), C.byref(numel)))
-            out.append((name.value.decode(), off.value, numel.value))
-        return out
-
     def named_grads(self):
         return {n: self.grads[o:o + k] for n, o, k in self.named_offsets()}
 

@@ -6,6 +6,8 @@ re-rank formula of distill/wrapper.py:34-38 / pyterrier_t5.MonoT5ReRanker in eva
 handed over by HuggingFace state_dict name, so a ``save_pretrained`` directory's tensors load as they are.
 """
 import ctypes as C
+import json
+import os
 from dataclasses import dataclass
 
 import torch
@@ -88,6 +90,73 @@ def random_state_dict(dims, seed=0, device="cuda"):
     return w
 
 
+_TIED = ("encoder.embed_tokens.weight", "decoder.embed_tokens.weight", "lm_head.weight")
+
+
+def dims_from_hf_config(cfg):
+    """T5Dims from a HuggingFace ``config.json`` dict (the checkpoints lceT5.py:106 / eval.py:14 load)."""
+    proj = cfg.get("feed_forward_proj", "relu")
+    if proj != "relu":
+        raise ValueError(f"feed_forward_proj={proj!r}: only the ReLU feed-forward of t5-* / monot5-* is built")
+    if not cfg.get("tie_word_embeddings", True):
+        raise ValueError("untied lm_head is not supported (t5-* / monot5-* tie it to the embedding)")
+    return T5Dims(vocab=cfg["vocab_size"], d_model=cfg["d_model"], d_kv=cfg["d_kv"], d_ff=cfg["d_ff"],
+                  n_layers=cfg["num_layers"], n_dec_layers=cfg.get("num_decoder_layers") or cfg["num_layers"],
+                  n_heads=cfg["num_heads"], rel_buckets=cfg.get("relative_attention_num_buckets", 32),
+                  rel_max_dist=cfg.get("relative_attention_max_distance", 128),
+                  eps=cfg.get("layer_norm_epsilon", 1e-6), pad_id=cfg.get("pad_token_id", 0) or 0)
+
+
+def hf_config(dims):
+    """The ``config.json`` a ``T5ForConditionalGeneration.from_pretrained`` needs to rebuild these dims."""
+    return {"architectures": ["T5ForConditionalGeneration"], "model_type": "t5", "vocab_size": dims.vocab,
+            "d_model": dims.d_model, "d_kv": dims.d_kv, "d_ff": dims.d_ff, "num_layers": dims.n_layers,
+            "num_decoder_layers": dims.n_dec_layers, "num_heads": dims.n_heads,
+            "relative_attention_num_buckets": dims.rel_buckets, "relative_attention_max_distance": dims.rel_max_dist,
+            "layer_norm_epsilon": dims.eps, "dropout_rate": 0.0, "feed_forward_proj": "relu",
+            "dense_act_fn": "relu", "is_gated_act": False, "is_encoder_decoder": True, "initializer_factor": 1.0,
+            "tie_word_embeddings": True, "use_cache": True, "pad_token_id": dims.pad_id, "eos_token_id": 1,
+            "decoder_start_token_id": dims.pad_id}
+
+
+def _tensor_shape(name, numel, dims):
+    """Shape of a parameter from its HF name (the flat buffer only records sizes)."""
+    d, di, ff = dims.d_model, dims.d_inner, dims.d_ff
+    if name == "shared.weight":
+        return (dims.vocab, d)
+    if name.endswith("relative_attention_bias.weight"):
+        return (dims.rel_buckets, dims.n_heads)
+    if name.endswith("layer_norm.weight"):
+        return (d,)
+    leaf = name.rsplit(".", 2)[-2]
+    shape = {"q": (di, d), "k": (di, d), "v": (di, d), "o": (d, di), "wi": (ff, d), "wo": (d, ff)}.get(leaf)
+    if shape is None or shape[0] * shape[1] != numel:
+        raise KeyError(f"cannot infer the shape of {name} ({numel} elements)")
+    return shape
+
+
+def load_checkpoint(path):
+    """(T5Dims, state_dict) of a local ``save_pretrained`` directory: config.json + model.safetensors or
+    pytorch_model.bin.  No network access: ``path`` must exist."""
+    with open(os.path.join(path, "config.json")) as f:
+        dims = dims_from_hf_config(json.load(f))
+    st = os.path.join(path, "model.safetensors")
+    if os.path.exists(st):
+        from safetensors.torch import load_file
+        sd = load_file(st)
+    else:
+        sd = torch.load(os.path.join(path, "pytorch_model.bin"), map_location="cpu", weights_only=True)
+    return dims, sd
+
+
+class _DeviceFloats:
+    """Zero-copy torch view of a device buffer the library owns."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 2}
+
+
 class MonoT5Scorer:
     """dims: T5Dims; state_dict: {hf_name: tensor} (any float dtype, CPU or CUDA)."""
 
@@ -124,6 +193,55 @@ class MonoT5Scorer:
                 _lib.lib().pn_t5_destroy(h)
             except Exception:
                 pass
+
+    @classmethod
+    def from_pretrained(cls, path, **kw):
+        """Build from a local HuggingFace checkpoint directory (``T5ForConditionalGeneration.from_pretrained``
+        at lceT5.py:106, ``MonoT5ReRanker(model=...)`` at eval.py:14)."""
+        dims, sd = load_checkpoint(path)
+        return cls(dims, sd, **kw)
+
+    def parameters_flat(self):
+        """fp32 view [num_params] of the library's master parameters (HF state_dict order); shares memory."""
+        lib = _lib.lib()
+        ptr = lib.pn_t5_params(self._h)
+        if not ptr:
+            raise RuntimeError(lib.pn_last_error().decode())
+        return torch.as_tensor(_DeviceFloats(ptr, lib.pn_t5_num_params(self._h)), device="cuda")
+
+    def named_offsets(self):
+        """[(hf_name, offset, numel)] of the flat parameter / gradient buffers."""
+        lib = _lib.lib()
+        out = []
+        name = C.create_string_buffer(256)
+        off, numel = C.c_int64(), C.c_int64()
+        for i in range(int(lib.pn_t5_num_tensors(self._h))):
+            _lib.check(lib.pn_t5_tensor_info(self._h, i, name, 256, C.byref(off), C.byref(numel)))
+            out.append((name.value.decode(), off.value, numel.value))
+        return out
+
+    def state_dict(self, tied=False):
+        """{hf_name: fp32 CPU tensor} of the current master parameters; ``tied`` adds the three aliases of
+        shared.weight that older HF checkpoints carry."""
+        flat = self.parameters_flat()
+        sd = {n: flat[o:o + k].view(_tensor_shape(n, k, self.dims)).cpu() for n, o, k in self.named_offsets()}
+        if tied:
+            for alias in _TIED:
+                sd[alias] = sd["shared.weight"]
+        return sd
+
+    def save_pretrained(self, path, safe_serialization=True):
+        """Write config.json + model.safetensors (or pytorch_model.bin) that ``T5ForConditionalGeneration
+        .from_pretrained(path)`` loads — train/train_lce.py:103 calls this on the trained model."""
+        os.makedirs(path, exist_ok=True)
+        with open(os.path.join(path, "config.json"), "w") as f:
+            json.dump(hf_config(self.dims), f, indent=2)
+        sd = {k: v.contiguous() for k, v in self.state_dict().items()}
+        if safe_serialization:
+            from safetensors.torch import save_file
+            save_file(sd, os.path.join(path, "model.safetensors"), metadata={"format": "pt"})
+        else:
+            torch.save(sd, os.path.join(path, "pytorch_model.bin"))
 
     def _workspace(self, docs, S, T):
         key = (docs, S, T)

@@ -403,6 +403,78 @@ def gold_train(rt, out):
         names=np.array(names), **{k_: np.asarray(v) for k_, v in res.items()})
 
 
+def gold_newwrapper(rp, rw, out):
+    """The reference's NewWrapper.meta_loop + main_loop (pairwrapper.py:219-258) executed unmodified on a tiny
+    random-init HF T5 (fp32, CPU) for three batches: table rows, losses and parameter movement."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    from transformers import T5Config, T5ForConditionalGeneration, get_linear_schedule_with_warmup
+    dims = ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
+    w = ot.init_weights(dims, seed=29)
+    cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
+                   num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
+                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   pad_token_id=0, eos_token_id=1, feed_forward_proj="relu", tie_word_embeddings=True)
+    m = T5ForConditionalGeneration(cfg).train()
+    sd = {k_: torch.tensor(v) for k_, v in w.items()}
+    sd["encoder.embed_tokens.weight"] = sd["decoder.embed_tokens.weight"] = sd["shared.weight"]
+    sd["lm_head.weight"] = sd["shared.weight"]
+    missing = m.load_state_dict(sd, strict=False)
+    assert not missing.missing_keys and not missing.unexpected_keys, missing
+    B, S, nb = 4, 128, 3
+    rel_id, nrel_id = 117, 213
+    rng = np.random.RandomState(977)
+    pids = rng.randint(2, dims.vocab, size=(nb, B, S)).astype(np.int64)
+    nids = rng.randint(2, dims.vocab, size=(nb, B, S)).astype(np.int64)
+    pids[:, :, -1] = 1
+    nids[:, :, -1] = 1
+    lr, warm, total = 2e-3, 2, 12
+
+    class Tok:   # batches arrive as ("p", j) / ("n", j) / label words; prep_batch's own slicing is exercised
+        def __call__(self, x, padding=True, return_tensors="pt"):
+            if isinstance(x, tuple):
+                ids = torch.tensor((pids if x[0] == "p" else nids)[x[1]])
+            else:
+                ids = torch.tensor([[rel_id if t == "true" else nrel_id, 1] for t in x])
+            return types.SimpleNamespace(input_ids=ids)
+
+    seen = []
+
+    class Loader:
+        def get_batch(self, j, weights):
+            seen.append(weights.detach().numpy().copy())
+            return ("p", j), ("n", j), ["true"] * B, ["false"] * B
+
+        def __len__(self):
+            return nb * B
+
+    wrap = object.__new__(rp.NewWrapper)
+    wrap.device = torch.device("cpu")
+    wrap.loss_fn = torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none")
+    wrap.model = m
+    wrap.tokenizer = Tok()
+    wrap.optimizer = LegacyAdamW(m.parameters(), lr=lr)
+    wrap.batch_size = B
+    wrap.weights = rw.Weights((nb, B), device=torch.device("cpu"))
+    wrap.train_loader = Loader()
+    wrap.scheduler = get_linear_schedule_with_warmup(wrap.optimizer, num_warmup_steps=warm,
+                                                     num_training_steps=total)
+    res = {}
+    before = {n_: p.detach().clone() for n_, p in m.named_parameters()}
+    for j in range(nb):
+        wrap.meta_loop(j)
+        res[f"row{j}"] = wrap.weights.weight[j].detach().numpy().copy()
+        res[f"loss{j}"] = np.float32(wrap.main_loop(j))
+        res[f"lr{j}"] = np.float32(wrap.scheduler.get_last_lr()[0])
+    for n_, p in m.named_parameters():
+        res["dnorm/" + n_] = float((p.detach() - before[n_]).norm())
+    res["seen"] = np.stack(seen)
+    np.savez_compressed(
+        out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
+                            dims.n_heads]), seed=np.array(29), pids=pids, nids=nids,
+        hp=np.array([B, lr, warm, total, rel_id, nrel_id]), **{k_: np.asarray(v) for k_, v in res.items()})
+
+
 def main():
     rw, rd, rl, rt, rp = import_reference()
     gold_weights(rw, rt, os.path.join(HERE, "weights_golden.npz"))
@@ -411,6 +483,7 @@ def main():
     gold_table_update(rp, rw, os.path.join(HERE, "table_update_golden.npz"))
     gold_t5(rt, os.path.join(HERE, "t5_tiny_golden.npz"))
     gold_train(rt, os.path.join(HERE, "train_golden.npz"))
+    gold_newwrapper(rp, rw, os.path.join(HERE, "newwrapper_golden.npz"))
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -58,3 +58,27 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+
+
+def test_checkpoint_directory_loader(tmp_path):
+    """load_checkpoint reads what HF save_pretrained writes (lceT5.py:106 / eval.py:14 wire format)."""
+    import torch
+    from transformers import T5Config, T5ForConditionalGeneration
+    from pacednegatives_b200.scorer import dims_from_hf_config, hf_config, load_checkpoint, T5Dims, _tensor_shape
+    cfg = T5Config(vocab_size=96, d_model=64, d_kv=16, d_ff=128, num_layers=2, num_decoder_layers=1, num_heads=4,
+                   dropout_rate=0.0, decoder_start_token_id=0, pad_token_id=0, eos_token_id=1,
+                   feed_forward_proj="relu", tie_word_embeddings=True)
+    hf = T5ForConditionalGeneration(cfg)
+    hf.save_pretrained(str(tmp_path))
+    dims, sd = load_checkpoint(str(tmp_path))
+    assert dims == T5Dims(vocab=96, d_model=64, d_kv=16, d_ff=128, n_layers=2, n_dec_layers=1, n_heads=4)
+    ref = hf.state_dict()
+    assert torch.equal(sd["shared.weight"], ref["shared.weight"])
+    for k, v in sd.items():
+        if k not in ("encoder.embed_tokens.weight", "decoder.embed_tokens.weight", "lm_head.weight"):
+            assert _tensor_shape(k, v.numel(), dims) == tuple(v.shape), k
+    back = T5Config(**hf_config(dims))
+    assert dims_from_hf_config(back.to_dict()) == dims
+    import pytest
+    with pytest.raises(ValueError):
+        dims_from_hf_config({**hf_config(dims), "feed_forward_proj": "gated-gelu"})
