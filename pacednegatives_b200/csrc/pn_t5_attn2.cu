@@ -71,6 +71,25 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&h);
 }
+// packed fp32 pairs (sm_100 FFMA2 / FADD2): one issue slot for two elements of the softmax row
+__device__ __forceinline__ uint64_t f2pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
 
 __global__ void __launch_bounds__(kThreads, 1)
 t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args a) {
@@ -264,13 +283,12 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
       }
       // columns 0..31: x = s*log2e + bias*log2e, and their max (seeds the row max of a fresh query block)
       float m0 = -INFINITY, m1 = -INFINITY;
+      const uint64_t l2e2 = f2pack(kLog2e, kLog2e);
 #pragma unroll
       for (int jj = 0; jj < 32; jj += 4) {
         const float4 b = bp[jj >> 2];
-        x[jj + 0] = fmaf(x[jj + 0], kLog2e, b.x);
-        x[jj + 1] = fmaf(x[jj + 1], kLog2e, b.y);
-        x[jj + 2] = fmaf(x[jj + 2], kLog2e, b.z);
-        x[jj + 3] = fmaf(x[jj + 3], kLog2e, b.w);
+        f2unpack(fma2(f2pack(x[jj + 0], x[jj + 1]), l2e2, f2pack(b.x, b.y)), x[jj + 0], x[jj + 1]);
+        f2unpack(fma2(f2pack(x[jj + 2], x[jj + 3]), l2e2, f2pack(b.z, b.w)), x[jj + 2], x[jj + 3]);
         m0 = fmax3(m0, x[jj + 0], x[jj + 1]);
         m1 = fmax3(m1, x[jj + 2], x[jj + 3]);
       }
@@ -305,7 +323,9 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
       // single pass: bias (columns 32..127), running max, p = 2^(x - m_used) against the STALE max so that the
       // exponentials do not wait for the row max; P -> its own TMEM buffer as packed bf16 (64 columns)
       float nm = -m_used;
-      float ls0 = 0.0f, ls1 = 0.0f, ls2 = 0.0f, ls3 = 0.0f;
+      uint64_t nm2 = f2pack(nm, nm);
+      uint64_t lsa = f2pack(0.0f, 0.0f), lsb = lsa;
+      float ls0 = 0.0f, ls1 = 0.0f;
       float m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
       for (int h2 = 0; h2 < 2; ++h2) {
@@ -313,23 +333,28 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
           const int jj = h2 * 64 + 2 * e;
+          uint64_t xa, xb;
           if (jj >= 32) {
             const float4 b = bp[jj >> 2];
-            x[jj + 0] = fmaf(x[jj + 0], kLog2e, b.x);
-            x[jj + 1] = fmaf(x[jj + 1], kLog2e, b.y);
-            x[jj + 2] = fmaf(x[jj + 2], kLog2e, b.z);
-            x[jj + 3] = fmaf(x[jj + 3], kLog2e, b.w);
+            xa = fma2(f2pack(x[jj + 0], x[jj + 1]), l2e2, f2pack(b.x, b.y));
+            xb = fma2(f2pack(x[jj + 2], x[jj + 3]), l2e2, f2pack(b.z, b.w));
+            f2unpack(xa, x[jj + 0], x[jj + 1]);
+            f2unpack(xb, x[jj + 2], x[jj + 3]);
             m2 = fmax3(m2, x[jj + 0], x[jj + 1]);
             m3 = fmax3(m3, x[jj + 2], x[jj + 3]);
+          } else {
+            xa = f2pack(x[jj + 0], x[jj + 1]);
+            xb = f2pack(x[jj + 2], x[jj + 3]);
           }
-          const float p0 = ex2_approx(x[jj] + nm);
-          const float p1 = ex2_approx(x[jj + 1] + nm);
-          const float p2 = ex2_approx(x[jj + 2] + nm);
-          const float p3 = ex2_approx(x[jj + 3] + nm);
-          ls0 += p0;
-          ls1 += p1;
-          ls2 += p2;
-          ls3 += p3;
+          float e0, e1, e2, e3;
+          f2unpack(add2(xa, nm2), e0, e1);
+          f2unpack(add2(xb, nm2), e2, e3);
+          const float p0 = ex2_approx(e0);
+          const float p1 = ex2_approx(e1);
+          const float p2 = ex2_approx(e2);
+          const float p3 = ex2_approx(e3);
+          lsa = add2(lsa, f2pack(p0, p1));
+          lsb = add2(lsb, f2pack(p2, p3));
           pk[e] = pack_bf16x2(p0, p1);
           pk[e + 1] = pack_bf16x2(p2, p3);
         }
@@ -342,7 +367,8 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
             if (c > 0) rescale_o(m_new);
             m_used = m_new;
             nm = -m_used;
-            ls0 = ls1 = ls2 = ls3 = 0.0f;
+            nm2 = f2pack(nm, nm);
+            lsa = lsb = f2pack(0.0f, 0.0f);
             if (!pfree_seen) {
               mbar_wait(bar(BAR_PFREE + wg), (n - 1) & 1);
               tc_fence_after();
@@ -373,7 +399,12 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
         }
         tmem_st_32x32(p_addr + h2 * 32, pk);
       }
-      l += (ls0 + ls1) + (ls2 + ls3);
+      {
+        float a0, a1, b0, b1;
+        f2unpack(lsa, a0, a1);
+        f2unpack(lsb, b0, b1);
+        l += ((a0 + a1) + (b0 + b1)) + (ls0 + ls1);
+      }
       if (warp == 0 && lane == 0) DBG_STAMP(0, n, 5);
       tmem_st_wait();
       tc_fence_before();
