@@ -270,6 +270,13 @@ int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* labels, int6
                         float* logits_out, void* workspace, int64_t workspace_bytes, void* stream);
 int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S, int32_t T,
                          void* workspace, int64_t workspace_bytes, void* stream);
+/* Data-parallel overlap (DDP's bucketed all-reduce under `manual_backward`, lceT5.py:155 with strategy='ddp'
+ * train/train_lce.py:89-91): fn(user, offset, numel) is called on the host thread while pn_t5_train_backward
+ * enqueues work, each time a contiguous range of the gradient buffer has received its last contribution
+ * (decoder parameters first, the upper encoder layers half way, the rest at the end; the ranges tile the buffer).
+ * The range is final once the work enqueued so far has run: record an event, all-reduce on a side stream.
+ * fn == NULL removes the hook.  Only meaningful when one backward call produces the whole step's gradient. */
+int pn_t5_set_grad_hook(PnT5* m, void (*fn)(void* user, int64_t offset, int64_t numel), void* user);
 int pn_t5_zero_grad(PnT5* m, void* stream);
 int pn_t5_adamw_step(PnT5* m, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
                      float gscale, void* stream);

@@ -67,6 +67,10 @@ struct PnT5 {
   int64_t enc_rel_off = 0, dec_rel_off = 0;
   float *enc_bias = nullptr;                     // [heads, 1023] expanded by (j - i + 511)
   float *dec_bias = nullptr;                     // [heads, 2, 2] for T <= 2
+  // called on the host while pn_t5_train_backward enqueues work: gradients [offset, offset + numel) are final once
+  // the work enqueued so far has run (data-parallel callers start that range's all-reduce on a side stream)
+  void (*grad_hook)(void* user, int64_t offset, int64_t numel) = nullptr;
+  void* grad_hook_user = nullptr;
   std::map<const void*, std::array<int64_t, 3>> fwd_ws;   // training workspaces holding a forward pass: docs, S, T
   bool finalized = false;
   bool xattn = true;                 // projection-free cross-attention where the shapes allow ("xattn" option)

@@ -276,6 +276,22 @@ extern "C" int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* l
   return PN_OK;
 }
 
+extern "C" int pn_t5_set_grad_hook(PnT5* m, void (*fn)(void*, int64_t, int64_t), void* user) {
+  PN_CHECK_ARG(m);
+  m->grad_hook = fn;
+  m->grad_hook_user = user;
+  return PN_OK;
+}
+
+namespace {
+// first element of the first parameter whose HF name starts with `prefix` (n_params when there is none)
+int64_t first_offset(const PnT5* m, const std::string& prefix) {
+  for (const PnParam& p : m->params)
+    if (p.name.compare(0, prefix.size(), prefix) == 0) return p.off;
+  return m->n_params;
+}
+}  // namespace
+
 // Accumulates d loss / d parameters into the gradient buffer, given dlogits = d loss / d logits (fp32
 // [docs*T, vocab_pad]) for the forward pass whose activations `workspace` holds.
 extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S,
@@ -378,6 +394,12 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     RC(pn_t5_norm_bwd(w.dgbuf, 0, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st));
   }
   RC(pn_t5_embed_bwd(w.dec_ids, w.ddH, drows, d, m->cfg.vocab, G + m->emb_off, st));
+  // gradient ranges in the order they become final (flat buffer = HF order: shared | encoder.block.* |
+  // encoder.final_layer_norm | decoder.*): the decoder's now, the upper encoder layers half way, the rest at the end
+  const int64_t dec_off = first_offset(m, "decoder.");
+  const int split_layer = L / 2;
+  const int64_t mid_off = first_offset(m, "encoder.block." + std::to_string(split_layer) + ".");
+  if (m->grad_hook) m->grad_hook(m->grad_hook_user, dec_off, m->n_params - dec_off);
   if (w.xattn) {
     // G = rs (.) ([P | dSc]_all-layers . [dC'; QK]_all-layers): every layer's cross-attention gradient of the
     // normalised encoder states in one block-diagonal GEMM (K = 64 per layer)
@@ -406,9 +428,14 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     RC(wgrad_folded(m, w.dbig, 3 * di, hb0, E.wqkv, w.dWtmp, rows, st));
     RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, PN_EPI_F32, rows, st));
     RC(pn_t5_norm_bwd(w.gbuf, 0, hb0, rs0, rows, d, 1, w.dH, w.dHb, st));
+    if (l == split_layer && l > 0 && m->grad_hook) m->grad_hook(m->grad_hook_user, mid_off, dec_off - mid_off);
   }
   RC(pn_t5_embed_bwd(ids, w.dH, rows, d, m->cfg.vocab, G + m->emb_off, st));
   RC(pn_t5_rel_bias_grad(w.diag, bucket_of, H, m->cfg.rel_buckets, G + m->enc_rel_off, st));
+  if (m->grad_hook) {
+    const int64_t rest = split_layer > 0 ? mid_off : dec_off;
+    m->grad_hook(m->grad_hook_user, 0, rest);
+  }
   return PN_OK;
 }
 

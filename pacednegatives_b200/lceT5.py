@@ -52,6 +52,7 @@ class _ModelFn(torch.autograd.Function):
         _lib.check(lib.pn_t5_train_forward(model._h, _lib.ptr(ids), _lib.ptr(labels), N, S, T, _lib.ptr(logits),
                                            _lib.ptr(ws), need, _lib.stream()))
         ctx.model, ctx.ws, ctx.ids, ctx.shape = model, ws, ids, (N, S, T)
+        model._pending += 1
         return logits.view(N, T, model.vocab_pad)
 
     @staticmethod
@@ -59,8 +60,17 @@ class _ModelFn(torch.autograd.Function):
         N, S, T = ctx.shape
         model = ctx.model
         d = dlogits.contiguous().float()
-        _lib.check(_lib.lib().pn_t5_train_backward(model._h, _lib.ptr(ctx.ids), _lib.ptr(d), N, S, T,
-                                                   _lib.ptr(ctx.ws), ctx.ws.numel(), _lib.stream()))
+        # gradient ranges may leave for their all-reduce as they complete only if this backward is the step's last
+        model._hook_live = model._pending == 1 and model._overlap_ready()
+        model._pending -= 1
+        try:
+            _lib.check(_lib.lib().pn_t5_train_backward(model._h, _lib.ptr(ctx.ids), _lib.ptr(d), N, S, T,
+                                                       _lib.ptr(ctx.ws), ctx.ws.numel(), _lib.stream()))
+        finally:
+            model._hook_live = False
+        if model._hook_error is not None:
+            err, model._hook_error = model._hook_error, None
+            raise err
         ctx.ws = None
         return torch.zeros_like(model._anchor), None, None, None
 
@@ -80,6 +90,22 @@ class MonoT5Model(MonoT5Scorer):
                                                _lib.ptr(self.exp_avg_sq)))
         self._anchor = torch.zeros(1, device="cuda", requires_grad=True)
         self.opt_steps = 0
+        # gradient all-reduce overlapped with the backward pass (DDP's bucketing): libpn_b200 calls _on_grad_range
+        # while it enqueues the backward; ranges go out on a side stream behind an event
+        self.overlap_grad_reduce = True
+        self.reduce_group = None
+        self._pending, self._hook_live, self._hook_error = 0, False, None
+        self._reduced, self._comm_stream, self._comm_done = [], None, None
+        import ctypes as C
+        import weakref
+        me = weakref.ref(self)   # the C callback must not keep the model alive
+
+        def hook(_user, off, numel):
+            obj = me()
+            if obj is not None:
+                obj._on_grad_range(off, numel)
+        self._hook_c = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64)(hook)
+        _lib.check(lib.pn_t5_set_grad_hook(self._h, C.cast(self._hook_c, C.c_void_p), None))
 
     def __call__(self, input_ids, labels, attention_mask=None):
         if attention_mask is not None and not bool(torch.as_tensor(attention_mask).all()):
@@ -95,13 +121,53 @@ class MonoT5Model(MonoT5Scorer):
     def zero_grad(self):
         _lib.check(_lib.lib().pn_t5_zero_grad(self._h, _lib.stream()))
 
+    def _overlap_ready(self):
+        return (self.overlap_grad_reduce and dist.is_available() and dist.is_initialized()
+                and dist.get_world_size(self.reduce_group) > 1 and not self._reduced)
+
+    def _on_grad_range(self, off, numel):
+        """Host callback from pn_t5_train_backward: gradients [off, off+numel) are final once the work enqueued so
+        far has run.  SUM all-reduce of that slice on the side stream, behind an event on the compute stream."""
+        if not self._hook_live or numel <= 0:
+            return
+        try:
+            if self._comm_stream is None:
+                self._comm_stream = torch.cuda.Stream()
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            self._comm_stream.wait_event(ev)
+            with torch.cuda.stream(self._comm_stream):
+                dist.all_reduce(self.grads[off:off + numel], op=dist.ReduceOp.SUM, group=self.reduce_group)
+                self._comm_done = torch.cuda.Event()
+                self._comm_done.record(self._comm_stream)
+            self._reduced.append((int(off), int(numel)))
+        except Exception as e:   # never unwind through the C frame
+            self._hook_error = e
+
     def all_reduce_grads(self, group=None):
-        """DDP's gradient mean: one all-reduce over the flat buffer; returns the scale still to apply."""
-        return all_reduce_mean_scale(self.grads, group)
+        """DDP's gradient mean; returns the scale still to apply (folded into the AdamW kernel).  Ranges already
+        sent from inside the backward pass are only waited for; anything else is reduced here in one call."""
+        if self._reduced:
+            done = sorted(self._reduced)
+            self._reduced = []
+            covered = 0
+            for off, n in done:
+                if off != covered:
+                    break
+                covered = off + n
+            torch.cuda.current_stream().wait_event(self._comm_done)
+            if covered != self.grads.numel():
+                raise RuntimeError(f"overlapped gradient all-reduce covered {covered} of {self.grads.numel()} elements")
+            return 1.0 / dist.get_world_size(self.reduce_group)
+        return all_reduce_mean_scale(self.grads, group if group is not None else self.reduce_group)
 
     def step(self, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, gscale=1.0):
         """transformers.AdamW defaults (the optimiser of lceT5.py:172)."""
         self.opt_steps += 1
+        if self._reduced:   # ranges sent from inside the backward pass that nobody waited for
+            torch.cuda.current_stream().wait_event(self._comm_done)
+            self._reduced = []
+        self._pending = 0
         _lib.check(_lib.lib().pn_t5_adamw_step(self._h, float(lr), betas[0], betas[1], eps, weight_decay,
                                                self.opt_steps, float(gscale), _lib.stream()))
 
