@@ -463,15 +463,16 @@ def bench_rerank_reference(args):
 
 # ------------------------------------------------------------------------------------------------
 # workload: the LCE training step (BASELINE.json configs[2])
-def hf_train_sample(n_docs, S, steps, warmup, threads=None):
+def hf_train_sample(n_docs, S, steps, warmup, threads=None, large=False):
     """The reference's CPU path for one training step's model work on a bounded sample: HF
     T5ForConditionalGeneration fp32 forward + backward + AdamW over n_docs prompts with 2 label tokens and the
     reference's loss (lceT5.py:149-156).  Returns (docs/s, description, seconds)."""
     if threads:
         torch.set_num_threads(threads)
     from transformers import T5Config, T5ForConditionalGeneration
-    cfg = T5Config(vocab_size=32128, d_model=768, d_kv=64, d_ff=3072, num_layers=12, num_decoder_layers=12,
-                   num_heads=12, dropout_rate=0.0, decoder_start_token_id=0, pad_token_id=0, eos_token_id=1)
+    d, ff, L, H = (1024, 4096, 24, 16) if large else (768, 3072, 12, 12)
+    cfg = T5Config(vocab_size=32128, d_model=d, d_kv=64, d_ff=ff, num_layers=L, num_decoder_layers=L,
+                   num_heads=H, dropout_rate=0.0, decoder_start_token_id=0, pad_token_id=0, eos_token_id=1)
     torch.manual_seed(0)
     model = T5ForConditionalGeneration(cfg).train()
     opt = torch.optim.AdamW(model.parameters(), lr=1e-3, eps=1e-6, weight_decay=0.0)
@@ -498,16 +499,23 @@ def hf_train_sample(n_docs, S, steps, warmup, threads=None):
 def bench_train(args):
     from pacednegatives_b200 import _lib
     from pacednegatives_b200.lceT5 import LCEModel
-    from pacednegatives_b200.scorer import T5_BASE, random_state_dict, flops_per_doc
+    from pacednegatives_b200.scorer import T5_BASE, T5_LARGE, random_state_dict, flops_per_doc
     _lib.require_gpu()
     torch.cuda.set_device(LOCAL_RANK)
     dist = dist_setup(True)
     lib = _lib.lib()
-    S, T, k = 512, 2, 15
+    large = args.model == "large"
+    S, T = 512, 2
+    k = args.negatives if args.negatives else (31 if large else 15)
     Q = args.train_queries
-    dims = T5_BASE
+    dims = T5_LARGE if large else T5_BASE
+    # T5-large at 1+31 x 512: 512 documents of saved activations (~130 GB) do not fit beside the weights; walk the
+    # batch in micro-batches of 8 queries (256 documents) by default
+    mq = args.micro_queries if args.micro_queries >= 0 else (8 if large else 0)
     hp = dict(n=k, use_mean=True, ignore_index=-100, lr=1e-3, meta_lr=1e-3, warmup_steps=0,
-              total_steps=1000000, eta=0.3466)
+              total_steps=1000000, eta=0.3466, micro_queries=mq)
+    tag = "T5-large" if large else "monoT5-base"
+    cfg_i = 3 if large else 2
     m = LCEModel(hp, dims=dims, state_dict=random_state_dict(dims, seed=0), cta_group=args.cta_group)
     total = args.steps + args.warmup
     nbuf = min(total, 4)
@@ -560,12 +568,13 @@ def bench_train(args):
         return {"tflops": work / (t_ms / 1e3) / 1e12 if t_ms else 0.0, "launches": int(n),
                 "share_of_step": t_ms / ms if ms else None}
     line = {
-        "metric": "LCE training queries/s (1+15 docs per query)", "value": value, "unit": "queries/s",
+        "metric": f"LCE training queries/s (1+{k} docs per query)", "value": value, "unit": "queries/s",
         "n_gpus": WORLD, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-        "data": "synthetic (random-init t5-base dims, ids U{2..32099}, labels true/false + </s>)",
-        "config": {"workload": "LCE training step, monoT5-base, 1+15 docs per query, seq 512 (BASELINE configs[2])",
+        "data": f"synthetic (random-init {tag} dims, ids U{{2..32099}}, labels true/false + </s>)",
+        "config": {"workload": f"LCE training step, {tag}, 1+{k} docs per query, seq 512 (BASELINE configs[{cfg_i}])",
                    "queries_per_step_per_gpu": Q, "negatives": k, "seq_len": S, "label_tokens": T,
+                   "micro_queries": mq if 0 < mq < Q else None,
                    "no_grad_forward": "elided (identical arithmetic at dropout 0); FLOP count uses 3x forward",
                    "optimizer": "AdamW (transformers rule) on flat fp32 masters + eta meta step",
                    "l2": "activations per step (tens of GB) exceed the 126 MB L2; no flush needed",
@@ -589,7 +598,7 @@ def bench_train(args):
     if RANK == 0:
         if WORLD == 1 and not args.no_cpu_baseline:
             try:
-                v, how, dt = hf_train_sample(4, S, 1, 1)
+                v, how, dt = hf_train_sample(4, S, 1, 1, large=large)
                 line["cpu_baseline"] = {"value": v / (1 + k), "unit": "queries/s", "cores": torch.get_num_threads(),
                                         "host_cpus": os.cpu_count(), "kind": "port",
                                         "sample": f"4 docs x seq {S} x 1 step ({dt:.1f} s), {how}; docs/s / {1 + k}"}
@@ -639,6 +648,11 @@ def main():
     ap.add_argument("--select-queries", type=int, default=1000000)
     ap.add_argument("--select-elems", type=int, default=1 << 28)
     ap.add_argument("--train-queries", type=int, default=16)
+    ap.add_argument("--model", default="base", choices=["base", "large"],
+                    help="train workload: base = BASELINE configs[2] (1+15), large = configs[3] (1+31, micro-batched)")
+    ap.add_argument("--negatives", type=int, default=0, help="train workload: negatives per query (0 = config default)")
+    ap.add_argument("--micro-queries", type=int, default=-1,
+                    help="train workload: queries per micro-batch (0 = whole batch at once, -1 = config default)")
     ap.add_argument("--ref-train-docs", type=int, default=4)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

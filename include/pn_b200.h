@@ -115,6 +115,12 @@ int pn_lce_restricted_fwd(const float* z2, int64_t Q, int32_t G, float* loss_out
 int pn_lce_restricted_bwd(const float* z2, int64_t Q, int32_t G, const float* g, float* dz2,
                           void* stream);
 
+/* check_success / check_probs (old/levels.py:35-39, old/eta_bound.py:51-55): count_out[0] (device int32, zeroed
+ * by the call) = #{ i < n : softmax(pos[i,0,(rel,nrel)])[0] > softmax(neg[i,0,(rel,nrel)])[0] }; the caller divides
+ * by n.  pos/neg are fp32 logits [n, T, V] read at label position 0; *_stride = T*V elements per document. */
+int pn_check_success(const float* pos_logits, const float* neg_logits, int64_t n, int64_t pos_stride,
+                     int64_t neg_stride, int32_t rel_id, int32_t nrel_id, int32_t* count_out, void* stream);
+
 /* ------------------------------------------------------------------ a7
  * Level-paced negative pick (dataloader.py:29-33): r = floor|ceil(w * n_neg), n_neg = C-1,
  * computed in fp64 like the Python float the reference multiplies.

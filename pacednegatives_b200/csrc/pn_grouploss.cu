@@ -323,3 +323,42 @@ extern "C" int pn_lce_restricted_bwd(const float* z2, int64_t Q, int32_t G, cons
   PN_LAUNCHED();
   return PN_OK;
 }
+
+// ---- check_success / check_probs (old/levels.py:35-39, old/eta_bound.py:51-55): pair i succeeds when
+// softmax(pos[i, 0, (REL, NREL)])[0] > softmax(neg[i, 0, (REL, NREL)])[0]; only those four logits of each pair
+// are read from the [N, T, V] logits (row_stride = T*V elements between documents).
+__device__ __forceinline__ float pn_p_rel(float zt, float zf) {
+  // torch's fp32 softmax over two entries: exp(x - max) / sum
+  const float m = fmaxf(zt, zf);
+  const float et = expf(zt - m), ef = expf(zf - m);
+  return et / (et + ef);
+}
+
+__global__ void __launch_bounds__(kThreads) check_success_kernel(const float* __restrict__ pos,
+                                                                 const float* __restrict__ neg, int64_t n,
+                                                                 int64_t pos_stride, int64_t neg_stride, int rel,
+                                                                 int nrel, int32_t* __restrict__ count) {
+  int local = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float* p = pos + i * pos_stride;
+    const float* q = neg + i * neg_stride;
+    local += pn_p_rel(__ldg(p + rel), __ldg(p + nrel)) > pn_p_rel(__ldg(q + rel), __ldg(q + nrel)) ? 1 : 0;
+  }
+  local = __reduce_add_sync(0xffffffffu, local);
+  if ((threadIdx.x & 31) == 0 && local) atomicAdd(count, local);
+}
+
+extern "C" int pn_check_success(const float* pos_logits, const float* neg_logits, int64_t n, int64_t pos_stride,
+                                int64_t neg_stride, int32_t rel_id, int32_t nrel_id, int32_t* count_out,
+                                void* stream) {
+  PN_CHECK_ARG(n >= 0 && rel_id >= 0 && nrel_id >= 0 && count_out);
+  PN_CHECK_ARG(pos_stride > rel_id && pos_stride > nrel_id && neg_stride > rel_id && neg_stride > nrel_id);
+  cudaStream_t st = (cudaStream_t)stream;
+  PN_CUDA(cudaMemsetAsync(count_out, 0, sizeof(int32_t), st));
+  if (n == 0) return PN_OK;
+  PN_CHECK_ARG(pos_logits && neg_logits);
+  check_success_kernel<<<pn_grid(n, kThreads, 1, 8), kThreads, 0, st>>>(pos_logits, neg_logits, n, pos_stride,
+                                                                        neg_stride, rel_id, nrel_id, count_out);
+  PN_LAUNCHED();
+  return PN_OK;
+}

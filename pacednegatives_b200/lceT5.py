@@ -3,9 +3,10 @@
 ``LCEModel`` keeps the reference's interface for the hot path (``pair_loss`` lceT5.py:116-123,
 ``training_step`` lceT5.py:124-167, ``configure_optimizers`` lceT5.py:170-183) with the same hparams names;
 the model is ``MonoT5Model`` (libpn_b200.so: tcgen05 forward + backward, flat fp32 parameters, AdamW kernel)
-instead of ``transformers.T5ForConditionalGeneration`` + autograd + ``transformers.AdamW``.  Lightning, the
-tokenizer and ir_datasets (lceT5.py:13-75) are out of scope: a batch is the ``(p, n)`` pair of
-``{'input_ids', 'labels'}`` dicts that LCEDataModule.collate returns (lceT5.py:38-53).
+instead of ``transformers.T5ForConditionalGeneration`` + autograd + ``transformers.AdamW``.  A batch is the
+``(p, n)`` pair of ``{'input_ids', 'labels'}`` dicts that ``LCEDataModule.collate`` returns (lceT5.py:38-53);
+``LCEDataModule`` / ``ChangeDifficulty`` (lceT5.py:13-80) are mirrored as plain classes (Lightning itself, the
+SentencePiece tokenizer and ir_datasets are out of scope: pass any tokenizer callable and a corpus object).
 
 Data parallel (Lightning DDP in the reference): every rank runs the same step on its own queries; the flat
 gradient buffer and eta's gradient are all-reduced (mean) once per step over ``torch.distributed``.
@@ -20,6 +21,75 @@ from . import _lib
 from .loss import pair_loss as _pair_loss
 from .scorer import MonoT5Scorer
 from .weights import LCEWeights
+
+
+class LCEDataModule:
+    """lceT5.py:13-67.  Same constructor arguments and methods (``setup``, ``collate``, ``train_dataloader``).
+    ``corpus`` is an object with ``docs_iter()`` / ``queries_iter()`` (what ``ir_datasets.load(name)`` returns); a
+    string is resolved through ir_datasets when that package is importable.  The candidate file is the
+    ``[{query_id, doc_id_a, doc_id_b[C]}]`` json utilities/compute_all_bm25.py writes; it becomes the dense int32
+    [Q, C] candidate matrix in HBM that pn_select_binomial samples from (dataloader.LCEDataset).  The sampler runs
+    on this process's GPU, so batches are produced in the main process: ``num_workers`` is accepted and ignored
+    (forked DataLoader workers cannot use the CUDA context)."""
+
+    def __init__(self, data_dir: str = "path/to/dir", corpus="msmarco-passage", tokenizer=None,
+                 batch_size: int = 32, shuffle=False, use_max=False, var=0.01, n=2, init_weight=0. + 1e-10,
+                 num_workers=4):
+        self.data_dir = data_dir
+        if isinstance(corpus, str):
+            try:
+                import ir_datasets as irds
+            except ImportError as e:
+                raise RuntimeError("LCEDataModule: pass a corpus object with docs_iter()/queries_iter(); "
+                                   f"ir_datasets is not installed to resolve {corpus!r}") from e
+            corpus = irds.load(corpus)
+        self.corpus = corpus
+        self.tokenizer = tokenizer
+        self.batch_size = batch_size
+        self.shuffle = shuffle
+        self.use_max = use_max
+        self.var = var
+        self.n = n
+        self.num_workers = num_workers
+        self.weight = init_weight
+
+    def collate(self):
+        tokenizer = self.tokenizer
+
+        def collate_fn(batch):
+            pos = [x['pos'] for x in batch]
+            neg = [d for x in batch for d in x['neg']]      # query-major, lceT5.py:43
+            pos = tokenizer(pos, padding=True, return_tensors='pt')
+            neg = tokenizer(neg, padding=True, return_tensors='pt')
+            plab = tokenizer(['true'] * len(pos['input_ids']), padding=True, return_tensors='pt')['input_ids']
+            nlab = tokenizer(['false'] * len(neg['input_ids']), padding=True, return_tensors='pt')['input_ids']
+            return ({'input_ids': pos['input_ids'], 'labels': plab}, {'input_ids': neg['input_ids'], 'labels': nlab})
+        return collate_fn
+
+    def setup(self, stage: str = None):
+        import pandas as pd
+        from .dataloader import LCEDataset
+        with open(self.data_dir, 'r') as f:
+            dataset = pd.read_json(f, orient='records', dtype={'query_id': str, 'doc_id_a': str})
+        if self.shuffle:
+            dataset = dataset.sample(frac=1).reset_index(drop=True)
+        self.pairs = dataset[['query_id', 'doc_id_a']].values.tolist()
+        self.neg_idx = [[str(d) for d in row] for row in dataset['doc_id_b'].values]
+        self.dataset = LCEDataset(self.pairs, self.neg_idx, self.corpus, self.tokenizer, self.weight,
+                                  self.batch_size, var=self.var, n=self.n, min=0. + 1e-10, max=1.0 - 1e-10,
+                                  use_max=self.use_max)
+
+    def train_dataloader(self):
+        from torch.utils.data import DataLoader
+        return DataLoader(self.dataset, batch_size=self.batch_size, num_workers=0, collate_fn=self.collate(),
+                          pin_memory=True)
+
+
+class ChangeDifficulty:
+    """lceT5.py:77-80: before each batch the dataset's sampling mean follows the model's eta."""
+
+    def on_train_batch_start(self, trainer, pl_module, batch, batch_idx):
+        trainer.train_dataloader.dataset.weight = min(1 - 1e-10, pl_module.difficulty)
 
 
 def linear_schedule_with_warmup(step, warmup_steps, total_steps):
@@ -61,7 +131,7 @@ class _ModelFn(torch.autograd.Function):
         model = ctx.model
         d = dlogits.contiguous().float()
         # gradient ranges may leave for their all-reduce as they complete only if this backward is the step's last
-        model._hook_live = model._pending == 1 and model._overlap_ready()
+        model._hook_live = model._pending == 1 and not model.accumulating and model._overlap_ready()
         model._pending -= 1
         try:
             _lib.check(_lib.lib().pn_t5_train_backward(model._h, _lib.ptr(ctx.ids), _lib.ptr(d), N, S, T,
@@ -93,6 +163,7 @@ class MonoT5Model(MonoT5Scorer):
         # gradient all-reduce overlapped with the backward pass (DDP's bucketing): libpn_b200 calls _on_grad_range
         # while it enqueues the backward; ranges go out on a side stream behind an event
         self.overlap_grad_reduce = True
+        self.accumulating = False    # True while more micro-batches of this step will still add to `grads`
         self.reduce_group = None
         self._pending, self._hook_live, self._hook_error = 0, False, None
         self._reduced, self._comm_stream, self._comm_done = [], None, None
@@ -240,6 +311,68 @@ class LCEModel:
             return logits[:Q], logits[Q:].reshape(-1, k, V)
         return self.model(pi, pl), self.model(ni, nl).view(-1, k, V)
 
+    def _meta_step(self, loss, meta_opt, scale):
+        """lceT5.py:135-147: eta's AdamW step on mean(w * loss) and the three logged scalars."""
+        weights = self.weights(loss)
+        meta_loss = weights * loss
+        meta_opt.zero_grad()
+        meta_loss.mean().backward()
+        if self.weights.eta.grad is not None:
+            self.weights.eta.grad *= all_reduce_mean_scale(self.weights.eta.grad)
+        meta_opt.step(lr=self.hparams.meta_lr * scale)
+        self.log("avg_weight", weights.mean())
+        self.log("meta_loss", meta_loss.mean())
+        self.log("eta", self.weights.eta.item())
+        return weights, meta_loss
+
+    def _training_step_micro(self, p, n, mq, meta_opt, opt, scale):
+        """The same step with the batch walked in groups of `micro_queries` queries (T5-large at 1+31 x 512 does
+        not keep 512 documents of activations in HBM): every query's loss element, weight and gradient
+        contribution is independent of the other queries, so the gradients of mean(main_loss) are
+        the sum over micro-batches of d(sum(main_loss_mb) / (Q*T)), accumulated in the flat gradient buffer; the
+        all-reduce ranges leave during the LAST micro-batch's backward.  eta only enters the logged weights, so
+        running its step after the forwards (the reference runs it before, lceT5.py:135-147) changes nothing."""
+        k, V = int(self.hparams.n), self.model.dims.vocab
+        pi, ni = torch.as_tensor(p["input_ids"]), torch.as_tensor(n["input_ids"])
+        pl, nl = torch.as_tensor(p["labels"]), torch.as_tensor(n["labels"])
+        Q, T = pi.shape[0], pl.shape[1]
+        if not self.elide:
+            with torch.no_grad():
+                p0, _ = self.model.logits(pi, pl)
+                n0, _ = self.model.logits(ni, nl)
+                loss0 = self.pair_loss(p0.contiguous(), n0.reshape(-1, k, V).contiguous(), pl.cuda(), nl.cuda())
+        opt.zero_grad()
+        parts = []
+        try:
+            for a in range(0, Q, mq):
+                b = min(Q, a + mq)
+                pc = {"input_ids": pi[a:b], "labels": pl[a:b]}
+                nc = {"input_ids": ni[a * k:b * k], "labels": nl[a * k:b * k]}
+                plogits, nlogits = self._forward_pn(pc, nc, k, V)
+                main = self.pair_loss(plogits.contiguous(), nlogits.contiguous(), pc["labels"].cuda(),
+                                      nc["labels"].cuda())
+                parts.append(main.detach())
+                self.model.accumulating = b < Q
+                (main.sum() / float(Q * T)).backward()
+                del plogits, nlogits, main
+        finally:
+            self.model.accumulating = False
+        main_loss = torch.cat(parts)
+        loss = main_loss if self.elide else loss0
+        weights, meta_loss = self._meta_step(loss, meta_opt, scale)
+        gscale = opt.all_reduce_grads()
+        opt.step(lr=self.hparams.lr * scale, gscale=gscale)
+        self.global_step += 1
+        return self._step_output(loss, weights, main_loss, meta_loss)
+
+    def _step_output(self, loss, weights, main_loss, meta_loss):
+        tqdm_dict = {"meta_loss": loss.mean(), "avg_weight": weights.mean(), "main_loss": loss.mean()}
+        output = OrderedDict({"main_loss": main_loss.mean(), "meta_loss": meta_loss.mean(),
+                              "progress_bar": tqdm_dict, "log": tqdm_dict})
+        self.log("main_loss", loss.mean())
+        self.difficulty = self.weights.eta.item()
+        return output
+
     def training_step(self, batch, batch_nb=0):
         p, n = batch
         if self._opts is None:
@@ -247,6 +380,9 @@ class LCEModel:
         meta_opt, opt = self._opts
         k, V = int(self.hparams.n), self.model.dims.vocab
         scale = self._lr_scale()
+        mq = int(getattr(self.hparams, "micro_queries", 0) or 0)
+        if 0 < mq < len(p["input_ids"]):
+            return self._training_step_micro(p, n, mq, meta_opt, opt, scale)
 
         if self.elide:
             plogits, nlogits = self._forward_pn(p, n, k, V)
@@ -261,17 +397,7 @@ class LCEModel:
         with torch.no_grad():
             loss = self.pair_loss(p0.contiguous(), n0.contiguous(), op, on)
 
-        weights = self.weights(loss)
-        meta_loss = weights * loss
-        meta_opt.zero_grad()
-        meta_loss.mean().backward()
-        if self.weights.eta.grad is not None:
-            self.weights.eta.grad *= all_reduce_mean_scale(self.weights.eta.grad)
-        meta_opt.step(lr=self.hparams.meta_lr * scale)
-
-        self.log("avg_weight", weights.mean())
-        self.log("meta_loss", meta_loss.mean())
-        self.log("eta", self.weights.eta.item())
+        weights, meta_loss = self._meta_step(loss, meta_opt, scale)
 
         if not self.elide:
             plogits, nlogits = self._forward_pn(p, n, k, V)
@@ -282,10 +408,4 @@ class LCEModel:
         gscale = opt.all_reduce_grads()
         opt.step(lr=self.hparams.lr * scale, gscale=gscale)
         self.global_step += 1
-
-        tqdm_dict = {"meta_loss": loss.mean(), "avg_weight": weights.mean(), "main_loss": loss.mean()}
-        output = OrderedDict({"main_loss": main_loss.mean(), "meta_loss": meta_loss.mean(),
-                              "progress_bar": tqdm_dict, "log": tqdm_dict})
-        self.log("main_loss", loss.mean())
-        self.difficulty = self.weights.eta.item()
-        return output
+        return self._step_output(loss, weights, main_loss, meta_loss)

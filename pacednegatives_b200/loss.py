@@ -125,3 +125,25 @@ def lce_restricted(z2, G):
     """z2 [Q*G, 2] = (z_true, z_false) per document, positive first in each group.
     Returns (loss [Q], score [Q*G])."""
     return _LceRestricted.apply(z2, G)
+
+
+def check_success(pos, neg, rel_id, nrel_id):
+    """old/levels.py:35-39 / old/eta_bound.py:51-55: mean(softmax(pos[:, 0, (REL, NREL)])[:, 0] >
+    softmax(neg[:, 0, (REL, NREL)])[:, 0]) over paired rows, as a device scalar (one kernel, four logits per pair
+    read).  pos / neg: fp32 logits [n, T, V] (any V >= the token ids)."""
+    _lib.require_gpu()
+    pos, neg = pos.detach(), neg.detach()
+    if pos.dim() != 3 or neg.dim() != 3 or pos.shape[0] != neg.shape[0]:
+        raise ValueError(f"check_success: logits must be [n, T, V] with equal n, got {tuple(pos.shape)} / {tuple(neg.shape)}")
+    pos = pos if pos.dtype == torch.float32 and pos.stride(2) == 1 else pos.float().contiguous()
+    neg = neg if neg.dtype == torch.float32 and neg.stride(2) == 1 else neg.float().contiguous()
+    n = pos.shape[0]
+    count = torch.empty(1, dtype=torch.int32, device="cuda")
+    import ctypes as C
+    if not (pos.is_cuda and neg.is_cuda):
+        raise ValueError("expected CUDA tensors")
+    # rows may be views into vocab-padded logits: only element stride 1 within a row is required
+    _lib.check(_lib.lib().pn_check_success(C.c_void_p(pos.data_ptr()), C.c_void_p(neg.data_ptr()), n,
+                                           pos.stride(0), neg.stride(0),
+                                           int(rel_id), int(nrel_id), _lib.ptr(count), _lib.stream()))
+    return count.float() / max(n, 1)

@@ -475,6 +475,251 @@ def gold_newwrapper(rp, rw, out):
         hp=np.array([B, lr, warm, total, rel_id, nrel_id]), **{k_: np.asarray(v) for k_, v in res.items()})
 
 
+def _load_old(name):
+    """old/<name>.py by path (the directory is not a package); wandb and ir_datasets.log are stubbed."""
+    import importlib.util
+    import contextlib
+    wandb = types.ModuleType("wandb")
+    wandb.run = None
+    sys.modules["wandb"] = wandb
+    irds = sys.modules["ir_datasets"]
+
+    class _Bar:
+        def update(self, n):
+            pass
+
+        def set_postfix(self, d):
+            pass
+
+    class _Log:
+        @contextlib.contextmanager
+        def pbar_raw(self, **kw):
+            yield _Bar()
+    irds.log = types.SimpleNamespace(easy=lambda: _Log())
+    spec = importlib.util.spec_from_file_location("ref_old_" + name, os.path.join(REF, "old", name + ".py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def gold_scalar_wrappers(rp, rw, out):
+    """The reference's LevelWrapper / InterpWrapper / EtaWrapper train() loops (old/levels.py, old/interp.py,
+    old/eta_bound.py) executed unmodified on a tiny random-init HF T5 (fp32, CPU): per-step difficulty handed to
+    the loader, losses, learning rates, success rates, eta.  Two accommodations, both stated in the test:
+    the optimiser is the transformers.AdamW rule (LegacyAdamW; absent from this image's transformers), and
+    weights.gen_var returns a non-leaf tensor, which is what `.to(cuda)` makes of it on the reference's own
+    device — on CPU the in-place writes of EtaWeights.forward raise on the leaf (weights.py:34-43)."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    from torch.autograd import Variable
+    from transformers import T5Config, T5ForConditionalGeneration
+    rw.gen_var = lambda x, y: Variable(x, requires_grad=y).clone()
+    dims = ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
+    seed = 31
+    w = ot.init_weights(dims, seed=seed)
+    cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
+                   num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
+                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   pad_token_id=0, eos_token_id=1, feed_forward_proj="relu", tie_word_embeddings=True)
+
+    def model_init():
+        m = T5ForConditionalGeneration(cfg).train()
+        sd = {k_: torch.tensor(v) for k_, v in w.items()}
+        sd["encoder.embed_tokens.weight"] = sd["decoder.embed_tokens.weight"] = sd["shared.weight"]
+        sd["lm_head.weight"] = sd["shared.weight"]
+        missing = m.load_state_dict(sd, strict=False)
+        assert not missing.missing_keys and not missing.unexpected_keys, missing
+        return m
+
+    B, S, nb, n_neg = 4, 128, 10, 4
+    rel_id, nrel_id = 117, 213
+    rng = np.random.RandomState(1203)
+    pids = rng.randint(2, dims.vocab, size=(nb, B, S)).astype(np.int64)
+    # one negative prompt per (batch, query, rank): the loader hands out the rank the difficulty selects
+    nids = rng.randint(2, dims.vocab, size=(nb, B, n_neg + 1, S)).astype(np.int64)
+    pids[..., -1] = 1
+    nids[..., -1] = 1
+    lr, meta_lr, total = 3e-3, 5e-2, nb * B
+
+    class Tok:
+        def __call__(self, x, padding=True, return_tensors="pt"):
+            if isinstance(x, tuple):
+                ids = torch.tensor(pids[x[1]] if x[0] == "p" else nids[x[1], :, x[2]])
+            else:
+                ids = torch.tensor([[rel_id if t == "true" else nrel_id, 1] for t in x])
+            return types.SimpleNamespace(input_ids=ids)
+
+        def encode(self, word):
+            return [rel_id if word == "true" else nrel_id, 1]
+
+    class Loader:
+        batch_size = B
+        dataset = types.SimpleNamespace(n_neg=n_neg)
+
+        def __init__(self):
+            self.seen = []
+
+        def get_batch(self, j, weight):
+            self.seen.append(float(weight))
+            r = int(np.floor(float(weight) * n_neg))
+            return ("p", j), ("n", j, r), ["true"] * B, ["false"] * B
+
+        def __len__(self):
+            return nb * B
+
+    res = {}
+
+    def finish(tag, wrap, loader, before):
+        res[tag + "/seen"] = np.array(loader.seen, dtype=np.float64)
+        res[tag + "/dnorm"] = np.array([float((p_.detach() - before[n_]).norm())
+                                        for n_, p_ in wrap.model.named_parameters()])
+        res[tag + "/names"] = np.array([n_ for n_, _ in wrap.model.named_parameters()])
+
+    def start(wrap):
+        wrap.optimizer = LegacyAdamW(wrap.model.parameters(), lr=lr)
+        return {n_: p_.detach().clone() for n_, p_ in wrap.model.named_parameters()}
+
+    # ---- LevelWrapper: threshold 0.3, check every 2 steps
+    lv = _load_old("levels")
+    wrap = lv.LevelWrapper("synthetic", "tiny", B, model_init, Tok(), lr, -100, 0.45, 2)
+    before = start(wrap)
+    rates = []
+    orig = wrap.check_success
+
+    def spy(pos, neg):
+        pp = pos[:, 0, (rel_id, nrel_id)].softmax(dim=-1)[:, 0]
+        pn = neg[:, 0, (rel_id, nrel_id)].softmax(dim=-1)[:, 0]
+        rates.append((pp - pn).abs().min().item())
+        orig(pos, neg)
+        spy.last.append(wrap.success_rate[-1])
+    spy.last = []
+    wrap.check_success = spy
+    loader = Loader()
+    logs = wrap.train(loader, total, 2)
+    res["level/loss"] = np.array(logs["loss"]["train"], dtype=np.float64)
+    res["level/lr"] = np.array(logs["lr"], dtype=np.float64)
+    res["level/difficulty"] = np.array(logs["difficulty"]["train"], dtype=np.float64)
+    res["level/success"] = np.array(spy.last, dtype=np.float64)
+    res["level/margin"] = np.array(rates, dtype=np.float64)
+    finish("level", wrap, loader, before)
+
+    # ---- InterpWrapper: 0 -> 1 over 24 samples
+    ip = _load_old("interp")
+    wrap = ip.InterpWrapper("synthetic", "tiny", B, model_init, Tok(), lr, -100, 0.0, 1.0, 24)
+    before = start(wrap)
+    loader = Loader()
+    logs = wrap.train(loader, total, 2 * B)
+    res["interp/loss"] = np.array(logs["loss"]["train"], dtype=np.float64)
+    res["interp/lr"] = np.array(logs["lr"], dtype=np.float64)
+    res["interp/difficulty"] = np.array(logs["difficulty"]["train"], dtype=np.float64)
+    finish("interp", wrap, loader, before)
+
+    # ---- EtaWrapper: eta 0.5, Adam(meta_lr) on the threshold, clamp to [1e-10, 1]
+    eb = _load_old("eta_bound")
+    eb.EtaWeights = rw.EtaWeights
+    wrap = eb.EtaWrapper(0.9, "synthetic", "tiny", B, model_init, Tok(), lr, meta_lr, -100)
+    before = start(wrap)
+    loader = Loader()
+    pm, rm = [], []
+    orig_probs, orig_rate = wrap.check_probs, wrap.check_success_rate
+
+    def spy_probs(pos, neg):
+        pp = pos[:, 0, (rel_id, nrel_id)].softmax(dim=-1)[:, 0]
+        pn = neg[:, 0, (rel_id, nrel_id)].softmax(dim=-1)[:, 0]
+        pm.append((pp - pn).abs().min().item())
+        orig_probs(pos, neg)
+
+    def spy_rate(loss):
+        rm.append((loss - wrap.weights.eta.item()).abs().min().item())
+        orig_rate(loss)
+    wrap.check_probs, wrap.check_success_rate = spy_probs, spy_rate
+    logs = wrap.train(loader, total, 2 * B)
+    res["eta/probs_margin"] = np.array(pm, dtype=np.float64)
+    res["eta/rate_margin"] = np.array(rm, dtype=np.float64)
+    res["eta/loss_main"] = np.array(logs["loss"]["main"], dtype=np.float64)
+    res["eta/loss_meta"] = np.array(logs["loss"]["meta"], dtype=np.float64)
+    res["eta/lr_main"] = np.array(logs["lr"]["main"], dtype=np.float64)
+    res["eta/lr_meta"] = np.array(logs["lr"]["meta"], dtype=np.float64)
+    res["eta/eta"] = np.array(logs["eta"], dtype=np.float64)
+    res["eta/difficulty"] = np.array(logs["difficulty"], dtype=np.float64)
+    res["eta/probs"] = np.array(logs["probs"], dtype=np.float64)
+    res["eta/running_rate"] = np.array(wrap.running_rate, dtype=np.float64)
+    finish("eta", wrap, loader, before)
+    for k_, v in res.items():
+        if not k_.endswith("names") and not k_.endswith("dnorm"):
+            print(k_, np.asarray(v))
+    np.savez_compressed(
+        out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
+                            dims.n_heads]), seed=np.array(seed), pids=pids, nids=nids,
+        hp=np.array([B, lr, meta_lr, total, rel_id, nrel_id, n_neg]), **{k_: np.asarray(v) for k_, v in res.items()})
+
+
+def fake_tokenizer():
+    """Deterministic stand-in for T5Tokenizer (SentencePiece is out of scope): word -> 2 + crc32 % 30000, </s> = 1,
+    pad-to-longest with 0 — the call surface LCEDataModule.collate uses (lceT5.py:38-54).  Shared by the test."""
+    import zlib
+
+    class Enc(dict):
+        __getattr__ = dict.__getitem__
+
+    class Tok:
+        def __call__(self, texts, padding=True, return_tensors="pt"):
+            rows = [[2 + zlib.crc32(w.encode()) % 30000 for w in t.split()] + [1] for t in texts]
+            L = max(len(r) for r in rows)
+            ids = torch.tensor([r + [0] * (L - len(r)) for r in rows], dtype=torch.int64)
+            return Enc(input_ids=ids, attention_mask=(ids != 0).long())
+    return Tok()
+
+
+def datamodule_case(tmpdir):
+    """Synthetic candidate file in the format utilities/compute_all_bm25.py:34-49 writes."""
+    import json
+    rng = np.random.RandomState(77)
+    Q, C, D = 12, 50, 400
+    recs = []
+    for q in range(Q):
+        docs = rng.permutation(D)[:C + 1]
+        recs.append({"query_id": str(q), "doc_id_a": str(docs[0]), "doc_id_b": [str(x) for x in docs[1:]]})
+    path = os.path.join(tmpdir, "cands.json")
+    with open(path, "w") as f:
+        json.dump(recs, f)
+
+    class Corpus:
+        def docs_iter(self):
+            for i in range(D):
+                yield {"doc_id": str(i), "text": " ".join(f"w{(i * 7 + j) % 97}" for j in range(3 + i % 5))}
+
+        def queries_iter(self):
+            for i in range(Q):
+                yield {"query_id": str(i), "text": f"what is q{i} about"}
+    return path, Corpus()
+
+
+def gold_datamodule(rt, out):
+    """LCEDataModule.setup / collate / train_dataloader + ChangeDifficulty (lceT5.py:13-80) executed unmodified
+    (num_workers=0 so the global numpy stream is the one consumed): every batch's token ids and labels."""
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        path, corpus = datamodule_case(tmp)
+        sys.modules["ir_datasets"].load = lambda name: corpus
+        dm = rt.LCEDataModule(data_dir=path, corpus="synthetic", tokenizer=fake_tokenizer(), batch_size=4,
+                              shuffle=False, use_max=False, var=0.01, n=3, init_weight=0.3, num_workers=0)
+        dm.setup()
+        np.random.seed(2024)
+        dl = dm.train_dataloader()
+        cb = rt.ChangeDifficulty()
+        trainer = types.SimpleNamespace(train_dataloader=dl)
+        res = {}
+        for i, (p, n) in enumerate(dl):
+            res[f"p{i}"], res[f"n{i}"] = p["input_ids"].numpy(), n["input_ids"].numpy()
+            res[f"pl{i}"], res[f"nl{i}"] = p["labels"].numpy(), n["labels"].numpy()
+            cb.on_train_batch_start(trainer, types.SimpleNamespace(difficulty=0.2 + 0.35 * i), (p, n), i)
+            res[f"w{i}"] = np.float64(dl.dataset.weight)
+        res["after"] = np.float64(np.random.random_sample())
+        res["batches"] = np.array(i + 1)
+        np.savez_compressed(out, **res)
+
+
 def main():
     rw, rd, rl, rt, rp = import_reference()
     gold_weights(rw, rt, os.path.join(HERE, "weights_golden.npz"))
@@ -484,6 +729,8 @@ def main():
     gold_t5(rt, os.path.join(HERE, "t5_tiny_golden.npz"))
     gold_train(rt, os.path.join(HERE, "train_golden.npz"))
     gold_newwrapper(rp, rw, os.path.join(HERE, "newwrapper_golden.npz"))
+    gold_scalar_wrappers(rp, rw, os.path.join(HERE, "scalar_wrappers_golden.npz"))
+    gold_datamodule(rt, os.path.join(HERE, "datamodule_golden.npz"))
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -82,3 +82,20 @@ def test_checkpoint_directory_loader(tmp_path):
     import pytest
     with pytest.raises(ValueError):
         dims_from_hf_config({**hf_config(dims), "feed_forward_proj": "gated-gelu"})
+
+
+def test_host_pacing_helpers_without_gpu():
+    """interpolate_scalar (old/interp.py:10-18) and ChangeDifficulty (lceT5.py:77-80) are pure host logic."""
+    import types
+    from pacednegatives_b200.wrappers import interpolate_scalar
+    from pacednegatives_b200.lceT5 import ChangeDifficulty, linear_schedule_with_warmup
+    f = interpolate_scalar(0.0, 1.0, 24)
+    assert [f(s) for s in (0, 4, 24, 25, 1000)] == [0.0, 4 * (1.0 / 24), 24 * (1.0 / 24), 1.0, 1.0]
+    ds = types.SimpleNamespace(weight=0.0)
+    trainer = types.SimpleNamespace(train_dataloader=types.SimpleNamespace(dataset=ds))
+    cb = ChangeDifficulty()
+    cb.on_train_batch_start(trainer, types.SimpleNamespace(difficulty=0.4), None, 0)
+    assert ds.weight == 0.4
+    cb.on_train_batch_start(trainer, types.SimpleNamespace(difficulty=3.0), None, 1)
+    assert ds.weight == 1 - 1e-10
+    assert linear_schedule_with_warmup(1, 2, 12) == 0.5 and linear_schedule_with_warmup(7, 2, 12) == 0.5

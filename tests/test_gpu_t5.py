@@ -147,3 +147,45 @@ def test_missing_weight_is_an_error():
     del w["decoder.block.0.layer.1.EncDecAttention.k.weight"]
     with pytest.raises(ValueError, match="missing weight"):
         MonoT5Scorer(T5Dims(**dims.__dict__), w)
+
+
+LARGE_WIDTH = dict(vocab=2048, d_model=1024, d_kv=64, d_ff=4096, n_layers=2, n_dec_layers=2, n_heads=16)
+
+
+def test_large_width_score_vs_oracle():
+    """T5-large's layer shape (d 1024, 16 heads, ff 4096 — BASELINE configs[3]) at two layers per stack."""
+    dims = ot.T5Dims(**LARGE_WIDTH)
+    w, m = make(dims, 13, rel_id=117, nrel_id=213)
+    ids = rand_ids(np.random.RandomState(99), 3, 512, dims.vocab)
+    s, z2 = m.score(ids, return_z2=True)
+    es, ez = ot.score(w, dims, ids, 117, 213)
+    np.testing.assert_allclose(z2.cpu().numpy(), ez, atol=TOL)
+    np.testing.assert_allclose(s.cpu().numpy(), es, atol=TOL)
+
+
+def test_large_width_training_forward_and_gradients():
+    """Same layer shape through the training path: logits of the saved-activation forward equal the oracle's,
+    and the backward with the projection-free cross-attention (T*H = 32 query rows per document) agrees with the
+    K/V-projection backward."""
+    from pacednegatives_b200.lceT5 import MonoT5Model
+    from pacednegatives_b200.scorer import T5Dims
+    from pacednegatives_b200.loss import token_ce
+    dims = ot.T5Dims(**LARGE_WIDTH)
+    w = ot.init_weights(dims, seed=13)
+    sd = {k: torch.as_tensor(v) for k, v in w.items()}
+    ids = rand_ids(np.random.RandomState(5), 4, 256, dims.vocab)
+    lab = np.array([[117, 1], [213, 1], [213, 1], [213, 1]], dtype=np.int64)
+    exp = ot.logits(w, dims, ids, lab)
+    grads = []
+    for xattn in (True, False):
+        m = MonoT5Model(T5Dims(**dims.__dict__), sd, xattn=xattn)
+        logits = m(torch.tensor(ids), torch.tensor(lab))
+        np.testing.assert_allclose(logits.detach().cpu().numpy(), exp, atol=3e-2)
+        ce = token_ce(logits.reshape(-1, dims.vocab), torch.tensor(lab).cuda().view(-1))
+        m.zero_grad()
+        ce.mean().backward()
+        torch.cuda.synchronize()
+        assert torch.isfinite(m.grads).all()
+        grads.append(m.grads.clone())
+    rel = (grads[0] - grads[1]).norm().item() / grads[1].norm().item()
+    assert rel < 3e-2, rel

@@ -60,6 +60,33 @@ def test_training_step_vs_reference_golden(golden_dir, elide, xattn):
     assert abs(m.weights.eta.item() - float(g["eta1"])) < 2e-4
 
 
+@pytest.mark.parametrize("elide", [True, False])
+def test_micro_batched_step_matches_golden_and_full_batch(golden_dir, elide):
+    """hparams['micro_queries'] walks the batch in query groups (how T5-large 1+31 x 512 fits, BASELINE configs[3]):
+    same losses / eta as the reference's golden step, gradients equal to the single-batch step's up to the fp32
+    summation order of the split (bf16 rounding of each GEMM is per document, so it does not depend on the split)."""
+    from pacednegatives_b200.lceT5 import LCEModel
+    from pacednegatives_b200.scorer import T5Dims
+    g, dims, hp, batch = load_case(golden_dir)
+    w = ot.init_weights(dims, seed=int(g["seed"]))
+    sd = {k: torch.as_tensor(v) for k, v in w.items()}
+    Q = batch[0]["input_ids"].shape[0]
+    assert Q >= 2
+    full = LCEModel(dict(hp), dims=T5Dims(**dims.__dict__), state_dict=sd, elide_no_grad_forward=elide)
+    micro = LCEModel(dict(hp, micro_queries=max(1, Q // 2)), dims=T5Dims(**dims.__dict__),
+                     state_dict=sd, elide_no_grad_forward=elide)
+    of, om = full.training_step(batch, 0), micro.training_step(batch, 0)
+    assert abs(float(om["main_loss"]) - float(g["main_loss0"])) < 2e-2
+    assert abs(float(om["main_loss"]) - float(of["main_loss"])) < 1e-5
+    assert abs(float(om["meta_loss"]) - float(of["meta_loss"])) < 1e-5
+    assert abs(micro.weights.eta.item() - full.weights.eta.item()) < 1e-7
+    gf, gm = full.model.grads, micro.model.grads
+    assert (gf - gm).norm().item() < 2e-3 * gf.norm().item()
+    o1 = micro.training_step(batch, 1)
+    assert abs(float(o1["main_loss"]) - float(g["main_loss1"])) < 5e-2
+    assert abs(micro.weights.eta.item() - float(g["eta1"])) < 2e-4
+
+
 def test_adamw_kernel_vs_transformers_rule():
     from pacednegatives_b200 import _lib
     _lib.require_gpu()
