@@ -51,6 +51,21 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "src": "fallback"}
 
 
+def ncu_traffic(workload, rows_per_launch):
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture
+    (profiles/traffic.json), scaled by rows when the bench launch processes a different number of token rows than
+    the captured one (every operand and output of these GEMMs but the weights scales with rows).  None when no
+    capture of that workload is committed."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    with open(p) as f:
+        d = json.load(f).get(workload)
+    if not d:
+        return None, None
+    return d["traffic_bytes_per_launch"] * rows_per_launch / d["rows_per_launch"], d["source"]
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -271,6 +286,7 @@ def bench_rerank(args):
     e2e_value = pairs / (e2e_ms / 1e3)
     peaks = measured_peaks()
     fpd = flops_per_doc(dims, S, 1, False)
+    traffic, traffic_src = ncu_traffic("rerank", min(args.chunk_docs, n_docs) * S)
     gemm_tflops = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
     line = {
         "metric": "monoT5-base rerank pairs/s", "value": value, "unit": "pairs/s", "n_gpus": WORLD,
@@ -297,7 +313,7 @@ def bench_rerank(args):
                      "attention": {"tflops": a_flops / (a_ms / 1e3) / 1e12 if a_ms else 0.0,
                                    "launches": int(a_n), "share_of_step": a_ms / ms if ms else None},
                      "hbm_bound_gemms": hbm_gemm_entry(h_ms, h_n, h_bytes, ms, peaks),
-                     "traffic": None},
+                     "traffic": traffic, "traffic_source": traffic_src},
         "clocks": clk,
     }
     if RANK == 0:

@@ -121,6 +121,21 @@ int pn_lce_restricted_bwd(const float* z2, int64_t Q, int32_t G, const float* g,
 int pn_check_success(const float* pos_logits, const float* neg_logits, int64_t n, int64_t pos_stride,
                      int64_t neg_stride, int32_t rel_id, int32_t nrel_id, int32_t* count_out, void* stream);
 
+/* ------------------------------------------------------------------ a2 / 8f-2
+ * On-device prompt packing: 'Query: ' + q + ' Document: ' + d + ' Relevant:' (dataloader.py:43-44,66-67,153-155)
+ * from pre-tokenised pieces in HBM, padded to S like tokenizer(..., padding=True) (lceT5.py:46-47,
+ * pairwrapper.py:79-80).  prefix / middle / suffix: int32 ids of 'Query:', 'Document:', 'Relevant:' + </s>;
+ * q_tok/q_off, d_tok/d_off: CSR token stores (off has n+1 int64 entries); q_idx / d_idx [n]: the (query, document)
+ * of each output row (d_idx is what pn_select_* wrote as doc ids).  max_len = 0 keeps whole documents (the
+ * reference does not truncate); max_len > 0 drops the document's tail so the row ends in ' Relevant:</s>' within
+ * max_len tokens.  ids_out [n, S] nullable (NULL = lengths only), len_out [n] nullable (-1 for an out-of-range
+ * index), status_out[2] = {longest row, #rows that are out of range or longer than S (those rows are all pad)}. */
+int pn_pack_prompts(const int32_t* prefix, int32_t n_prefix, const int32_t* middle, int32_t n_middle,
+                    const int32_t* suffix, int32_t n_suffix, const int32_t* q_tok, const int64_t* q_off,
+                    int64_t n_queries, const int32_t* d_tok, const int64_t* d_off, int64_t n_docs,
+                    const int32_t* q_idx, const int32_t* d_idx, int64_t n, int32_t S, int32_t max_len,
+                    int32_t pad_id, int32_t* ids_out, int32_t* len_out, int32_t* status_out, void* stream);
+
 /* ------------------------------------------------------------------ a7
  * Level-paced negative pick (dataloader.py:29-33): r = floor|ceil(w * n_neg), n_neg = C-1,
  * computed in fp64 like the Python float the reference multiplies.

@@ -157,3 +157,31 @@ def np_pairwise_sum(a):
     n2 = n // 2
     n2 -= n2 % 8
     return np_pairwise_sum(a[:n2]) + np_pairwise_sum(a[n2:])
+
+
+def format_prompt(q, d):
+    """dataloader.py:43-44 / 66-67 / 153-155."""
+    return 'Query: ' + q + ' Document: ' + d + ' Relevant:'
+
+
+def pack_prompts(prefix, middle, suffix, q_tokens, d_tokens, q_idx, d_idx, S=None, max_len=0, pad_id=0):
+    """Token ids of ``tokenizer([format_prompt(q, d), ...], padding=True)`` (lceT5.py:46-47, pairwrapper.py:79-80)
+    assembled from pre-tokenised pieces: prefix = ids of 'Query:', middle = 'Document:', suffix = 'Relevant:' + </s>,
+    q_tokens / d_tokens = per-query / per-document id lists (no </s>).  SentencePiece segments whitespace-separated
+    words independently, so concatenating the pieces' ids equals tokenising the concatenated string.  max_len > 0
+    drops the document's tail so the row still ends in the suffix (the reference never truncates: max_len = 0).
+    Returns (ids int32 [n, S] padded with pad_id, lengths int32 [n]); S defaults to the longest row."""
+    rows = []
+    for qi, di in zip(q_idx, d_idx):
+        q, d = list(q_tokens[qi]), list(d_tokens[di])
+        fixed = len(prefix) + len(middle) + len(suffix) + len(q)
+        if max_len > 0 and fixed + len(d) > max_len:
+            d = d[:max(0, max_len - fixed)]
+        rows.append(list(prefix) + q + list(middle) + d + list(suffix))
+    lengths = np.array([len(r) for r in rows], dtype=np.int32)
+    S = int(lengths.max()) if S is None else S
+    out = np.full((len(rows), S), pad_id, dtype=np.int32)
+    for i, r in enumerate(rows):
+        if len(r) <= S:
+            out[i, :len(r)] = r
+    return out, lengths

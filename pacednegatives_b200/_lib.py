@@ -31,6 +31,8 @@ SIGNATURES = {
     "pn_lce_restricted_fwd": (c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, c_vp]),
     "pn_lce_restricted_bwd": (c_int, [c_vp, c_i64, c_i32, c_vp, c_vp, c_vp]),
     "pn_check_success": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i32, c_i32, c_vp, c_vp]),
+    "pn_pack_prompts": (c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64, c_vp, c_vp,
+                                c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "pn_select_level_scalar": (c_int, [c_vp, c_i64, c_i32, c_int, c_f64, c_int, c_vp, c_vp, c_vp,
                                        c_vp]),
     "pn_select_level_items": (c_int, [c_vp, c_i64, c_i32, c_int, c_vp, c_int, c_vp, c_vp, c_vp,

@@ -300,3 +300,75 @@ class LCEDataset(torch.utils.data.Dataset):
         qp, n = self.get((idx, _idx))
         q, p = qp
         return {'pos': self.format(q, p), 'neg': list(map(partial(self.format, q), n))}
+
+
+class TokenStore:
+    """Pre-tokenised texts as a CSR pair in HBM: ``tok`` int32 [total], ``off`` int64 [n + 1].  Built once from the
+    tokenizer's id lists (no </s>); MS MARCO passage (8.8 M x ~75 tokens) is ~2.7 GB."""
+
+    def __init__(self, id_lists):
+        lens = np.fromiter((len(x) for x in id_lists), dtype=np.int64, count=len(id_lists))
+        off = np.zeros(len(id_lists) + 1, dtype=np.int64)
+        np.cumsum(lens, out=off[1:])
+        flat = np.empty(int(off[-1]), dtype=np.int32)
+        for i, x in enumerate(id_lists):
+            flat[off[i]:off[i + 1]] = x
+        _lib.require_gpu()
+        self.n = len(id_lists)
+        self.tok = torch.from_numpy(flat).cuda()
+        self.off = torch.from_numpy(off).cuda()
+
+
+class PromptPacker:
+    """'Query: ' + q + ' Document: ' + d + ' Relevant:' (``format``, dataloader.py:43-44) assembled on the GPU from
+    token stores (pn_pack_prompts): rows come out as the int32 [n, S] matrix the scorer reads, padded like
+    ``tokenizer(prompts, padding=True)``; nothing passes through the host but the 8-byte status word.
+
+    ``tokenizer`` is only used here, once, for the three literal pieces (any callable ``encode(str) -> ids`` whose
+    result ends in </s>, like T5Tokenizer.encode)."""
+
+    def __init__(self, tokenizer=None, prefix=None, middle=None, suffix=None, pad_id=0):
+        if tokenizer is not None:
+            prefix = list(tokenizer.encode('Query:'))[:-1]
+            middle = list(tokenizer.encode('Document:'))[:-1]
+            suffix = list(tokenizer.encode('Relevant:'))
+        _lib.require_gpu()
+        self.pieces = [torch.tensor(list(x), dtype=torch.int32, device="cuda") for x in (prefix, middle, suffix)]
+        self.pad_id = int(pad_id)
+
+    def pack(self, queries, docs, q_idx, d_idx, S=None, max_len=0):
+        """queries / docs: TokenStore; q_idx / d_idx: int32 device tensors [n] (d_idx straight from the selection
+        kernels).  S None -> pad to the longest row of this batch (one extra lengths-only launch and a D2H of the
+        status word); a fixed S (e.g. 512) needs no host round trip before the scorer.  Returns (ids, lengths)."""
+        q_idx = q_idx.to(device="cuda", dtype=torch.int32).contiguous()
+        d_idx = d_idx.to(device="cuda", dtype=torch.int32).contiguous()
+        n = q_idx.numel()
+        if d_idx.numel() != n:
+            raise ValueError("q_idx and d_idx must have the same length")
+        lens = torch.empty(n, dtype=torch.int32, device="cuda")
+        status = torch.empty(2, dtype=torch.int32, device="cuda")
+        lib = _lib.lib()
+
+        def call(ids, width):
+            p = self.pieces
+            _lib.check(lib.pn_pack_prompts(_lib.ptr(p[0]), p[0].numel(), _lib.ptr(p[1]), p[1].numel(), _lib.ptr(p[2]),
+                                           p[2].numel(), _lib.ptr(queries.tok), _lib.ptr(queries.off), queries.n,
+                                           _lib.ptr(docs.tok), _lib.ptr(docs.off), docs.n, _lib.ptr(q_idx),
+                                           _lib.ptr(d_idx), n, width, int(max_len), self.pad_id, _lib.ptr(ids),
+                                           _lib.ptr(lens), _lib.ptr(status), _lib.stream()))
+        if S is None:
+            call(None, 0)
+            longest, bad = status.cpu().tolist()
+            if bad:
+                raise IndexError(f"pack: {bad} (query, document) indices out of range")
+            S = max(int(longest), 1)
+        ids = torch.empty(n, int(S), dtype=torch.int32, device="cuda")
+        call(ids, int(S))
+        self.last_status = status
+        return ids, lens
+
+    def check(self):
+        """Raise if the last pack() had rows longer than S or indices out of range (reads the status word)."""
+        longest, bad = self.last_status.cpu().tolist()
+        if bad:
+            raise ValueError(f"pack: {bad} rows out of range or longer than the row width (longest {longest})")

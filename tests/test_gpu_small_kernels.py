@@ -388,3 +388,65 @@ def test_argument_errors(pn):
     assert b"bad argument" in pn.lib.lib().pn_last_error()
     with pytest.raises(ValueError):
         pn.m.topk_metrics(torch.zeros(1, 5000).cuda())
+
+
+def _ragged(rng, n, lo, hi, vocab=32000):
+    return [rng.randint(2, vocab, size=rng.randint(lo, hi + 1)).tolist() for _ in range(n)]
+
+
+@pytest.mark.parametrize("n", [0, 1, 37, 3000])
+def test_pack_prompts_vs_oracle(n):
+    """pn_pack_prompts: bit-exact against the oracle for ragged stores, pad-to-longest and fixed
+    width, document truncation, and out-of-range indices."""
+    from oracle import select as osel
+    from pacednegatives_b200.dataloader import PromptPacker, TokenStore
+    rng = np.random.RandomState(n + 5)
+    q_tokens, d_tokens = _ragged(rng, 50, 0, 12), _ragged(rng, 400, 0, 90)
+    prefix, middle, suffix = [3, 4], [9], [7, 8, 1]
+    qs, ds = TokenStore(q_tokens), TokenStore(d_tokens)
+    pk = PromptPacker(prefix=prefix, middle=middle, suffix=suffix, pad_id=0)
+    q_idx = rng.randint(0, 50, size=n).astype(np.int32)
+    d_idx = rng.randint(0, 400, size=n).astype(np.int32)
+    tq, td = torch.tensor(q_idx).cuda(), torch.tensor(d_idx).cuda()
+    if n == 0:
+        ids, lens = pk.pack(qs, ds, tq, td, S=16)
+        assert ids.shape == (0, 16) and lens.numel() == 0
+        return
+    ids, lens = pk.pack(qs, ds, tq, td)                                   # pad to the longest row
+    eids, elens = osel.pack_prompts(prefix, middle, suffix, q_tokens, d_tokens, q_idx, d_idx)
+    np.testing.assert_array_equal(ids.cpu().numpy(), eids)
+    np.testing.assert_array_equal(lens.cpu().numpy(), elens)
+    ids, lens = pk.pack(qs, ds, tq, td, S=128)                            # fixed width, everything fits
+    eids, _ = osel.pack_prompts(prefix, middle, suffix, q_tokens, d_tokens, q_idx, d_idx, S=128)
+    np.testing.assert_array_equal(ids.cpu().numpy(), eids)
+    pk.check()
+    ids, lens = pk.pack(qs, ds, tq, td, S=64, max_len=40)                 # truncated documents
+    eids, elens = osel.pack_prompts(prefix, middle, suffix, q_tokens, d_tokens, q_idx, d_idx, S=64, max_len=40)
+    np.testing.assert_array_equal(ids.cpu().numpy(), eids)
+    np.testing.assert_array_equal(lens.cpu().numpy(), elens)
+    assert int(lens.max()) <= 40
+    if n >= 37:
+        ids, lens = pk.pack(qs, ds, tq, td, S=48)                         # rows longer than S are flagged, all pad
+        eids, elens = osel.pack_prompts(prefix, middle, suffix, q_tokens, d_tokens, q_idx, d_idx, S=48)
+        np.testing.assert_array_equal(ids.cpu().numpy(), eids)
+        assert (elens > 48).any()
+        with pytest.raises(ValueError):
+            pk.check()
+        bad = td.clone()
+        bad[3] = 400
+        with pytest.raises(IndexError):
+            pk.pack(qs, ds, tq, bad)
+
+
+def test_pack_prompts_feeds_the_reference_collate_batches(tmp_path):
+    """End to end against the reference: the positives' prompts of tests/golden/datamodule_golden.npz, packed on the
+    GPU from token stores, equal the ids LCEDataModule.collate produced (lceT5.py:38-54)."""
+    from test_oracle_golden import _datamodule_positive_case
+    from pacednegatives_b200.dataloader import PromptPacker, TokenStore
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "datamodule_golden.npz"))
+    (prefix, middle, suffix), q_tokens, d_tokens, q_idx, d_idx = _datamodule_positive_case(tmp_path)
+    qs, ds = TokenStore(q_tokens), TokenStore(d_tokens)
+    pk = PromptPacker(prefix=prefix, middle=middle, suffix=suffix)
+    for i in range(int(g["batches"])):
+        ids, _ = pk.pack(qs, ds, torch.tensor(q_idx[4 * i:4 * i + 4]), torch.tensor(d_idx[4 * i:4 * i + 4]))
+        np.testing.assert_array_equal(ids.cpu().numpy(), g[f"p{i}"])

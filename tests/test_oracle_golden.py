@@ -148,3 +148,43 @@ def test_relative_bucket_vs_hf():
     rel = torch.arange(-600, 601)
     hb = tr.T5Attention._relative_position_bucket(rel, bidirectional=True).numpy()
     np.testing.assert_array_equal(ot.relative_bucket(rel.numpy(), True), hb)
+
+
+def _datamodule_positive_case(tmp_path):
+    """Pieces of the prompts in tests/golden/datamodule_golden.npz (written by the reference's LCEDataModule)."""
+    import json
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_golden as mg
+    path, corpus = mg.datamodule_case(str(tmp_path))
+    tok = mg.fake_tokenizer()
+    enc = lambda s: tok([s])["input_ids"][0].tolist()      # ids + </s>
+    docs = list(corpus.docs_iter())
+    queries = list(corpus.queries_iter())
+    d_tokens = [enc(d["text"])[:-1] for d in docs]
+    q_tokens = [enc(q["text"])[:-1] for q in queries]
+    with open(path) as f:
+        recs = json.load(f)
+    q_idx = [int(r["query_id"]) for r in recs]
+    d_idx = [int(r["doc_id_a"]) for r in recs]
+    pieces = (enc("Query:")[:-1], enc("Document:")[:-1], enc("Relevant:"))
+    return pieces, q_tokens, d_tokens, q_idx, d_idx
+
+
+def test_pack_prompts_oracle_vs_reference_collate(tmp_path):
+    """oracle.select.pack_prompts == tokenizer(format(q, d), padding=True) as the reference's LCEDataModule.collate
+    produced it for the positives of every batch (lceT5.py:38-54 through dataloader.py:153-162)."""
+    from oracle import select as osel
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "datamodule_golden.npz"))
+    (prefix, middle, suffix), q_tokens, d_tokens, q_idx, d_idx = _datamodule_positive_case(tmp_path)
+    B = 4
+    for i in range(int(g["batches"])):
+        ids, lens = osel.pack_prompts(prefix, middle, suffix, q_tokens, d_tokens, q_idx[i * B:(i + 1) * B],
+                                      d_idx[i * B:(i + 1) * B])
+        np.testing.assert_array_equal(ids, g[f"p{i}"])
+        assert lens.max() == g[f"p{i}"].shape[1]
+    # truncation keeps the suffix and only shortens the document
+    ids, lens = osel.pack_prompts(prefix, middle, suffix, q_tokens, d_tokens, q_idx[:4], d_idx[:4], S=16, max_len=12)
+    assert (lens <= 12).all() and ids.shape == (4, 16)
+    for r, n in zip(ids, lens):
+        assert list(r[n - len(suffix):n]) == list(suffix) and (r[n:] == 0).all()
