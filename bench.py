@@ -629,16 +629,18 @@ def bench_train_reference(args):
     """`--impl reference --workload train`: HF fp32 forward+backward+AdamW on the host cores, rank 0 only."""
     if RANK != 0:
         return
-    S, k = 512, 15
+    large = args.model == "large"
+    S, k = 512, args.negatives if args.negatives else (31 if large else 15)
+    tag, cfg_i = ("T5-large", 3) if large else ("monoT5-base", 2)
     n = args.ref_train_docs
     torch.set_num_threads(os.cpu_count() or 1)
-    v, how, dt = hf_train_sample(n, S, args.steps, args.warmup)
+    v, how, dt = hf_train_sample(n, S, args.steps, args.warmup, large=large)
     qs = v / (1 + k)
-    line = {"impl": "reference", "metric": "LCE training queries/s (1+15 docs per query)", "value": qs,
+    line = {"impl": "reference", "metric": f"LCE training queries/s (1+{k} docs per query)", "value": qs,
             "unit": "queries/s", "n_gpus": WORLD, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "LCE training step, monoT5-base, 1+15 docs per query, seq 512 (BASELINE configs[2])",
+            "config": {"workload": f"LCE training step, {tag}, 1+{k} docs per query, seq 512 (BASELINE configs[{cfg_i}])",
                        "sample_docs_per_step": n, "seq_len": S},
             "gpu_launches": 0,
             "cpu_baseline": {"value": qs, "unit": "queries/s", "cores": torch.get_num_threads(),

@@ -5,8 +5,9 @@
 //   ndcg_cut_K: gain = rel (linear), discount log2(rank+1), ideal = the query's rels sorted desc
 //   recip_rank: 1 / rank of the first doc with rel >= 1 (whole list); rr@K the same cut at K
 //   map       : mean over relevant docs of precision at their rank
-// One CTA per query: C candidates (<= 4096) are packed to 64-bit keys in shared memory and sorted with
-// a bitonic network; HBM traffic is the C*(4+4+1) input bytes once.
+// One CTA per query: C candidates (<= 4096) are packed to 64-bit keys in shared memory; HBM traffic is the
+// C*(4+4+1) input bytes once.  K <= 32 (the nDCG@10 / MRR@10 case) takes the sort-free topk_count_kernel below;
+// larger K sorts the keys with a bitonic network.
 #include "pn_common.cuh"
 
 namespace {
@@ -135,6 +136,156 @@ topk_metrics_kernel(const float* __restrict__ scores, const int32_t* __restrict_
   }
 }
 
+// ---- K <= 32: no sort.  What the measures need is (a) the K best keys in order and (b) the rank of every RELEVANT
+// document, and judged-relevant documents are few (a few percent of the list):
+//   (a) K rounds of a block-wide arg-max over the keys still below the previous winner (keys are unique: the low
+//       word is the document id), one barrier per round;
+//   (b) rank(d) = #{keys > key_d}, counted by 4 threads per relevant document sweeping the shared key array
+//       (every load is a broadcast or a 32-byte row: no bank conflicts, no barriers, fully unrolled);
+//   AP then counts, for each relevant document, the relevant documents ranked at or above it.
+// Per query ~ R*C/32 + K*C/256 compare instructions per warp instead of 55 barrier-separated bitonic stages.
+constexpr int kFastMaxK = 32;
+
+__global__ void __launch_bounds__(kThreads)
+topk_count_kernel(const float* __restrict__ scores, const int32_t* __restrict__ docids,
+                  const uint8_t* __restrict__ rels, int64_t Q, int32_t C, int32_t K,
+                  int32_t* __restrict__ top_ids, float* __restrict__ top_scores, float* __restrict__ metrics) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int Cp = (C + 3) & ~3;
+  uint64_t* key = reinterpret_cast<uint64_t*>(smem_raw);          // [Cp], padding keys = 0 (below every real key)
+  uint16_t* rel_pos = reinterpret_cast<uint16_t*>(key + Cp);      // [C] positions of the relevant documents
+  uint16_t* rel_rank = rel_pos + Cp;                              // [C] their 0-based ranks
+  uint8_t* srel = reinterpret_cast<uint8_t*>(rel_rank + Cp);      // [C]
+  __shared__ int hist[256];
+  __shared__ int s_nrel, s_gmax;
+  __shared__ uint64_t s_best[2][kThreads / 32];
+  __shared__ uint64_t s_top[kFastMaxK];
+  __shared__ int s_toprel[kFastMaxK];
+  __shared__ double s_ap[kThreads / 32];
+  __shared__ int s_first[kThreads / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  for (int64_t q = blockIdx.x; q < Q; q += gridDim.x) {
+    const float* sc = scores + q * (int64_t)C;
+    const int32_t* ids = docids ? docids + q * (int64_t)C : nullptr;
+    const uint8_t* rl = rels ? rels + q * (int64_t)C : nullptr;
+    hist[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { s_nrel = 0; s_gmax = 0; }
+    if (threadIdx.x < kFastMaxK) { s_top[threadIdx.x] = 0ull; s_toprel[threadIdx.x] = 0; }
+    __syncthreads();
+    for (int i = threadIdx.x; i < Cp; i += kThreads) {
+      if (i < C) {
+        const int32_t id = ids ? __ldg(ids + i) : i;
+        key[i] = ((uint64_t)orderable(__ldg(sc + i)) << 32) | (uint32_t)(id ^ 0x80000000);
+        const uint8_t r = rl ? __ldg(rl + i) : 0;
+        srel[i] = r;
+        if (r) {
+          atomicAdd(&hist[r], 1);
+          atomicMax(&s_gmax, (int)r);
+          rel_pos[atomicAdd(&s_nrel, 1)] = (uint16_t)i;
+        }
+      } else {
+        key[i] = 0ull;
+      }
+    }
+    __syncthreads();
+    const int R = s_nrel;
+
+    // (b) ranks of the relevant documents: thread group of 4 per document, each sweeping every 4th key
+    if (metrics && R > 0) {
+      const int sub = threadIdx.x & 3;
+      for (int j0 = 0; j0 < R; j0 += kThreads / 4) {
+        const int j = j0 + (threadIdx.x >> 2);
+        const uint64_t kr = j < R ? key[rel_pos[j]] : ~0ull;
+        int cnt = 0;
+        if (j < R) {
+#pragma unroll 8
+          for (int i = sub; i < Cp; i += 4) cnt += key[i] > kr ? 1 : 0;
+        }
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, 2);
+        if (j < R && sub == 0) rel_rank[j] = (uint16_t)cnt;
+      }
+    }
+
+    // (a) the K best, in order
+    uint64_t prev = ~0ull;
+    const int rounds = K < C ? K : C;
+    for (int rnd = 0; rnd < rounds; ++rnd) {
+      uint64_t best = 0ull;
+      for (int i = threadIdx.x; i < C; i += kThreads) {
+        const uint64_t k = key[i];
+        if (k < prev && k > best) best = k;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const uint64_t other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other > best ? other : best;
+      }
+      if (lane == 0) s_best[rnd & 1][warp] = best;
+      __syncthreads();
+      best = s_best[rnd & 1][0];
+#pragma unroll
+      for (int w = 1; w < kThreads / 32; ++w) best = s_best[rnd & 1][w] > best ? s_best[rnd & 1][w] : best;
+      if (best == 0ull) break;      // fewer than K distinct keys
+      prev = best;
+      for (int i = threadIdx.x; i < C; i += kThreads)
+        if (key[i] == best) { s_top[rnd] = best; s_toprel[rnd] = srel[i]; }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < K; i += kThreads) {
+      const uint64_t k = i < kFastMaxK ? s_top[i] : 0ull;
+      const bool live = k != 0ull;
+      if (top_ids) top_ids[q * K + i] = live ? (int32_t)((uint32_t)k ^ 0x80000000u) : -1;
+      if (top_scores) top_scores[q * K + i] = live ? unorderable((uint32_t)(k >> 32)) : 0.0f;
+    }
+    if (metrics) {
+      // average precision and the first relevant rank, parallel over the relevant documents
+      double ap = 0.0;
+      int first = 0x7fffffff;
+      for (int j = threadIdx.x; j < R; j += kThreads) {
+        const int rk = rel_rank[j];
+        int upto = 0;
+        for (int t = 0; t < R; ++t) upto += rel_rank[t] <= rk ? 1 : 0;
+        ap += (double)upto / (double)(rk + 1);
+        first = min(first, rk);
+      }
+      ap = pn_warp_sum(ap);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+      if (lane == 0) { s_ap[warp] = ap; s_first[warp] = first; }
+      __syncthreads();
+      if (warp == 0) {
+        // DCG@K from the winners' grades; ideal DCG@K from the grade histogram, high to low: lane = slot
+        double dcg = 0.0, idcg = 0.0;
+        if (lane < K) {
+          const double disc = 1.0 / log2((double)(lane + 2));
+          if (s_toprel[lane]) dcg = (double)s_toprel[lane] * disc;
+          int cum = 0, grade = 0;
+          for (int g = s_gmax; g >= 1; --g) {
+            cum += hist[g];
+            if (cum > lane) { grade = g; break; }
+          }
+          idcg = (double)grade * disc;
+        }
+        dcg = pn_warp_sum(dcg);
+        idcg = pn_warp_sum(idcg);
+        if (lane == 0) {
+          double a = 0.0;
+          int f = 0x7fffffff;
+          for (int w = 0; w < kThreads / 32; ++w) { a += s_ap[w]; f = min(f, s_first[w]); }
+          float* m = metrics + q * 4;
+          m[0] = idcg > 0.0 ? (float)(dcg / idcg) : 0.0f;
+          m[1] = f < C ? (float)(1.0 / (double)(f + 1)) : 0.0f;
+          m[2] = f < K ? (float)(1.0 / (double)(f + 1)) : 0.0f;
+          m[3] = R > 0 ? (float)(a / (double)R) : 0.0f;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace
 
 extern "C" int pn_topk_metrics(const float* scores, const int32_t* docids, const uint8_t* rels,
@@ -143,6 +294,16 @@ extern "C" int pn_topk_metrics(const float* scores, const int32_t* docids, const
   PN_CHECK_ARG(Q >= 0 && C >= 1 && C <= 4096 && K >= 1);
   if (Q == 0) return PN_OK;
   PN_CHECK_ARG(scores != nullptr);
+  if (K <= kFastMaxK) {
+    const int Cp = (C + 3) & ~3;
+    const size_t smem = (size_t)Cp * (8 + 2 + 2 + 1);
+    PN_CUDA(cudaFuncSetAttribute(topk_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int grid = (int)(Q < 148 * 8 ? Q : 148 * 8);
+    topk_count_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(scores, docids, rels, Q, C, K, top_ids,
+                                                                      top_scores, metrics_out);
+    PN_LAUNCHED();
+    return PN_OK;
+  }
   int P = 2;
   while (P < C) P <<= 1;
   const size_t smem = (size_t)P * (8 + 2 + 1);

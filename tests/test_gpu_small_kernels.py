@@ -365,7 +365,28 @@ def test_triplet_loaders_dropin(pn, golden_dir):
 
 
 # ------------------------------------------------------------------ top-k + metrics (a12)
-@pytest.mark.parametrize("Q,C,K", [(200, 1000, 10), (3, 7, 10), (5, 1024, 10), (2, 4096, 100), (1, 1, 1)])
+def test_topk_metrics_dense_relevance_and_many_queries(pn):
+    """The sort-free path (K <= 32) when most documents are judged relevant (several counting passes), with more
+    queries than resident CTAs, K = 32, C not a multiple of 4, and grades up to 255."""
+    rng = np.random.RandomState(99)
+    Q, C, K = 1500, 203, 32
+    scores = np.round(rng.randn(Q, C).astype(np.float32), 1)            # heavy ties
+    docids = np.stack([rng.permutation(5000)[:C] for _ in range(Q)]).astype(np.int32)
+    rels = rng.choice([0, 1, 2, 3, 255], size=(Q, C), p=[.2, .4, .2, .15, .05]).astype(np.uint8)
+    rels[7] = 1        # every document relevant
+    rels[8] = 0
+    out = pn.m.topk_metrics(torch.tensor(scores).cuda(), torch.tensor(docids).cuda(), torch.tensor(rels).cuda(), K)
+    eids, esc, em = om.batch_metrics(scores, docids, rels, K)
+    np.testing.assert_array_equal(out["top_ids"].cpu().numpy(), eids)
+    np.testing.assert_array_equal(out["top_scores"].cpu().numpy(), esc)
+    np.testing.assert_allclose(out["metrics"].cpu().numpy(), em, rtol=1e-6, atol=1e-7)
+    # both paths agree on the same input (K = 33 takes the bitonic sort)
+    out33 = pn.m.topk_metrics(torch.tensor(scores).cuda(), torch.tensor(docids).cuda(), torch.tensor(rels).cuda(), 33)
+    np.testing.assert_array_equal(out33["top_ids"].cpu().numpy()[:, :32], eids)
+    np.testing.assert_allclose(out33["metrics"].cpu().numpy()[:, [1, 3]], em[:, [1, 3]], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("Q,C,K", [(200, 1000, 10), (3, 7, 10), (5, 1024, 10), (2, 4096, 100), (1, 1, 1), (4, 4096, 10)])
 def test_topk_metrics(pn, Q, C, K):
     rng = np.random.RandomState(3456 + C)
     scores = rng.randn(Q, C).astype(np.float32)
