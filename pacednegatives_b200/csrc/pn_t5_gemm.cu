@@ -244,6 +244,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N;
       if (args.mode == PN_EPI_BF16) {
+        // this row's 64 mask entries of a chunk are one 128-byte line; the line of the NEXT chunk is requested a
+        // chunk ahead (the first one before the accumulator is even ready) so its latency is never exposed
+        uint4 mk[8], mkn[8];
+        auto load_mask = [&](uint4(&dst)[8], int c) {
+          const uint4* mp = reinterpret_cast<const uint4*>(args.mask + (size_t)row * args.ld_mask + col0 + c * 64);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = live ? __ldg(mp + j) : make_uint4(0u, 0u, 0u, 0u);
+        };
+        if (args.mask) load_mask(mkn, 0);
         mbar_wait(tfull_bar(as), aph);
         tc_fence_after();
 #pragma unroll 1
@@ -252,11 +261,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           uint32_t v0[32], v1[32];
           tmem_ld_32x32(t_row + c * 64, v0);
           tmem_ld_32x32(t_row + c * 64 + 32, v1);
-          uint4 mk[8];                               // this row's 64 mask entries (one 128-byte line)
           if (args.mask) {
-            const uint4* mp = reinterpret_cast<const uint4*>(args.mask + (size_t)row * args.ld_mask + col0 + c * 64);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) mk[j] = live ? __ldg(mp + j) : make_uint4(0u, 0u, 0u, 0u);
+            for (int j = 0; j < 8; ++j) mk[j] = mkn[j];
+            if (c + 1 < BLOCK_N / 64) load_mask(mkn, c + 1);
           }
           if (lane == 0) tma_store_wait_read<1>();   // the store that used this buffer two chunks ago has drained
           __syncwarp();
