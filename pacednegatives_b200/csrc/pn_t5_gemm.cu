@@ -244,13 +244,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N;
       if (args.mode == PN_EPI_BF16) {
-        // this row's 64 mask entries of a chunk are one 128-byte line; the line of the NEXT chunk is requested a
-        // chunk ahead (the first one before the accumulator is even ready) so its latency is never exposed
+        // ReLU-backward mask: read with the coalesced mapping (lanes 0..7 = the eight 16-byte pieces of one 128-byte
+        // row, four rows per instruction: 4 L1 wavefronts instead of the 32 of a thread-per-row read) and applied to
+        // the staged tile in shared memory just before the TMA store.  The mask of the NEXT chunk is requested a
+        // chunk ahead (the first one before the accumulator is even ready).
         uint4 mk[8], mkn[8];
         auto load_mask = [&](uint4(&dst)[8], int c) {
-          const uint4* mp = reinterpret_cast<const uint4*>(args.mask + (size_t)row * args.ld_mask + col0 + c * 64);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) dst[j] = live ? __ldg(mp + j) : make_uint4(0u, 0u, 0u, 0u);
+          for (int i = 0; i < 8; ++i) {
+            const int r = row0 + 4 * i + rrow;
+            dst[i] = r < args.M ? __ldg(reinterpret_cast<const uint4*>(args.mask + (size_t)r * args.ld_mask + col0 +
+                                                                       c * 64 + rj * 8))
+                                : make_uint4(0u, 0u, 0u, 0u);
+          }
         };
         if (args.mask) load_mask(mkn, 0);
         mbar_wait(tfull_bar(as), aph);
@@ -278,17 +284,29 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               float x0 = __uint_as_float(v[(j & 3) * 8 + 2 * e]) * rs;
               float x1 = __uint_as_float(v[(j & 3) * 8 + 2 * e + 1]) * rs;
               if (args.relu) { x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
-              if (args.mask) {   // the mask holds ReLU outputs (>= 0): positive <=> any magnitude bit set
-                const uint32_t mw = e == 0 ? mk[j].x : (e == 1 ? mk[j].y : (e == 2 ? mk[j].z : mk[j].w));
-                x0 = (mw & 0x00007fffu) ? x0 : 0.0f;
-                x1 = (mw & 0x7fff0000u) ? x1 : 0.0f;
-              }
               __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
               pk[e] = *reinterpret_cast<uint32_t*>(&h);
             }
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * 128 + ((j ^ swz) << 4)),
                          "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
                          : "memory");
+          }
+          if (args.mask) {
+            __syncwarp();
+            // the mask holds ReLU outputs (>= 0): positive <=> any magnitude bit set
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int rr = 4 * i + rrow;
+              const uint32_t addr = buf + rr * 128 + ((rj ^ (rr & 7)) << 4);
+              uint32_t x0, x1, x2, x3;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(addr));
+              auto keep = [](uint32_t x, uint32_t m) {
+                return x & (((m & 0x00007fffu) ? 0x0000ffffu : 0u) | ((m & 0x7fff0000u) ? 0xffff0000u : 0u));
+              };
+              x0 = keep(x0, mk[i].x); x1 = keep(x1, mk[i].y); x2 = keep(x2, mk[i].z); x3 = keep(x3, mk[i].w);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x0), "r"(x1), "r"(x2), "r"(x3)
+                           : "memory");
+            }
           }
           fence_proxy_async();
           __syncwarp();
