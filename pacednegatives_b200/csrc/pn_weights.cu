@@ -3,6 +3,7 @@
 //   pn_weights_table_update  pairwrapper.py:219-239, weights.py:87-88
 // HBM-bound: 4 B read + 4 B write (+1 B keep mask) per element; the six reductions ride along
 // in registers -> warp shuffle -> one fp64 atomic per CTA per statistic.
+#include <stdlib.h>
 #include "pn_common.cuh"
 
 namespace {
@@ -241,7 +242,12 @@ extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, fl
   PN_CHECK_ARG(loss != nullptr && w_out != nullptr);
   const bool vec = (((uintptr_t)loss | (uintptr_t)w_out) & 15) == 0 &&
                    (keep_out == nullptr || ((uintptr_t)keep_out & 3) == 0);
-  const int grid = pn_grid(n, kThreads, vec ? 4 * kUnroll : 4, 8);
+  static int ctas_per_sm = 0;   // PN_W_CTAS: tuning knob for the grid size (resident CTAs per SM)
+  if (!ctas_per_sm) {
+    const char* e = getenv("PN_W_CTAS");
+    ctas_per_sm = e && atoi(e) > 0 ? atoi(e) : 8;
+  }
+  const int grid = pn_grid(n, kThreads, vec ? 4 * kUnroll : 4, ctas_per_sm);
 #define LAUNCH(V, VEC)                                                                       \
   weights_fwd_kernel<V, VEC><<<grid, kThreads, 0, st>>>(loss, n, eta, mask, w_out, keep_out, \
                                                         stats_dev)
