@@ -97,6 +97,21 @@ __device__ __forceinline__ float4 pn_ldg_stream(const float4* p) {
                : "l"(p));
   return r;
 }
+// 256-bit streaming accesses (sm_100: LDG.256 / STG.256): 32-byte aligned, eight floats per thread per access
+struct __align__(32) pn_float8 { float v[8]; };
+__device__ __forceinline__ pn_float8 pn_ldg_stream8(const pn_float8* p) {
+  pn_float8 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]),
+                 "=f"(r.v[7])
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void pn_stg_stream8(pn_float8* p, const pn_float8& r) {
+  asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(r.v[0]), "f"(r.v[1]),
+               "f"(r.v[2]), "f"(r.v[3]), "f"(r.v[4]), "f"(r.v[5]), "f"(r.v[6]), "f"(r.v[7])
+               : "memory");
+}
 __device__ __forceinline__ void pn_stg_stream(float4* p, float4 v) {
   asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),
                "f"(v.y), "f"(v.z), "f"(v.w)

@@ -165,33 +165,47 @@ template <int LANES>
 __global__ void __launch_bounds__(kThreads)
 lce_restricted_fwd_kernel(const float* __restrict__ z2, int64_t Q, int32_t G,
                           float* __restrict__ loss_out, float* __restrict__ score_out) {
+  // A CTA owns kU x (queries per CTA pass) CONSECUTIVE queries at a time: the first document of each lane for all kU
+  // of them is requested before any arithmetic (kU loads in flight per thread instead of one), and the CTA's reads
+  // and writes stay inside one contiguous span of z2 / score_out.
+  constexpr int kU = 4;
+  constexpr int kPerWarp = 32 / LANES;
+  constexpr int kPerCta = (kThreads / 32) * kPerWarp;
   const int lane = threadIdx.x & 31;
   const int sub = lane % LANES;
-  const int64_t slot = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5) * (32 / LANES) + lane / LANES;
-  const int64_t nslots = (((int64_t)gridDim.x * kThreads) >> 5) * (32 / LANES);
-  const int64_t iters = (Q + nslots - 1) / nslots;       // uniform trip count: shuffles stay convergent
-  for (int64_t itq = 0; itq < iters; ++itq) {
-    const int64_t q = slot + itq * nslots;
-    const bool live = q < Q;
-    float m = -INFINITY, s = 0.0f, s0 = 0.0f;
-    if (live) {
-      const float2* zz = reinterpret_cast<const float2*>(z2) + q * G;
-      for (int j = sub; j < G; j += LANES) {
-        const float2 z = zz[j];
-        const float sc = rel_score(z.x, z.y);
-        if (score_out) score_out[q * G + j] = sc;
-        if (j == 0) s0 = sc;
-        online_add(m, s, sc);
-      }
+  const int local = (threadIdx.x >> 5) * kPerWarp + lane / LANES;
+  const float2* zall = reinterpret_cast<const float2*>(z2);
+  for (int64_t tile = blockIdx.x; tile * (kU * kPerCta) < Q; tile += gridDim.x) {   // uniform trip count per CTA
+    const int64_t q0 = tile * (kU * kPerCta) + local;
+    float2 zf[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t q = q0 + (int64_t)u * kPerCta;
+      zf[u] = (q < Q && sub < G) ? __ldg(zall + q * G + sub) : make_float2(0.0f, 0.0f);
     }
 #pragma unroll
-    for (int o = LANES / 2; o > 0; o >>= 1) {
-      const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
-      const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
-      online_merge(m, s, m2, s2);
+    for (int u = 0; u < kU; ++u) {
+      const int64_t q = q0 + (int64_t)u * kPerCta;
+      const bool live = q < Q;
+      float m = -INFINITY, s = 0.0f, s0 = 0.0f;
+      if (live) {
+        for (int j = sub; j < G; j += LANES) {
+          const float2 z = j == sub ? zf[u] : __ldg(zall + q * G + j);
+          const float sc = rel_score(z.x, z.y);
+          if (score_out) score_out[q * G + j] = sc;
+          if (j == 0) s0 = sc;
+          online_add(m, s, sc);
+        }
+      }
+#pragma unroll
+      for (int o = LANES / 2; o > 0; o >>= 1) {
+        const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+        const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
+        online_merge(m, s, m2, s2);
+      }
+      s0 = __shfl_sync(0xffffffffu, s0, lane - sub);
+      if (live && sub == 0) loss_out[q] = (m + logf(s)) - s0;
     }
-    s0 = __shfl_sync(0xffffffffu, s0, lane - sub);
-    if (live && sub == 0) loss_out[q] = (m + logf(s)) - s0;
   }
 }
 
@@ -302,13 +316,13 @@ extern "C" int pn_lce_restricted_fwd(const float* z2, int64_t Q, int32_t G, floa
   PN_CHECK_ARG(z2 && loss_out);
   cudaStream_t st = (cudaStream_t)stream;
   if (G <= 4)
-    lce_restricted_fwd_kernel<4><<<pn_grid(Q * 4, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
+    lce_restricted_fwd_kernel<4><<<pn_grid(Q * 4, kThreads, 4, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
   else if (G <= 8)
-    lce_restricted_fwd_kernel<8><<<pn_grid(Q * 8, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
+    lce_restricted_fwd_kernel<8><<<pn_grid(Q * 8, kThreads, 4, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
   else if (G <= 16)
-    lce_restricted_fwd_kernel<16><<<pn_grid(Q * 16, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
+    lce_restricted_fwd_kernel<16><<<pn_grid(Q * 16, kThreads, 4, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
   else
-    lce_restricted_fwd_kernel<32><<<pn_grid(Q * 32, kThreads, 1, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
+    lce_restricted_fwd_kernel<32><<<pn_grid(Q * 32, kThreads, 4, 8), kThreads, 0, st>>>(z2, Q, G, loss_out, score_out);
   PN_LAUNCHED();
   return PN_OK;
 }

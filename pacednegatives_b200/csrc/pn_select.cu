@@ -225,14 +225,43 @@ __device__ int choice_one(const double* sp, const double* scdf, int C, int k, co
         const double pi = (mask[i >> 5] >> (i & 31)) & 1u ? 0.0 : sp[i];
         tot = (i == 0) ? pi : __dadd_rn(tot, pi);
       }
-      for (int j = 0; j < m; ++j) nw[j] = 0;
+      // searchsorted(cdf / tot, x, 'right') = index of the first entry with fl(c_i / tot) > x (the cdf is
+      // non-decreasing).  The draws are visited in ascending order, so each entry is compared with ONE draw; the
+      // correctly rounded quotient is only formed when c_i lies within 2^-48 (relative) of x * tot — outside that
+      // band the comparison of fl(c_i / tot) with x is decided by c_i against x * tot alone.
+      int ord[kMaxK];
+      for (int j = 0; j < m; ++j) {
+        int t = j;
+        while (t > 0 && xs[ord[t - 1]] > xs[j]) { ord[t] = ord[t - 1]; --t; }
+        ord[t] = j;
+      }
+      int t = 0;
+      double lo_t = 0.0, hi_t = 0.0, x_t = 0.0;
+      auto next_draw = [&]() {
+        if (t < m) {
+          x_t = xs[ord[t]];
+          const double xt = __dmul_rn(x_t, tot);
+          lo_t = __dmul_rn(xt, 1.0 - 0x1p-48);
+          hi_t = __dmul_rn(xt, 1.0 + 0x1p-48);
+        }
+      };
+      next_draw();
       double c = 0.0;
-      for (int i = 0; i < C; ++i) {
+      for (int i = 0; i < C && t < m; ++i) {
         const double pi = (mask[i >> 5] >> (i & 31)) & 1u ? 0.0 : sp[i];
         c = (i == 0) ? pi : __dadd_rn(c, pi);
-        const double cn = __ddiv_rn(c, tot);
-        for (int j = 0; j < m; ++j) nw[j] += (cn <= xs[j]) ? 1 : 0;
+        while (t < m) {
+          bool le;
+          if (c <= lo_t) le = true;
+          else if (c > hi_t) le = false;
+          else le = __ddiv_rn(c, tot) <= x_t;
+          if (le) break;
+          nw[ord[t]] = i;
+          ++t;
+          next_draw();
+        }
       }
+      for (; t < m; ++t) nw[ord[t]] = C;
     }
     // first-occurrence unique, original order kept
     int kept = 0;

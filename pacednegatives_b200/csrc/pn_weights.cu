@@ -42,7 +42,7 @@ __device__ __forceinline__ float weight_one(float l, float eta, float mask, Raw&
   return w;
 }
 
-template <int VARIANT, bool VEC>
+template <int VARIANT, int VEC>   // VEC: 0 scalar, 1 = 128-bit accesses, 2 = 256-bit accesses (32-byte aligned)
 __global__ void __launch_bounds__(kThreads)
 weights_fwd_kernel(const float* __restrict__ loss, int64_t n, const float* __restrict__ eta_p,
                    float mask, float* __restrict__ w_out, uint8_t* __restrict__ keep_out,
@@ -58,20 +58,64 @@ weights_fwd_kernel(const float* __restrict__ loss, int64_t n, const float* __res
   const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x;
   const int64_t nthreads = (int64_t)gridDim.x * kThreads;
 
-  if (VEC) {
+  if (VEC == 2) {
+    const int64_t n8 = n >> 3;
+    const pn_float8* in8 = reinterpret_cast<const pn_float8*>(loss);
+    pn_float8* out8 = reinterpret_cast<pn_float8*>(w_out);
+    // a CTA works on one contiguous 32 KB tile at a time (kUnroll x 256 x 32 B): its accesses stay inside a few DRAM
+    // pages instead of being spread kUnroll grid-widths apart
+    const int64_t tile_elems = (int64_t)kUnroll * kThreads;
+    for (int64_t tile = blockIdx.x; tile * tile_elems < n8; tile += gridDim.x) {
+      const int64_t base = tile * tile_elems + threadIdx.x;
+      pn_float8 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * kThreads;
+        if (i < n8) v[u] = pn_ldg_stream8(in8 + i);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * kThreads;
+        if (i < n8) {
+          pn_float8 w;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w.v[j] = weight_one<VARIANT>(v[u].v[j], eta, mask, r);
+          pn_stg_stream8(out8 + i, w);
+          if (keep_out) {
+            uint32_t lo = 0, hi = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              lo |= (uint32_t)(!(v[u].v[j] > eta)) << (8 * j);
+              hi |= (uint32_t)(!(v[u].v[4 + j] > eta)) << (8 * j);
+            }
+            reinterpret_cast<uint2*>(keep_out)[i] = make_uint2(lo, hi);
+          }
+        }
+        flush(r);
+      }
+    }
+    for (int64_t i = (n8 << 3) + tid; i < n; i += nthreads) {   // scalar tail
+      const float l = loss[i];
+      w_out[i] = weight_one<VARIANT>(l, eta, mask, r);
+      if (keep_out) keep_out[i] = !(l > eta);
+    }
+    flush(r);
+  } else if (VEC) {
     const int64_t n4 = n >> 2;
     const float4* in4 = reinterpret_cast<const float4*>(loss);
     float4* out4 = reinterpret_cast<float4*>(w_out);
-    for (int64_t base = tid; base < n4; base += nthreads * kUnroll) {
+    const int64_t tile_elems = (int64_t)kUnroll * kThreads;   // contiguous 16 KB tile per CTA, as above
+    for (int64_t tile = blockIdx.x; tile * tile_elems < n4; tile += gridDim.x) {
+      const int64_t base = tile * tile_elems + threadIdx.x;
       float4 v[kUnroll];
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        const int64_t i = base + (int64_t)u * nthreads;
+        const int64_t i = base + (int64_t)u * kThreads;
         if (i < n4) v[u] = pn_ldg_stream(in4 + i);
       }
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        const int64_t i = base + (int64_t)u * nthreads;
+        const int64_t i = base + (int64_t)u * kThreads;
         if (i < n4) {
           float4 w;
           w.x = weight_one<VARIANT>(v[u].x, eta, mask, r);
@@ -149,19 +193,58 @@ weights_fwd_kernel(const float* __restrict__ loss, int64_t n, const float* __res
   }
 }
 
+__device__ __forceinline__ float table_update_one(float v, float cp, float cn, bool has_p, bool has_n, float inv_len,
+                                                  float lr) {
+  float acc = 0.0f;
+  if (has_p) acc = __fmul_rn(cp, inv_len);
+  if (has_n) acc = has_p ? __fadd_rn(acc, __fmul_rn(cn, inv_len)) : __fmul_rn(cn, inv_len);
+  const float g = __fadd_rn(acc, -1.0f);
+  const float x = __fsub_rn(v, __fmul_rn(lr, g));
+  return 1.0f / (1.0f + expf(-x));
+}
+
+// VEC: the three arrays are 16-byte aligned -> float4 accesses, one contiguous 16 KB tile per CTA at a time
+template <bool VEC>
 __global__ void __launch_bounds__(kThreads)
 table_update_kernel(float* __restrict__ row, const float* __restrict__ ce_p,
                     const float* __restrict__ ce_n, int64_t n, float inv_len, float lr) {
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n;
-       i += (int64_t)gridDim.x * kThreads) {
-    float g = -1.0f;
-    float acc = 0.0f;
-    if (ce_p) acc = __fmul_rn(ce_p[i], inv_len);
-    if (ce_n) acc = ce_p ? __fadd_rn(acc, __fmul_rn(ce_n[i], inv_len)) : __fmul_rn(ce_n[i], inv_len);
-    g = __fadd_rn(acc, -1.0f);
-    const float x = __fsub_rn(row[i], __fmul_rn(lr, g));
-    row[i] = 1.0f / (1.0f + expf(-x));
+  const bool hp = ce_p != nullptr, hn = ce_n != nullptr;
+  int64_t done = 0;
+  if (VEC) {
+    const int64_t n4 = n >> 2;
+    const int64_t tile_elems = (int64_t)kUnroll * kThreads;
+    float4* r4 = reinterpret_cast<float4*>(row);
+    const float4* p4 = reinterpret_cast<const float4*>(ce_p);
+    const float4* q4 = reinterpret_cast<const float4*>(ce_n);
+    for (int64_t tile = blockIdx.x; tile * tile_elems < n4; tile += gridDim.x) {
+      const int64_t base = tile * tile_elems + threadIdx.x;
+      float4 v[kUnroll], a[kUnroll], b[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * kThreads;
+        if (i < n4) {
+          v[u] = r4[i];
+          a[u] = hp ? pn_ldg_stream(p4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          b[u] = hn ? pn_ldg_stream(q4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * kThreads;
+        if (i < n4) {
+          float4 o;
+          o.x = table_update_one(v[u].x, a[u].x, b[u].x, hp, hn, inv_len, lr);
+          o.y = table_update_one(v[u].y, a[u].y, b[u].y, hp, hn, inv_len, lr);
+          o.z = table_update_one(v[u].z, a[u].z, b[u].z, hp, hn, inv_len, lr);
+          o.w = table_update_one(v[u].w, a[u].w, b[u].w, hp, hn, inv_len, lr);
+          r4[i] = o;
+        }
+      }
+    }
+    done = n4 << 2;
   }
+  for (int64_t i = done + (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
+    row[i] = table_update_one(row[i], hp ? ce_p[i] : 0.0f, hn ? ce_n[i] : 0.0f, hp, hn, inv_len, lr);
 }
 
 template <int VARIANT>
@@ -242,19 +325,26 @@ extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, fl
   PN_CHECK_ARG(loss != nullptr && w_out != nullptr);
   const bool vec = (((uintptr_t)loss | (uintptr_t)w_out) & 15) == 0 &&
                    (keep_out == nullptr || ((uintptr_t)keep_out & 3) == 0);
+  static int want8 = -1;        // PN_W_VEC8=0 falls back to 128-bit accesses
+  if (want8 < 0) {
+    const char* e = getenv("PN_W_VEC8");
+    want8 = e ? atoi(e) : 1;
+  }
+  const bool vec8 = want8 && (((uintptr_t)loss | (uintptr_t)w_out) & 31) == 0 &&
+                    (keep_out == nullptr || ((uintptr_t)keep_out & 7) == 0);
   static int ctas_per_sm = 0;   // PN_W_CTAS: tuning knob for the grid size (resident CTAs per SM)
   if (!ctas_per_sm) {
     const char* e = getenv("PN_W_CTAS");
     ctas_per_sm = e && atoi(e) > 0 ? atoi(e) : 8;
   }
-  const int grid = pn_grid(n, kThreads, vec ? 4 * kUnroll : 4, ctas_per_sm);
+  const int grid = pn_grid(n, kThreads, vec8 ? 8 * kUnroll : (vec ? 4 * kUnroll : 4), ctas_per_sm);
 #define LAUNCH(V, VEC)                                                                       \
   weights_fwd_kernel<V, VEC><<<grid, kThreads, 0, st>>>(loss, n, eta, mask, w_out, keep_out, \
                                                         stats_dev)
   if (variant == PN_W_LCE) {
-    if (vec) LAUNCH(PN_W_LCE, true); else LAUNCH(PN_W_LCE, false);
+    if (vec8) LAUNCH(PN_W_LCE, 2); else if (vec) LAUNCH(PN_W_LCE, 1); else LAUNCH(PN_W_LCE, 0);
   } else {
-    if (vec) LAUNCH(PN_W_ETA, true); else LAUNCH(PN_W_ETA, false);
+    if (vec8) LAUNCH(PN_W_ETA, 2); else if (vec) LAUNCH(PN_W_ETA, 1); else LAUNCH(PN_W_ETA, 0);
   }
 #undef LAUNCH
   PN_LAUNCHED();
@@ -269,8 +359,10 @@ extern "C" int pn_weights_table_update(float* row, const float* ce_p, const floa
   if (n == 0) return PN_OK;
   PN_CHECK_ARG(row != nullptr);
   PN_CHECK_ARG(ce_p != nullptr || ce_n != nullptr);
-  const int grid = pn_grid(n, kThreads, 4, 8);
-  table_update_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(row, ce_p, ce_n, n, inv_len, lr);
+  const bool vec = (((uintptr_t)row | (uintptr_t)ce_p | (uintptr_t)ce_n) & 15) == 0;
+  const int grid = pn_grid(n, kThreads, vec ? 4 * kUnroll : 4, 8);
+  if (vec) table_update_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(row, ce_p, ce_n, n, inv_len, lr);
+  else table_update_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(row, ce_p, ce_n, n, inv_len, lr);
   PN_LAUNCHED();
   return PN_OK;
 }
