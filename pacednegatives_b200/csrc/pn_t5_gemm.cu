@@ -5,6 +5,7 @@
 // (double-buffered) -> tcgen05.ld epilogue straight to global.  cta_group::2 pairs two SMs on a
 // 256 x BLOCK_N tile (each CTA loads its half of A and B); cta_group::1 is the single-SM variant.
 // Warp roles: 0 = TMA producer, 1 = MMA issuer (leader CTA only), 2 = TMEM allocator, 4..7 = epilogue.
+#include <type_traits>
 #include "pn_common.cuh"
 #include "pn_tc.cuh"
 #include "pn_t5_internal.cuh"
@@ -322,65 +323,76 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         float ssq[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) ssq[i] = 0.0f;
-        float4 pre[2][8];                              // residual rows of the next two chunks (register prefetch)
-        auto prefetch = [&](float4(&dst)[8], int c) {
+        // The four epilogue warps are one warp per scheduler, so this path is bound by its own instruction count:
+        // row pointers are formed once per tile (row i of the read-back mapping = base + i * 4 rows, a 32-bit
+        // multiple folded into one IMAD.WIDE per access) and a slab that lies entirely inside M takes the copy of
+        // the loop without the per-row bound checks.
+        float* const orow = outf + (size_t)(row0 + rrow) * args.ldc + col0 + rj * 4;
+        const uint32_t ostep = 4u * (uint32_t)args.ldc;
+        __nv_bfloat16* const crow =
+            args.copy_out ? args.copy_out + (size_t)(row0 + rrow) * args.ld_copy + col0 + rj * 4 : nullptr;
+        const uint32_t cstep = 4u * (uint32_t)args.ld_copy;
+        auto run = [&](auto full_tag) {
+          constexpr bool kFull = decltype(full_tag)::value;
+          auto row_ok = [&](int i) { return kFull || row0 + 4 * i + rrow < args.M; };
+          float4 pre[2][8];                            // residual rows of the next two chunks (register prefetch)
+          auto prefetch = [&](float4(&dst)[8], int c) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = row0 + 4 * i + rrow;
-            dst[i] = (resid && r < args.M && c < BLOCK_N / 32)
-                         ? *reinterpret_cast<const float4*>(outf + (size_t)r * args.ldc + col0 + c * 32 + rj * 4)
-                         : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = 0; i < 8; ++i)
+              dst[i] = (resid && c < BLOCK_N / 32 && row_ok(i))
+                           ? *reinterpret_cast<const float4*>(orow + (size_t)(i * ostep) + c * 32)
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+          };
+          prefetch(pre[0], 0);                         // issued before the accumulator is even ready
+          prefetch(pre[1], 1);
+          mbar_wait(tfull_bar(as), aph);
+          tc_fence_after();
+#pragma unroll 1
+          for (int c2 = 0; c2 < BLOCK_N / 32; c2 += 2) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u, ++cc) {
+              const int c = c2 + u;
+              uint8_t* bufg = stage_gen + (cc & 1) * EPI_BUF_BYTES;
+              uint32_t v[32];
+              tmem_ld_32x32(t_row + c * 32, v);
+              tmem_ld_wait();
+              __syncwarp();                            // every lane finished reading this buffer two chunks ago
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float4 f;
+                f.x = __uint_as_float(v[j * 4 + 0]) * rs;
+                f.y = __uint_as_float(v[j * 4 + 1]) * rs;
+                f.z = __uint_as_float(v[j * 4 + 2]) * rs;
+                f.w = __uint_as_float(v[j * 4 + 3]) * rs;
+                *reinterpret_cast<float4*>(bufg + lane * 128 + ((j ^ swz) << 4)) = f;
+              }
+              __syncwarp();
+              // read-back: rows 4*i + rrow; (rr & 7) = ((i & 1) * 4 + rrow) & 7 takes two values per lane
+              const uint32_t sw_even = (uint32_t)((rj ^ (rrow & 7)) << 4), sw_odd = (uint32_t)((rj ^ ((rrow + 4) & 7)) << 4);
+              const uint8_t* rb = bufg + rrow * 128;
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float4 acc = *reinterpret_cast<const float4*>(rb + i * 512 + ((i & 1) ? sw_odd : sw_even));
+                float4 h = pre[u][i];
+                h.x += acc.x; h.y += acc.y; h.z += acc.z; h.w += acc.w;
+                if (row_ok(i)) {
+                  float4* dst = reinterpret_cast<float4*>(orow + (size_t)(i * ostep) + c * 32);
+                  if (atomic) atomicAdd(dst, h);       // red.global.add.v4.f32
+                  else *dst = h;
+                  if (crow) {
+                    __nv_bfloat162 lo = __floats2bfloat162_rn(h.x, h.y), hi = __floats2bfloat162_rn(h.z, h.w);
+                    *reinterpret_cast<uint2*>(crow + (size_t)(i * cstep) + c * 32) =
+                        make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+                  }
+                }
+                ssq[i] += h.x * h.x + h.y * h.y + h.z * h.z + h.w * h.w;
+              }
+              prefetch(pre[u], c + 2);   // the registers just consumed take the rows of two chunks ahead
+            }
           }
         };
-        prefetch(pre[0], 0);                           // issued before the accumulator is even ready
-        prefetch(pre[1], 1);
-        mbar_wait(tfull_bar(as), aph);
-        tc_fence_after();
-#pragma unroll 1
-        for (int c2 = 0; c2 < BLOCK_N / 32; c2 += 2) {
-#pragma unroll
-          for (int u = 0; u < 2; ++u, ++cc) {
-            const int c = c2 + u;
-            uint8_t* bufg = stage_gen + (cc & 1) * EPI_BUF_BYTES;
-            uint32_t v[32];
-            tmem_ld_32x32(t_row + c * 32, v);
-            tmem_ld_wait();
-            __syncwarp();                              // every lane finished reading this buffer two chunks ago
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float4 f;
-              f.x = __uint_as_float(v[j * 4 + 0]) * rs;
-              f.y = __uint_as_float(v[j * 4 + 1]) * rs;
-              f.z = __uint_as_float(v[j * 4 + 2]) * rs;
-              f.w = __uint_as_float(v[j * 4 + 3]) * rs;
-              *reinterpret_cast<float4*>(bufg + lane * 128 + ((j ^ swz) << 4)) = f;
-            }
-            __syncwarp();
-            float4 cur[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) cur[i] = pre[u][i];
-            prefetch(pre[u], c + 2);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int rr = 4 * i + rrow;
-              const int r = row0 + rr;
-              const float4 acc = *reinterpret_cast<const float4*>(bufg + rr * 128 + ((rj ^ (rr & 7)) << 4));
-              float4 h = cur[i];
-              h.x += acc.x; h.y += acc.y; h.z += acc.z; h.w += acc.w;
-              if (r < args.M) {
-                const size_t off = (size_t)r * args.ldc + col0 + c * 32 + rj * 4;
-                if (atomic) atomicAdd(reinterpret_cast<float4*>(outf + off), h);   // red.global.add.v4.f32
-                else *reinterpret_cast<float4*>(outf + off) = h;
-                if (args.copy_out) {
-                  __nv_bfloat162 lo = __floats2bfloat162_rn(h.x, h.y), hi = __floats2bfloat162_rn(h.z, h.w);
-                  uint2 uu = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
-                  *reinterpret_cast<uint2*>(args.copy_out + (size_t)r * args.ld_copy + col0 + c * 32 + rj * 4) = uu;
-                }
-              }
-              ssq[i] += h.x * h.x + h.y * h.y + h.z * h.z + h.w * h.w;
-            }
-          }
-        }
+        if (row0 + 32 <= args.M) run(std::true_type{});
+        else run(std::false_type{});
         if (args.sumsq_out) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
