@@ -10,7 +10,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpn_b200.so")
+# PN_B200_LIB: another build of the same library (A/B measurements of a build-time option on one box)
+LIB_PATH = os.environ.get("PN_B200_LIB") or os.path.join(_HERE, "libpn_b200.so")
 
 c_i32, c_i64, c_u64, c_f32, c_f64, c_vp, c_int = (C.c_int32, C.c_int64, C.c_uint64, C.c_float,
                                                  C.c_double, C.c_void_p, C.c_int)

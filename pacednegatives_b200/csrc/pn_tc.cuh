@@ -45,8 +45,20 @@ __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
       "r"(cta)
       : "memory");
 }
+// PN_MBAR_HINT_NS (build-time, default off): suspend-time hint of try_wait in nanoseconds.  A waiting thread is put to
+// sleep for up to that long (it still wakes as soon as the phase completes) instead of re-polling every few cycles,
+// so the waiting warps stop competing for issue slots with the working warps of their scheduler.
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
+#ifdef PN_MBAR_HINT_NS
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity), "r"((uint32_t)PN_MBAR_HINT_NS)
+      : "memory");
+#else
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -54,6 +66,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "=r"(ok)
       : "r"(bar), "r"(parity)
       : "memory");
+#endif
   return ok != 0;
 }
 // non-blocking probe (never suspends the thread): for issuers that poll several barriers
