@@ -471,3 +471,24 @@ def test_pack_prompts_feeds_the_reference_collate_batches(tmp_path):
     for i in range(int(g["batches"])):
         ids, _ = pk.pack(qs, ds, torch.tensor(q_idx[4 * i:4 * i + 4]), torch.tensor(d_idx[4 * i:4 * i + 4]))
         np.testing.assert_array_equal(ids.cpu().numpy(), g[f"p{i}"])
+
+
+def test_empty_inputs_are_no_ops(pn):
+    """Zero-length batches go through every bandwidth entry point without a launch error and with empty results
+    (the reference's python loops simply do not execute on an empty batch)."""
+    from pacednegatives_b200.loss import check_success, token_ce, lce_restricted
+    dev = "cuda"
+    e = torch.zeros(0, device=dev)
+    eta = torch.tensor([0.5], device=dev)
+    w, keep, stats = pn.w.spl_weights(e, eta, 0.0, 0, want_keep=True, want_stats=True)
+    assert w.numel() == 0 and keep.numel() == 0 and float(stats.abs().sum()) == 0.0
+    ce = token_ce(torch.zeros(0, 32, device=dev), torch.zeros(0, dtype=torch.int64, device=dev))
+    assert ce.numel() == 0
+    loss, sc = lce_restricted(torch.zeros(0, 2, device=dev), 4)
+    assert loss.numel() == 0 and sc.numel() == 0
+    assert check_success(torch.zeros(0, 1, 8, device=dev), torch.zeros(0, 1, 8, device=dev), 1, 2).item() == 0.0
+    out = pn.m.topk_metrics(torch.zeros(0, 10, device=dev), None, None, 5)
+    assert out["top_ids"].shape == (0, 5)
+    cm = pn.d.CandidateMatrix(np.zeros((0, 7), dtype=np.int32), pn.d.ROW, Q=0, C=7)
+    idx, doc = cm.select_level(0.5)
+    assert idx.numel() == 1 and doc.numel() == 0
