@@ -197,14 +197,16 @@ lce_restricted_fwd_kernel(const float* __restrict__ z2, int64_t Q, int32_t G,
           online_add(m, s, sc);
         }
       }
+      // group max first, then ONE exponential per lane to bring its partial sum to that reference (a pairwise
+      // online merge costs two exponentials per lane per shuffle round)
+      float gm = m;
 #pragma unroll
-      for (int o = LANES / 2; o > 0; o >>= 1) {
-        const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
-        const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
-        online_merge(m, s, m2, s2);
-      }
+      for (int o = LANES / 2; o > 0; o >>= 1) gm = fmaxf(gm, __shfl_xor_sync(0xffffffffu, gm, o));
+      float gs = (m == -INFINITY) ? 0.0f : s * __expf(m - gm);
+#pragma unroll
+      for (int o = LANES / 2; o > 0; o >>= 1) gs += __shfl_xor_sync(0xffffffffu, gs, o);
       s0 = __shfl_sync(0xffffffffu, s0, lane - sub);
-      if (live && sub == 0) loss_out[q] = (m + logf(s)) - s0;
+      if (live && sub == 0) loss_out[q] = (gm + logf(gs)) - s0;
     }
   }
 }

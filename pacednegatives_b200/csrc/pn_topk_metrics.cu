@@ -211,6 +211,43 @@ topk_count_kernel(const float* __restrict__ scores, const int32_t* __restrict__ 
     // (a) the K best, in order
     uint64_t prev = ~0ull;
     const int rounds = K < C ? K : C;
+    if (C <= 4 * kThreads) {
+      // register path: a thread keeps its (up to) four keys sorted, so its candidate of a round is just the head;
+      // the block-wide arg-max is two REDUX instructions per level (high word, then low word among the ties)
+      uint64_t k4[4];
+      uint32_t p4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = threadIdx.x + j * kThreads;
+        k4[j] = i < C ? key[i] : 0ull;
+        p4[j] = (uint32_t)i;
+      }
+      auto cswap = [&](int a, int b) {
+        if (k4[a] < k4[b]) {
+          const uint64_t tk = k4[a]; k4[a] = k4[b]; k4[b] = tk;
+          const uint32_t tp = p4[a]; p4[a] = p4[b]; p4[b] = tp;
+        }
+      };
+      cswap(0, 1); cswap(2, 3); cswap(0, 2); cswap(1, 3); cswap(1, 2);
+      for (int rnd = 0; rnd < rounds; ++rnd) {
+        const uint32_t chi = (uint32_t)(k4[0] >> 32), clo = (uint32_t)k4[0];
+        const uint32_t whi = __reduce_max_sync(0xffffffffu, chi);
+        const uint32_t wlo = __reduce_max_sync(0xffffffffu, chi == whi ? clo : 0u);
+        if (lane == 0) s_best[rnd & 1][warp] = ((uint64_t)whi << 32) | wlo;
+        __syncthreads();
+        const uint64_t b = lane < kThreads / 32 ? s_best[rnd & 1][lane] : 0ull;
+        const uint32_t bhi = __reduce_max_sync(0xffffffffu, (uint32_t)(b >> 32));
+        const uint32_t blo = __reduce_max_sync(0xffffffffu, (uint32_t)(b >> 32) == bhi ? (uint32_t)b : 0u);
+        const uint64_t best = ((uint64_t)bhi << 32) | blo;
+        if (best == 0ull) break;    // fewer than K keys
+        if (k4[0] == best) {
+          s_top[rnd] = best;
+          s_toprel[rnd] = srel[p4[0]];
+          k4[0] = k4[1]; k4[1] = k4[2]; k4[2] = k4[3]; k4[3] = 0ull;
+          p4[0] = p4[1]; p4[1] = p4[2]; p4[2] = p4[3];
+        }
+      }
+    } else
     for (int rnd = 0; rnd < rounds; ++rnd) {
       uint64_t best = 0ull;
       for (int i = threadIdx.x; i < C; i += kThreads) {
