@@ -9,4 +9,5 @@ python bench.py --steps 5 --warmup 3 > gpurun_out/${TAG}_bench_rerank.json 2> gp
 python bench.py --workload train --steps 10 --warmup 3 > gpurun_out/${TAG}_bench_train.json 2> gpurun_out/${TAG}_bench_train.err; echo "train rc=$?"
 python bench.py --workload train --model large --steps 3 --warmup 3 > gpurun_out/${TAG}_bench_train_large.json 2> gpurun_out/${TAG}_bench_train_large.err; echo "large rc=$?"
 python bench.py --impl reference --steps 1 --warmup 1 > gpurun_out/${TAG}_bench_rerank_reference.json 2> gpurun_out/${TAG}_bench_rerank_reference.err; echo "ref rc=$?"
-for f in rerank train train_large rerank_reference; do head -c 330 gpurun_out/${TAG}_bench_$f.json; echo; done
+python bench.py --workload select --steps 5 --warmup 3 > gpurun_out/${TAG}_bench_select.json 2> gpurun_out/${TAG}_bench_select.err; echo "select rc=$?"
+for f in rerank train train_large rerank_reference select; do head -c 330 gpurun_out/${TAG}_bench_$f.json; echo; done
