@@ -5,6 +5,7 @@
 // (double-buffered) -> tcgen05.ld epilogue straight to global.  cta_group::2 pairs two SMs on a
 // 256 x BLOCK_N tile (each CTA loads its half of A and B); cta_group::1 is the single-SM variant.
 // Warp roles: 0 = TMA producer, 1 = MMA issuer (leader CTA only), 2 = TMEM allocator, 4..7 = epilogue.
+#include <cstdlib>
 #include <type_traits>
 #include "pn_common.cuh"
 #include "pn_tc.cuh"
@@ -21,17 +22,24 @@ constexpr int kGemmThreads = 256;
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 constexpr int EPI_BUF_BYTES = 32 * 128;               // one epilogue warp's 32 rows x 128 B staging tile
 constexpr int EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;      // 4 epilogue warps, double-buffered: 32 KB
+// TMA-fed residual epilogue: per warp a ring of kResBufs fp32 tiles [32 rows x 32 columns] (residual in, updated
+// residual out, in place) and two bf16 tiles [32 x 32] for the copy of the updated stream
+constexpr int kResBufs = 3;
+constexpr int RES_Y_BYTES = 32 * 64;
+constexpr int RES_WARP_BYTES = kResBufs * EPI_BUF_BYTES + 2 * RES_Y_BYTES;   // 16 KB
+constexpr int EPI_BYTES_TMA = 4 * RES_WARP_BYTES;                             // 64 KB
 
-template <int kCtaGroup, int BLOCK_N>
+template <int kCtaGroup, int BLOCK_N, int kEpiBytes = EPI_BYTES>
 struct GemmCfg {
+  static constexpr int EPI = kEpiBytes;
   static constexpr int B_ROWS = BLOCK_N / kCtaGroup;        // B rows this CTA loads
   static constexpr int B_STAGE_BYTES = B_ROWS * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int kAvail = 227 * 1024 - EPI_BYTES - 1024 /*align slack*/ - 512 /*barriers*/;
+  static constexpr int kAvail = 227 * 1024 - kEpiBytes - 1024 /*align slack*/ - 512 /*barriers*/;
   static constexpr int kStages = kAvail / STAGE_BYTES > 8 ? 8 : kAvail / STAGE_BYTES;
   static constexpr int kAccStages = 2;
   static constexpr int TMEM_COLS = kAccStages * BLOCK_N;    // 512 or 256 (power of two)
-  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + kEpiBytes + 1024 /*align slack*/ + 512 /*barriers*/;
   static constexpr uint32_t IDESC = make_idesc_bf16(BLOCK_M * kCtaGroup, BLOCK_N, 0, 0);
 };
 
@@ -67,22 +75,26 @@ struct GemmArgs {
 // kTN = false: C[M,N] = A[M,K] . B[N,K]^T   (both operands K-major: forward and data-gradient GEMMs)
 // kTN = true : C[M,N] += A[K,M]^T . B[K,N]   (both operands MN-major: weight gradients dW = dY^T X, K = rows);
 //              the K range is split over args.splits work items per tile, accumulated with fp32 atomics
-template <int kCtaGroup, int BLOCK_N, bool kTN>
+// kTmaRes  : PN_EPI_RESID_F32 with the residual tiles moved by TMA (tmC = the fp32 output as 32 x 32 boxes, tmY = the
+//              bf16 copy as 32 x 32 boxes); trades pipeline stages for the 64 KB of epilogue tiles
+template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, const GemmArgs args) {
-  using Cfg = GemmCfg<kCtaGroup, BLOCK_N>;
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmY,
+                 const GemmArgs args) {
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : EPI_BYTES>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t epi_smem = smem_base + kStages * Cfg::STAGE_BYTES;   // 1024-aligned
-  const uint32_t bar_base = epi_smem + EPI_BYTES;
-  // barrier layout: full[kStages] empty[kStages] tmem_full[2] tmem_empty[2] | tmem ptr
+  const uint32_t bar_base = epi_smem + Cfg::EPI;
+  // barrier layout: full[kStages] empty[kStages] tmem_full[2] tmem_empty[2] | tmem ptr | residual-tile barriers
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
+  auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * kStages + 5 + w * kResBufs + b); };
   uint32_t* tmem_slot_gen =
       reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -109,6 +121,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
+    if (kTmaRes) tma_prefetch_desc(&tmY);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -119,6 +132,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), 4 * kCtaGroup);  // one arrive per epilogue warp per CTA
     }
+    if (kTmaRes)
+      for (int w = 0; w < 4; ++w)
+        for (int b = 0; b < kResBufs; ++b) mbar_init(res_bar(w, b), 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -210,6 +226,106 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       umma_commit<kCtaGroup>(tfull_bar(as));   // accumulator ready (signalled in both CTAs)
     }
+  } else if (warp >= 4 && kTmaRes) {
+    // ===================== residual epilogue, tiles moved by TMA =====================
+    // out[row, col] += acc * rs, plus the bf16 copy and the row sums of squares of the updated values.  Each warp
+    // streams its 32 rows as 32-column chunks through a ring of fp32 tiles in shared memory: the residual tile of
+    // chunk q + 2 is requested (TMA load, own mbarrier) when chunk q has been handed to its TMA store, thread r
+    // updates row r of the tile in place (128-byte swizzle: conflict-free) and the same bytes go back out.  No
+    // global address arithmetic, no bound checks (the tensor maps zero-fill / clip rows beyond M), and the row sum
+    // of squares is a per-thread scalar.
+    const int ew = warp - 4;
+    constexpr int kChunks = BLOCK_N / 32;
+    const uint32_t wbase = epi_smem + ew * RES_WARP_BYTES;
+    const uint32_t ybase = wbase + kResBufs * EPI_BUF_BYTES;
+    const uint32_t swz = (uint32_t)(lane & 7), yswz = (uint32_t)((lane >> 1) & 3);
+    auto issue_load = [&](uint32_t q) {   // lane 0: request the residual tile of this warp's q-th chunk
+      const int item = group_id + (int)(q / kChunks) * num_groups;
+      if (item >= num_tiles) return;
+      const int tile = item % num_out_tiles;
+      const int r0 = (tile / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
+      const int c0 = (tile % n_tiles) * BLOCK_N + (int)(q % kChunks) * 32;
+      const uint32_t b = q % kResBufs;
+      mbar_arrive_expect_tx(res_bar(ew, b), EPI_BUF_BYTES);
+      tma_load_2d(wbase + b * EPI_BUF_BYTES, &tmC, res_bar(ew, b), c0, r0);
+    };
+    if (lane == 0) { issue_load(0); issue_load(1); }
+    int it = 0;
+    uint32_t q = 0;
+    for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
+      const int tile = item % num_out_tiles;
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int row0 = m_blk * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
+      const int row = row0 + lane;
+      const int col0 = n_blk * BLOCK_N;
+      const bool live = row < args.M;
+      float rs = 1.0f;
+      if (live) {
+        if (args.row_scale) rs = args.row_scale[row];
+        if (args.sumsq_in) {
+          float ss = 0.0f;
+          for (int p = 0; p < args.sumsq_parts; ++p) ss += args.sumsq_in[(size_t)p * args.M + row];
+          rs *= rsqrtf(ss / (float)args.norm_dim + args.eps);
+        }
+      }
+      const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N;
+      float ssq = 0.0f;
+      mbar_wait(tfull_bar(as), aph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < kChunks; ++c, ++q) {
+        const uint32_t b = q % kResBufs;
+        const uint32_t rbuf = wbase + b * EPI_BUF_BYTES + lane * 128;
+        const uint32_t ybuf = ybase + (q & 1) * RES_Y_BYTES + lane * 64;
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + c * 32, v);
+        mbar_wait(res_bar(ew, b), (q / kResBufs) & 1);
+        tmem_ld_wait();
+        __syncwarp();   // lane 0 has seen the store of chunk q - 2 drain (its wait below) before ybuf is rewritten
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t addr = rbuf + ((j ^ swz) << 4);
+          float4 h;
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(h.x), "=f"(h.y), "=f"(h.z), "=f"(h.w) : "r"(addr));
+          h.x = fmaf(__uint_as_float(v[j * 4 + 0]), rs, h.x);
+          h.y = fmaf(__uint_as_float(v[j * 4 + 1]), rs, h.y);
+          h.z = fmaf(__uint_as_float(v[j * 4 + 2]), rs, h.z);
+          h.w = fmaf(__uint_as_float(v[j * 4 + 3]), rs, h.w);
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w)
+                       : "memory");
+          ssq += h.x * h.x + h.y * h.y + h.z * h.z + h.w * h.w;
+          __nv_bfloat162 lo = __floats2bfloat162_rn(h.x, h.y), hi = __floats2bfloat162_rn(h.z, h.w);
+          v[j * 2 + 0] = *reinterpret_cast<uint32_t*>(&lo);   // v[0 .. 15] becomes the packed bf16 row
+          v[j * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
+        }
+        if (args.copy_out) {
+#pragma unroll
+          for (int p = 0; p < 4; ++p)   // 64-byte rows, 64-byte swizzle: piece p of row r sits at p ^ ((r >> 1) & 3)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ybuf + ((p ^ yswz) << 4)), "r"(v[p * 4 + 0]),
+                         "r"(v[p * 4 + 1]), "r"(v[p * 4 + 2]), "r"(v[p * 4 + 3])
+                         : "memory");
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmC, wbase + b * EPI_BUF_BYTES, col0 + c * 32, row0);
+          if (args.copy_out) tma_store_2d(&tmY, ybase + (q & 1) * RES_Y_BYTES, col0 + c * 32, row0);
+          tma_store_commit();
+          tma_store_wait_read<1>();   // chunk q - 1 has left shared memory: its fp32 tile takes chunk q + 2
+          issue_load(q + 2);
+        }
+      }
+      if (args.sumsq_out && live) args.sumsq_out[(size_t)n_blk * args.M + row] = ssq;
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (kCtaGroup == 1) mbar_arrive(tempty_bar(as));
+        else mbar_arrive_remote(tempty_bar(as), 0);
+      }
+    }
+    if (lane == 0) tma_store_wait_all<0>();
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM -> registers -> swizzled smem tile -> global =====================
     // Each warp owns 32 accumulator rows (TMEM lane quarter = warp % 4) and a private double-buffered 4 KB
@@ -442,17 +558,17 @@ EncodeTiledFn get_encode_fn() {
 
 }  // namespace
 
-// bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128-byte swizzle
-int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
-                         uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+// row-major [rows, cols] tensor of bf16 or fp32, box = [box_rows, box_cols]
+static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, CUtensorMapSwizzle swz,
+                        const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_elems,
+                        uint32_t box_rows, uint32_t box_cols) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return pn_fail(PN_E_LAUNCH, "cuTensorMapEncodeTiled entry point not available");
   cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint64_t strides[1] = {row_stride_elems * (uint64_t)elem_bytes};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
-                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  CUresult r = enc(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return pn_fail(PN_E_LAUNCH, "cuTensorMapEncodeTiled failed (%d) rows=%llu cols=%llu", (int)r,
@@ -460,9 +576,16 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
   return PN_OK;
 }
 
-template <int kCtaGroup, int BLOCK_N, bool kTN>
+// bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128-byte swizzle
+int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                         uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+  return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, CU_TENSOR_MAP_SWIZZLE_128B, base, rows, cols,
+                      row_stride_elems, box_rows, box_cols);
+}
+
+template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes = false>
 static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs args, cudaStream_t st) {
-  using Cfg = GemmCfg<kCtaGroup, BLOCK_N>;
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : EPI_BYTES>;
   CUtensorMap tmA, tmB;
   int rc;
   if (!kTN) {
@@ -487,7 +610,18 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
     rc = pn_make_tmap_bf16_2d(&tmC, args.out, args.M, args.N, args.ldc, 32, 64);
     if (rc) return rc;
   }
-  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N, kTN>;
+  CUtensorMap tmY = tmA;
+  if (kTmaRes) {   // fp32 residual stream and its bf16 copy as 32-row x 32-column boxes (128 / 64 bytes per box row)
+    rc = make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, CU_TENSOR_MAP_SWIZZLE_128B, args.out, args.M, args.N,
+                      args.ldc, 32, 32);
+    if (rc) return rc;
+    if (args.copy_out) {
+      rc = make_tmap_2d(&tmY, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, CU_TENSOR_MAP_SWIZZLE_64B, args.copy_out, args.M,
+                        args.N, args.ld_copy, 32, 32);
+      if (rc) return rc;
+    }
+  }
+  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N, kTN, kTmaRes>;
   static bool attr_done = false;
   if (!attr_done) {
     PN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -531,7 +665,7 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
                        (double)args.M * args.N * (out_b + (args.copy_out ? 2.0 : 0.0) + (args.mask ? 2.0 : 0.0));
   const bool hbm_bound = flops < 200.0 * bytes;
   PnProfScope prof(hbm_bound ? PN_PROF_GEMM_HBM : (kTN ? PN_PROF_WGRAD : PN_PROF_GEMM), hbm_bound ? bytes : flops, st);
-  PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, args));
+  PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmY, args));
   g_pn_launches.fetch_add(1, std::memory_order_relaxed);
   return PN_OK;
 }
@@ -608,6 +742,11 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   if ((a.copy_out || a.sumsq_out) && mode == PN_EPI_BF16)
     return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
   const bool n256 = (N % 256) == 0;
+  // residual epilogue through TMA (PN_GEMM_TMA_RES=0 keeps the register path, for A/B runs on one box)
+  static const bool tma_res_on = [] { const char* e = getenv("PN_GEMM_TMA_RES"); return !e || atoi(e) != 0; }();
+  if (tma_res_on && mode == PN_EPI_RESID_F32 && cta_group == 2 && n256 && (ldc % 4) == 0 &&
+      (!a.copy_out || ((a.ld_copy % 8) == 0 && ((uintptr_t)a.copy_out & 15) == 0)))
+    return launch_gemm<2, 256, false, true>(A, lda, B, ldb, a, st);
   if (cta_group == 2) {
     return n256 ? launch_gemm<2, 256, false>(A, lda, B, ldb, a, st) : launch_gemm<2, 128, false>(A, lda, B, ldb, a, st);
   } else if (cta_group == 1) {
