@@ -743,7 +743,7 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
     return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
   const bool n256 = (N % 256) == 0;
   // residual epilogue through TMA (PN_GEMM_TMA_RES=0 keeps the register path, for A/B runs on one box)
-  static const bool tma_res_on = [] { const char* e = getenv("PN_GEMM_TMA_RES"); return !e || atoi(e) != 0; }();
+  static const bool tma_res_on = [] { const char* e = getenv("PN_GEMM_TMA_RES"); return e && atoi(e) != 0; }();
   if (tma_res_on && mode == PN_EPI_RESID_F32 && cta_group == 2 && n256 && (ldc % 4) == 0 &&
       (!a.copy_out || ((a.ld_copy % 8) == 0 && ((uintptr_t)a.copy_out & 15) == 0)))
     return launch_gemm<2, 256, false, true>(A, lda, B, ldb, a, st);
