@@ -742,9 +742,13 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   if ((a.copy_out || a.sumsq_out) && mode == PN_EPI_BF16)
     return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
   const bool n256 = (N % 256) == 0;
-  // residual epilogue through TMA (PN_GEMM_TMA_RES=0 keeps the register path, for A/B runs on one box)
-  static const bool tma_res_on = [] { const char* e = getenv("PN_GEMM_TMA_RES"); return e && atoi(e) != 0; }();
-  if (tma_res_on && mode == PN_EPI_RESID_F32 && cta_group == 2 && n256 && (ldc % 4) == 0 &&
+  // Residual epilogue through TMA for the launches whose epilogue is the bound (the narrow output projections,
+  // < 200 FLOP per byte: 4.10 -> 4.48 TB/s for that class in the re-rank step, r2y); the deep-K FFN output projection
+  // hides its epilogue behind the main loop and keeps the sixth pipeline stage instead (1 237 vs 1 215 TFLOP/s).
+  // PN_GEMM_TMA_RES=0 keeps the register path everywhere, =2 forces TMA for every residual launch (A/B runs).
+  static const int tma_res = [] { const char* e = getenv("PN_GEMM_TMA_RES"); return e ? atoi(e) : 1; }();
+  const bool epi_bound = 2.0 * N * K < 200.0 * (2.0 * K + N * (a.copy_out ? 10.0 : 8.0));
+  if (tma_res && (epi_bound || tma_res == 2) && mode == PN_EPI_RESID_F32 && cta_group == 2 && n256 && (ldc % 4) == 0 &&
       (!a.copy_out || ((a.ld_copy % 8) == 0 && ((uintptr_t)a.copy_out & 15) == 0)))
     return launch_gemm<2, 256, false, true>(A, lda, B, ldb, a, st);
   if (cta_group == 2) {

@@ -66,6 +66,24 @@ def test_gemm_relu_rowscale_and_residual(cta_group):
     assert (outw[:, :128] == 0).all() and (outw[:, 128 + N:] == 0).all()
 
 
+@pytest.mark.parametrize("M,N,K", [(100, 256, 64), (148 * 128 * 2 + 77, 768, 768), (4096 + 31, 1024, 1024),
+                                   (2048 + 5, 768, 3072)])
+def test_gemm_residual_epilogue_ragged_strided(M, N, K):
+    """fp32 read-modify-write epilogue: narrow-K launches take the TMA-fed tile ring (several tiles per CTA pair, a
+    ragged last slab, a pair whose second CTA lies beyond M), K = 3072 the register path; the output is a column
+    slice of a wider buffer whose margins must stay untouched."""
+    torch.manual_seed(M + K)
+    A = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    B = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    rs = torch.rand(M, device="cuda") + 0.5
+    wide = torch.randn(M, N + 64, device="cuda")
+    before = wide.clone()
+    run_gemm(A, B, wide[:, 32:32 + N], mode=1, row_scale=rs, cta_group=2)
+    ref = before[:, 32:32 + N] + ref_mm(A, B) * rs[:, None]
+    assert torch.allclose(wide[:, 32:32 + N], ref, rtol=1e-4, atol=2e-3)
+    assert torch.equal(wide[:, :32], before[:, :32]) and torch.equal(wide[:, 32 + N:], before[:, 32 + N:])
+
+
 def test_gemm_rejects_bad_shapes():
     from pacednegatives_b200 import _lib
     A = torch.zeros(64, 100, device="cuda", dtype=torch.bfloat16)
