@@ -23,11 +23,17 @@ constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 constexpr int EPI_BUF_BYTES = 32 * 128;               // one epilogue warp's 32 rows x 128 B staging tile
 constexpr int EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;      // 4 epilogue warps, double-buffered: 32 KB
 // TMA-fed residual epilogue: per warp a ring of kResBufs fp32 tiles [32 rows x 32 columns] (residual in, updated
-// residual out, in place) and two bf16 tiles [32 x 32] for the copy of the updated stream
-constexpr int kResBufs = 3;
+// residual out, in place) and two bf16 tiles [32 x 32] for the copy of the updated stream.  The path is bound by the
+// latency of the residual loads: [131072 x 768] x [768 x 768] takes 205 us with 3 tiles (5 stages), 195 us with 4 or 5
+// (4 stages); requesting the tiles into L2 eight chunks ahead as well makes it slower (203 -> 209 us).
+#ifndef PN_RES_BUFS
+#define PN_RES_BUFS 5
+#endif
+constexpr int kResBufs = PN_RES_BUFS;   // tiles are requested kResBufs - 1 chunks ahead
 constexpr int RES_Y_BYTES = 32 * 64;
-constexpr int RES_WARP_BYTES = kResBufs * EPI_BUF_BYTES + 2 * RES_Y_BYTES;   // 16 KB
-constexpr int EPI_BYTES_TMA = 4 * RES_WARP_BYTES;                             // 64 KB
+constexpr int RES_WARP_BYTES = kResBufs * EPI_BUF_BYTES + 2 * RES_Y_BYTES;   // 24 KB
+constexpr int EPI_BYTES_TMA = 4 * RES_WARP_BYTES;                             // 96 KB: 4 pipeline stages left
+static_assert(8 * (2 * 8 + 5 + 4 * kResBufs) <= 512, "barrier area");
 
 template <int kCtaGroup, int BLOCK_N, int kEpiBytes = EPI_BYTES>
 struct GemmCfg {
@@ -239,17 +245,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t wbase = epi_smem + ew * RES_WARP_BYTES;
     const uint32_t ybase = wbase + kResBufs * EPI_BUF_BYTES;
     const uint32_t swz = (uint32_t)(lane & 7), yswz = (uint32_t)((lane >> 1) & 3);
-    auto issue_load = [&](uint32_t q) {   // lane 0: request the residual tile of this warp's q-th chunk
+    auto chunk_origin = [&](uint32_t q, int& r0, int& c0) {
       const int item = group_id + (int)(q / kChunks) * num_groups;
-      if (item >= num_tiles) return;
+      if (item >= num_tiles) return false;
       const int tile = item % num_out_tiles;
-      const int r0 = (tile / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
-      const int c0 = (tile % n_tiles) * BLOCK_N + (int)(q % kChunks) * 32;
+      r0 = (tile / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
+      c0 = (tile % n_tiles) * BLOCK_N + (int)(q % kChunks) * 32;
+      return true;
+    };
+    auto issue_load = [&](uint32_t q) {   // lane 0: request the residual tile of this warp's q-th chunk
+      int r0, c0;
+      if (!chunk_origin(q, r0, c0)) return;
       const uint32_t b = q % kResBufs;
       mbar_arrive_expect_tx(res_bar(ew, b), EPI_BUF_BYTES);
       tma_load_2d(wbase + b * EPI_BUF_BYTES, &tmC, res_bar(ew, b), c0, r0);
     };
-    if (lane == 0) { issue_load(0); issue_load(1); }
+    if (lane == 0)
+      for (uint32_t i = 0; i + 1 < (uint32_t)kResBufs; ++i) issue_load(i);
     int it = 0;
     uint32_t q = 0;
     for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
@@ -313,8 +325,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_store_2d(&tmC, wbase + b * EPI_BUF_BYTES, col0 + c * 32, row0);
           if (args.copy_out) tma_store_2d(&tmY, ybase + (q & 1) * RES_Y_BYTES, col0 + c * 32, row0);
           tma_store_commit();
-          tma_store_wait_read<1>();   // chunk q - 1 has left shared memory: its fp32 tile takes chunk q + 2
-          issue_load(q + 2);
+          tma_store_wait_read<1>();   // chunk q - 1 has left shared memory: its fp32 tile takes chunk q + kResBufs - 1
+          issue_load(q + kResBufs - 1);
         }
       }
       if (args.sumsq_out && live) args.sumsq_out[(size_t)n_blk * args.M + row] = ssq;
