@@ -137,6 +137,9 @@ def dist_setup(use_cuda):
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
+        # stdout carries the one JSON line: NCCL's own banner / debug lines (it prints "NCCL version ..." to stdout
+        # at the box's default debug level) go to stderr instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl" if use_cuda else "gloo", rank=RANK, world_size=WORLD,
                                 device_id=torch.device("cuda", LOCAL_RANK) if use_cuda else None)
         return dist
