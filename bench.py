@@ -132,14 +132,36 @@ def synth_rels(Q, C, seed):
     return rng.choice(4, size=(Q, C), p=[0.95, 0.03, 0.015, 0.005]).astype(np.uint8)
 
 
+# stdout carries exactly one JSON line.  Native libraries write there too (NCCL prints "NCCL version ..." on stdout
+# at the box's debug level), so file descriptor 1 is pointed at stderr for the whole run and the line goes to the
+# saved descriptor.
+_STDOUT_FD = None
+
+
+def claim_stdout():
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    text = (json.dumps(line) + "\n").encode()
+    if _STDOUT_FD is None:
+        sys.stdout.write(text.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_STDOUT_FD, text)
+
+
 def dist_setup(use_cuda):
+    claim_stdout()
     if WORLD > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
-        # stdout carries the one JSON line: NCCL's own banner / debug lines (it prints "NCCL version ..." to stdout
-        # at the box's default debug level) go to stderr instead
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl" if use_cuda else "gloo", rank=RANK, world_size=WORLD,
                                 device_id=torch.device("cuda", LOCAL_RANK) if use_cuda else None)
         return dist
@@ -325,7 +347,7 @@ def bench_rerank(args):
             line["cpu_baseline"] = {"value": v, "unit": "pairs/s", "cores": torch.get_num_threads(),
                                     "host_cpus": os.cpu_count(), "kind": "port",
                                     "sample": f"{args.cpu_sample_docs} docs x seq {S}, t5-base, {how}, {dt:.1f} s"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -417,7 +439,7 @@ def bench_select(args):
                          "unit": "GB/s", "frac": top["frac_of_hbm_peak"], "peak_source": peaks["src"], "traffic": None},
             "kernels": res}
     if RANK == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -477,7 +499,7 @@ def bench_rerank_reference(args):
                              "host_cpus": os.cpu_count(), "kind": "port",
                              "sample": f"{n} docs x seq {S} per step, {how}"},
             "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -623,7 +645,7 @@ def bench_train(args):
                                         "sample": f"4 docs x seq {S} x 1 step ({dt:.1f} s), {how}; docs/s / {1 + k}"}
             except Exception as e:   # transformers missing: say so rather than invent a number
                 line["cpu_baseline"] = {"value": None, "unit": "queries/s", "kind": "port", "sample": f"failed: {e}"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -650,7 +672,7 @@ def bench_train_reference(args):
                              "host_cpus": os.cpu_count(), "kind": "port",
                              "sample": f"{n} docs x seq {S} per step, {how}; docs/s / {1 + k}"},
             "e2e": {"value": qs, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
