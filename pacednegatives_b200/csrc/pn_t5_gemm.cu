@@ -245,23 +245,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t wbase = epi_smem + ew * RES_WARP_BYTES;
     const uint32_t ybase = wbase + kResBufs * EPI_BUF_BYTES;
     const uint32_t swz = (uint32_t)(lane & 7), yswz = (uint32_t)((lane >> 1) & 3);
-    auto chunk_origin = [&](uint32_t q, int& r0, int& c0) {
-      const int item = group_id + (int)(q / kChunks) * num_groups;
-      if (item >= num_tiles) return false;
-      const int tile = item % num_out_tiles;
-      r0 = (tile / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
-      c0 = (tile % n_tiles) * BLOCK_N + (int)(q % kChunks) * 32;
-      return true;
-    };
-    auto issue_load = [&](uint32_t q) {   // lane 0: request the residual tile of this warp's q-th chunk
-      int r0, c0;
-      if (!chunk_origin(q, r0, c0)) return;
-      const uint32_t b = q % kResBufs;
+    // lane 0 requests tiles kResBufs - 1 chunks ahead; the origin of the NEXT work item is formed once per tile, so
+    // the per-chunk issue path has no divisions (it sits on the warp's critical path: the others wait at __syncwarp)
+    static_assert(kResBufs - 1 <= kChunks, "prefetch distance reaches at most into the next tile");
+    auto load_tile = [&](uint32_t b, int r0, int c0) {
       mbar_arrive_expect_tx(res_bar(ew, b), EPI_BUF_BYTES);
       tma_load_2d(wbase + b * EPI_BUF_BYTES, &tmC, res_bar(ew, b), c0, r0);
     };
-    if (lane == 0)
-      for (uint32_t i = 0; i + 1 < (uint32_t)kResBufs; ++i) issue_load(i);
+    auto tile_origin = [&](int item, int& r0, int& c0) {
+      const int tile = item % num_out_tiles;
+      r0 = (tile / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
+      c0 = (tile % n_tiles) * BLOCK_N;
+    };
+    if (lane == 0 && group_id < num_tiles) {
+      int r0, c0;
+      tile_origin(group_id, r0, c0);
+      for (int i = 0; i + 1 < kResBufs; ++i) load_tile(i, r0, c0 + i * 32);
+    }
+    uint32_t rb = 0, rph = 0;   // ring slot and mbarrier phase of the current chunk
     int it = 0;
     uint32_t q = 0;
     for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
@@ -283,17 +284,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
       const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N;
+      int nrow0 = 0, ncol0 = 0;
+      const bool nvalid = item + num_groups < num_tiles;
+      if (nvalid) tile_origin(item + num_groups, nrow0, ncol0);
       float ssq = 0.0f;
       mbar_wait(tfull_bar(as), aph);
       tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < kChunks; ++c, ++q) {
-        const uint32_t b = q % kResBufs;
-        const uint32_t rbuf = wbase + b * EPI_BUF_BYTES + lane * 128;
+        const uint32_t rbuf = wbase + rb * EPI_BUF_BYTES + lane * 128;
         const uint32_t ybuf = ybase + (q & 1) * RES_Y_BYTES + lane * 64;
         uint32_t v[32];
         tmem_ld_32x32(t_row + c * 32, v);
-        mbar_wait(res_bar(ew, b), (q / kResBufs) & 1);
+        mbar_wait(res_bar(ew, rb), rph);
         tmem_ld_wait();
         __syncwarp();   // lane 0 has seen the store of chunk q - 2 drain (its wait below) before ybuf is rewritten
 #pragma unroll
@@ -322,12 +325,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&tmC, wbase + b * EPI_BUF_BYTES, col0 + c * 32, row0);
+          tma_store_2d(&tmC, wbase + rb * EPI_BUF_BYTES, col0 + c * 32, row0);
           if (args.copy_out) tma_store_2d(&tmY, ybase + (q & 1) * RES_Y_BYTES, col0 + c * 32, row0);
           tma_store_commit();
           tma_store_wait_read<1>();   // chunk q - 1 has left shared memory: its fp32 tile takes chunk q + kResBufs - 1
-          issue_load(q + kResBufs - 1);
+          const uint32_t bl = rb == 0 ? kResBufs - 1 : rb - 1;
+          const int cn = c + kResBufs - 1;
+          if (cn < kChunks) load_tile(bl, row0, col0 + cn * 32);
+          else if (nvalid) load_tile(bl, nrow0, ncol0 + (cn - kChunks) * 32);
         }
+        if (++rb == kResBufs) { rb = 0; rph ^= 1; }
       }
       if (args.sumsq_out && live) args.sumsq_out[(size_t)n_blk * args.M + row] = ssq;
       tc_fence_before();
@@ -755,11 +762,11 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
     return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
   const bool n256 = (N % 256) == 0;
   // Residual epilogue through TMA for the launches whose epilogue is the bound (the narrow output projections,
-  // < 200 FLOP per byte: 4.10 -> 4.48 TB/s for that class in the re-rank step, r2y); the deep-K FFN output projection
+  // < 256 FLOP per byte: 4.10 -> 4.48 TB/s for that class in the re-rank step, r2y); the deep-K FFN output projection
   // hides its epilogue behind the main loop and keeps the sixth pipeline stage instead (1 237 vs 1 215 TFLOP/s).
   // PN_GEMM_TMA_RES=0 keeps the register path everywhere, =2 forces TMA for every residual launch (A/B runs).
   static const int tma_res = [] { const char* e = getenv("PN_GEMM_TMA_RES"); return e ? atoi(e) : 1; }();
-  const bool epi_bound = 2.0 * N * K < 200.0 * (2.0 * K + N * (a.copy_out ? 10.0 : 8.0));
+  const bool epi_bound = 2.0 * N * K < 256.0 * (2.0 * K + N * (a.copy_out ? 10.0 : 8.0));
   if (tma_res && (epi_bound || tma_res == 2) && mode == PN_EPI_RESID_F32 && cta_group == 2 && n256 && (ldc % 4) == 0 &&
       (!a.copy_out || ((a.ld_copy % 8) == 0 && ((uintptr_t)a.copy_out & 15) == 0)))
     return launch_gemm<2, 256, false, true>(A, lda, B, ldb, a, st);
