@@ -25,7 +25,8 @@ constexpr int EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;      // 4 epilogue warps, doubl
 // TMA-fed residual epilogue: per warp a ring of kResBufs fp32 tiles [32 rows x 32 columns] (residual in, updated
 // residual out, in place) and two bf16 tiles [32 x 32] for the copy of the updated stream.  The path is bound by the
 // latency of the residual loads: [131072 x 768] x [768 x 768] takes 205 us with 3 tiles (5 stages), 195 us with 4 or 5
-// (4 stages); requesting the tiles into L2 eight chunks ahead as well makes it slower (203 -> 209 us).
+// (4 stages); requesting the tiles into L2 eight chunks ahead as well makes it slower (203 -> 209 us), and so does
+// requesting two column-adjacent tiles per round instead of one per chunk (194 -> 198 us).
 #ifndef PN_RES_BUFS
 #define PN_RES_BUFS 5
 #endif
