@@ -67,7 +67,8 @@ struct GemmArgs {
   // residual mode extras: bf16 copy of the updated residual stream and per-n-tile row sums of squares of it
   __nv_bfloat16* copy_out;  // nullable, [M, ld_copy]
   int ld_copy;
-  float* sumsq_out;         // nullable, [N / BLOCK_N][M]
+  float* sumsq_out;         // nullable, [N / BLOCK_N][ss_stride]
+  long long ss_stride;      // rows of the whole sumsq_out array (= M unless the launch is one row slab of a larger call)
   // bf16 mode, nullable: ReLU backward fused into a data-gradient GEMM, out = mask[row, col] > 0 ? acc : 0
   const __nv_bfloat16* mask;
   int ld_mask;
@@ -337,7 +338,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (++rb == kResBufs) { rb = 0; rph ^= 1; }
       }
-      if (args.sumsq_out && live) args.sumsq_out[(size_t)n_blk * args.M + row] = ssq;
+      if (args.sumsq_out && live) args.sumsq_out[(size_t)n_blk * args.ss_stride + row] = ssq;
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -537,7 +538,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             t += __shfl_xor_sync(0xffffffffu, t, 2);
             t += __shfl_xor_sync(0xffffffffu, t, 4);
             const int r = row0 + 4 * i + rrow;
-            if (rj == 0 && r < args.M) args.sumsq_out[(size_t)n_blk * args.M + r] = t;
+            if (rj == 0 && r < args.M) args.sumsq_out[(size_t)n_blk * args.ss_stride + r] = t;
           }
         }
       }
@@ -761,7 +762,28 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
     return pn_fail(PN_E_BADARG, "pn_gemm: bf16 copy must be 8-byte aligned with ld %% 4 == 0");
   if ((a.copy_out || a.sumsq_out) && mode == PN_EPI_BF16)
     return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
+  a.ss_stride = M;
   const bool n256 = (N % 256) == 0;
+  // Deep-K residual launches over very many rows go out as row slabs: with the static tile order the CTA pairs that
+  // share an A block drift apart over the ~80 waves of an M = 512 000 launch until the block has left L2 between
+  // their reads (1.45x the DRAM reads, profiles/r2b_gemm_traffic.csv); at 131 072 rows per launch they do not.
+  // PN_GEMM_SLAB = rows per slab (0 = one launch).
+  static const int slab_rows = [] { const char* e = getenv("PN_GEMM_SLAB"); return e ? atoi(e) : 0; }();
+  if (slab_rows >= 256 && mode == PN_EPI_RESID_F32 && cta_group == 2 && K >= 2048 && M >= 2 * slab_rows &&
+      !a.row_scale && !a.sumsq_in && a.group_rows == 0) {
+    const int step = slab_rows / 256 * 256;
+    for (int r0 = 0; r0 < M; r0 += step) {
+      GemmArgs b = a;
+      b.M = M - r0 < step ? M - r0 : step;
+      b.out = reinterpret_cast<float*>(out) + (size_t)r0 * ldc;
+      if (a.copy_out) b.copy_out = a.copy_out + (size_t)r0 * a.ld_copy;
+      if (a.sumsq_out) b.sumsq_out = a.sumsq_out + r0;
+      const __nv_bfloat16* Ab = reinterpret_cast<const __nv_bfloat16*>(A) + (size_t)r0 * lda;
+      const int rc = n256 ? launch_gemm<2, 256, false>(Ab, lda, B, ldb, b, st) : launch_gemm<2, 128, false>(Ab, lda, B, ldb, b, st);
+      if (rc) return rc;
+    }
+    return PN_OK;
+  }
   // Residual epilogue through TMA for the launches whose epilogue is the bound (the narrow output projections,
   // < 256 FLOP per byte: 4.10 -> 4.48 TB/s for that class in the re-rank step, r2y); the deep-K FFN output projection
   // hides its epilogue behind the main loop and keeps the sixth pipeline stage instead (1 237 vs 1 215 TFLOP/s).
