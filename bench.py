@@ -428,6 +428,7 @@ def bench_select(args):
                     "frac_of_hbm_peak": gbs / peaks["hbm_gbs"]})
     launches = _lib.launch_count() - l0
     top = res[0]
+    sel_traffic, sel_traffic_src = ncu_traffic("select", Mw)   # dram bytes of one spl_weights launch, scaled by elements
     line = {"metric": "paced selection + weighting kernels, queries/s through one pass of all kernels",
             "value": Q * WORLD / (tot_ms / 1e3), "unit": "queries/s", "n_gpus": WORLD, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": tot_ms, "higher_is_better": True, "scaling": "weak",
@@ -436,7 +437,8 @@ def bench_select(args):
                        "queries": Q, "candidates": C, "k": k, "weight_elems": Mw, "l2": "256 MB flush between iterations"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peaks["hbm_gbs"],
-                         "unit": "GB/s", "frac": top["frac_of_hbm_peak"], "peak_source": peaks["src"], "traffic": None},
+                         "unit": "GB/s", "frac": top["frac_of_hbm_peak"], "peak_source": peaks["src"],
+                         "traffic": sel_traffic, "traffic_source": sel_traffic_src},
             "kernels": res}
     if RANK == 0:
         emit(line)
