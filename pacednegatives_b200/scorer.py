@@ -11,6 +11,7 @@ import os
 from dataclasses import dataclass
 
 import torch
+import torch.distributed as dist
 
 from . import _lib
 from .metrics import topk_metrics
@@ -147,6 +148,45 @@ def load_checkpoint(path):
     else:
         sd = torch.load(os.path.join(path, "pytorch_model.bin"), map_location="cpu", weights_only=True)
     return dims, sd
+
+
+def _world(group=None):
+    return dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+
+
+def gather_rows(t, group=None, equal_shards=True):
+    """Rank-major concatenation along dim 0 of every rank's `t` (the re-rank score / metric gather of SURVEY 8e
+    collective 3: the reference evaluates ONE table over all queries, eval.py:23-26,41-43).  One
+    all_gather_into_tensor when every rank holds the same number of rows (the sharding bench.py and
+    MonoT5Scorer.rerank use); otherwise the row counts are exchanged first and the shards padded to the longest
+    (one host sync to trim)."""
+    W = _world(group)
+    t = t.contiguous()
+    if W == 1:
+        return t
+    if equal_shards:
+        out = t.new_empty((W * t.shape[0],) + tuple(t.shape[1:]))
+        dist.all_gather_into_tensor(out, t, group=group)
+        return out
+    n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+    counts = torch.empty(W, dtype=torch.int64, device=t.device)
+    dist.all_gather_into_tensor(counts, n, group=group)
+    counts = counts.tolist()
+    mx = max(counts)
+    pad = t.new_zeros((mx,) + tuple(t.shape[1:]))
+    pad[:t.shape[0]] = t
+    out = t.new_empty((W * mx,) + tuple(t.shape[1:]))
+    dist.all_gather_into_tensor(out, pad, group=group)
+    return torch.cat([out[r * mx:r * mx + c] for r, c in enumerate(counts)])
+
+
+def reduce_metric_means(metrics, group=None):
+    """Global means of per-query measures [Q_local, M] over every rank's queries: one (M+1)-float SUM all-reduce
+    of (sum of each measure, query count) — the metrics-only form of the gather above."""
+    sums = torch.cat([metrics.double().sum(0), metrics.new_full((1,), metrics.shape[0], dtype=torch.float64)])
+    if _world(group) > 1:
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    return (sums[:-1] / sums[-1].clamp(min=1)).float()
 
 
 class _DeviceFloats:
@@ -297,13 +337,29 @@ class MonoT5Scorer:
             logits = logits.view(N, T, self.vocab_pad)[:, :, :self.dims.vocab]
         return logits, z2.view(N, T, 2)
 
-    def rerank(self, input_ids, docids=None, rels=None, K=10):
+    def rerank(self, input_ids, docids=None, rels=None, K=10, group=None, gather=None, equal_shards=True):
         """Score Q x C candidate prompts (input_ids [Q, C, S]), rank each query's candidates and, when
-        ``rels`` [Q, C] is given, evaluate nDCG@K / RR / RR@K / AP (eval.py:26,41-43)."""
+        ``rels`` [Q, C] is given, evaluate nDCG@K / RR / RR@K / AP (eval.py:26,41-43).
+
+        Data parallel (queries sharded over the ranks of ``group``; all C candidates of a query stay on one rank):
+        ``gather='scores'`` adds ``scores_all`` [sum Q, C] (+ ``top_ids_all``, ``top_scores_all``, ``metrics_all``) —
+        the one global result table the reference evaluates (eval.py:23-26) — and ``mean_metrics``;
+        ``gather='metrics'`` only all-reduces the (M+1) floats behind ``mean_metrics``.  Default: 'scores' when a
+        process group with more than one rank is initialised, else nothing."""
         ids = torch.as_tensor(input_ids)
         Q, Cn, S = ids.shape
         scores = self.score(ids.reshape(Q * Cn, S)).view(Q, Cn)
         out = topk_metrics(scores, docids, rels, K)
         out["scores"] = scores
+        if gather is None:
+            gather = "scores" if _world(group) > 1 else "none"
+        if gather == "scores":
+            out["scores_all"] = gather_rows(scores, group, equal_shards)
+            out["top_ids_all"] = gather_rows(out["top_ids"], group, equal_shards)
+            out["top_scores_all"] = gather_rows(out["top_scores"], group, equal_shards)
+            if "metrics" in out:
+                out["metrics_all"] = gather_rows(out["metrics"], group, equal_shards)
+        if gather in ("scores", "metrics") and "metrics" in out:
+            out["mean_metrics"] = reduce_metric_means(out["metrics"], group)
         return out
 

@@ -403,6 +403,112 @@ def gold_train(rt, out):
         names=np.array(names), **{k_: np.asarray(v) for k_, v in res.items()})
 
 
+def _sample_index(name, numel, count=8192):
+    """Seeded element sample of a gradient tensor (the wide goldens cannot commit 130 MB of full gradients): the
+    relative L2 error over the sample estimates the tensor's; tests re-derive the same indices from the name."""
+    import zlib
+    if numel <= 65536:
+        return np.arange(numel, dtype=np.int64)
+    rng = np.random.RandomState(zlib.crc32(name.encode()) & 0x7FFFFFFF)
+    return np.sort(rng.choice(numel, size=count, replace=False)).astype(np.int64)
+
+
+def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_id=1176, nrel_id=6136, steps=1,
+                    lr=1e-3, meta_lr=1e-2):
+    """The reference's own LCEModel.training_step (lceT5.py:124-167), unmodified, on HF T5 fp32 CPU at the widths
+    the bench runs: per parameter the gradient norm, a seeded element sample (all elements for
+    tensors <= 65536) and, for matrices, the row and column sums (a wrong head / block shows up there even when the
+    sample misses it).  eta=None puts the threshold midway between the two middle losses of the step so both weight branches run."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    from transformers import T5Config, T5ForConditionalGeneration, get_linear_schedule_with_warmup
+    w = ot.init_weights(dims, seed=seed)
+    cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
+                   num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
+                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   pad_token_id=0, eos_token_id=1, feed_forward_proj="relu", tie_word_embeddings=True)
+    m = T5ForConditionalGeneration(cfg).train()
+    sd = {k_: torch.tensor(v) for k_, v in w.items()}
+    sd["encoder.embed_tokens.weight"] = sd["decoder.embed_tokens.weight"] = sd["shared.weight"]
+    sd["lm_head.weight"] = sd["shared.weight"]
+    missing = m.load_state_dict(sd, strict=False)
+    assert not missing.missing_keys and not missing.unexpected_keys, missing
+    rng = np.random.RandomState(ids_seed)
+    hi = min(dims.vocab, 32100)
+    pids = rng.randint(2, hi, size=(Q, S)).astype(np.int64)
+    nids = rng.randint(2, hi, size=(Q * k, S)).astype(np.int64)
+    pids[:, -1] = 1
+    nids[:, -1] = 1
+    plab = np.tile([[rel_id, 1]], (Q, 1)).astype(np.int64)
+    nlab = np.tile([[nrel_id, 1]], (Q * k, 1)).astype(np.int64)
+    batch = ({"input_ids": torch.tensor(pids), "labels": torch.tensor(plab)},
+             {"input_ids": torch.tensor(nids), "labels": torch.tensor(nlab)})
+    loss_fn = torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none")
+    if eta is None:
+        probe = types.SimpleNamespace(loss_fn=loss_fn, hparams=types.SimpleNamespace(use_mean=True))
+        with torch.no_grad():
+            pl = m(**batch[0]).logits
+            nl = m(**batch[1]).logits.view(-1, k, dims.vocab)
+            ls = np.sort(rt.LCEModel.pair_loss(probe, pl, nl, batch[0]["labels"], batch[1]["labels"]).numpy())
+            # midway between the two middle losses: no element sits on the threshold, so bf16 noise cannot flip one
+            eta = float(np.float32(0.5 * (ls[len(ls) // 2 - 1] + ls[len(ls) // 2])))
+    hp = types.SimpleNamespace(n=k, use_mean=True, ignore_index=-100, lr=lr, meta_lr=meta_lr, warmup_steps=0,
+                               total_steps=10, eta=eta)
+    self = types.SimpleNamespace()
+    self.hparams = hp
+    self.model = m
+    self.weights = rt.LCEWeights(hp)
+    self.loss_fn = loss_fn
+    self.pair_loss = lambda p, n, op, on: rt.LCEModel.pair_loss(self, p, n, op, on)
+    meta_opt = LegacyAdamW(self.weights.parameters(), lr=hp.meta_lr)
+    opt = LegacyAdamW(m.parameters(), lr=hp.lr)
+    scheds = [get_linear_schedule_with_warmup(o, num_warmup_steps=hp.warmup_steps,
+                                              num_training_steps=hp.total_steps) for o in (meta_opt, opt)]
+    self.optimizers = lambda: (meta_opt, opt)
+    self.lr_schedulers = lambda: scheds
+    self.manual_backward = lambda loss: loss.backward()
+    logged = {}
+    self.log = lambda name, v: logged.__setitem__(name, float(v))
+    names = [n_ for n_, _ in m.named_parameters()]
+    res = {}
+    for step in range(steps):
+        o = rt.LCEModel.training_step(self, batch, step)
+        res[f"main_loss{step}"] = float(o["main_loss"])
+        res[f"meta_loss{step}"] = float(o["meta_loss"])
+        res[f"eta{step}"] = float(self.weights.eta.item())
+        res[f"avg_weight{step}"] = logged["avg_weight"]
+        if step == 0:
+            for n_, p in m.named_parameters():
+                g = p.grad.detach()
+                flat = g.reshape(-1)
+                res["gnorm/" + n_] = float(flat.double().norm())
+                res["gsample/" + n_] = flat[torch.from_numpy(_sample_index(n_, flat.numel()))].numpy().copy()
+                if g.dim() == 2 and flat.numel() > 65536:
+                    res["growsum/" + n_] = g.double().sum(1).float().numpy()
+                    res["gcolsum/" + n_] = g.double().sum(0).float().numpy()
+    np.savez_compressed(
+        out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
+                            dims.n_heads]), seed=np.array(seed), pids=pids, nids=nids, plab=plab, nlab=nlab,
+        hp=np.array([hp.n, int(hp.use_mean), hp.lr, hp.meta_lr, hp.warmup_steps, hp.total_steps, hp.eta],
+                    dtype=np.float64),
+        steps=np.array(steps), names=np.array(names), **{k_: np.asarray(v) for k_, v in res.items()})
+
+
+def gold_train_widths(rt):
+    """VERDICT r1 'next' item 1: (i) t5-base width, (ii) T5-large width (2+2 layers, S 512, vocab 32128), (iii)
+    SURVEY 8d cfg1 exactly (full t5-small, Q 8, k 7, S 128, eta 0.3466, one optimiser step)."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    gold_train_wide(rt, os.path.join(HERE, "train_golden_base.npz"),
+                    ot.T5Dims(vocab=32128, d_model=768, d_kv=64, d_ff=3072, n_layers=2, n_dec_layers=2, n_heads=12),
+                    Q=2, k=3, S=512, seed=31, steps=2)
+    gold_train_wide(rt, os.path.join(HERE, "train_golden_large.npz"),
+                    ot.T5Dims(vocab=32128, d_model=1024, d_kv=64, d_ff=4096, n_layers=2, n_dec_layers=2, n_heads=16),
+                    Q=2, k=3, S=512, seed=37, steps=1)
+    gold_train_wide(rt, os.path.join(HERE, "train_golden_cfg1.npz"), ot.T5_SMALL, Q=8, k=7, S=128, seed=0,
+                    eta=0.3466, ids_seed=1234, steps=1, meta_lr=1e-3)
+
+
 def gold_newwrapper(rp, rw, out):
     """The reference's NewWrapper.meta_loop + main_loop (pairwrapper.py:219-258) executed unmodified on a tiny
     random-init HF T5 (fp32, CPU) for three batches: table rows, losses and parameter movement."""
@@ -728,6 +834,8 @@ def main():
     gold_table_update(rp, rw, os.path.join(HERE, "table_update_golden.npz"))
     gold_t5(rt, os.path.join(HERE, "t5_tiny_golden.npz"))
     gold_train(rt, os.path.join(HERE, "train_golden.npz"))
+    if "--wide" in sys.argv or "--all" in sys.argv:   # minutes of CPU: only on request
+        gold_train_widths(rt)
     gold_newwrapper(rp, rw, os.path.join(HERE, "newwrapper_golden.npz"))
     gold_scalar_wrappers(rp, rw, os.path.join(HERE, "scalar_wrappers_golden.npz"))
     gold_datamodule(rt, os.path.join(HERE, "datamodule_golden.npz"))
