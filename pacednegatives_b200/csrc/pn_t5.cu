@@ -359,6 +359,11 @@ extern "C" int pn_t5_set_option(PnT5* m, const char* name, int64_t value) {
     m->xattn = value != 0;
     return PN_OK;
   }
+  if (!strcmp(name, "grad_ranges")) {   // encoder layer groups handed to the gradient hook separately
+    PN_CHECK_ARG(value >= 1 && value <= 64);
+    m->grad_ranges = (int)value;
+    return PN_OK;
+  }
   if (!strcmp(name, "train")) {   // must precede the first pn_t5_load_weight: also keeps transposed operands
     if (m->flat) return pn_fail(PN_E_BADARG, "pn_t5_set_option: \"train\" must be set before weights are loaded");
     m->want_train = value != 0;

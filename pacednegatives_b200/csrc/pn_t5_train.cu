@@ -20,6 +20,7 @@
 #include "pn_t5_model.cuh"
 
 #include <string.h>
+#include <algorithm>
 
 namespace {
 
@@ -392,14 +393,27 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     RC(wgrad_folded(m, w.ddbig, 3 * di, hb0, D.wqkv, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, 3 * di, D.wqkv, w.dgbuf, PN_EPI_F32, drows, st));
     RC(pn_t5_norm_bwd(w.dgbuf, 0, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st));
+    if (m->grad_hook && Ld >= 2 && l == Ld / 2) {   // decoder layers [Ld/2, Ld) and the final decoder norm are done
+      const int64_t dmid = first_offset(m, "decoder.block." + std::to_string(l) + ".");
+      m->grad_hook(m->grad_hook_user, dmid, m->n_params - dmid);
+    }
   }
   RC(pn_t5_embed_bwd(w.dec_ids, w.ddH, drows, d, m->cfg.vocab, G + m->emb_off, st));
-  // gradient ranges in the order they become final (flat buffer = HF order: shared | encoder.block.* |
-  // encoder.final_layer_norm | decoder.*): the decoder's now, the upper encoder layers half way, the rest at the end
+  // Gradient ranges in the order they become final (flat buffer = HF order: shared | encoder.block.* |
+  // encoder.final_layer_norm | decoder.block.* | decoder.final_layer_norm): the upper decoder half (+ its final
+  // norm) left above when decoder layer Ld/2 was done, the lower half now (decoder.block.0 holds the relative bias
+  // every decoder layer adds to), then the encoder in `grad_ranges` groups of layers from the top (the first one
+  // carries encoder.final_layer_norm, which every cross K/V projection adds to); the bottom group ends with the
+  // embedding and the encoder's relative bias, final only after the last kernel.
   const int64_t dec_off = first_offset(m, "decoder.");
-  const int split_layer = L / 2;
-  const int64_t mid_off = first_offset(m, "encoder.block." + std::to_string(split_layer) + ".");
-  if (m->grad_hook) m->grad_hook(m->grad_hook_user, dec_off, m->n_params - dec_off);
+  if (m->grad_hook) {
+    const int64_t dmid = Ld >= 2 ? first_offset(m, "decoder.block." + std::to_string(Ld / 2) + ".") : m->n_params;
+    m->grad_hook(m->grad_hook_user, dec_off, dmid - dec_off);
+  }
+  const int groups = std::max(1, std::min(m->grad_ranges, L));
+  // group g (0 = bottom) covers encoder layers [L*g/groups, L*(g+1)/groups)
+  auto group_lo = [&](int g) { return (int)((int64_t)L * g / groups); };
+  auto enc_layer_off = [&](int l) { return first_offset(m, "encoder.block." + std::to_string(l) + "."); };
   if (w.xattn) {
     // G = rs (.) ([P | dSc]_all-layers . [dC'; QK]_all-layers): every layer's cross-attention gradient of the
     // normalised encoder states in one block-diagonal GEMM (K = 64 per layer)
@@ -428,12 +442,18 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
     RC(wgrad_folded(m, w.dbig, 3 * di, hb0, E.wqkv, w.dWtmp, rows, st));
     RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, PN_EPI_F32, rows, st));
     RC(pn_t5_norm_bwd(w.gbuf, 0, hb0, rs0, rows, d, 1, w.dH, w.dHb, st));
-    if (l == split_layer && l > 0 && m->grad_hook) m->grad_hook(m->grad_hook_user, mid_off, dec_off - mid_off);
+    if (m->grad_hook && l > 0)
+      for (int g = groups - 1; g >= 1; --g)
+        if (group_lo(g) == l) {   // layers [l, top of group g) are done
+          const int64_t lo = enc_layer_off(l);
+          const int64_t hi = g == groups - 1 ? dec_off : enc_layer_off(group_lo(g + 1));
+          m->grad_hook(m->grad_hook_user, lo, hi - lo);
+        }
   }
   RC(pn_t5_embed_bwd(ids, w.dH, rows, d, m->cfg.vocab, G + m->emb_off, st));
   RC(pn_t5_rel_bias_grad(w.diag, bucket_of, H, m->cfg.rel_buckets, G + m->enc_rel_off, st));
   if (m->grad_hook) {
-    const int64_t rest = split_layer > 0 ? mid_off : dec_off;
+    const int64_t rest = groups > 1 && group_lo(1) > 0 ? enc_layer_off(group_lo(1)) : dec_off;
     m->grad_hook(m->grad_hook_user, 0, rest);
   }
   return PN_OK;

@@ -165,6 +165,7 @@ class MonoT5Model(MonoT5Scorer):
         self.overlap_grad_reduce = True
         self.accumulating = False    # True while more micro-batches of this step will still add to `grads`
         self.reduce_group = None
+        self.skip_grad_reduce = False   # measurement only (bench.py): run the step without the gradient exchange
         self._pending, self._hook_live, self._hook_error = 0, False, None
         self._reduced, self._comm_stream, self._comm_done = [], None, None
         import ctypes as C
@@ -193,7 +194,7 @@ class MonoT5Model(MonoT5Scorer):
         _lib.check(_lib.lib().pn_t5_zero_grad(self._h, _lib.stream()))
 
     def _overlap_ready(self):
-        return (self.overlap_grad_reduce and dist.is_available() and dist.is_initialized()
+        return (self.overlap_grad_reduce and not self.skip_grad_reduce and dist.is_available() and dist.is_initialized()
                 and dist.get_world_size(self.reduce_group) > 1 and not self._reduced)
 
     def _on_grad_range(self, off, numel):
@@ -230,6 +231,8 @@ class MonoT5Model(MonoT5Scorer):
             if covered != self.grads.numel():
                 raise RuntimeError(f"overlapped gradient all-reduce covered {covered} of {self.grads.numel()} elements")
             return 1.0 / dist.get_world_size(self.reduce_group)
+        if self.skip_grad_reduce:
+            return 1.0
         return all_reduce_mean_scale(self.grads, group if group is not None else self.reduce_group)
 
     def step(self, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, gscale=1.0):

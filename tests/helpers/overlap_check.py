@@ -16,7 +16,10 @@ def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     ngpu = torch.cuda.device_count()
     torch.cuda.set_device(rank % ngpu)
-    dist.init_process_group("nccl" if ngpu >= world else "gloo", rank=rank, world_size=world)
+    if ngpu < world and os.environ.get("PN_REQUIRE_NCCL") == "1":
+        raise SystemExit(f"PN_REQUIRE_NCCL=1: {world} ranks need {world} GPUs for NCCL, {ngpu} visible (no gloo fallback)")
+    backend = "nccl" if ngpu >= world else "gloo"
+    dist.init_process_group(backend, rank=rank, world_size=world)
     from oracle import t5 as ot
     from pacednegatives_b200.lceT5 import LCEModel
     from pacednegatives_b200.scorer import T5Dims
@@ -72,7 +75,7 @@ def main():
     own = float((solo.model.grads - one.model.grads).abs().max() / total.abs().max())
     assert own > 1e-2, "ranks were supposed to train on different queries"
     # the reduced gradient is the SUM over ranks (1/world is applied inside AdamW): differs from a local one
-    print(f"rank {rank}: overlap check ok ({g.numel()} gradient elements)", flush=True)
+    print(f"rank {rank}: overlap check ok ({g.numel()} gradient elements, backend {backend})", flush=True)
     dist.destroy_process_group()
 
 
