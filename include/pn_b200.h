@@ -187,6 +187,14 @@ int pn_select_binomial(const int32_t* cand, int64_t Q, int32_t C, int layout, co
 int pn_topk_metrics(const float* scores, const int32_t* docids, const uint8_t* rels, int64_t Q,
                     int32_t C, int32_t K, int32_t* top_ids, float* top_scores, float* metrics_out,
                     void* stream);
+/* The same with the query's qrel totals (eval.py:26,41-43: pt.Experiment / trec_eval judge against ALL judged
+ * documents of a query, including relevant ones the first stage did not retrieve): qrel_num int32 [Q] (nullable) =
+ * number of judged documents with rel >= 1, the average-precision denominator; qrel_idcg double [Q] (nullable) =
+ * ideal DCG@K of the query's judged grades.  NULL = derive each from the candidates' rels (every judged-relevant
+ * document is in the list). */
+int pn_topk_metrics_qrels(const float* scores, const int32_t* docids, const uint8_t* rels,
+                          const int32_t* qrel_num, const double* qrel_idcg, int64_t Q, int32_t C, int32_t K,
+                          int32_t* top_ids, float* top_scores, float* metrics_out, void* stream);
 
 /* ------------------------------------------------------------------ a1 (building block)
  * bf16 GEMM on the tcgen05 tensor path, the T5 linear layers (HF modeling_t5.py:277,298-299,338,92-103):
@@ -265,6 +273,13 @@ int32_t pn_t5_vocab_pad(const PnT5* m);
  * start token, two-row head: z2_out[d] = (z_true, z_false), score_out[d] = log_softmax(z2)[0]. */
 int pn_t5_score(PnT5* m, const int32_t* ids, int64_t docs, int32_t S, int32_t rel_id, int32_t nrel_id,
                 float* score_out, float* z2_out, void* workspace, int64_t workspace_bytes, void* stream);
+/* The same with the tokenizer's attention_mask, as pyterrier_t5.MonoT5ReRanker (eval.py:14,23) and
+ * distill/wrapper.py:36 call the model (`self.model(**enc)`, padding='longest'): lens int32 [docs] (nullable = no
+ * mask) is the number of real tokens of each right-padded prompt; keys at positions >= lens[d] are excluded from the
+ * encoder self-attention and the cross-attention (HF's extended attention mask), 1 <= lens[d] <= S. */
+int pn_t5_score_lens(PnT5* m, const int32_t* ids, const int32_t* lens, int64_t docs, int32_t S, int32_t rel_id,
+                     int32_t nrel_id, float* score_out, float* z2_out, void* workspace, int64_t workspace_bytes,
+                     void* stream);
 /* model(input_ids=ids, labels=labels).logits for T = 1 or 2 label positions (int64 [docs,T]):
  * logits_out fp32 [docs*T, pn_t5_vocab_pad()] (nullable), z2_out fp32 [docs*T, 2] (nullable). */
 int pn_t5_logits(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S, int32_t T,

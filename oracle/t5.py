@@ -106,6 +106,16 @@ def _rms(x, w, eps):
     return w * (x * torch.rsqrt(var + eps))
 
 
+def _key_mask(attention_mask):
+    """HF's extended attention mask (modeling_utils get_extended_attention_mask, used at HF:730-760): padded keys
+    get the dtype's most negative value added to their scores, in the encoder self-attention and, through
+    encoder_attention_mask, in every cross-attention.  [N, S] 0/1 -> additive [N, 1, 1, S] (None -> None)."""
+    if attention_mask is None:
+        return None
+    m = torch.as_tensor(np.asarray(attention_mask), dtype=torch.float32)
+    return ((1.0 - m) * torch.finfo(torch.float32).min)[:, None, None, :]
+
+
 def _attn(xq, xkv, w, prefix, dims, bias):
     N, Tq, _ = xq.shape
     Tk = xkv.shape[1]
@@ -139,10 +149,13 @@ def decoder_bias(w, dims, T):
 
 
 @torch.no_grad()
-def encode(w, dims, input_ids):
+def encode(w, dims, input_ids, attention_mask=None):
     ids = torch.as_tensor(np.asarray(input_ids), dtype=torch.long)
     x = w["shared.weight"][ids]
     bias = encoder_bias(w, dims, ids.shape[1])
+    km = _key_mask(attention_mask)
+    if km is not None:
+        bias = bias + km
     for i in range(dims.n_layers):
         p = f"encoder.block.{i}.layer."
         h = _rms(x, w[p + "0.layer_norm.weight"], dims.eps)
@@ -153,17 +166,18 @@ def encode(w, dims, input_ids):
 
 
 @torch.no_grad()
-def decode(w, dims, enc, decoder_input_ids):
+def decode(w, dims, enc, decoder_input_ids, attention_mask=None):
     """Returns the decoder output after the final norm and the d_model**-0.5 head scaling, [N,T,d]."""
     ids = torch.as_tensor(np.asarray(decoder_input_ids), dtype=torch.long)
     x = w["shared.weight"][ids]
     bias = decoder_bias(w, dims, ids.shape[1])
+    km = _key_mask(attention_mask)
     for i in range(dims.n_dec_layers):
         p = f"decoder.block.{i}.layer."
         h = _rms(x, w[p + "0.layer_norm.weight"], dims.eps)
         x = x + _attn(h, h, w, p + "0.SelfAttention.", dims, bias)
         h = _rms(x, w[p + "1.layer_norm.weight"], dims.eps)
-        x = x + _attn(h, enc, w, p + "1.EncDecAttention.", dims, None)
+        x = x + _attn(h, enc, w, p + "1.EncDecAttention.", dims, km)
         h = _rms(x, w[p + "2.layer_norm.weight"], dims.eps)
         x = x + torch.relu(h @ w[p + "2.DenseReluDense.wi.weight"].T) @ w[p + "2.DenseReluDense.wo.weight"].T
     x = _rms(x, w["decoder.final_layer_norm.weight"], dims.eps)
@@ -189,12 +203,13 @@ def logits(w, dims, input_ids, labels):
 
 
 @torch.no_grad()
-def score(w, dims, input_ids, rel_id, nrel_id):
-    """monoT5 re-rank score (distill/wrapper.py:34-38) with one decoder step.
+def score(w, dims, input_ids, rel_id, nrel_id, attention_mask=None):
+    """monoT5 re-rank score (distill/wrapper.py:34-38) with one decoder step; ``attention_mask`` [N, S] as
+    pyterrier_t5.MonoT5ReRanker / distill/wrapper.py:36 pass it (``self.model(**enc)`` with padding='longest').
     Returns (score float32[N], z2 float32[N,2] = (z_true, z_false))."""
-    enc = encode(w, dims, input_ids)
+    enc = encode(w, dims, input_ids, attention_mask)
     N = enc.shape[0]
-    y = decode(w, dims, enc, np.full((N, 1), dims.pad_id, dtype=np.int64))[:, 0]
+    y = decode(w, dims, enc, np.full((N, 1), dims.pad_id, dtype=np.int64), attention_mask)[:, 0]
     rows = w["shared.weight"][[rel_id, nrel_id]]
     z2 = (y @ rows.T)
     s = torch.log_softmax(z2, dim=1)[:, 0]

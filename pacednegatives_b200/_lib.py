@@ -68,11 +68,13 @@ SIGNATURES = {
     "pn_t5_workspace_bytes": (c_i64, [c_vp, c_i64, c_i32, c_i32, c_int]),
     "pn_t5_vocab_pad": (c_i32, [c_vp]),
     "pn_t5_score": (c_int, [c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp]),
+    "pn_t5_score_lens": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "pn_t5_logits": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp,
                              c_i64, c_vp]),
     "pn_prof_enable": (c_int, [c_int]),
     "pn_prof_read": (c_int, [c_int, c_vp, c_vp, c_vp]),
     "pn_topk_metrics": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "pn_topk_metrics_qrels": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
 }
 
 _lib = None

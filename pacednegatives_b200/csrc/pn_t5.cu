@@ -106,7 +106,7 @@ size_t carve(const PnT5* m, int64_t docs, int S, int T, int want_logits, uint8_t
 // On return xn/ss describe the PRE-final-norm encoder output; the final norm is folded into the cross K/V
 // projections of the decoder.
 int encoder_forward(const PnT5* m, const int32_t* ids, int64_t docs, int S, const Workspace& w,
-                    cudaStream_t st) {
+                    cudaStream_t st, const int32_t* lens = nullptr) {
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
   const int rows = (int)(docs * S);
   const int parts = pn_gemm_sumsq_parts(d);
@@ -115,7 +115,8 @@ int encoder_forward(const PnT5* m, const int32_t* ids, int64_t docs, int S, cons
   for (size_t l = 0; l < m->enc.size(); ++l) {
     const PnEncLayer& L = m->enc[l];
     RC(gemm_normed(m, w.xn, w.ss, cur_parts, L.wqkv, w.big, 3 * di, rows, 0, st));
-    RC(pn_t5_self_attn(w.big, 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx, di, nullptr, st));
+    RC(pn_t5_self_attn_masked(w.big, 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, lens, w.ctx, di, nullptr,
+                              st));
     RC(gemm_resid(m, w.ctx, L.wo, w.hidden, w.xn, w.ss, rows, st));
     cur_parts = parts;
     RC(gemm_normed(m, w.xn, w.ss, cur_parts, L.wi, w.big, ff, rows, 1, st));
@@ -125,7 +126,8 @@ int encoder_forward(const PnT5* m, const int32_t* ids, int64_t docs, int S, cons
 }
 
 // decoder over T tokens per doc (dec_ids [docs*T]); leaves the pre-final-norm hidden in w.dh
-int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& w, cudaStream_t st) {
+int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& w, cudaStream_t st,
+                    const int32_t* lens = nullptr) {
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
   const int rows = (int)(docs * S), drows = (int)(docs * T);
   const int parts = pn_gemm_sumsq_parts(d);
@@ -159,7 +161,7 @@ int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& 
       ex.row_scale = w.rs_enc; ex.group_rows = S; ex.group_b_rows = Mp;
       RC(pn_gemm_bf16_ex(w.xn, d, w.qk, d, w.scores, 128, rows, 128, d, PN_EPI_F32, 0, &ex, (S % 256) == 0 ? 2 : 1,
                          st));
-      RC(pn_t5_cross_softmax(w.scores, 128, w.rs_enc, docs, S, TH, Mp, w.P, st));
+      RC(pn_t5_cross_softmax(w.scores, 128, w.rs_enc, docs, S, TH, Mp, w.P, st, lens));
       // C'[doc] = P[doc]^T . X[doc]  (batched MN-major GEMM), then out = C' . Wv^T and the per-head diagonal blocks
       PN_CUDA(cudaMemsetAsync(w.cprime, 0, (size_t)R * d * 4, st));
       RC(pn_gemm_tn_batched(w.P, Mp, w.xn, d, w.cprime, d, Mp, d, S, (int)docs, st));
@@ -170,7 +172,7 @@ int decoder_forward(const PnT5* m, int64_t docs, int S, int T, const Workspace& 
     } else {
       RC(gemm_normed(m, w.xn, w.ss, enc_parts, L.ckv, w.big, 2 * di, rows, 0, st));
       RC(pn_t5_dec_attn(w.dbig, di, 0, w.big, w.big, 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
-                        w.dctx, di, st));
+                        w.dctx, di, st, lens));
     }
     RC(gemm_resid(m, w.dctx, L.co, w.dh, w.dxn, w.dss, drows, st));
     // FFN
@@ -426,10 +428,18 @@ extern "C" int64_t pn_t5_workspace_bytes(const PnT5* m, int64_t docs, int32_t S,
   return (int64_t)carve(m, docs, S, T, want_logits, nullptr, &w);
 }
 
-// monoT5 re-rank score: encoder + ONE decoder step + two-row head (distill/wrapper.py:34-38)
 extern "C" int pn_t5_score(PnT5* m, const int32_t* ids, int64_t docs, int32_t S, int32_t rel_id,
                            int32_t nrel_id, float* score_out, float* z2_out, void* workspace,
                            int64_t workspace_bytes, void* stream) {
+  return pn_t5_score_lens(m, ids, nullptr, docs, S, rel_id, nrel_id, score_out, z2_out, workspace, workspace_bytes,
+                          stream);
+}
+
+// monoT5 re-rank score: encoder + ONE decoder step + two-row head (distill/wrapper.py:34-38); lens (nullable) =
+// the tokenizer's attention_mask of right-padded prompts as per-document lengths
+extern "C" int pn_t5_score_lens(PnT5* m, const int32_t* ids, const int32_t* lens, int64_t docs, int32_t S,
+                                int32_t rel_id, int32_t nrel_id, float* score_out, float* z2_out, void* workspace,
+                                int64_t workspace_bytes, void* stream) {
   PN_CHECK_ARG(m && m->finalized);
   PN_CHECK_ARG(docs >= 0 && S >= 1 && S <= 512);
   PN_CHECK_ARG(rel_id >= 0 && rel_id < m->cfg.vocab && nrel_id >= 0 && nrel_id < m->cfg.vocab);
@@ -441,10 +451,10 @@ extern "C" int pn_t5_score(PnT5* m, const int32_t* ids, int64_t docs, int32_t S,
   if ((int64_t)need > workspace_bytes)
     return pn_fail(PN_E_BADARG, "pn_t5_score: workspace %lld < %zu bytes", (long long)workspace_bytes, need);
   cudaStream_t st = (cudaStream_t)stream;
-  RC(encoder_forward(m, ids, docs, S, w, st));
+  RC(encoder_forward(m, ids, docs, S, w, st, lens));
   fill_i32_kernel<<<pn_grid(docs, 256, 1, 4), 256, 0, st>>>(w.dec_ids, docs, m->cfg.pad_id);
   PN_LAUNCHED();
-  RC(decoder_forward(m, docs, S, 1, w, st));
+  RC(decoder_forward(m, docs, S, 1, w, st, lens));
   RC(pn_t5_head2(w.dh, m->dec_final, m->emb, docs, m->cfg.d_model, m->cfg.eps, rel_id, nrel_id,
                  score_out, z2_out, st));
   return PN_OK;

@@ -280,6 +280,7 @@ struct DecAttnArgs {
   const float* bias;      // nullable [n_heads, T, Sk] additive
   __nv_bfloat16* out; int ld_out;         // [docs*T, ld_out]
   int n_heads; int docs;
+  const int32_t* klen;                     // optional [docs]: cross-attention key-padding mask
 };
 
 __global__ void __launch_bounds__(128)
@@ -299,7 +300,7 @@ dec_attn_kernel(const DecAttnArgs a) {
     const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(q + d));
     qf[d] = f.x; qf[d + 1] = f.y;
   }
-  const int nk = a.causal ? (t + 1) : a.Sk;
+  const int nk = a.causal ? (t + 1) : (a.klen ? min(a.Sk, max(1, a.klen[doc])) : a.Sk);
   float mx = -INFINITY;
   for (int j = lane; j < nk; j += 32) {
     const __nv_bfloat16* kr = a.k + ((size_t)doc * a.Sk + j) * a.ld_kv + a.k_col + head * DK;
@@ -367,12 +368,13 @@ int pn_t5_self_attn_v1(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_co
 int pn_t5_dec_attn(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_bfloat16* k,
                    const __nv_bfloat16* v, int ld_kv, int k_col, int v_col, int docs, int T, int Sk,
                    int n_heads, int causal, const float* bias, __nv_bfloat16* out, int ld_out,
-                   cudaStream_t st) {
+                   cudaStream_t st, const int32_t* klen) {
   if (Sk < 1 || Sk > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "decoder attention: Sk=%d not in [1,512]", Sk);
   DecAttnArgs a;
   a.q = q; a.ld_q = ld_q; a.q_col = q_col; a.k = k; a.v = v; a.ld_kv = ld_kv; a.k_col = k_col;
   a.v_col = v_col; a.Sk = Sk; a.T = T; a.causal = causal; a.bias = bias; a.out = out;
   a.ld_out = ld_out; a.n_heads = n_heads; a.docs = docs;
+  a.klen = klen;
   const int64_t warps = (int64_t)docs * n_heads * T;
   dec_attn_kernel<<<(unsigned)((warps + 3) / 4), 128, 0, st>>>(a);
   PN_LAUNCHED();

@@ -59,6 +59,7 @@ struct Attn2Args {
   __nv_bfloat16* out;
   int ld_out;
   float* lse;                     // optional [docs*S, n_heads]: log2-domain logsumexp of each row (training)
+  const int32_t* klen;            // optional [docs]: keys >= klen[doc] are padding (HF attention_mask, right-padded)
   long long* dbg;                 // optional [2][64][8] clock64 stamps of CTA 0 (PN_ATTN_DBG)
 };
 
@@ -256,7 +257,12 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
       const int qb = 2 * rd + wg;
       if (qb >= n_qb) continue;
       const int qi = qb * QB + r;                   // query position inside the document
-      const int kvalid = min(KC, S - c * KC);
+      // keys beyond the document's length (attention_mask == 0, or beyond S in the ragged last chunk) get a score no
+      // exponential survives: -inf without a mask (bit-identical to the unmasked kernel), a finite -1e30 with one so
+      // that a chunk with NO valid key leaves the running max alone (chunk 0 always holds key 0: klen >= 1)
+      const int klen = a.klen ? min(S, max(1, a.klen[doc0 + it * a.cph])) : S;
+      const int kvalid = min(KC, klen - c * KC);
+      const float kmasked = a.klen ? -1e30f : -INFINITY;
       if (warp == 0 && lane == 0) DBG_STAMP(0, n, 0);
       mbar_wait(bar(BAR_SFULL + wg), n & 1);
       tc_fence_after();
@@ -279,7 +285,7 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
       if (kvalid < KC) {   // ragged last chunk: keys beyond S do not exist (-inf survives the bias FFMA)
 #pragma unroll
         for (int jj = 0; jj < KC; ++jj)
-          if (jj >= kvalid) x[jj] = -INFINITY;
+          if (jj >= kvalid) x[jj] = kmasked;
       }
       // columns 0..31: x = s*log2e + bias*log2e, and their max (seeds the row max of a fresh query block)
       float m0 = -INFINITY, m1 = -INFINITY;
@@ -492,7 +498,14 @@ static int attn_impl() {
 int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
                     int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
                     cudaStream_t st) {
-  if (attn_impl() == 1 && !lse_out)
+  return pn_t5_self_attn_masked(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, nullptr, out, ld_out,
+                                lse_out, st);
+}
+
+int pn_t5_self_attn_masked(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
+                           int S, int n_heads, const float* bias, const int32_t* klen, __nv_bfloat16* out,
+                           int ld_out, float* lse_out, cudaStream_t st) {
+  if (attn_impl() == 1 && !lse_out && !klen)
     return pn_t5_self_attn_v1(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, out, ld_out, st);
   if (S < 1 || S > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "self-attention: S=%d not in [1,512]", S);
   if (docs <= 0) return PN_OK;
@@ -507,6 +520,7 @@ int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, 
   a.q_col = q_col; a.k_col = k_col; a.v_col = v_col;
   a.bias = bias; a.out = out; a.ld_out = ld_out;
   a.lse = lse_out;
+  a.klen = klen;
   a.dbg = nullptr;
   if (getenv("PN_ATTN_DBG")) {
     static long long* dbg = nullptr;

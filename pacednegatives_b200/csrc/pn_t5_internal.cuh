@@ -48,6 +48,11 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
 int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
                     int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
                     cudaStream_t st);
+// Same with a key-padding mask: keys at positions >= klen[doc] (nullable, [docs]) are excluded from every row's
+// softmax — HF's attention_mask for right-padded prompts (the re-rank path, eval.py:14,23 / distill/wrapper.py:36).
+int pn_t5_self_attn_masked(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
+                           int S, int n_heads, const float* bias, const int32_t* klen, __nv_bfloat16* out,
+                           int ld_out, float* lse_out, cudaStream_t st);
 // Backward of pn_t5_self_attn (pn_t5_attn_bwd.cu): dqkv <- (dq | dk | dv) (each row optionally scaled by
 // row_scale), dbias_diag [H, 1023] += per-diagonal sums of dS; lse2 is the forward's lse_out, dvec a [rows, H]
 // workspace.
@@ -62,7 +67,7 @@ int pn_t5_rel_bias_grad(const float* dbias_diag, const int* bucket_of, int n_hea
 int pn_t5_dec_attn(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_bfloat16* k,
                    const __nv_bfloat16* v, int ld_kv, int k_col, int v_col, int docs, int T, int Sk,
                    int n_heads, int causal, const float* bias, __nv_bfloat16* out, int ld_out,
-                   cudaStream_t st);
+                   cudaStream_t st, const int32_t* klen = nullptr);   // klen [docs]: keys >= klen[doc] are padding
 
 // Backward of pn_t5_dec_attn (pn_t5_dec_attn_bwd.cu).  dq rows are scaled by rs_q, dk / dv rows by rs_kv (both
 // nullable); grad_rel (nullable) accumulates the decoder relative_attention_bias gradient [buckets, H].

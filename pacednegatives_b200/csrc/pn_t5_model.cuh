@@ -107,7 +107,7 @@ int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float e
 int pn_t5_cross_expand_q(const __nv_bfloat16* q, int ld_q, int64_t docs, int T, int H, int Mp, __nv_bfloat16* qexp,
                          cudaStream_t st);
 int pn_t5_cross_softmax(const float* scores, int lds, const float* rs, int64_t docs, int S, int TH, int Mp,
-                        __nv_bfloat16* P, cudaStream_t st);
+                        __nv_bfloat16* P, cudaStream_t st, const int32_t* klen = nullptr);
 int pn_t5_cross_gather(const __nv_bfloat16* full, int Mp, int64_t docs, int T, int H, __nv_bfloat16* ctx, int ld_ctx,
                        cudaStream_t st);
 

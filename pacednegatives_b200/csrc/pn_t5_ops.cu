@@ -261,7 +261,7 @@ cross_expand_q_kernel(const __nv_bfloat16* __restrict__ q, int ld_q, int64_t doc
 // P^T . X sums the normalised states); pad columns th >= TH are written as zero.  One CTA per document.
 __global__ void __launch_bounds__(256)
 cross_softmax_kernel(const float* __restrict__ scores, int lds, const float* __restrict__ rs, int S, int TH, int Mp,
-                     __nv_bfloat16* __restrict__ P) {
+                     __nv_bfloat16* __restrict__ P, const int32_t* __restrict__ klen) {
   __shared__ float red[8][32];
   __shared__ float stat[32];
   const int64_t row0 = (int64_t)blockIdx.x * S;
@@ -271,10 +271,11 @@ cross_softmax_kernel(const float* __restrict__ scores, int lds, const float* __r
   const bool act = th < TH;
   float v[64];   // this lane's column, rows warp, warp + 8, ... (S <= 512)
   float mx = -INFINITY;
+  const int nk = klen ? min(S, max(1, klen[blockIdx.x])) : S;   // encoder rows >= klen[doc] are padding: P = 0 there
 #pragma unroll
   for (int i = 0; i < 64; ++i) {
     const int j = warp + 8 * i;
-    v[i] = (act && j < S) ? scores[(size_t)(row0 + j) * lds + th] : -INFINITY;
+    v[i] = (act && j < nk) ? scores[(size_t)(row0 + j) * lds + th] : -INFINITY;
     mx = fmaxf(mx, v[i]);
   }
   red[warp][lane] = mx;
@@ -339,10 +340,10 @@ int pn_t5_cross_expand_q(const __nv_bfloat16* q, int ld_q, int64_t docs, int T, 
   return PN_OK;
 }
 int pn_t5_cross_softmax(const float* scores, int lds, const float* rs, int64_t docs, int S, int TH, int Mp,
-                        __nv_bfloat16* P, cudaStream_t st) {
+                        __nv_bfloat16* P, cudaStream_t st, const int32_t* klen) {
   if (docs == 0) return PN_OK;
   if (Mp > 32 || TH > Mp) return pn_fail(PN_E_UNSUPPORTED, "cross softmax: T*H=%d > 32", TH);
-  cross_softmax_kernel<<<(unsigned)docs, 256, 0, st>>>(scores, lds, rs, S, TH, Mp, P);
+  cross_softmax_kernel<<<(unsigned)docs, 256, 0, st>>>(scores, lds, rs, S, TH, Mp, P, klen);
   PN_LAUNCHED();
   return PN_OK;
 }

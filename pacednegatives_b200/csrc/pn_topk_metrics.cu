@@ -28,7 +28,8 @@ __global__ void __launch_bounds__(kThreads)
 topk_metrics_kernel(const float* __restrict__ scores, const int32_t* __restrict__ docids,
                     const uint8_t* __restrict__ rels, int64_t Q, int32_t C, int32_t P, int32_t K,
                     int32_t* __restrict__ top_ids, float* __restrict__ top_scores,
-                    float* __restrict__ metrics) {
+                    float* __restrict__ metrics,
+    const int32_t* __restrict__ qrel_num, const double* __restrict__ qrel_idcg) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* key = reinterpret_cast<uint64_t*>(smem_raw);       // [P]
   uint16_t* pos = reinterpret_cast<uint16_t*>(key + P);        // [P]
@@ -124,6 +125,10 @@ topk_metrics_kernel(const float* __restrict__ scores, const int32_t* __restrict_
             nrel += c;
             for (int j = 0; j < c && slot < K; ++j, ++slot) idcg += (double)g / log2((double)(slot + 2));
           }
+          // trec_eval divides by ALL judged-relevant documents of the query and builds the ideal ranking from ALL
+          // judged grades, retrieved or not: the caller's qrel totals replace the candidate-list ones when given
+          if (qrel_idcg) idcg = qrel_idcg[q];
+          if (qrel_num) nrel = qrel_num[q];
           float* m = metrics + q * 4;
           m[0] = idcg > 0.0 ? (float)(d / idcg) : 0.0f;
           m[1] = f < C ? (float)(1.0 / (double)(f + 1)) : 0.0f;
@@ -149,7 +154,8 @@ constexpr int kFastMaxK = 32;
 __global__ void __launch_bounds__(kThreads)
 topk_count_kernel(const float* __restrict__ scores, const int32_t* __restrict__ docids,
                   const uint8_t* __restrict__ rels, int64_t Q, int32_t C, int32_t K,
-                  int32_t* __restrict__ top_ids, float* __restrict__ top_scores, float* __restrict__ metrics) {
+                  int32_t* __restrict__ top_ids, float* __restrict__ top_scores, float* __restrict__ metrics,
+    const int32_t* __restrict__ qrel_num, const double* __restrict__ qrel_idcg) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int Cp = (C + 3) & ~3;
   uint64_t* key = reinterpret_cast<uint64_t*>(smem_raw);          // [Cp], padding keys = 0 (below every real key)
@@ -311,11 +317,13 @@ topk_count_kernel(const float* __restrict__ scores, const int32_t* __restrict__ 
           double a = 0.0;
           int f = 0x7fffffff;
           for (int w = 0; w < kThreads / 32; ++w) { a += s_ap[w]; f = min(f, s_first[w]); }
+          if (qrel_idcg) idcg = qrel_idcg[q];
+          const int nrel = qrel_num ? qrel_num[q] : R;
           float* m = metrics + q * 4;
           m[0] = idcg > 0.0 ? (float)(dcg / idcg) : 0.0f;
           m[1] = f < C ? (float)(1.0 / (double)(f + 1)) : 0.0f;
           m[2] = f < K ? (float)(1.0 / (double)(f + 1)) : 0.0f;
-          m[3] = R > 0 ? (float)(a / (double)R) : 0.0f;
+          m[3] = nrel > 0 ? (float)(a / (double)nrel) : 0.0f;
         }
       }
     }
@@ -328,6 +336,14 @@ topk_count_kernel(const float* __restrict__ scores, const int32_t* __restrict__ 
 extern "C" int pn_topk_metrics(const float* scores, const int32_t* docids, const uint8_t* rels,
                                int64_t Q, int32_t C, int32_t K, int32_t* top_ids, float* top_scores,
                                float* metrics_out, void* stream) {
+  return pn_topk_metrics_qrels(scores, docids, rels, nullptr, nullptr, Q, C, K, top_ids, top_scores, metrics_out,
+                               stream);
+}
+
+extern "C" int pn_topk_metrics_qrels(const float* scores, const int32_t* docids, const uint8_t* rels,
+                                     const int32_t* qrel_num, const double* qrel_idcg, int64_t Q, int32_t C,
+                                     int32_t K, int32_t* top_ids, float* top_scores, float* metrics_out,
+                                     void* stream) {
   PN_CHECK_ARG(Q >= 0 && C >= 1 && C <= 4096 && K >= 1);
   if (Q == 0) return PN_OK;
   PN_CHECK_ARG(scores != nullptr);
@@ -337,7 +353,7 @@ extern "C" int pn_topk_metrics(const float* scores, const int32_t* docids, const
     PN_CUDA(cudaFuncSetAttribute(topk_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (int)(Q < 148 * 8 ? Q : 148 * 8);
     topk_count_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(scores, docids, rels, Q, C, K, top_ids,
-                                                                      top_scores, metrics_out);
+                                                                      top_scores, metrics_out, qrel_num, qrel_idcg);
     PN_LAUNCHED();
     return PN_OK;
   }
@@ -348,7 +364,7 @@ extern "C" int pn_topk_metrics(const float* scores, const int32_t* docids, const
                                (int)smem));
   const int grid = (int)(Q < 148 * 4 ? Q : 148 * 4);
   topk_metrics_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(
-      scores, docids, rels, Q, C, P, K, top_ids, top_scores, metrics_out);
+      scores, docids, rels, Q, C, P, K, top_ids, top_scores, metrics_out, qrel_num, qrel_idcg);
   PN_LAUNCHED();
   return PN_OK;
 }

@@ -246,60 +246,192 @@ class MonoT5Model(MonoT5Scorer):
                                                self.opt_steps, float(gscale), _lib.stream()))
 
 
-class _AdamWTensor:
-    """transformers.AdamW on one small device tensor (the eta parameter, lceT5.py:171)."""
-
-    def __init__(self, param, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0):
-        self.param, self.lr, self.betas, self.eps, self.wd = param, float(lr), betas, eps, weight_decay
-        self.m = torch.zeros_like(param.data)
-        self.v = torch.zeros_like(param.data)
-        self.steps = 0
-
-    def zero_grad(self):
-        self.param.grad = None
-
-    def step(self, lr=None):
-        if self.param.grad is None:
-            return
-        self.steps += 1
-        g = self.param.grad.contiguous().float()
-        _lib.check(_lib.lib().pn_adamw(_lib.ptr(self.param.data), _lib.ptr(g), _lib.ptr(self.m), _lib.ptr(self.v),
-                                       self.param.numel(), self.lr if lr is None else float(lr), self.betas[0],
-                                       self.betas[1], self.eps, self.wd, self.steps, 1.0, _lib.stream()))
+class _HParams(dict):
+    """Lightning's AttributeDict for the plain-class build: hparams.n and hparams['n'] both work."""
+    __getattr__ = dict.__getitem__
+    __setattr__ = dict.__setitem__
 
 
-class LCEModel:
-    """hparams: dict or namespace with the reference's keys — n, use_mean, ignore_index, lr, meta_lr,
-    warmup_steps, total_steps, eta — plus `dims` / `state_dict` in place of `model_name` (no hub access).
-    `elide_no_grad_forward` (default True) reuses the gradient-tracking forward's logits for the meta step: with
-    dropout 0 the reference's no-grad forward (lceT5.py:131-133) computes exactly the same numbers."""
+class _AdamWTensor(torch.optim.Optimizer):
+    """transformers.AdamW (eps 1e-6, no weight decay, bias-corrected: lceT5.py:171) on small device tensors — the
+    eta parameter — through the pn_adamw kernel.  A real torch Optimizer, so transformers'
+    get_linear_schedule_with_warmup (a LambdaLR) and Lightning's optimizer plumbing accept it."""
 
-    def __init__(self, hparams, dims=None, state_dict=None, model=None, elide_no_grad_forward=True, **model_kw):
-        if isinstance(hparams, dict):
-            hparams = SimpleNamespace(**hparams)
-        self.hparams = hparams
-        self.model = model if model is not None else MonoT5Model(dims, state_dict, **model_kw)
-        self.weights = LCEWeights(hparams)
-        self.elide = bool(elide_no_grad_forward)
+    def __init__(self, params, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0):
+        if torch.is_tensor(params):
+            params = [params]
+        super().__init__(params, dict(lr=float(lr), betas=betas, eps=eps, weight_decay=weight_decay))
+
+    @torch.no_grad()
+    def step(self, closure=None, lr=None):
+        loss = closure() if closure is not None else None
+        for g in self.param_groups:
+            for p in g["params"]:
+                if p.grad is None:
+                    continue
+                st = self.state[p]
+                if not st:
+                    st["step"], st["m"], st["v"] = 0, torch.zeros_like(p.data), torch.zeros_like(p.data)
+                st["step"] += 1
+                grad = p.grad.contiguous().float()
+                _lib.check(_lib.lib().pn_adamw(_lib.ptr(p.data), _lib.ptr(grad), _lib.ptr(st["m"]), _lib.ptr(st["v"]),
+                                               p.numel(), g["lr"] if lr is None else float(lr), g["betas"][0],
+                                               g["betas"][1], g["eps"], g["weight_decay"], st["step"], 1.0,
+                                               _lib.stream()))
+        return loss
+
+
+class _ModelAdamW(torch.optim.Optimizer):
+    """transformers.AdamW over the model's flat fp32 parameter buffer (lceT5.py:172) = one pn_t5_adamw_step launch
+    (+ the bf16 operand repack).  The optimiser's single parameter is a tensor VIEW of the library's master buffer
+    whose .grad is the flat gradient buffer, so torch-side tools (LambdaLR, LearningRateMonitor, gradient
+    inspection) see real tensors; the data-parallel gradient mean is finished here (``all_reduce_grads``)."""
+
+    def __init__(self, model, lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0):
+        self.model = model
+        flat = model.parameters_flat().requires_grad_(True)
+        flat.grad = model.grads
+        super().__init__([flat], dict(lr=float(lr), betas=betas, eps=eps, weight_decay=weight_decay))
+
+    def zero_grad(self, set_to_none=False):
+        self.model.zero_grad()     # the buffer stays: the library accumulates into it
+
+    def all_reduce_grads(self, group=None):
+        return self.model.all_reduce_grads(group)
+
+    @torch.no_grad()
+    def step(self, closure=None, lr=None, gscale=None):
+        loss = closure() if closure is not None else None
+        g = self.param_groups[0]
+        if gscale is None:
+            gscale = self.model.all_reduce_grads()
+        self.model.step(g["lr"] if lr is None else float(lr), g["betas"], g["eps"], g["weight_decay"], gscale)
+        return loss
+
+
+def _linear_schedule(optimizer, num_warmup_steps, num_training_steps):
+    """transformers.get_linear_schedule_with_warmup (lceT5.py:174-179); the same LambdaLR built here when
+    transformers is not importable."""
+    try:
+        from transformers import get_linear_schedule_with_warmup
+        return get_linear_schedule_with_warmup(optimizer, num_warmup_steps=num_warmup_steps,
+                                               num_training_steps=num_training_steps)
+    except ImportError:
+        from torch.optim.lr_scheduler import LambdaLR
+        return LambdaLR(optimizer, lambda s: linear_schedule_with_warmup(s, num_warmup_steps, num_training_steps))
+
+
+class TokenCELoss:
+    """``nn.CrossEntropyLoss(ignore_index=..., reduction='none')`` (lceT5.py:110) as one streaming kernel per row
+    (pn_token_ce_fwd / _bwd): ``loss_fn(logits[rows, V], target[rows]) -> [rows]``."""
+
+    def __init__(self, ignore_index=-100, reduction="none"):
+        if reduction != "none":
+            raise ValueError("the LCE path uses reduction='none' (lceT5.py:110)")
+        self.ignore_index, self.reduction = int(ignore_index), reduction
+
+    def __call__(self, logits, target):
+        from .loss import token_ce
+        return token_ce(logits, target, self.ignore_index)
+
+
+try:     # the reference's base class, when the package exists (it is not in this image: plain class then)
+    import lightning as _pl
+    _LightningBase = _pl.LightningModule
+except ImportError:
+    _pl, _LightningBase = None, object
+
+
+class LCEModel(_LightningBase):
+    """Drop-in for ``pacednegatives.lceT5.LCEModel`` (lceT5.py:101-182): ``LCEModel(hparams)`` with the reference's
+    keys — model_name, total_steps, eta, batch_size, lr, meta_lr, n, warmup_steps, use_mean, ignore_index.
+
+    ``model_name`` is a LOCAL HuggingFace checkpoint directory (no hub access): the model comes from
+    ``MonoT5Model.from_pretrained`` and, when the directory holds SentencePiece files, ``self.tokenizer`` from
+    ``T5Tokenizer.from_pretrained``.  Without ``model_name`` pass ``dims=`` + ``state_dict=`` (or ``model=``).
+    Attributes as in the reference: ``.model``, ``.tokenizer``, ``.weights`` (``.eta``), ``.loss_fn``,
+    ``.difficulty``, ``.hparams``, ``automatic_optimization = False``.  Subclasses ``lightning.LightningModule`` when
+    that package is importable (manual optimisation: ``self.optimizers()``, ``self.lr_schedulers()``,
+    ``self.manual_backward``), a plain class with the same methods otherwise.
+
+    Extra hparams (all optional): ``micro_queries`` (walk the batch in query groups), ``dropout_rate``.
+    ``elide_no_grad_forward`` (default: True when dropout is 0) reuses the gradient-tracking forward's logits for the
+    meta step: without dropout the reference's no-grad forward (lceT5.py:131-133) computes exactly the same numbers."""
+
+    def __init__(self, hparams, dims=None, state_dict=None, model=None, elide_no_grad_forward=None, tokenizer=None,
+                 **model_kw):
+        if _pl is not None:
+            super().__init__()
+        if not isinstance(hparams, dict):
+            hparams = dict(vars(hparams))
+        if _pl is not None:
+            for key in hparams.keys():
+                self.hparams[key] = hparams[key]
+        else:
+            self.hparams = _HParams(hparams)
+        self.hparams.setdefault("ignore_index", -100)
+        self.hparams.setdefault("use_mean", False)
+        self.hparams.setdefault("warmup_steps", 0)
+        self.hparams.setdefault("meta_lr", self.hparams.get("lr"))
+        name = self.hparams.get("model_name")
+        if model is not None:
+            self.model = model
+        elif dims is not None:
+            self.model = MonoT5Model(dims, state_dict, **model_kw)
+        elif name is not None:
+            self.model = MonoT5Model.from_pretrained(name, **model_kw)
+        else:
+            raise ValueError("LCEModel: give hparams['model_name'] (a local checkpoint directory) or dims= + state_dict=")
+        self.tokenizer = tokenizer
+        if tokenizer is None and name is not None and model is None and dims is None:
+            self.tokenizer = _load_tokenizer(name)
+        self.weights = LCEWeights(self.hparams)
+        self.loss_fn = TokenCELoss(ignore_index=int(self.hparams.ignore_index), reduction="none")
+        self.automatic_optimization = False
+        if _pl is not None:
+            self.save_hyperparameters()
+        self.elide = bool(elide_no_grad_forward) if elide_no_grad_forward is not None else True
         self.difficulty = self.weights.eta.item()
-        self.global_step = 0
+        self._pn_step = 0
         self.logged = {}
-        self._opts = None
+        self._opts = self._scheds = None
 
-    def log(self, name, value):
-        self.logged[name] = value
+    # ---- the slice of the LightningModule interface training_step uses (plain-class build)
+    if _pl is None:
+        @property
+        def global_step(self):
+            return self._pn_step
+
+        def log(self, name, value, *a, **kw):
+            self.logged[name] = value
+
+        def optimizers(self):
+            if self._opts is None:
+                self._opts, self._scheds = self.configure_optimizers()
+            return self._opts
+
+        def lr_schedulers(self):
+            self.optimizers()
+            return self._scheds
+
+        def manual_backward(self, loss):
+            loss.backward()
+    else:
+        def log(self, name, value, *a, **kw):
+            self.logged[name] = value
+            if getattr(self, "_trainer", None) is not None:
+                super().log(name, value, *a, **kw)
 
     def pair_loss(self, p, n, op, on):
         return _pair_loss(p, n, op, on, use_mean=bool(self.hparams.use_mean),
-                          ignore_index=int(getattr(self.hparams, "ignore_index", -100)))
+                          ignore_index=int(self.hparams.ignore_index))
 
     def configure_optimizers(self):
-        meta_opt = _AdamWTensor(self.weights.eta, lr=self.hparams.meta_lr)
-        return [meta_opt, self.model], [None, None]
-
-    def _lr_scale(self):
-        return linear_schedule_with_warmup(self.global_step, int(self.hparams.warmup_steps),
-                                           int(self.hparams.total_steps))
+        meta_opt = _AdamWTensor(self.weights.parameters(), lr=self.hparams.meta_lr)
+        opt = _ModelAdamW(self.model, lr=self.hparams.lr)
+        meta_sched = _linear_schedule(meta_opt, int(self.hparams.warmup_steps), int(self.hparams.total_steps))
+        sched = _linear_schedule(opt, int(self.hparams.warmup_steps), int(self.hparams.total_steps))
+        return [meta_opt, opt], [meta_sched, sched]
 
     def _forward_pn(self, p, n, k, V):
         """`self.model(**p).logits`, `self.model(**n).logits` (lceT5.py:149-150).  Documents are independent, so
@@ -314,21 +446,27 @@ class LCEModel:
             return logits[:Q], logits[Q:].reshape(-1, k, V)
         return self.model(pi, pl), self.model(ni, nl).view(-1, k, V)
 
-    def _meta_step(self, loss, meta_opt, scale):
-        """lceT5.py:135-147: eta's AdamW step on mean(w * loss) and the three logged scalars."""
+    @staticmethod
+    def _raw(opt):
+        """the optimiser behind Lightning's LightningOptimizer wrapper (or the object itself)"""
+        return getattr(opt, "optimizer", opt)
+
+    def _meta_step(self, loss, meta_opt, meta_scheduler):
+        """lceT5.py:135-147: eta's AdamW step on mean(w * loss), its scheduler step and the three logged scalars."""
         weights = self.weights(loss)
         meta_loss = weights * loss
         meta_opt.zero_grad()
-        meta_loss.mean().backward()
-        if self.weights.eta.grad is not None:
+        self.manual_backward(meta_loss.mean())
+        if self.weights.eta.grad is not None:     # DDP's mean over ranks of eta's gradient
             self.weights.eta.grad *= all_reduce_mean_scale(self.weights.eta.grad)
-        meta_opt.step(lr=self.hparams.meta_lr * scale)
+        meta_opt.step()
+        meta_scheduler.step()
         self.log("avg_weight", weights.mean())
         self.log("meta_loss", meta_loss.mean())
         self.log("eta", self.weights.eta.item())
         return weights, meta_loss
 
-    def _training_step_micro(self, p, n, mq, meta_opt, opt, scale):
+    def _training_step_micro(self, p, n, mq, meta_opt, opt, meta_scheduler, scheduler):
         """The same step with the batch walked in groups of `micro_queries` queries (T5-large at 1+31 x 512 does
         not keep 512 documents of activations in HBM): every query's loss element, weight and gradient
         contribution is independent of the other queries, so the gradients of mean(main_loss) are
@@ -356,16 +494,16 @@ class LCEModel:
                                       nc["labels"].cuda())
                 parts.append(main.detach())
                 self.model.accumulating = b < Q
-                (main.sum() / float(Q * T)).backward()
+                self.manual_backward(main.sum() / float(Q * T))
                 del plogits, nlogits, main
         finally:
             self.model.accumulating = False
         main_loss = torch.cat(parts)
         loss = main_loss if self.elide else loss0
-        weights, meta_loss = self._meta_step(loss, meta_opt, scale)
-        gscale = opt.all_reduce_grads()
-        opt.step(lr=self.hparams.lr * scale, gscale=gscale)
-        self.global_step += 1
+        weights, meta_loss = self._meta_step(loss, meta_opt, meta_scheduler)
+        opt.step()
+        scheduler.step()
+        self._pn_step += 1
         return self._step_output(loss, weights, main_loss, meta_loss)
 
     def _step_output(self, loss, weights, main_loss, meta_loss):
@@ -377,15 +515,15 @@ class LCEModel:
         return output
 
     def training_step(self, batch, batch_nb=0):
+        """lceT5.py:125-168, statement for statement; the model calls go to libpn_b200."""
         p, n = batch
-        if self._opts is None:
-            self._opts = self.configure_optimizers()[0]
-        meta_opt, opt = self._opts
+
+        meta_opt, opt = self.optimizers()
+        meta_scheduler, scheduler = self.lr_schedulers()
         k, V = int(self.hparams.n), self.model.dims.vocab
-        scale = self._lr_scale()
-        mq = int(getattr(self.hparams, "micro_queries", 0) or 0)
+        mq = int(self.hparams.get("micro_queries", 0) or 0)
         if 0 < mq < len(p["input_ids"]):
-            return self._training_step_micro(p, n, mq, meta_opt, opt, scale)
+            return self._training_step_micro(p, n, mq, meta_opt, opt, meta_scheduler, scheduler)
 
         if self.elide:
             plogits, nlogits = self._forward_pn(p, n, k, V)
@@ -400,15 +538,25 @@ class LCEModel:
         with torch.no_grad():
             loss = self.pair_loss(p0.contiguous(), n0.contiguous(), op, on)
 
-        weights, meta_loss = self._meta_step(loss, meta_opt, scale)
+        weights, meta_loss = self._meta_step(loss, meta_opt, meta_scheduler)
 
         if not self.elide:
             plogits, nlogits = self._forward_pn(p, n, k, V)
         main_loss = self.pair_loss(plogits.contiguous(), nlogits.contiguous(), op, on)
 
         opt.zero_grad()
-        main_loss.mean().backward()
-        gscale = opt.all_reduce_grads()
-        opt.step(lr=self.hparams.lr * scale, gscale=gscale)
-        self.global_step += 1
+        self.manual_backward(main_loss.mean())
+        opt.step()          # finishes the data-parallel gradient mean (ranges sent during the backward), then AdamW
+        scheduler.step()
+        self._pn_step += 1
         return self._step_output(loss, weights, main_loss, meta_loss)
+
+
+def _load_tokenizer(path):
+    """T5Tokenizer.from_pretrained(model_name) (lceT5.py:107) from the local directory; None when it holds no
+    SentencePiece / tokenizer files (random-init test models): using `.tokenizer` then fails where it is used."""
+    import os
+    if not any(os.path.exists(os.path.join(path, f)) for f in ("spiece.model", "tokenizer.json")):
+        return None
+    from transformers import T5Tokenizer
+    return T5Tokenizer.from_pretrained(path)

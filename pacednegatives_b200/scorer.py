@@ -108,16 +108,23 @@ def dims_from_hf_config(cfg):
                   eps=cfg.get("layer_norm_epsilon", 1e-6), pad_id=cfg.get("pad_token_id", 0) or 0)
 
 
-def hf_config(dims):
-    """The ``config.json`` a ``T5ForConditionalGeneration.from_pretrained`` needs to rebuild these dims."""
-    return {"architectures": ["T5ForConditionalGeneration"], "model_type": "t5", "vocab_size": dims.vocab,
-            "d_model": dims.d_model, "d_kv": dims.d_kv, "d_ff": dims.d_ff, "num_layers": dims.n_layers,
-            "num_decoder_layers": dims.n_dec_layers, "num_heads": dims.n_heads,
-            "relative_attention_num_buckets": dims.rel_buckets, "relative_attention_max_distance": dims.rel_max_dist,
-            "layer_norm_epsilon": dims.eps, "dropout_rate": 0.0, "feed_forward_proj": "relu",
-            "dense_act_fn": "relu", "is_gated_act": False, "is_encoder_decoder": True, "initializer_factor": 1.0,
-            "tie_word_embeddings": True, "use_cache": True, "pad_token_id": dims.pad_id, "eos_token_id": 1,
-            "decoder_start_token_id": dims.pad_id}
+def hf_config(dims, base=None, dropout_rate=None):
+    """The ``config.json`` a ``T5ForConditionalGeneration.from_pretrained`` needs to rebuild these dims.  ``base``:
+    the config the weights were loaded from — every field of it is preserved (dropout_rate, task_specific_params,
+    n_positions ...) and only the architecture fields are (re)written from ``dims``; without one, HF's t5 defaults
+    (dropout_rate 0.1, what t5-* / monot5-* ship) are written."""
+    cfg = dict(base) if base else {"architectures": ["T5ForConditionalGeneration"], "model_type": "t5",
+                                   "dropout_rate": 0.1, "feed_forward_proj": "relu", "dense_act_fn": "relu",
+                                   "is_gated_act": False, "is_encoder_decoder": True, "initializer_factor": 1.0,
+                                   "tie_word_embeddings": True, "use_cache": True, "eos_token_id": 1}
+    cfg.update({"vocab_size": dims.vocab, "d_model": dims.d_model, "d_kv": dims.d_kv, "d_ff": dims.d_ff,
+                "num_layers": dims.n_layers, "num_decoder_layers": dims.n_dec_layers, "num_heads": dims.n_heads,
+                "relative_attention_num_buckets": dims.rel_buckets,
+                "relative_attention_max_distance": dims.rel_max_dist, "layer_norm_epsilon": dims.eps,
+                "pad_token_id": dims.pad_id, "decoder_start_token_id": dims.pad_id})
+    if dropout_rate is not None:
+        cfg["dropout_rate"] = float(dropout_rate)
+    return cfg
 
 
 def _tensor_shape(name, numel, dims):
@@ -136,18 +143,22 @@ def _tensor_shape(name, numel, dims):
     return shape
 
 
-def load_checkpoint(path):
-    """(T5Dims, state_dict) of a local ``save_pretrained`` directory: config.json + model.safetensors or
-    pytorch_model.bin.  No network access: ``path`` must exist."""
+def load_checkpoint(path, return_config=False):
+    """(T5Dims, state_dict[, config dict]) of a local ``save_pretrained`` directory: config.json +
+    model.safetensors or pytorch_model.bin.  No network access: ``path`` must exist."""
+    if not os.path.isdir(path):
+        raise FileNotFoundError(f"{path!r} is not a local checkpoint directory (there is no hub access: pass the "
+                                "path of a save_pretrained directory with config.json + model.safetensors)")
     with open(os.path.join(path, "config.json")) as f:
-        dims = dims_from_hf_config(json.load(f))
+        cfg = json.load(f)
+    dims = dims_from_hf_config(cfg)
     st = os.path.join(path, "model.safetensors")
     if os.path.exists(st):
         from safetensors.torch import load_file
         sd = load_file(st)
     else:
         sd = torch.load(os.path.join(path, "pytorch_model.bin"), map_location="cpu", weights_only=True)
-    return dims, sd
+    return (dims, sd, cfg) if return_config else (dims, sd)
 
 
 def _world(group=None):
@@ -216,12 +227,25 @@ class MonoT5Scorer:
         _lib.check(lib.pn_t5_set_option(self._h, b"xattn", int(bool(xattn))))
         if train:   # also keep the transposed operands of the data-gradient GEMMs (must precede the weights)
             _lib.check(lib.pn_t5_set_option(self._h, b"train", 1))
+        self.hf_config_base = None      # config.json of the checkpoint the weights came from (from_pretrained)
+        known = {n for n, _, _ in self.named_offsets()} | set(_TIED)
+        skipped = []
         for name, t in state_dict.items():
             if not torch.is_tensor(t) or not t.is_floating_point():
+                continue
+            if name not in known:
+                # e.g. decoder.block.0.layer.1.EncDecAttention.relative_attention_bias.weight, which stock t5-* /
+                # monot5-* checkpoints still carry and HF drops (_keys_to_ignore_on_load_unexpected); a MISSING
+                # weight still fails in pn_t5_finalize
+                skipped.append(name)
                 continue
             src = t.detach().to(device="cuda", dtype=torch.float32).contiguous()
             _lib.check(lib.pn_t5_load_weight(self._h, name.encode(), _lib.ptr(src), src.numel(),
                                              _lib.stream()))
+        if skipped:
+            import warnings
+            warnings.warn(f"MonoT5Scorer: ignored {len(skipped)} checkpoint tensor(s) outside the model: "
+                          + ", ".join(skipped[:4]) + (" ..." if len(skipped) > 4 else ""))
         _lib.check(lib.pn_t5_finalize(self._h, _lib.stream()))
         self.vocab_pad = int(lib.pn_t5_vocab_pad(self._h))
         self._ws, self._ws_key = None, None
@@ -238,8 +262,10 @@ class MonoT5Scorer:
     def from_pretrained(cls, path, **kw):
         """Build from a local HuggingFace checkpoint directory (``T5ForConditionalGeneration.from_pretrained``
         at lceT5.py:106, ``MonoT5ReRanker(model=...)`` at eval.py:14)."""
-        dims, sd = load_checkpoint(path)
-        return cls(dims, sd, **kw)
+        dims, sd, cfg = load_checkpoint(path, return_config=True)
+        m = cls(dims, sd, **kw)
+        m.hf_config_base = cfg
+        return m
 
     def parameters_flat(self):
         """fp32 view [num_params] of the library's master parameters (HF state_dict order); shares memory."""
@@ -275,7 +301,8 @@ class MonoT5Scorer:
         .from_pretrained(path)`` loads — train/train_lce.py:103 calls this on the trained model."""
         os.makedirs(path, exist_ok=True)
         with open(os.path.join(path, "config.json"), "w") as f:
-            json.dump(hf_config(self.dims), f, indent=2)
+            json.dump(hf_config(self.dims, self.hf_config_base, getattr(self, "dropout_rate", None)
+                                if self.hf_config_base is None else None), f, indent=2)
         sd = {k: v.contiguous() for k, v in self.state_dict().items()}
         if safe_serialization:
             from safetensors.torch import save_file
@@ -299,20 +326,50 @@ class MonoT5Scorer:
             ids = ids.to(torch.int32)
         return ids.contiguous()
 
-    def score(self, input_ids, return_z2=False):
+    @staticmethod
+    def _lengths(attention_mask, lengths, N, S):
+        """int32 [N] device lengths from the tokenizer's attention_mask (right padding, as T5Tokenizer pads) or
+        explicit lengths; None when neither is given or nothing is padded."""
+        if lengths is None and attention_mask is None:
+            return None
+        if lengths is None:
+            m = torch.as_tensor(attention_mask)
+            if tuple(m.shape) != (N, S):
+                raise ValueError(f"attention_mask must be [{N}, {S}], got {tuple(m.shape)}")
+            m = m.to(device="cuda") != 0
+            lengths = m.sum(1)
+            prefix = torch.arange(S, device="cuda")[None, :] < lengths[:, None]
+            if not bool((m == prefix).all()):
+                raise NotImplementedError("attention_mask must be a prefix of ones per row (right padding, what "
+                                          "T5Tokenizer produces); left padding / holes are not supported")
+        lens = torch.as_tensor(lengths).to(device="cuda", dtype=torch.int32).contiguous()
+        if lens.numel() != N:
+            raise ValueError(f"lengths must have {N} entries")
+        if bool((lens < 1).any()) or bool((lens > S).any()):
+            raise ValueError("every prompt needs 1 <= length <= S")
+        return lens
+
+    def score(self, input_ids, return_z2=False, attention_mask=None, lengths=None):
         """input_ids [N, S] (int32/int64, CPU or CUDA) -> score fp32 [N] (= log_softmax over the
-        'true'/'false' logits of the first decoder step), optionally z2 [N, 2]."""
+        'true'/'false' logits of the first decoder step), optionally z2 [N, 2].
+
+        ``attention_mask`` [N, S] (or ``lengths`` [N]): the tokenizer's mask for prompts right-padded to the batch
+        maximum, as pyterrier_t5.MonoT5ReRanker (eval.py:14,23) and distill/wrapper.py:36 pass it — padded keys are
+        excluded from the encoder self-attention and the cross-attention.  Without one every position is attended
+        (the training path of the reference drops the mask: lceT5.py:53, pairwrapper.py:79-80)."""
         ids = self._ids(input_ids)
         N, S = ids.shape
+        lens = self._lengths(attention_mask, lengths, N, S)
         score = torch.empty(N, dtype=torch.float32, device="cuda")
         z2 = torch.empty(N, 2, dtype=torch.float32, device="cuda")
         lib = _lib.lib()
         for lo in range(0, N, self.chunk_docs):
             n = min(self.chunk_docs, N - lo)
             ws, need = self._workspace(min(self.chunk_docs, N), S, 1)
-            _lib.check(lib.pn_t5_score(self._h, _lib.ptr(ids[lo:lo + n]), n, S, self.rel_id,
-                                       self.nrel_id, _lib.ptr(score[lo:lo + n]), _lib.ptr(z2[lo:lo + n]),
-                                       _lib.ptr(ws), ws.numel(), _lib.stream()))
+            _lib.check(lib.pn_t5_score_lens(self._h, _lib.ptr(ids[lo:lo + n]),
+                                            _lib.ptr(lens[lo:lo + n]) if lens is not None else None, n, S,
+                                            self.rel_id, self.nrel_id, _lib.ptr(score[lo:lo + n]),
+                                            _lib.ptr(z2[lo:lo + n]), _lib.ptr(ws), ws.numel(), _lib.stream()))
         return (score, z2) if return_z2 else score
 
     def logits(self, input_ids, labels, want_logits=True):
@@ -337,9 +394,11 @@ class MonoT5Scorer:
             logits = logits.view(N, T, self.vocab_pad)[:, :, :self.dims.vocab]
         return logits, z2.view(N, T, 2)
 
-    def rerank(self, input_ids, docids=None, rels=None, K=10, group=None, gather=None, equal_shards=True):
+    def rerank(self, input_ids, docids=None, rels=None, K=10, group=None, gather=None, equal_shards=True,
+               attention_mask=None, lengths=None):
         """Score Q x C candidate prompts (input_ids [Q, C, S]), rank each query's candidates and, when
-        ``rels`` [Q, C] is given, evaluate nDCG@K / RR / RR@K / AP (eval.py:26,41-43).
+        ``rels`` [Q, C] is given, evaluate nDCG@K / RR / RR@K / AP (eval.py:26,41-43).  ``attention_mask``
+        [Q, C, S] / ``lengths`` [Q, C]: the tokenizer's padding mask (see ``score``).
 
         Data parallel (queries sharded over the ranks of ``group``; all C candidates of a query stay on one rank):
         ``gather='scores'`` adds ``scores_all`` [sum Q, C] (+ ``top_ids_all``, ``top_scores_all``, ``metrics_all``) —
@@ -348,7 +407,11 @@ class MonoT5Scorer:
         process group with more than one rank is initialised, else nothing."""
         ids = torch.as_tensor(input_ids)
         Q, Cn, S = ids.shape
-        scores = self.score(ids.reshape(Q * Cn, S)).view(Q, Cn)
+        if attention_mask is not None:
+            attention_mask = torch.as_tensor(attention_mask).reshape(Q * Cn, S)
+        if lengths is not None:
+            lengths = torch.as_tensor(lengths).reshape(Q * Cn)
+        scores = self.score(ids.reshape(Q * Cn, S), attention_mask=attention_mask, lengths=lengths).view(Q, Cn)
         out = topk_metrics(scores, docids, rels, K)
         out["scores"] = scores
         if gather is None:

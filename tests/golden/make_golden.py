@@ -304,6 +304,49 @@ def gold_t5(rt, out):
         pair_loss=ce.numpy(), rel_ids=np.array([rel_id, nrel_id]), k=np.array(k))
 
 
+def gold_t5_mask(out):
+    """HF T5ForConditionalGeneration with the tokenizer's attention_mask, as the re-rank path calls it
+    (pyterrier_t5.MonoT5ReRanker in eval.py:14,23; distill/wrapper.py:36 `self.model(**enc)`): right-padded
+    prompts of different lengths, one decoder step, the two-row score."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    from transformers import T5Config, T5ForConditionalGeneration
+    dims = ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
+    w = ot.init_weights(dims, seed=13)
+    cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
+                   num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
+                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   pad_token_id=0, eos_token_id=1, feed_forward_proj="relu", tie_word_embeddings=True)
+    m = T5ForConditionalGeneration(cfg).eval()
+    sd = dict(w)
+    sd["encoder.embed_tokens.weight"] = sd["decoder.embed_tokens.weight"] = w["shared.weight"]
+    sd["lm_head.weight"] = w["shared.weight"]
+    missing = m.load_state_dict(sd, strict=False)
+    assert not missing.missing_keys and not missing.unexpected_keys, missing
+    rng = np.random.RandomState(77)
+    rel_id, nrel_id = 117, 213
+    res = {}
+    for S in (128, 200, 384):
+        N = 7
+        lens = np.array([S, 1, 5, 31, S // 2, S - 1, 130 if S > 130 else S - 3], dtype=np.int32)
+        ids = rng.randint(2, dims.vocab, size=(N, S)).astype(np.int64)
+        mask = (np.arange(S)[None, :] < lens[:, None]).astype(np.int64)
+        ids[mask == 0] = 0
+        ids[np.arange(N), lens - 1] = 1
+        with torch.no_grad():
+            lg = m(input_ids=torch.tensor(ids), attention_mask=torch.tensor(mask),
+                   decoder_input_ids=torch.zeros(N, 1, dtype=torch.long)).logits
+            sc = torch.log_softmax(lg[:, 0, (rel_id, nrel_id)], dim=1)[:, 0]
+            lg_nomask = m(input_ids=torch.tensor(ids), decoder_input_ids=torch.zeros(N, 1, dtype=torch.long)).logits
+        res[f"ids_{S}"], res[f"lens_{S}"] = ids, lens
+        res[f"z2_{S}"] = lg[:, 0, (rel_id, nrel_id)].numpy()
+        res[f"score_{S}"] = sc.numpy()
+        res[f"z2_nomask_{S}"] = lg_nomask[:, 0, (rel_id, nrel_id)].numpy()
+    np.savez_compressed(out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers,
+                                            dims.n_dec_layers, dims.n_heads]), seed=np.array(13),
+                        rel_ids=np.array([rel_id, nrel_id]), **res)
+
+
 class LegacyAdamW(torch.optim.Optimizer):
     """Restatement of transformers.AdamW.step (transformers <= 4.x optimization.py, the class lceT5.py:5,171-172
     constructs; removed from the transformers 5.x in this image): defaults betas (0.9, 0.999), eps 1e-6,
@@ -833,6 +876,7 @@ def main():
     gold_select(rd, os.path.join(HERE, "select_golden.npz"))
     gold_table_update(rp, rw, os.path.join(HERE, "table_update_golden.npz"))
     gold_t5(rt, os.path.join(HERE, "t5_tiny_golden.npz"))
+    gold_t5_mask(os.path.join(HERE, "t5_mask_golden.npz"))
     gold_train(rt, os.path.join(HERE, "train_golden.npz"))
     if "--wide" in sys.argv or "--all" in sys.argv:   # minutes of CPU: only on request
         gold_train_widths(rt)

@@ -403,6 +403,40 @@ def test_topk_metrics(pn, Q, C, K):
     np.testing.assert_allclose(out["metrics"].cpu().numpy(), em, rtol=1e-6, atol=1e-7)
 
 
+def test_topk_metrics_with_qrel_totals(pn):
+    """AP / nDCG denominators from the queries' full qrels (relevant documents missing from the candidate list):
+    hand case of tests/test_oracle_golden.py + a random batch against the oracle, both kernel variants (K <= 32 and
+    the sort path)."""
+    from pacednegatives_b200.metrics import qrel_totals, docno_order_ids
+    sc = torch.tensor([[0.5, 0.9, 0.5, 0.1]]).cuda()
+    ids = torch.tensor([[10, 11, 12, 13]], dtype=torch.int32).cuda()
+    rels = torch.tensor([[1, 0, 2, 0]], dtype=torch.uint8).cuda()
+    num_rel, idcg = qrel_totals([[1, 0, 2, 0, 3]], K=3)
+    out = pn.m.topk_metrics(sc, ids, rels, 3, num_rel=num_rel, idcg=idcg)
+    dcg = 2 / np.log2(3) + 1 / np.log2(4)
+    assert abs(out["ndcg"].item() - dcg / idcg[0]) < 1e-6
+    assert abs(out["ap"].item() - (1 / 2 + 2 / 3) / 3) < 1e-6 and abs(out["rr"].item() - 0.5) < 1e-7
+    rng = np.random.RandomState(3)
+    Q, C = 37, 200
+    scores = rng.randn(Q, C).astype(np.float32)
+    docids = np.stack([rng.permutation(5000)[:C] for _ in range(Q)]).astype(np.int32)
+    rl = rng.choice(4, size=(Q, C), p=[.9, .05, .03, .02]).astype(np.uint8)
+    missing = [rng.choice(4, size=rng.randint(0, 6), p=[.3, .3, .2, .2]) for _ in range(Q)]   # judged, not retrieved
+    for K in (10, 40):
+        nr, ig = qrel_totals([np.concatenate([rl[q], missing[q]]) for q in range(Q)], K)
+        enr, eig = om.qrel_totals([np.concatenate([rl[q], missing[q]]) for q in range(Q)], K)
+        assert np.array_equal(nr, enr) and np.array_equal(ig, eig)
+        out = pn.m.topk_metrics(torch.tensor(scores).cuda(), torch.tensor(docids).cuda(), torch.tensor(rl).cuda(), K,
+                                num_rel=nr, idcg=ig)
+        eids, esc, em = om.batch_metrics(scores, docids, rl, K, num_rel=enr, idcg=eig)
+        np.testing.assert_array_equal(out["top_ids"].cpu().numpy(), eids)
+        np.testing.assert_allclose(out["metrics"].cpu().numpy(), em, rtol=1e-6, atol=1e-7)
+    # docno strings -> ids with the strings' order (trec_eval's tie-break is on the docno string)
+    d = docno_order_ids([["D10", "D9", "D100"], ["a", "c", "b"]])
+    assert d[0].tolist() == [0, 2, 1] or (d[0, 1] > d[0, 0] > d[0, 2])     # "D9" > "D10" > "D100" as strings
+    assert d[1, 1] > d[1, 2] > d[1, 0]
+
+
 def test_argument_errors(pn):
     with pytest.raises(ValueError):
         pn.lib.check(pn.lib.lib().pn_weights_fwd(None, -1, None, 0.0, 0, None, None, None, None))

@@ -189,3 +189,44 @@ def test_large_width_training_forward_and_gradients():
         grads.append(m.grads.clone())
     rel = (grads[0] - grads[1]).norm().item() / grads[1].norm().item()
     assert rel < 3e-2, rel
+
+
+@pytest.mark.parametrize("xattn", [True, False])
+@pytest.mark.parametrize("S", [128, 200, 384])
+def test_score_with_attention_mask_vs_hf_golden(golden_dir, S, xattn):
+    """The re-rank call of the reference passes the tokenizer's attention_mask (pyterrier_t5.MonoT5ReRanker,
+    distill/wrapper.py:36): right-padded prompts of lengths 1 .. S against HF run with that mask
+    (tests/golden/make_golden.py::gold_t5_mask); without the mask the same rows differ by ~1.0."""
+    g = np.load(os.path.join(golden_dir, "t5_mask_golden.npz"))
+    v, d, kv, ff, L, Ld, H = [int(x) for x in g["dims"]]
+    dims = ot.T5Dims(vocab=v, d_model=d, d_kv=kv, d_ff=ff, n_layers=L, n_dec_layers=Ld, n_heads=H)
+    rel, nrel = [int(x) for x in g["rel_ids"]]
+    w, m = make(dims, int(g["seed"]), rel_id=rel, nrel_id=nrel, chunk_docs=4, xattn=xattn)
+    ids, lens = g[f"ids_{S}"], g[f"lens_{S}"]
+    mask = (np.arange(S)[None, :] < lens[:, None]).astype(np.int64)
+    s, z2 = m.score(ids, return_z2=True, attention_mask=mask)
+    np.testing.assert_allclose(z2.cpu().numpy(), g[f"z2_{S}"], atol=TOL)
+    np.testing.assert_allclose(s.cpu().numpy(), g[f"score_{S}"], atol=TOL)
+    s2 = m.score(ids, lengths=lens)
+    assert torch.equal(s, s2)
+    # no mask = the training path's semantics (pad tokens attended): HF without a mask
+    _, z0 = m.score(ids, return_z2=True)
+    np.testing.assert_allclose(z0.cpu().numpy(), g[f"z2_nomask_{S}"], atol=TOL)
+    full = m.score(ids, attention_mask=np.ones_like(mask))
+    assert torch.equal(full, m.score(ids))          # an all-ones mask is bit-identical to no mask
+    with pytest.raises(NotImplementedError):
+        m.score(ids, attention_mask=mask[:, ::-1].copy())      # left padding
+
+
+def test_rerank_with_padding_mask_ranks_like_the_oracle():
+    dims = ot.T5Dims(vocab=512, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
+    w, m = make(dims, 9, rel_id=5, nrel_id=6)
+    rng = np.random.RandomState(11)
+    Q, C, S = 2, 24, 160
+    lens = rng.randint(8, S + 1, size=(Q, C)).astype(np.int32)
+    ids = rand_ids(rng, Q * C, S, dims.vocab).reshape(Q, C, S)
+    mask = (np.arange(S)[None, None, :] < lens[:, :, None]).astype(np.int64)
+    ids[mask == 0] = 0
+    out = m.rerank(ids, None, None, K=10, attention_mask=mask)
+    es, _ = ot.score(w, dims, ids.reshape(Q * C, S), 5, 6, attention_mask=mask.reshape(Q * C, S))
+    np.testing.assert_allclose(out["scores"].cpu().numpy().reshape(-1), es, atol=TOL)

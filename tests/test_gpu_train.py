@@ -124,7 +124,9 @@ def test_adamw_kernel_vs_transformers_rule():
 #   gradient tensors: relative L2 error <= 6e-2 for weight matrices (every entry is a sum over docs*S products of
 #     two bf16-rounded factors: relative rounding 2^-9 each, summed incoherently, plus the bf16 dS / dP tiles of the
 #     attention backward), <= 8e-2 for the RMSNorm gains and the relative-position tables (differences of large
-#     cancelling sums); norms within 3e-2.
+#     cancelling sums); norms within 3e-2; row / column sums of each matrix within 2x the class tolerance of |grad|_F
+#     (noise-scaled, see the loop).  Measured on the B200 (profiles/r4_train_width_parity.md): worst relative L2
+#     0.036 (base), 0.040 (large), 0.047 (t5-small cfg1), norms within 0.8 %.
 def _sample_index(name, numel, count=8192):
     import zlib
     if numel <= 65536:
@@ -197,7 +199,12 @@ def test_training_step_at_bench_widths(golden_dir, case, xattn, cta_group):
             G = got.view(shape).double()
             for key, dim in (("growsum/", 1), ("gcolsum/", 0)):
                 r = torch.tensor(g[key + n]).cuda().double()
-                entry[key[1:-1]] = ((G.sum(dim) - r).norm() / max(r.norm().item(), 1e-30)).item()
+                # Noise-scaled: independent entry errors of relative size eps move a vector of sums by
+                # ~ eps * |G|_F whatever the sums themselves are (those of o.weight / wo.weight cancel to a small
+                # fraction of |G|_F: the residual-stream gradient is nearly orthogonal to the all-ones vector), while a
+                # coherent error (a head, a block, a diagonal of the bias gradient) moves them by up to sqrt(dim) more.
+                entry[key[1:-1]] = ((G.sum(dim) - r).norm() / max(ref_norm, 1e-30)).item()
+                entry[key[1:-1] + "_rel_to_sums"] = ((G.sum(dim) - r).norm() / max(r.norm().item(), 1e-30)).item()
         report["tensors"][n] = entry
         cls = _tensor_class(n)
         worst[cls] = max(worst.get(cls, 0.0), rel)
@@ -211,7 +218,7 @@ def test_training_step_at_bench_widths(golden_dir, case, xattn, cta_group):
             fails.append(f"{n}: |grad| off by {rel_norm:.4f}")
         for key in ("rowsum", "colsum"):
             if key in entry and entry[key] > 2 * WIDE_TOL[cls]:
-                fails.append(f"{n}: {key} relative error {entry[key]:.4f}")
+                fails.append(f"{n}: {key} off by {entry[key]:.4f} of |grad|")
     report["worst_rel_l2_by_class"] = worst
     os.makedirs(os.path.join(os.path.dirname(golden_dir), "..", "gpurun_out"), exist_ok=True)
     with open(os.path.join(os.path.dirname(golden_dir), "..", "gpurun_out",

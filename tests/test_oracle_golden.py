@@ -125,6 +125,24 @@ def test_metrics_hand_cases():
     assert m[0].tolist() == [0, 0, 0, 0]
 
 
+def test_metrics_with_a_relevant_document_missing_from_the_candidates():
+    """trec_eval judges against ALL judged documents of the query (eval.py:26: pt.Experiment over the qrels): a
+    relevant document BM25 did not retrieve lowers AP and nDCG.  Hand case: candidates (grades 1, 0, 2, 0 ranked
+    0.9 > 0.5(id 12) > 0.5(id 10) > 0.1), qrels also hold an unretrieved grade-3 document."""
+    sc = np.array([[0.5, 0.9, 0.5, 0.1]], np.float32)
+    ids = np.array([[10, 11, 12, 13]])
+    rels = np.array([[1, 0, 2, 0]])
+    num_rel, idcg = om.qrel_totals([[1, 0, 2, 0, 3]], K=3)
+    assert num_rel.tolist() == [3] and abs(idcg[0] - (3 / np.log2(2) + 2 / np.log2(3) + 1 / np.log2(4))) < 1e-12
+    _, _, m = om.batch_metrics(sc, ids, rels, K=3, num_rel=num_rel, idcg=idcg)
+    dcg = 0 / np.log2(2) + 2 / np.log2(3) + 1 / np.log2(4)
+    assert abs(m[0, 0] - dcg / idcg[0]) < 1e-6                    # nDCG@3 against the full ideal ranking
+    assert abs(m[0, 3] - (1 / 2 + 2 / 3) / 3) < 1e-6              # AP over 3 judged-relevant documents, not 2
+    assert abs(m[0, 1] - 0.5) < 1e-7                              # RR does not depend on the totals
+    _, _, m0 = om.batch_metrics(sc, ids, rels, K=3)
+    assert m0[0, 0] > m[0, 0] and m0[0, 3] > m[0, 3]              # candidate-only totals inflate both
+
+
 def test_t5_oracle_vs_hf_golden(golden_dir):
     g = load(golden_dir, "t5_tiny_golden.npz")
     v, d, kv, ff, L, Ld, H = [int(x) for x in g["dims"]]
@@ -188,3 +206,20 @@ def test_pack_prompts_oracle_vs_reference_collate(tmp_path):
     assert (lens <= 12).all() and ids.shape == (4, 16)
     for r, n in zip(ids, lens):
         assert list(r[n - len(suffix):n]) == list(suffix) and (r[n:] == 0).all()
+
+
+@pytest.mark.parametrize("S", [128, 200, 384])
+def test_oracle_attention_mask_vs_hf_golden(golden_dir, S):
+    """oracle.t5.score(attention_mask=) against HF run with the tokenizer-style mask (gold_t5_mask)."""
+    g = np.load(os.path.join(golden_dir, "t5_mask_golden.npz"))
+    v, d, kv, ff, L, Ld, H = [int(x) for x in g["dims"]]
+    dims = ot.T5Dims(vocab=v, d_model=d, d_kv=kv, d_ff=ff, n_layers=L, n_dec_layers=Ld, n_heads=H)
+    w = ot.init_weights(dims, seed=int(g["seed"]))
+    ids, lens = g[f"ids_{S}"], g[f"lens_{S}"]
+    mask = (np.arange(S)[None, :] < lens[:, None]).astype(np.int64)
+    rel, nrel = [int(x) for x in g["rel_ids"]]
+    s, z2 = ot.score(w, dims, ids, rel, nrel, attention_mask=mask)
+    np.testing.assert_allclose(z2, g[f"z2_{S}"], atol=2e-5)
+    np.testing.assert_allclose(s, g[f"score_{S}"], atol=2e-5)
+    _, z0 = ot.score(w, dims, ids, rel, nrel)
+    np.testing.assert_allclose(z0, g[f"z2_nomask_{S}"], atol=2e-5)
