@@ -63,7 +63,8 @@ int pn_prof_read(int kind, double* ms_sum, int64_t* launches, double* work_sum);
  *       weights.py:26-45
  * fp32 IEEE ops in the reference's order, so w and the keep mask are bit-exact.
  * keep_out[i] = !(loss[i] > eta)  (nullable).
- * stats_out (nullable, double[6], overwritten):
+ * stats_out (nullable, double[13], overwritten): the six statistics in [0..5], [6..12] is the call's scratch
+ * (raw partial sums + the grid's completion counter; the library keeps no state between or across calls):
  *   [0] sum w   [1] sum w*l   [2] d(sum w*l)/d eta   [3] #(l < eta)  (old/eta_bound.py:57-58)
  *   [4] sum l   [5] #(!(l > eta))
  */
@@ -306,6 +307,17 @@ int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* labels, int6
                         float* logits_out, void* workspace, int64_t workspace_bytes, void* stream);
 int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S, int32_t T,
                          void* workspace, int64_t workspace_bytes, void* stream);
+/* Restricted-head training (north_star kernels (1) + (2): the LM head restricted to the 'true' / 'false' rows and
+ * the group-wise log-softmax LCE of pn_lce_restricted_fwd / _bwd): the same forward with the two-row head of the
+ * re-rank score (distill/wrapper.py:34-38) instead of the [docs*T, vocab] logits — z2_out fp32 [docs*T, 2] =
+ * (z_true, z_false) — and the backward from dz2 = d loss / d z2 (the [docs*T, vocab_pad] logits and their gradient
+ * never exist).  Same workspace contract as pn_t5_train_forward / _backward. */
+int pn_t5_train_forward_z2(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S, int32_t T,
+                           int32_t rel_id, int32_t nrel_id, float* z2_out, void* workspace, int64_t workspace_bytes,
+                           void* stream);
+int pn_t5_train_backward_z2(PnT5* m, const int32_t* ids, const float* dz2, int32_t rel_id, int32_t nrel_id,
+                            int64_t docs, int32_t S, int32_t T, void* workspace, int64_t workspace_bytes,
+                            void* stream);
 /* Data-parallel overlap (DDP's bucketed all-reduce under `manual_backward`, lceT5.py:155 with strategy='ddp'
  * train/train_lce.py:89-91): fn(user, offset, numel) is called on the host thread while pn_t5_train_backward
  * enqueues work, each time a contiguous range of the gradient buffer has received its last contribution
@@ -318,6 +330,11 @@ int pn_t5_adamw_step(PnT5* m, float lr, float beta1, float beta2, float eps, flo
                      float gscale, void* stream);
 int pn_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
              float eps, float weight_decay, int64_t step, float gscale, void* stream);
+/* StdWrapper's look-ahead copy (pairwrapper.py:57-74 update_params, called at :126-128): one plain SGD step
+ * p -= lr * grad on the flat parameters from element `first_elem` on (0 = every parameter; the offset of the first
+ * non-embedding tensor reproduces transformers 5.x, where replacing `shared.weight` does not reach the tied
+ * embedding / head modules), then the packed bf16 operands are rebuilt. */
+int pn_t5_sgd_step(PnT5* m, float lr, int64_t first_elem, void* stream);
 
 #ifdef __cplusplus
 }

@@ -52,9 +52,12 @@ SIGNATURES = {
     "pn_t5_set_train_buffers": (c_int, [c_vp, c_vp, c_vp, c_vp]),
     "pn_t5_train_forward": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_i64, c_vp]),
     "pn_t5_train_backward": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
+    "pn_t5_train_forward_z2": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_i64, c_vp]),
+    "pn_t5_train_backward_z2": (c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
     "pn_t5_zero_grad": (c_int, [c_vp, c_vp]),
     "pn_t5_set_grad_hook": (c_int, [c_vp, c_vp, c_vp]),
     "pn_t5_adamw_step": (c_int, [c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_i64, c_f32, c_vp]),
+    "pn_t5_sgd_step": (c_int, [c_vp, c_f32, c_i64, c_vp]),
     "pn_adamw": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_f32, c_f32, c_f32, c_f32, c_f32, c_i64, c_f32, c_vp]),
     "pn_t5_num_params": (c_i64, [c_vp]),
     "pn_t5_num_tensors": (c_i32, [c_vp]),

@@ -100,6 +100,8 @@ int pn_t5_rmsnorm(const float* x, const float* w, int64_t rows, int d, float eps
 int pn_t5_f32_to_bf16(const float* src, __nv_bfloat16* dst, int64_t n, cudaStream_t st);
 int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, int d, float eps,
                 int rel_id, int nrel_id, float* score, float* z2, cudaStream_t st);
+int pn_t5_head2_bwd(const float* x, const float* w, const float* emb, const float* dz2, int64_t rows, int d, float eps,
+                    int rel_id, int nrel_id, float* dhead_in, float* grad_emb, cudaStream_t st);
 int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float eps,
                     __nv_bfloat16* out, cudaStream_t st);
 
@@ -132,5 +134,6 @@ int pn_t5_embed_bwd(const int32_t* ids, const float* dh, int64_t rows, int d, in
                     cudaStream_t st);
 int pn_t5_final_norm_bwd(const float* dy, const float* x, const float* w, int64_t rows, int d, float eps,
                          float* dx, __nv_bfloat16* dxb, float* dw, cudaStream_t st);
+int pn_t5_sgd(float* p, const float* g, int64_t n, float lr, cudaStream_t st);
 int pn_t5_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                 float wd, int64_t step, float gscale, cudaStream_t st);

@@ -153,6 +153,32 @@ head2_kernel(const float* __restrict__ x, const float* __restrict__ w, const flo
   }
 }
 
+// Backward of head2_kernel's two dot products (restricted-head training): with head_in = x * w * rs * d^-0.5,
+// z[r, c] = head_in[r, :] . E[id_c, :]  ->  dhead_in[r, :] = dz[r, 0] E[rel] + dz[r, 1] E[nrel] (what
+// final_norm_bwd consumes) and grad_E[id_c, :] += sum_r dz[r, c] head_in[r, :].  One warp per decoder row.
+__global__ void __launch_bounds__(kThreads)
+head2_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ emb,
+                 const float* __restrict__ dz2, int64_t rows, int d, float eps, int rel_id, int nrel_id,
+                 float* __restrict__ dhead_in, float* __restrict__ grad_emb) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  if (r >= rows) return;
+  const float* xr = x + (size_t)r * d;
+  const float* et = emb + (size_t)rel_id * d;
+  const float* ef = emb + (size_t)nrel_id * d;
+  float ss = 0.0f;
+  for (int i = lane; i < d; i += 32) ss += xr[i] * xr[i];
+  ss = pn_warp_sum(ss);
+  const float k = rsqrtf(ss / (float)d + eps) * rsqrtf((float)d);
+  const float g0 = dz2[2 * r], g1 = dz2[2 * r + 1];
+  for (int i = lane; i < d; i += 32) {
+    dhead_in[(size_t)r * d + i] = g0 * et[i] + g1 * ef[i];
+    const float hi = xr[i] * w[i] * k;
+    atomicAdd(grad_emb + (size_t)rel_id * d + i, g0 * hi);
+    atomicAdd(grad_emb + (size_t)nrel_id * d + i, g1 * hi);
+  }
+}
+
 // bf16 y = rmsnorm(x) * w * d^-0.5 for the full-vocabulary head GEMM
 __global__ void __launch_bounds__(kThreads)
 head_prep_kernel(const float* __restrict__ x, const float* __restrict__ w, int64_t rows, int d,
@@ -218,6 +244,15 @@ int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, 
   if (rows == 0) return PN_OK;
   head2_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(
       x, w, emb, rows, d, eps, rel_id, nrel_id, score, z2);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_head2_bwd(const float* x, const float* w, const float* emb, const float* dz2, int64_t rows, int d, float eps,
+                    int rel_id, int nrel_id, float* dhead_in, float* grad_emb, cudaStream_t st) {
+  if (rows == 0) return PN_OK;
+  head2_bwd_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(
+      x, w, emb, dz2, rows, d, eps, rel_id, nrel_id, dhead_in, grad_emb);
   PN_LAUNCHED();
   return PN_OK;
 }

@@ -201,15 +201,16 @@ extern "C" int pn_t5_set_train_buffers(PnT5* m, float* grads, float* adam_m, flo
 
 // logits_out fp32 [docs*T, vocab_pad] = self.model(input_ids=ids, labels=labels).logits with every activation the
 // backward needs left in `workspace`
-extern "C" int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S,
-                                   int32_t T, float* logits_out, void* workspace, int64_t workspace_bytes,
-                                   void* stream) {
+static int train_forward_impl(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S,
+                              int32_t T, float* logits_out, float* z2_out, int32_t rel_id, int32_t nrel_id,
+                              void* workspace, int64_t workspace_bytes, void* stream) {
   PN_CHECK_ARG(m && m->finalized);
   if (!m->want_train) return pn_fail(PN_E_BADARG, "pn_t5_train_forward: model was not created with option \"train\"");
   PN_CHECK_ARG(docs >= 0 && S >= 1 && S <= 512 && (T == 1 || T == 2));
   if (docs == 0) return PN_OK;
-  PN_CHECK_ARG(ids && labels && logits_out && workspace);
+  PN_CHECK_ARG(ids && labels && (logits_out || z2_out) && workspace);
   PN_CHECK_ARG(docs * (int64_t)S < (1ll << 31));
+  if (z2_out) PN_CHECK_ARG(rel_id >= 0 && rel_id < m->cfg.vocab && nrel_id >= 0 && nrel_id < m->cfg.vocab);
   TrainWs w;
   const size_t need = carve_train(m, docs, S, T, (uint8_t*)workspace, &w);
   if ((int64_t)need > workspace_bytes)
@@ -270,11 +271,31 @@ extern "C" int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* l
     RC(lin_fwd(m, w.dhb[3 * l + 2], w.drs[3 * l + 2], D.wi, w.dact[l], drows, 1, st));
     RC(lin_resid(m, w.dact[l], D.wo2, w.dec_hidden, w.dhb[3 * l + 3], w.dss, w.drs[3 * l + 3], drows, st));
   }
-  // ---- tied head: logits = (RMSNorm(h) * d^-0.5) E^T  (HF:1107-1110)
-  RC(pn_t5_head_prep(w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.head_in, st));
-  RC(pn_gemm_bf16_internal(w.head_in, d, m->emb_bf16, d, logits_out, m->vocab_pad, drows, m->vocab_pad, d,
-                           PN_EPI_F32, 0, nullptr, m->cta_group, st));
+  // ---- tied head: logits = (RMSNorm(h) * d^-0.5) E^T  (HF:1107-1110); restricted mode: only the two rows of E
+  // the re-rank score reads (distill/wrapper.py:34-38), in fp32
+  if (z2_out)
+    RC(pn_t5_head2(w.dec_hidden, m->dec_final, m->emb, drows, d, m->cfg.eps, rel_id, nrel_id, nullptr, z2_out, st));
+  if (logits_out) {
+    RC(pn_t5_head_prep(w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.head_in, st));
+    RC(pn_gemm_bf16_internal(w.head_in, d, m->emb_bf16, d, logits_out, m->vocab_pad, drows, m->vocab_pad, d,
+                             PN_EPI_F32, 0, nullptr, m->cta_group, st));
+  }
   return PN_OK;
+}
+
+extern "C" int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S,
+                                   int32_t T, float* logits_out, void* workspace, int64_t workspace_bytes,
+                                   void* stream) {
+  PN_CHECK_ARG(logits_out);
+  return train_forward_impl(m, ids, labels, docs, S, T, logits_out, nullptr, 0, 0, workspace, workspace_bytes, stream);
+}
+
+extern "C" int pn_t5_train_forward_z2(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S,
+                                      int32_t T, int32_t rel_id, int32_t nrel_id, float* z2_out, void* workspace,
+                                      int64_t workspace_bytes, void* stream) {
+  PN_CHECK_ARG(z2_out);
+  return train_forward_impl(m, ids, labels, docs, S, T, nullptr, z2_out, rel_id, nrel_id, workspace, workspace_bytes,
+                            stream);
 }
 
 extern "C" int pn_t5_set_grad_hook(PnT5* m, void (*fn)(void*, int64_t, int64_t), void* user) {
@@ -295,13 +316,15 @@ int64_t first_offset(const PnT5* m, const std::string& prefix) {
 
 // Accumulates d loss / d parameters into the gradient buffer, given dlogits = d loss / d logits (fp32
 // [docs*T, vocab_pad]) for the forward pass whose activations `workspace` holds.
-extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S,
-                                    int32_t T, void* workspace, int64_t workspace_bytes, void* stream) {
+static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits, const float* dz2, int32_t rel_id,
+                               int32_t nrel_id, int64_t docs, int32_t S, int32_t T, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
   PN_CHECK_ARG(m && m->finalized && m->want_train);
   if (!m->grads) return pn_fail(PN_E_BADARG, "pn_t5_train_backward: no gradient buffer (pn_t5_set_train_buffers)");
   PN_CHECK_ARG(docs >= 0 && S >= 1 && S <= 512 && (T == 1 || T == 2));
   if (docs == 0) return PN_OK;
-  PN_CHECK_ARG(ids && dlogits && workspace);
+  PN_CHECK_ARG(ids && (dlogits || dz2) && workspace);
+  if (dz2) PN_CHECK_ARG(rel_id >= 0 && rel_id < m->cfg.vocab && nrel_id >= 0 && nrel_id < m->cfg.vocab);
   if (m->cfg.vocab % 8)
     return pn_fail(PN_E_UNSUPPORTED, "pn_t5_train_backward: vocab=%d must be a multiple of 8", m->cfg.vocab);
   TrainWs w;
@@ -323,10 +346,16 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
   const int* bucket_of = (const int*)m->allocs[0];
 
   // ---- head: d head_in = dlogits E,  dE += dlogits^T head_in,  then the final decoder norm
-  RC(pn_t5_f32_to_bf16(dlogits, w.dlb, (int64_t)drows * Vp, st));
-  RC(pn_gemm_wgrad(w.dlb, Vp, w.head_in, d, G + m->emb_off, d, m->cfg.vocab, d, drows, m->cta_group, st));
-  RC(pn_gemm_bf16_internal(w.dlb, Vp, m->embT_bf16, Vp, w.dgbuf, d, drows, d, Vp, PN_EPI_F32, 0, nullptr,
-                           m->cta_group, st));
+  if (dz2) {
+    // restricted head: z[r, c] = head_in[r, :] . E[id_c, :]  ->  d head_in = dz E[(rel, nrel)], dE[id_c] += dz^T head_in
+    RC(pn_t5_head2_bwd(w.dec_hidden, m->dec_final, m->emb, dz2, drows, d, m->cfg.eps, rel_id, nrel_id, w.dgbuf,
+                       G + m->emb_off, st));
+  } else {
+    RC(pn_t5_f32_to_bf16(dlogits, w.dlb, (int64_t)drows * Vp, st));
+    RC(pn_gemm_wgrad(w.dlb, Vp, w.head_in, d, G + m->emb_off, d, m->cfg.vocab, d, drows, m->cta_group, st));
+    RC(pn_gemm_bf16_internal(w.dlb, Vp, m->embT_bf16, Vp, w.dgbuf, d, drows, d, Vp, PN_EPI_F32, 0, nullptr,
+                             m->cta_group, st));
+  }
   RC(pn_t5_final_norm_bwd(w.dgbuf, w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.ddH, w.ddHb,
                           G + m->dec_final_off, st));
 
@@ -459,6 +488,19 @@ extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dl
   return PN_OK;
 }
 
+extern "C" int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S,
+                                    int32_t T, void* workspace, int64_t workspace_bytes, void* stream) {
+  PN_CHECK_ARG(dlogits);
+  return train_backward_impl(m, ids, dlogits, nullptr, 0, 0, docs, S, T, workspace, workspace_bytes, stream);
+}
+
+extern "C" int pn_t5_train_backward_z2(PnT5* m, const int32_t* ids, const float* dz2, int32_t rel_id,
+                                       int32_t nrel_id, int64_t docs, int32_t S, int32_t T, void* workspace,
+                                       int64_t workspace_bytes, void* stream) {
+  PN_CHECK_ARG(dz2);
+  return train_backward_impl(m, ids, nullptr, dz2, rel_id, nrel_id, docs, S, T, workspace, workspace_bytes, stream);
+}
+
 extern "C" int pn_t5_zero_grad(PnT5* m, void* stream) {
   PN_CHECK_ARG(m && m->grads);
   PN_CUDA(cudaMemsetAsync(m->grads, 0, (size_t)m->n_params * 4, (cudaStream_t)stream));
@@ -473,6 +515,15 @@ extern "C" int pn_t5_adamw_step(PnT5* m, float lr, float beta1, float beta2, flo
   cudaStream_t st = (cudaStream_t)stream;
   RC(pn_t5_adamw(m->flat, m->grads, m->adam_m, m->adam_v, m->n_params, lr, beta1, beta2, eps, weight_decay, step,
                  gscale, st));
+  return pn_t5_repack(m, st);
+}
+
+// One plain SGD step on the parameters from element `first_elem` on (StdWrapper's look-ahead copy,
+// pairwrapper.py:57-74,126-128: theta' = theta - lr * grad), then the bf16 operands are rebuilt
+extern "C" int pn_t5_sgd_step(PnT5* m, float lr, int64_t first_elem, void* stream) {
+  PN_CHECK_ARG(m && m->finalized && m->grads && first_elem >= 0 && first_elem <= m->n_params);
+  cudaStream_t st = (cudaStream_t)stream;
+  RC(pn_t5_sgd(m->flat + first_elem, m->grads + first_elem, m->n_params - first_elem, lr, st));
   return pn_t5_repack(m, st);
 }
 

@@ -341,6 +341,22 @@ int pn_t5_final_norm_bwd(const float* dy, const float* x, const float* w, int64_
   return PN_OK;
 }
 
+namespace {
+__global__ void __launch_bounds__(kThreads)
+sgd_kernel(float* __restrict__ p, const float* __restrict__ g, int64_t n, float lr) {
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
+    p[i] -= lr * g[i];
+}
+}  // namespace
+
+// p -= lr * g: the functional one-step copy of StdWrapper.update_params (pairwrapper.py:68-73), 12 B per parameter
+int pn_t5_sgd(float* p, const float* g, int64_t n, float lr, cudaStream_t st) {
+  if (n <= 0) return PN_OK;
+  sgd_kernel<<<pn_grid(n, kThreads, 4, 8), kThreads, 0, st>>>(p, g, n, lr);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
 int pn_t5_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                 float wd, int64_t step, float gscale, cudaStream_t st) {
   if (n == 0) return PN_OK;

@@ -309,17 +309,12 @@ extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, fl
   PN_CHECK_ARG(variant == PN_W_LCE || variant == PN_W_ETA);
   PN_CHECK_ARG(eta != nullptr);
   cudaStream_t st = (cudaStream_t)stream;
-  // the kernel accumulates raw sums (and its done-counter) in a 13-double scratch and the last CTA writes the six
-  // statistics into its first half.  The scratch is stream-ordered memory of THIS call (cudaMallocAsync /
-  // cudaFreeAsync on the caller's stream): calls on different streams or from different host threads never share it
-  double* stats_dev = nullptr;
-  if (stats_out && n == 0) PN_CUDA(cudaMemsetAsync(stats_out, 0, 6 * sizeof(double), st));
+  // the kernel accumulates raw sums (and its done-counter) in stats_out[6..12] — the CALLER's buffer, so calls on
+  // different streams or from different host threads share nothing — and the last CTA folds them into [0..5]
+  double* stats_dev = stats_out;
+  if (stats_out) PN_CUDA(cudaMemsetAsync(stats_out, 0, 13 * sizeof(double), st));
   if (n == 0) return PN_OK;
   PN_CHECK_ARG(loss != nullptr && w_out != nullptr);
-  if (stats_out) {
-    PN_CUDA(cudaMallocAsync((void**)&stats_dev, 13 * sizeof(double), st));
-    PN_CUDA(cudaMemsetAsync(stats_dev, 0, 13 * sizeof(double), st));
-  }
   const bool vec = (((uintptr_t)loss | (uintptr_t)w_out) & 15) == 0 &&
                    (keep_out == nullptr || ((uintptr_t)keep_out & 3) == 0);
   static int want8 = -1;        // PN_W_VEC8=0 falls back to 128-bit accesses
@@ -344,15 +339,7 @@ extern "C" int pn_weights_fwd(const float* loss, int64_t n, const float* eta, fl
     if (vec8) LAUNCH(PN_W_ETA, 2); else if (vec) LAUNCH(PN_W_ETA, 1); else LAUNCH(PN_W_ETA, 0);
   }
 #undef LAUNCH
-  g_pn_launches.fetch_add(1, std::memory_order_relaxed);
-  const cudaError_t launch_err = cudaGetLastError();
-  if (stats_out) {
-    if (launch_err == cudaSuccess)
-      cudaMemcpyAsync(stats_out, stats_dev, 6 * sizeof(double), cudaMemcpyDeviceToDevice, st);
-    cudaFreeAsync(stats_dev, st);
-  }
-  if (launch_err != cudaSuccess)
-    return pn_fail(PN_E_LAUNCH, "%s: launch failed: %s", __func__, cudaGetErrorString(launch_err));
+  PN_LAUNCHED();
   return PN_OK;
 }
 

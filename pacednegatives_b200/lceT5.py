@@ -145,6 +145,44 @@ class _ModelFn(torch.autograd.Function):
         return torch.zeros_like(model._anchor), None, None, None
 
 
+class _ModelZ2Fn(torch.autograd.Function):
+    """z2 = model(input_ids=, labels=).logits[..., (rel, nrel)] through the two-row head (pn_t5_train_forward_z2), the
+    backward wired to pn_t5_train_backward_z2: the [N*T, vocab] logits and their gradient never exist."""
+
+    @staticmethod
+    def forward(ctx, anchor, model, ids, labels):
+        N, S = ids.shape
+        T = labels.shape[1]
+        lib = _lib.lib()
+        need = int(lib.pn_t5_train_workspace_bytes(model._h, N, S, T))
+        ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+        z2 = torch.empty(N * T, 2, dtype=torch.float32, device="cuda")
+        _lib.check(lib.pn_t5_train_forward_z2(model._h, _lib.ptr(ids), _lib.ptr(labels), N, S, T, model.rel_id,
+                                              model.nrel_id, _lib.ptr(z2), _lib.ptr(ws), need, _lib.stream()))
+        ctx.model, ctx.ws, ctx.ids, ctx.shape = model, ws, ids, (N, S, T)
+        model._pending += 1
+        return z2.view(N, T, 2)
+
+    @staticmethod
+    def backward(ctx, dz2):
+        N, S, T = ctx.shape
+        model = ctx.model
+        d = dz2.contiguous().float()
+        model._hook_live = model._pending == 1 and not model.accumulating and model._overlap_ready()
+        model._pending -= 1
+        try:
+            _lib.check(_lib.lib().pn_t5_train_backward_z2(model._h, _lib.ptr(ctx.ids), _lib.ptr(d), model.rel_id,
+                                                          model.nrel_id, N, S, T, _lib.ptr(ctx.ws), ctx.ws.numel(),
+                                                          _lib.stream()))
+        finally:
+            model._hook_live = False
+        if model._hook_error is not None:
+            err, model._hook_error = model._hook_error, None
+            raise err
+        ctx.ws = None
+        return torch.zeros_like(model._anchor), None, None, None
+
+
 class MonoT5Model(MonoT5Scorer):
     """Trainable monoT5: ``model(input_ids, labels)`` returns logits [N, T, vocab] that backpropagate into the
     flat gradient buffer ``grads`` (HF state_dict order, see ``named_offsets``)."""
@@ -187,8 +225,35 @@ class MonoT5Model(MonoT5Scorer):
         out = _ModelFn.apply(self._anchor, self, ids, lab)
         return out[:, :, :self.dims.vocab]
 
+    def z2(self, input_ids, labels=None):
+        """Differentiable two-row head: fp32 [N, T, 2] = (z_true, z_false) at each label position (T = 1 when
+        ``labels`` is None: the single decoder step of the re-rank score)."""
+        ids = self._ids(input_ids)
+        if labels is None:
+            lab = torch.zeros(ids.shape[0], 1, dtype=torch.int64, device="cuda")
+        else:
+            lab = torch.as_tensor(labels).to(device="cuda", dtype=torch.int64).contiguous()
+        return _ModelZ2Fn.apply(self._anchor, self, ids, lab)
+
     def named_grads(self):
         return {n: self.grads[o:o + k] for n, o, k in self.named_offsets()}
+
+    def load_parameters_from(self, other):
+        """``self.load_state_dict(other.state_dict())`` (pairwrapper.py:105): one device copy of the flat master
+        buffer, then the packed bf16 operands are rebuilt."""
+        self.parameters_flat().copy_(other.parameters_flat())
+        _lib.check(_lib.lib().pn_t5_finalize(self._h, _lib.stream()))
+
+    def sgd_step(self, lr, include_embedding=False):
+        """theta <- theta - lr * grad on this model's own gradient buffer (StdWrapper.update_params,
+        pairwrapper.py:68-73).  ``include_embedding=False`` leaves shared.weight alone: with transformers 5.x the
+        reference's ``set_param`` replaces ``model.shared.weight`` only, which no forward path reads (the embedding
+        and head modules keep the tied original), so its look-ahead model differs from theta everywhere BUT there."""
+        first = 0
+        if not include_embedding:
+            offs = self.named_offsets()
+            first = offs[0][2] if offs[0][0] == "shared.weight" else 0
+        _lib.check(_lib.lib().pn_t5_sgd_step(self._h, float(lr), first, _lib.stream()))
 
     def zero_grad(self):
         _lib.check(_lib.lib().pn_t5_zero_grad(self._h, _lib.stream()))
@@ -514,12 +579,41 @@ class LCEModel(_LightningBase):
         self.difficulty = self.weights.eta.item()
         return output
 
+    def _training_step_restricted(self, p, n, meta_opt, opt, meta_scheduler, scheduler):
+        """hparams['mode'] = 'restricted' — the fast mode of north_star items (1) + (2), not a reference formula:
+        ONE decoder step, the LM head restricted to the 'true' / 'false' rows (the re-rank score of
+        distill/wrapper.py:34-38, s = log_softmax(z_true, z_false)[0]) and the canonical localized contrastive
+        estimation over each query's group, loss[q] = logsumexp_j s[q, j] - s[q, 0] (pn_lce_restricted_fwd / _bwd,
+        positive first).  Same step structure as lceT5.py:125-168 (eta meta step on the detached losses, unweighted
+        main step); the [N*T, vocab] logits, their log-softmax and their gradient never exist."""
+        from .loss import lce_restricted
+        k = int(self.hparams.n)
+        pi, ni = torch.as_tensor(p["input_ids"]).cuda(), torch.as_tensor(n["input_ids"]).cuda()
+        Q, G = pi.shape[0], 1 + k
+        if pi.shape[1] != ni.shape[1]:
+            S = max(pi.shape[1], ni.shape[1])      # pad tokens are attended on this path (no mask, lceT5.py:53)
+            pi = torch.nn.functional.pad(pi, (0, S - pi.shape[1]), value=self.model.dims.pad_id)
+            ni = torch.nn.functional.pad(ni, (0, S - ni.shape[1]), value=self.model.dims.pad_id)
+        z2 = self.model.z2(torch.cat([pi, ni]))[:, 0]                      # [Q + Q*k, 2]
+        grouped = torch.cat([z2[:Q].unsqueeze(1), z2[Q:].view(Q, k, 2)], dim=1)   # [Q, G, 2], positive first
+        main_loss, _ = lce_restricted(grouped.reshape(-1, 2), G)
+        loss = main_loss.detach()
+        weights, meta_loss = self._meta_step(loss, meta_opt, meta_scheduler)
+        opt.zero_grad()
+        self.manual_backward(main_loss.mean())
+        opt.step()
+        scheduler.step()
+        self._pn_step += 1
+        return self._step_output(loss, weights, main_loss, meta_loss)
+
     def training_step(self, batch, batch_nb=0):
         """lceT5.py:125-168, statement for statement; the model calls go to libpn_b200."""
         p, n = batch
 
         meta_opt, opt = self.optimizers()
         meta_scheduler, scheduler = self.lr_schedulers()
+        if self.hparams.get("mode", "parity") == "restricted":
+            return self._training_step_restricted(p, n, meta_opt, opt, meta_scheduler, scheduler)
         k, V = int(self.hparams.n), self.model.dims.vocab
         mq = int(self.hparams.get("micro_queries", 0) or 0)
         if 0 < mq < len(p["input_ids"]):

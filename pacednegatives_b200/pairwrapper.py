@@ -14,8 +14,8 @@ must return a ``pacednegatives_b200.lceT5.MonoT5Model`` (the reference passes a 
 * table row update (closed form of the autograd graph at :226-238, negative term only): pn_weights_table_update
 * optimiser: pn_t5_adamw_step (transformers.AdamW defaults, :53) under ``get_linear_schedule_with_warmup``
 
-``StdWrapper`` (:91-206) dereferences ``self.meta_model``, which the reference's constructor leaves commented out
-(:51), so it cannot run upstream either; it is declared here and raises.
+``StdWrapper`` (:91-206) adds the one-step look-ahead copy (``meta_model``; the reference's constructor leaves it
+commented out at :51, so upstream the class raises AttributeError — here it is built): pn_t5_sgd_step.
 """
 import time
 from collections import defaultdict
@@ -99,12 +99,71 @@ class PacedWrapper:
 
 
 class StdWrapper(PacedWrapper):
-    """pairwrapper.py:91-206 — look-ahead meta model; not runnable in the reference (``meta_model`` is never
-    created, :51) and needs a double backward through the T5 kernels."""
+    """pairwrapper.py:91-206 — per-sample weights updated from a one-step LOOK-AHEAD copy of the model.
 
-    def __init__(self, *args, **kw) -> None:
-        raise NotImplementedError("StdWrapper needs self.meta_model, which pairwrapper.py:51 never creates; "
-                                  "use NewWrapper")
+    The reference never constructs ``self.meta_model`` (:51 is commented out), so upstream this class raises
+    AttributeError; here the constructor builds it with ``model_init()``.  What the reference's code then computes
+    (pinned by ``tests/golden/stdwrapper_golden.npz`` = the reference's own meta_loop / main_loop, run with that one
+    attribute supplied):
+
+    * meta_loop (:102-151): meta_model <- model; theta' = theta - lr_t * d/dtheta [sum(ce_p v)/B + sum(ce_n v)/B]
+      (``update_params``; ``nn.Parameter(param - lr * grad)`` makes theta' a LEAF, so despite ``create_graph=True`` no
+      second-order term survives, and the later losses run under ``no_grad`` anyway); then
+      ``grad(weighted_ce, (v,))`` sees only the LAST clone ``weights.forward`` handed out (the negatives' one):
+      d/dv = ce_n(theta') / B - 1, and W[j] <- sigmoid(v - lr_t * d/dv).  With transformers 5.x ``set_param`` on
+      'shared.weight' does not reach the tied embedding / head modules, so theta' keeps theta there.
+    * main_loop (:153-179): positives through ``self.model``, negatives through ``self.meta_model`` (theta'), loss
+      = sum(ce_p v)/B + sum(ce_n v)/B; only the positive term reaches the optimised parameters.
+    Upstream the second meta_loop call fails under transformers 5.x (``grad`` over a replaced, now unused
+    ``shared.weight``); the golden re-creates the meta model per batch, which is what this class does in effect
+    (``load_parameters_from`` overwrites every master value)."""
+
+    def __init__(self, dataset, model_name, batch_size, model_init, tokenizer, lr, ignore_index,
+                 lookahead_updates_embedding=False) -> None:
+        super().__init__(dataset, model_name, batch_size, model_init, tokenizer, lr, ignore_index)
+        self.meta_model = model_init()
+        self.lookahead_updates_embedding = bool(lookahead_updates_embedding)
+
+    def _ce(self, model, x, o, grad):
+        if grad:
+            logits = model(x, o)
+        else:
+            with torch.no_grad():
+                logits, _ = model.logits(x, o)
+        return self.loss_fn(logits.reshape(-1, logits.size(-1)), o.view(-1)), logits.shape[-2]
+
+    def meta_loop(self, j):
+        px, nx, o_p, o_n = self.prep_batch(self.train_loader.get_batch(j, self.weights[j]))
+        self.meta_model.load_parameters_from(self.model)
+        v = self.weights.weight.data[j]
+        ce, T = self._ce(self.meta_model, px, o_p, True)
+        weighted_ce_p = torch.sum(ce * v.view(-1, 1).repeat(1, T).view(-1)) / len(ce)
+        ce, T = self._ce(self.meta_model, nx, o_n, True)
+        weighted_ce_n = torch.sum(ce * v.view(-1, 1).repeat(1, T).view(-1)) / len(ce)
+        self.meta_model.zero_grad()
+        (weighted_ce_p + weighted_ce_n).backward()
+        lr = self.scheduler.get_last_lr()[0]
+        self.meta_model.sgd_step(lr, include_embedding=self.lookahead_updates_embedding)      # theta'
+        ce_n, _ = self._ce(self.meta_model, nx, o_n, False)
+        self.weights.meta_update(j, ce_n, lr)          # W[j] <- sigmoid(v - lr (ce_n(theta') / B - 1))
+
+    def main_loop(self, j):
+        px, nx, o_p, o_n = self.prep_batch(self.train_loader.get_batch(j, self.weights[j]))
+        v = self.weights.weight.data[j]
+        ce, T = self._ce(self.model, px, o_p, True)
+        weighted_ce_p = torch.sum(ce * v.view(-1, 1).repeat(1, T).view(-1)) / len(ce)
+        ce, T = self._ce(self.meta_model, nx, o_n, False)
+        weighted_ce_n = torch.sum(ce * v.view(-1, 1).repeat(1, T).view(-1)) / len(ce)
+        loss = torch.mean(weighted_ce_p + weighted_ce_n)
+        self.model.zero_grad()
+        loss.backward()
+        gscale = self.model.all_reduce_grads()
+        self.model.step(self.scheduler.get_last_lr()[0], gscale=gscale)
+        self.scheduler.step()
+        return loss.item()
+
+    def train(self, train_loader, epochs, warmup_steps, progress=None):
+        return NewWrapper.train(self, train_loader, epochs, warmup_steps, progress)
 
 
 class NewWrapper(PacedWrapper):

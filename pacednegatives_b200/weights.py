@@ -24,11 +24,11 @@ def spl_weights(loss, eta, mask=0.0, variant=LCE, want_keep=False, want_stats=Fa
     eta_t = eta.detach().reshape(-1)[:1].contiguous().float()
     w = torch.empty_like(loss)
     keep = torch.empty(loss.shape, dtype=torch.uint8, device=loss.device) if want_keep else None
-    stats = torch.empty(6, dtype=torch.float64, device=loss.device) if want_stats else None
+    stats = torch.empty(13, dtype=torch.float64, device=loss.device) if want_stats else None   # [6:] = scratch
     _lib.check(_lib.lib().pn_weights_fwd(_lib.ptr(loss), loss.numel(), _lib.ptr(eta_t), float(mask),
                                          variant, _lib.ptr(w), _lib.ptr(keep), _lib.ptr(stats),
                                          _lib.stream()))
-    return w, keep, stats
+    return w, keep, (stats[:6] if stats is not None else None)
 
 
 class _SplWeightFn(torch.autograd.Function):

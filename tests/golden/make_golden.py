@@ -460,8 +460,8 @@ def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_i
                     lr=1e-3, meta_lr=1e-2):
     """The reference's own LCEModel.training_step (lceT5.py:124-167), unmodified, on HF T5 fp32 CPU at the widths
     the bench runs: per parameter the gradient norm, a seeded element sample (all elements for
-    tensors <= 65536) and, for matrices, the row and column sums (a wrong head / block shows up there even when the
-    sample misses it).  eta=None puts the threshold midway between the two middle losses of the step so both weight branches run."""
+    tensors <= 65536) and, for matrices, the row / column sums and the norm of every 64 x 64 block (a wrong head /
+    block shows up there even when the sample misses it).  eta=None puts the threshold midway between the two middle losses of the step so both weight branches run."""
     sys.path.insert(0, ROOT)
     from oracle import t5 as ot
     from transformers import T5Config, T5ForConditionalGeneration, get_linear_schedule_with_warmup
@@ -529,6 +529,11 @@ def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_i
                 if g.dim() == 2 and flat.numel() > 65536:
                     res["growsum/" + n_] = g.double().sum(1).float().numpy()
                     res["gcolsum/" + n_] = g.double().sum(0).float().numpy()
+                    # Frobenius norm of every 64 x 64 block (one head's slice of a projection): no cancellation, so a
+                    # wrong head / block / diagonal shows up here even when the element sample misses it
+                    R, C = g.shape
+                    gb = g.double()[:R - R % 64, :C - C % 64].reshape(R // 64, 64, C // 64, 64)
+                    res["gblock/" + n_] = gb.pow(2).sum((1, 3)).sqrt().float().numpy()
     np.savez_compressed(
         out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
                             dims.n_heads]), seed=np.array(seed), pids=pids, nids=nids, plab=plab, nlab=nlab,
@@ -621,6 +626,101 @@ def gold_newwrapper(rp, rw, out):
     np.savez_compressed(
         out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
                             dims.n_heads]), seed=np.array(29), pids=pids, nids=nids,
+        hp=np.array([B, lr, warm, total, rel_id, nrel_id]), **{k_: np.asarray(v) for k_, v in res.items()})
+
+
+def gold_stdwrapper(rp, rw, out):
+    """The reference's StdWrapper.meta_loop + main_loop (pairwrapper.py:102-179) executed unmodified on a tiny
+    random-init HF T5 (fp32, CPU) for three batches.  The harness supplies the one attribute the reference's
+    constructor leaves commented out (pairwrapper.py:51: `self.meta_model`), freshly per batch: with transformers
+    5.x the reference's second meta_loop call on the SAME meta model raises (update_params replaced `shared.weight`
+    with a Parameter no forward path reads, and `grad` refuses unused inputs), so upstream runs exactly one batch."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    from transformers import T5Config, T5ForConditionalGeneration, get_linear_schedule_with_warmup
+    dims = ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2)
+    w = ot.init_weights(dims, seed=43)
+    cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
+                   num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
+                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   pad_token_id=0, eos_token_id=1, feed_forward_proj="relu", tie_word_embeddings=True)
+
+    def model_init():
+        m_ = T5ForConditionalGeneration(cfg).train()
+        sd = {k_: torch.tensor(v) for k_, v in w.items()}
+        sd["encoder.embed_tokens.weight"] = sd["decoder.embed_tokens.weight"] = sd["shared.weight"]
+        sd["lm_head.weight"] = sd["shared.weight"]
+        missing = m_.load_state_dict(sd, strict=False)
+        assert not missing.missing_keys and not missing.unexpected_keys, missing
+        return m_
+
+    m = model_init()
+    B, S, nb = 4, 128, 3
+    rel_id, nrel_id = 117, 213
+    rng = np.random.RandomState(1977)
+    pids = rng.randint(2, dims.vocab, size=(nb, B, S)).astype(np.int64)
+    nids = rng.randint(2, dims.vocab, size=(nb, B, S)).astype(np.int64)
+    pids[:, :, -1] = 1
+    nids[:, :, -1] = 1
+    lr, warm, total = 2e-2, 0, 12     # a look-ahead step large enough to move the losses well past bf16 noise
+
+    class Tok:
+        def __call__(self, x, padding=True, return_tensors="pt"):
+            if isinstance(x, tuple):
+                ids = torch.tensor((pids if x[0] == "p" else nids)[x[1]])
+            else:
+                ids = torch.tensor([[rel_id if t == "true" else nrel_id, 1] for t in x])
+            return types.SimpleNamespace(input_ids=ids)
+
+    seen = []
+
+    class Loader:
+        def get_batch(self, j, weights):
+            seen.append(weights.detach().numpy().copy())
+            return ("p", j), ("n", j), ["true"] * B, ["false"] * B
+
+        def __len__(self):
+            return nb * B
+
+    ces = []
+    ce_fn = torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none")
+
+    def loss_fn(logits, target):
+        o = ce_fn(logits, target)
+        ces.append(o.detach().numpy().copy())
+        return o
+
+    wrap = object.__new__(rp.StdWrapper)
+    wrap.device = torch.device("cpu")
+    wrap.loss_fn = loss_fn
+    wrap.model = m
+    wrap.tokenizer = Tok()
+    wrap.optimizer = LegacyAdamW(m.parameters(), lr=lr)
+    wrap.batch_size = B
+    wrap.weights = rw.Weights((nb, B), device=torch.device("cpu"))
+    wrap.weights.weight.data[:] = torch.tensor(rng.uniform(0.3, 1.0, size=(nb, B)).astype(np.float32))
+    wrap.train_loader = Loader()
+    wrap.scheduler = get_linear_schedule_with_warmup(wrap.optimizer, num_warmup_steps=warm,
+                                                     num_training_steps=total)
+    res = {"w0": wrap.weights.weight.detach().numpy().copy()}
+    before = {n_: p.detach().clone() for n_, p in m.named_parameters()}
+    for j in range(nb):
+        wrap.meta_model = model_init()       # pairwrapper.py:51, commented out upstream
+        del ces[:]
+        wrap.meta_loop(j)
+        # loss_fn calls of meta_loop: ce_p(theta), ce_n(theta), ce_p(theta'), ce_n(theta')
+        res[f"meta_ce{j}"] = np.stack(ces)
+        res[f"row{j}"] = wrap.weights.weight[j].detach().numpy().copy()
+        del ces[:]
+        res[f"loss{j}"] = np.float32(wrap.main_loop(j))
+        res[f"main_ce{j}"] = np.stack(ces)   # ce_p(model), ce_n(meta model = theta')
+        res[f"lr{j}"] = np.float32(wrap.scheduler.get_last_lr()[0])
+    for n_, p in m.named_parameters():
+        res["dnorm/" + n_] = float((p.detach() - before[n_]).norm())
+    res["seen"] = np.stack(seen)
+    np.savez_compressed(
+        out, dims=np.array([dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
+                            dims.n_heads]), seed=np.array(43), pids=pids, nids=nids,
         hp=np.array([B, lr, warm, total, rel_id, nrel_id]), **{k_: np.asarray(v) for k_, v in res.items()})
 
 
@@ -881,6 +981,7 @@ def main():
     if "--wide" in sys.argv or "--all" in sys.argv:   # minutes of CPU: only on request
         gold_train_widths(rt)
     gold_newwrapper(rp, rw, os.path.join(HERE, "newwrapper_golden.npz"))
+    gold_stdwrapper(rp, rw, os.path.join(HERE, "stdwrapper_golden.npz"))
     gold_scalar_wrappers(rp, rw, os.path.join(HERE, "scalar_wrappers_golden.npz"))
     gold_datamodule(rt, os.path.join(HERE, "datamodule_golden.npz"))
     for f in sorted(os.listdir(HERE)):
