@@ -235,6 +235,19 @@ int pn_t5_self_attention_bwd(const void* qkv, int32_t docs, int32_t S, int32_t n
                              const void* ctx, const void* dctx, const float* lse2, const float* row_scale,
                              void* dqkv, float* dbias_diag, float* dvec_ws, void* stream);
 
+/* Allocation-free variant of pn_t5_self_attention_bwd.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid allocation).  Same inputs, outputs and arithmetic, but the [docs*S, n_heads]
+ * fp32 workspace is a file-scope device array of the library (4 MiB, held by every GPU that loads the library until
+ * exit) instead of a caller buffer: the call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limit: docs * S * n_heads <= 1 048 576 (e.g. 128 documents x 512 tokens x 16 heads); larger shapes return
+ * PN_E_UNSUPPORTED with a message.  Every call on a device shares the one array: nothing in it has to start at zero
+ * (the call overwrites every entry it reads), but two calls that overlap on the GPU (different streams, or graphs
+ * replayed concurrently) race on it; serialise them on one stream. */
+int pn_t5_self_attention_bwd_static(const void* qkv, int32_t docs, int32_t S, int32_t n_heads, const float* bias,
+                                    const void* ctx, const void* dctx, const float* lse2, const float* row_scale,
+                                    void* dqkv, float* dbias_diag, void* stream);
+
 /* ------------------------------------------------------------------ a1 / a9 / a12: monoT5 scorer
  * Replaces transformers.T5ForConditionalGeneration as the reference calls it (lceT5.py:106,132-133,
  * 149-150; pairwrapper.py:223-247; the re-rank formula distill/wrapper.py:34-38).  ReLU FFN, RMSNorm,

@@ -48,6 +48,8 @@ SIGNATURES = {
     "pn_t5_self_attention_lse": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "pn_t5_self_attention_bwd": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                          c_vp, c_vp]),
+    "pn_t5_self_attention_bwd_static": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                                c_vp]),
     "pn_t5_train_workspace_bytes": (c_i64, [c_vp, c_i64, c_i32, c_i32]),
     "pn_t5_set_train_buffers": (c_int, [c_vp, c_vp, c_vp, c_vp]),
     "pn_t5_train_forward": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_i64, c_vp]),

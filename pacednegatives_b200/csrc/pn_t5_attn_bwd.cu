@@ -645,3 +645,52 @@ extern "C" int pn_t5_self_attention_bwd(const void* qkv, int32_t docs, int32_t S
                              (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, di, lse2, dvec_ws,
                              row_scale, (__nv_bfloat16*)dqkv, dbias_diag, (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free variant of pn_t5_self_attention_bwd (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc).  The D-vector workspace [docs*S, H] the two backward passes read lives in a file-scope device
+// array instead of a caller buffer.  Every GPU that loads the library holds the array until exit.
+constexpr long long PN_ATTN_BWD_STATIC_MAX = 1ll << 20;   // docs * S * n_heads <= 1 Mi floats (4 MiB)
+static __device__ __align__(256) float g_attn_bwd_dvec_scratch[PN_ATTN_BWD_STATIC_MAX];
+
+// In host code the array's name is a host-side stand-in, not a device address: the device address is looked up once
+// per device, with that device current (cudaGetSymbolAddress allocates nothing), and cached.
+static int attn_bwd_static_scratch(float** out) {
+  static float* cached[64] = {nullptr};
+  static std::atomic<int> ready[64];
+  int dev = 0;
+  PN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return pn_fail(PN_E_UNSUPPORTED, "pn_t5_self_attention_bwd_static: device index %d >= 64", dev);
+  if (!ready[dev].load(std::memory_order_acquire)) {
+    float* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_attn_bwd_dvec_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return pn_fail(PN_E_LAUNCH, "pn_t5_self_attention_bwd_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                     cudaGetErrorString(e));
+    cached[dev] = p;                       // two racing threads look up the same address
+    ready[dev].store(1, std::memory_order_release);
+  }
+  *out = cached[dev];
+  return PN_OK;
+}
+
+extern "C" int pn_t5_self_attention_bwd_static(const void* qkv, int32_t docs, int32_t S, int32_t n_heads,
+                                               const float* bias, const void* ctx, const void* dctx,
+                                               const float* lse2, const float* row_scale, void* dqkv,
+                                               float* dbias_diag, void* stream) {
+  PN_CHECK_ARG(qkv && bias && ctx && dctx && lse2 && dqkv && dbias_diag && docs >= 0 && n_heads > 0 && S >= 1);
+  const long long need = (long long)docs * S * n_heads;
+  if (need > PN_ATTN_BWD_STATIC_MAX)
+    return pn_fail(PN_E_UNSUPPORTED,
+                   "pn_t5_self_attention_bwd_static: docs*S*n_heads = %lld exceeds the built-in scratch of %lld floats; "
+                   "use pn_t5_self_attention_bwd with a caller workspace",
+                   need, PN_ATTN_BWD_STATIC_MAX);
+  float* dvec = nullptr;
+  if (int rc = attn_bwd_static_scratch(&dvec)) return rc;
+  // nothing in the scratch has to start at zero: attn_dvec_kernel overwrites every entry the passes read
+  const int di = n_heads * DK;
+  return pn_t5_self_attn_bwd((const __nv_bfloat16*)qkv, 3 * di, 0, di, 2 * di, docs, S, n_heads, bias,
+                             (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, di, lse2, dvec, row_scale,
+                             (__nv_bfloat16*)dqkv, dbias_diag, (cudaStream_t)stream);
+}
