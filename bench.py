@@ -670,8 +670,9 @@ def run_train(args, dist):
     # T5-large at 1+31 x 512: 512 documents of saved activations (~130 GB) do not fit beside the weights; walk the
     # batch in micro-batches of 8 queries (256 documents) by default
     mq = args.micro_queries if args.micro_queries >= 0 else (8 if large else 0)
+    dr = float(getattr(args, "train_dropout", 0.0) or 0.0)
     hp = dict(n=k, use_mean=True, ignore_index=-100, lr=1e-3, meta_lr=1e-3, warmup_steps=0,
-              total_steps=1000000, eta=0.3466, micro_queries=mq)
+              total_steps=1000000, eta=0.3466, micro_queries=mq, dropout_rate=dr, seed=1)
     tag = "T5-large" if large else "monoT5-base"
     cfg_i = 3 if large else 2
     m = LCEModel(hp, dims=dims, state_dict=random_state_dict(dims, seed=0), cta_group=args.cta_group)
@@ -728,8 +729,9 @@ def run_train(args, dist):
     value = queries / (ms / 1e3)
     e2e_value = queries / (e2e_ms / 1e3)
     peaks = measured_peaks()
-    # forward + backward (2x forward) with the redundant no-grad forward elided: 3x the forward count
-    step_flops = Q * (1 + k) * flops_per_doc(dims, S, T, True) * 3.0
+    # forward + backward (2x forward) with the redundant no-grad forward elided: 3x the forward count; with dropout
+    # the no-grad forward sees other masks and is run: 4x
+    step_flops = Q * (1 + k) * flops_per_doc(dims, S, T, True) * (4.0 if dr > 0.0 else 3.0)
     g_ms, g_n, g_flops = prof["gemm"]
     gemm_tflops = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
 
@@ -748,7 +750,9 @@ def run_train(args, dist):
         "config": {"workload": f"LCE training step, {tag}, 1+{k} docs per query, seq 512 (BASELINE configs[{cfg_i}])",
                    "queries_per_step_per_gpu": Q, "negatives": k, "seq_len": S, "label_tokens": T,
                    "micro_queries": mq if 0 < mq < Q else None,
-                   "no_grad_forward": "elided (identical arithmetic at dropout 0); FLOP count uses 3x forward",
+                   "dropout_rate": dr,
+                   "no_grad_forward": ("elided (identical arithmetic at dropout 0); FLOP count uses 3x forward" if dr == 0.0
+                                       else "run in train mode with its own masks; FLOP count uses 4x forward"),
                    "optimizer": "AdamW (transformers rule) on flat fp32 masters + eta meta step",
                    "l2": "activations per step (tens of GB) exceed the 126 MB L2; no flush needed",
                    "parallelism": f"dp{WORLD}: fp32 SUM all-reduce of the flat gradient buffer in 6 ranges overlapped "
@@ -788,7 +792,8 @@ def train_flat(tr):
            "train_e2e_queries_per_s": tr["e2e"]["value"], "train_e2e_ms_per_step": tr["e2e"]["ms_per_step"],
            "train_queries_per_step_per_gpu": c["queries_per_step_per_gpu"], "train_negatives": c["negatives"],
            "train_model_tflops": tr["model_tflops"], "train_model_frac": tr["model_frac_of_sustained_peak"],
-           "train_flop_count": "3x forward (no-grad forward elided at dropout 0)",
+           "train_flop_count": "3x forward (no-grad forward elided at dropout 0)" if not c.get("dropout_rate") else "4x forward",
+           "train_dropout_rate": c.get("dropout_rate", 0.0),
            "train_gpu_launches_per_step": tr["gpu_launches"] / max(tr["steps"], 1),
            "train_allreduce_bytes": c["allreduce_bytes_per_step"], "train_allreduce_dtype": c["allreduce_dtype"],
            "train_allreduce_exposed_ms": c["allreduce_exposed_ms"],
@@ -934,6 +939,10 @@ def main():
     ap.add_argument("--micro-queries", type=int, default=-1,
                     help="train workload: queries per micro-batch (0 = whole batch at once, -1 = config default)")
     ap.add_argument("--ref-train-docs", type=int, default=4)
+    ap.add_argument("--train-dropout", type=float, default=0.0,
+                    help="train workload: dropout_rate (0.1 = the reference's train-mode regime: 4 forwards' worth of work)")
+    ap.add_argument("--no-dropout-regime", action="store_true",
+                    help="workload all: skip the short second training measurement at dropout 0.1")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3   # timing rule: at least 3 warm-up steps
@@ -974,6 +983,22 @@ def main():
             line["config"].update(train_flat(tr))
             if RANK == 0:
                 print(json.dumps(tr), file=sys.stderr, flush=True)
+            if not args.no_dropout_regime and args.train_dropout == 0.0:
+                # the reference's own regime (Lightning train mode: dropout 0.1 in both forwards), a short run
+                import copy
+                a2 = copy.copy(args)
+                a2.train_dropout, a2.steps = 0.1, max(3, min(args.steps, 5))
+                try:
+                    td = run_train(a2, dist)
+                    line["config"].update({"train_dropout01_queries_per_s": td["value"],
+                                           "train_dropout01_ms_per_step": td["ms_per_step"],
+                                           "train_dropout01_model_frac": td["model_frac_of_sustained_peak"],
+                                           "train_dropout01_flop_count": "4x forward",
+                                           "train_dropout01_steps": td["steps"]})
+                    if RANK == 0:
+                        print(json.dumps(td), file=sys.stderr, flush=True)
+                except Exception as e:
+                    line["config"]["train_dropout01_error"] = f"{type(e).__name__}: {e}"[:200]
     if args.workload == "select":
         line = run_select(args, dist)
         if solo:

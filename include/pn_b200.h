@@ -318,6 +318,15 @@ int64_t pn_t5_train_workspace_bytes(const PnT5* m, int64_t docs, int32_t S, int3
 int pn_t5_set_train_buffers(PnT5* m, float* grads, float* adam_m, float* adam_v);
 int pn_t5_train_forward(PnT5* m, const int32_t* ids, const int64_t* labels, int64_t docs, int32_t S, int32_t T,
                         float* logits_out, void* workspace, int64_t workspace_bytes, void* stream);
+/* Train-mode dropout (the reference's LCEModel is a LightningModule in train() mode, so HF T5 applies
+ * nn.Dropout(config.dropout_rate = 0.1) in BOTH forwards of lceT5.py:131-133,149-150: embedding output, every
+ * sub-layer output, FFN hidden activation, attention probabilities, the two final norms).  p, seed and doc_offset
+ * apply to the NEXT pn_t5_train_forward / _forward_z2 and to the backward that consumes its workspace; p = 0
+ * (default) is eval-mode arithmetic.  Masks are counter-based — a pure function of (seed, dropout site, element
+ * index with documents numbered from doc_offset) — so the backward regenerates them instead of storing them, and
+ * tests replay the same masks inside HF.  pn_t5_train_workspace_bytes depends on whether p > 0 (the projection-free
+ * cross-attention is the p = 0 path). */
+int pn_t5_set_dropout(PnT5* m, float p, uint64_t seed, int64_t doc_offset);
 int pn_t5_train_backward(PnT5* m, const int32_t* ids, const float* dlogits, int64_t docs, int32_t S, int32_t T,
                          void* workspace, int64_t workspace_bytes, void* stream);
 /* Restricted-head training (north_star kernels (1) + (2): the LM head restricted to the 'true' / 'false' rows and

@@ -56,6 +56,7 @@ SIGNATURES = {
     "pn_t5_train_backward": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
     "pn_t5_train_forward_z2": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_i64, c_vp]),
     "pn_t5_train_backward_z2": (c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
+    "pn_t5_set_dropout": (c_int, [c_vp, c_f32, c_u64, c_i64]),
     "pn_t5_zero_grad": (c_int, [c_vp, c_vp]),
     "pn_t5_set_grad_hook": (c_int, [c_vp, c_vp, c_vp]),
     "pn_t5_adamw_step": (c_int, [c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_i64, c_f32, c_vp]),

@@ -281,6 +281,7 @@ struct DecAttnArgs {
   __nv_bfloat16* out; int ld_out;         // [docs*T, ld_out]
   int n_heads; int docs;
   const int32_t* klen;                     // optional [docs]: cross-attention key-padding mask
+  PnDrop drop;                             // dropout of the attention probabilities (training), index [doc,h,t,j]
 };
 
 __global__ void __launch_bounds__(128)
@@ -321,9 +322,12 @@ dec_attn_kernel(const DecAttnArgs a) {
   }
   mx = pn_warp_max(mx);
   float sum = 0.0f;
+  const int skp = a.Sk + (a.Sk & 1);
+  const unsigned long long dbase = (unsigned long long)a.drop.idx_offset +
+                                   ((unsigned long long)(doc * a.n_heads + head) * a.T + t) * skp;
   for (int j = lane; j < nk; j += 32) {
     const float p = __expf(sp[w][j] - mx);
-    sp[w][j] = p;
+    sp[w][j] = p * pn_drop_mul(a.drop, dbase + j);   // the row sum stays that of the un-dropped softmax
     sum += p;
   }
   sum = pn_warp_sum(sum);
@@ -368,13 +372,14 @@ int pn_t5_self_attn_v1(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_co
 int pn_t5_dec_attn(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_bfloat16* k,
                    const __nv_bfloat16* v, int ld_kv, int k_col, int v_col, int docs, int T, int Sk,
                    int n_heads, int causal, const float* bias, __nv_bfloat16* out, int ld_out,
-                   cudaStream_t st, const int32_t* klen) {
+                   cudaStream_t st, const int32_t* klen, PnDrop drop) {
   if (Sk < 1 || Sk > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "decoder attention: Sk=%d not in [1,512]", Sk);
   DecAttnArgs a;
   a.q = q; a.ld_q = ld_q; a.q_col = q_col; a.k = k; a.v = v; a.ld_kv = ld_kv; a.k_col = k_col;
   a.v_col = v_col; a.Sk = Sk; a.T = T; a.causal = causal; a.bias = bias; a.out = out;
   a.ld_out = ld_out; a.n_heads = n_heads; a.docs = docs;
   a.klen = klen;
+  a.drop = drop;
   const int64_t warps = (int64_t)docs * n_heads * T;
   dec_attn_kernel<<<(unsigned)((warps + 3) / 4), 128, 0, st>>>(a);
   PN_LAUNCHED();

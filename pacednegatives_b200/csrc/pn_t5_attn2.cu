@@ -61,6 +61,7 @@ struct Attn2Args {
   float* lse;                     // optional [docs*S, n_heads]: log2-domain logsumexp of each row (training)
   const int32_t* klen;            // optional [docs]: keys >= klen[doc] are padding (HF attention_mask, right-padded)
   long long* dbg;                 // optional [2][64][8] clock64 stamps of CTA 0 (PN_ATTN_DBG)
+  PnDrop drop;                    // training: dropout of the probabilities (HF:331); the row sum stays un-dropped
 };
 
 #define DBG_STAMP(who, step, ev)                                                        \
@@ -328,6 +329,11 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
       }
       // single pass: bias (columns 32..127), running max, p = 2^(x - m_used) against the STALE max so that the
       // exponentials do not wait for the row max; P -> its own TMEM buffer as packed bf16 (64 columns)
+      // dropout mask of this row's chunk: element [doc, head, qi, c*KC + jj] at an even row pitch
+      const bool dropping = a.drop.thresh != 0;
+      const unsigned long long dbase =
+          (unsigned long long)a.drop.idx_offset +
+          ((unsigned long long)((doc0 + it * a.cph) * a.n_heads + head) * S + (qi < S ? qi : 0)) * (S + (S & 1)) + c * KC;
       float nm = -m_used;
       uint64_t nm2 = f2pack(nm, nm);
       uint64_t lsa = f2pack(0.0f, 0.0f), lsb = lsa;
@@ -361,8 +367,16 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
           const float p3 = ex2_approx(e3);
           lsa = add2(lsa, f2pack(p0, p1));
           lsb = add2(lsb, f2pack(p2, p3));
-          pk[e] = pack_bf16x2(p0, p1);
-          pk[e + 1] = pack_bf16x2(p2, p3);
+          if (dropping) {
+            float m0, m1, m2, m3;
+            pn_drop_mul2(a.drop, dbase + jj, m0, m1);
+            pn_drop_mul2(a.drop, dbase + jj + 2, m2, m3);
+            pk[e] = pack_bf16x2(p0 * m0, p1 * m1);
+            pk[e + 1] = pack_bf16x2(p2 * m2, p3 * m3);
+          } else {
+            pk[e] = pack_bf16x2(p0, p1);
+            pk[e + 1] = pack_bf16x2(p2, p3);
+          }
         }
         if (h2 == 1) {
           // the whole row is known now; if the stale max was off by more than 2^60 redo the chunk exactly
@@ -389,7 +403,9 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
                 const float p1 = ex2_approx(x[g * 64 + 2 * e + 1] + nm);
                 ls0 += p0;
                 ls1 += p1;
-                pq[e] = pack_bf16x2(p0, p1);
+                float m0 = 1.0f, m1 = 1.0f;
+                if (dropping) pn_drop_mul2(a.drop, dbase + g * 64 + 2 * e, m0, m1);
+                pq[e] = pack_bf16x2(p0 * m0, p1 * m1);
               }
               tmem_st_32x32(p_addr + g * 32, pq);
             }
@@ -495,17 +511,35 @@ static int attn_impl() {
   return impl;
 }
 
+static int self_attn_impl(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs, int S,
+                          int n_heads, const float* bias, const int32_t* klen, __nv_bfloat16* out, int ld_out,
+                          float* lse_out, PnDrop drop, cudaStream_t st);
+
 int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
                     int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
                     cudaStream_t st) {
-  return pn_t5_self_attn_masked(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, nullptr, out, ld_out,
-                                lse_out, st);
+  return self_attn_impl(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, nullptr, out, ld_out, lse_out,
+                        PnDrop(), st);
+}
+
+int pn_t5_self_attn_drop(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
+                         int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
+                         PnDrop drop, cudaStream_t st) {
+  return self_attn_impl(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, nullptr, out, ld_out, lse_out, drop,
+                        st);
 }
 
 int pn_t5_self_attn_masked(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
                            int S, int n_heads, const float* bias, const int32_t* klen, __nv_bfloat16* out,
                            int ld_out, float* lse_out, cudaStream_t st) {
-  if (attn_impl() == 1 && !lse_out && !klen)
+  return self_attn_impl(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, klen, out, ld_out, lse_out, PnDrop(),
+                        st);
+}
+
+static int self_attn_impl(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs, int S,
+                          int n_heads, const float* bias, const int32_t* klen, __nv_bfloat16* out, int ld_out,
+                          float* lse_out, PnDrop drop, cudaStream_t st) {
+  if (attn_impl() == 1 && !lse_out && !klen && !drop.thresh)
     return pn_t5_self_attn_v1(qkv, ld_qkv, q_col, k_col, v_col, docs, S, n_heads, bias, out, ld_out, st);
   if (S < 1 || S > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "self-attention: S=%d not in [1,512]", S);
   if (docs <= 0) return PN_OK;
@@ -521,6 +555,7 @@ int pn_t5_self_attn_masked(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int 
   a.bias = bias; a.out = out; a.ld_out = ld_out;
   a.lse = lse_out;
   a.klen = klen;
+  a.drop = drop;
   a.dbg = nullptr;
   if (getenv("PN_ATTN_DBG")) {
     static long long* dbg = nullptr;

@@ -58,6 +58,7 @@ struct BwdArgs {
   __nv_bfloat16* dqkv;              // [rows, ld] gradients, same layout as qkv
   int ld;
   float* dbias_diag;                // [H, 1023] += per-diagonal sums (MODE 0 only)
+  PnDrop drop;                      // dropout of the probabilities in the forward (HF:331), regenerated here
 };
 
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
@@ -302,6 +303,12 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         row_stats(g + 1, lse_nx, dv_nx);
         const float nlse = -lse;
         const bool full = __all_sync(0xffffffffu, kvalid == 64);   // no padding rows or keys in this warp's block
+        // dropout mask of row qi: element [doc, head, qi, key] at an even row pitch.  With dropout O = (P (.) M) V:
+        // dV sums P (.) M, and dS = P (.) (M (.) dP - D) with D = rowsum(dO (.) O) as before.
+        const bool dropping = a.drop.thresh != 0;
+        const unsigned long long dbase =
+            (unsigned long long)a.drop.idx_offset +
+            ((unsigned long long)(item_doc(it) * a.n_heads + head) * S + (qi < S ? qi : 0)) * (S + (S & 1)) + k0;
         mbar_wait(bar(B_SP_FULL), g & 1);
         tc_fence_after();
         uint32_t pp[32], pd[32];                    // P and dS of this thread's 64 columns, packed bf16
@@ -334,11 +341,16 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 float x0, x1;
                 f2unpack(x, x0, x1);
                 const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
-                const uint64_t dpv = f2pack(__uint_as_float(dp[j + 2 * h2]), __uint_as_float(dp[j + 2 * h2 + 1]));
+                uint64_t dpv = f2pack(__uint_as_float(dp[j + 2 * h2]), __uint_as_float(dp[j + 2 * h2 + 1]));
+                float m0 = 1.0f, m1 = 1.0f;
+                if (dropping) {
+                  pn_drop_mul2(a.drop, dbase + c2 * 32 + j + 2 * h2, m0, m1);
+                  dpv = mul2(dpv, f2pack(m0, m1));
+                }
                 const uint64_t dsv = mul2(f2pack(p0, p1), add2(dpv, ndv2));
                 float d0, d1;
                 f2unpack(dsv, d0, d1);
-                pp[c2 * 16 + (j >> 1) + h2] = pack2(p0, p1);
+                pp[c2 * 16 + (j >> 1) + h2] = pack2(p0 * m0, p1 * m1);
                 pd[c2 * 16 + (j >> 1) + h2] = pack2(d0, d1);
               }
             }
@@ -352,7 +364,9 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
               for (int e = 0; e < 4; ++e) {
                 const float x = fmaf(__uint_as_float(s[j + e]), kLog2e, bb[e]) + nlse;
                 p[e] = (c2 * 32 + j + e < kvalid) ? ex2_approx(x) : 0.0f;
-                d[e] = p[e] * (__uint_as_float(dp[j + e]) - dv);
+                const float mk = pn_drop_mul(a.drop, dbase + c2 * 32 + j + e);
+                d[e] = p[e] * (__uint_as_float(dp[j + e]) * mk - dv);
+                p[e] *= mk;
               }
               pp[c2 * 16 + (j >> 1)] = pack2(p[0], p[1]);
               pp[c2 * 16 + (j >> 1) + 1] = pack2(p[2], p[3]);
@@ -568,7 +582,7 @@ __global__ void rel_bias_grad_kernel(const float* __restrict__ diag, const int* 
 int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, int v_col, int docs, int S,
                         int n_heads, const float* bias, const __nv_bfloat16* ctx, const __nv_bfloat16* dctx,
                         int ld_ctx, const float* lse2, float* dvec, const float* row_scale,
-                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st) {
+                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st, PnDrop drop) {
   if (S < 1 || S > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "self-attention backward: S=%d not in [1,512]", S);
   if (docs <= 0) return PN_OK;
   const int64_t rows = (int64_t)docs * S;
@@ -597,6 +611,7 @@ int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, 
   a.q_col = q_col; a.k_col = k_col; a.v_col = v_col;
   a.bias = bias; a.lse2 = lse2; a.dvec = dvec; a.row_scale = row_scale;
   a.dqkv = dqkv; a.ld = ld; a.dbias_diag = dbias_diag;
+  a.drop = drop;
   // five [128 x 128 x 64] products per (query block, key block) pair, S and dP formed twice
   PnProfScope prof(PN_PROF_ATTN_BWD, 14.0 * docs * n_heads * (double)S * S * DK, st);
   auto launched = [&](const void* fn, const char* which) -> int {

@@ -23,6 +23,7 @@ struct DecBwdArgs {
   __nv_bfloat16 *dq, *dkv;
   int ld_dq, dq_col, ld_dkv, dk_col, dv_col;
   float* grad_rel;         // [buckets, H] gradient of the decoder's relative_attention_bias (self) or null
+  PnDrop drop;             // dropout of the attention probabilities in the forward (regenerated here)
 };
 
 __device__ __forceinline__ void unpack8(const uint4& raw, float (&f)[8]) {
@@ -95,16 +96,22 @@ dec_attn_bwd_kernel(const DecBwdArgs a) {
     }
     sum = pn_warp_sum(sum);
     const float inv = 1.0f / sum;
+    // with dropout O = sum_j p_j m_j v_j: dV sees p m, dp is masked, and D = sum_j p_j m_j dp_j
+    const int skp = Sk + (Sk & 1);
+    const unsigned long long dbase = (unsigned long long)a.drop.idx_offset +
+                                     ((unsigned long long)(doc * a.n_heads + head) * T + t) * skp;
     float dsum = 0.0f;
     for (int j = lane; j < Sk; j += 32) {
       const float p = sp[t][j] * inv;
       sp[t][j] = p;
+      sds[t][j] *= pn_drop_mul(a.drop, dbase + j);
       dsum += p * sds[t][j];
     }
     dsum = pn_warp_sum(dsum);
     for (int j = lane; j < Sk; j += 32) {
       const float ds = sp[t][j] * (sds[t][j] - dsum);
       sds[t][j] = ds;
+      sp[t][j] *= pn_drop_mul(a.drop, dbase + j);    // what dV = (p m)^T do reads below
       // decoder buckets are the distance itself for distance < 16 (unidirectional, HF:218-234)
       if (a.grad_rel && j <= t) atomicAdd(a.grad_rel + (size_t)(t - j) * a.n_heads + head, ds);
     }
@@ -163,7 +170,7 @@ int pn_t5_dec_attn_bwd(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_b
                        int ld_do, int docs, int T, int Sk, int n_heads, int causal, const float* bias,
                        const float* rs_q, const float* rs_kv, __nv_bfloat16* dq, int ld_dq, int dq_col,
                        __nv_bfloat16* dkv, int ld_dkv, int dk_col, int dv_col, float* grad_rel,
-                       cudaStream_t st) {
+                       cudaStream_t st, PnDrop drop) {
   if (Sk < 1 || Sk > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "decoder attention backward: Sk=%d not in [1,512]", Sk);
   if (T < 1 || T > MAX_T) return pn_fail(PN_E_UNSUPPORTED, "decoder attention backward: T=%d not in [1,2]", T);
   if (docs <= 0) return PN_OK;
@@ -174,6 +181,7 @@ int pn_t5_dec_attn_bwd(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_b
   a.bias = bias; a.rs_q = rs_q; a.rs_kv = rs_kv;
   a.dq = dq; a.dkv = dkv; a.ld_dq = ld_dq; a.dq_col = dq_col; a.ld_dkv = ld_dkv; a.dk_col = dk_col; a.dv_col = dv_col;
   a.grad_rel = grad_rel;
+  a.drop = drop;
   dec_attn_bwd_kernel<<<docs * n_heads, kThreads, 0, st>>>(a);
   PN_LAUNCHED();
   return PN_OK;

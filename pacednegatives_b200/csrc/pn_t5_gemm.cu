@@ -78,6 +78,8 @@ struct GemmArgs {
   // batched kTN: split s covers the K rows of batch s and writes its own output at out + s*batch_stride
   long long batch_stride;
   int batches;
+  PnDrop drop;             // dropout on the produced values (thresh 0 = off), see PnGemmExtra
+  float out_scale;         // scalar factor folded into the row scale
 };
 
 // kTN = false: C[M,N] = A[M,K] . B[N,K]^T   (both operands K-major: forward and data-gradient GEMMs)
@@ -276,9 +278,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int row = row0 + lane;
       const int col0 = n_blk * BLOCK_N;
       const bool live = row < args.M;
-      float rs = 1.0f;
+      float rs = args.out_scale;
       if (live) {
-        if (args.row_scale) rs = args.row_scale[row];
+        if (args.row_scale) rs *= args.row_scale[row];
         if (args.sumsq_in) {
           float ss = 0.0f;
           for (int p = 0; p < args.sumsq_parts; ++p) ss += args.sumsq_in[(size_t)p * args.M + row];
@@ -306,10 +308,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t addr = rbuf + ((j ^ swz) << 4);
           float4 h;
           asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(h.x), "=f"(h.y), "=f"(h.z), "=f"(h.w) : "r"(addr));
-          h.x = fmaf(__uint_as_float(v[j * 4 + 0]), rs, h.x);
-          h.y = fmaf(__uint_as_float(v[j * 4 + 1]), rs, h.y);
-          h.z = fmaf(__uint_as_float(v[j * 4 + 2]), rs, h.z);
-          h.w = fmaf(__uint_as_float(v[j * 4 + 3]), rs, h.w);
+          float k0 = rs, k1 = rs, k2 = rs, k3 = rs;
+          if (args.drop.thresh) {   // sub-layer output dropout: the mask multiplies the product, not the residual
+            const unsigned long long e0 =
+                (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N + (col0 + c * 32 + j * 4);
+            float m0, m1, m2, m3;
+            pn_drop_mul2(args.drop, e0, m0, m1);
+            pn_drop_mul2(args.drop, e0 + 2, m2, m3);
+            k0 *= m0; k1 *= m1; k2 *= m2; k3 *= m3;
+          }
+          h.x = fmaf(__uint_as_float(v[j * 4 + 0]), k0, h.x);
+          h.y = fmaf(__uint_as_float(v[j * 4 + 1]), k1, h.y);
+          h.z = fmaf(__uint_as_float(v[j * 4 + 2]), k2, h.z);
+          h.w = fmaf(__uint_as_float(v[j * 4 + 3]), k3, h.w);
           asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w)
                        : "memory");
           ssq += h.x * h.x + h.y * h.y + h.z * h.z + h.w * h.w;
@@ -371,9 +382,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int row = row0 + lane;
       const int col0 = n_blk * BLOCK_N;
       const bool live = row < args.M;
-      float rs = 1.0f;
+      float rs = args.out_scale;
       if (live) {
-        if (args.row_scale) rs = args.row_scale[row];
+        if (args.row_scale) rs *= args.row_scale[row];
         if (args.sumsq_in) {
           float ss = 0.0f;
           for (int p = 0; p < args.sumsq_parts; ++p) ss += args.sumsq_in[(size_t)p * args.M + row];
@@ -422,6 +433,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               float x0 = __uint_as_float(v[(j & 3) * 8 + 2 * e]) * rs;
               float x1 = __uint_as_float(v[(j & 3) * 8 + 2 * e + 1]) * rs;
               if (args.relu) { x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
+              if (args.drop.thresh) {   // FFN hidden dropout (after the activation, HF:103)
+                float m0, m1;
+                pn_drop_mul2(args.drop, (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N +
+                                            (col0 + c * 64 + j * 8 + 2 * e), m0, m1);
+                x0 *= m0; x1 *= m1;
+              }
               __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
               pk[e] = *reinterpret_cast<uint32_t*>(&h);
             }
@@ -501,6 +518,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 f.y = __uint_as_float(v[j * 4 + 1]) * rs;
                 f.z = __uint_as_float(v[j * 4 + 2]) * rs;
                 f.w = __uint_as_float(v[j * 4 + 3]) * rs;
+                if (args.drop.thresh) {   // sub-layer output dropout (staged thread-per-row: this thread owns `row`)
+                  const unsigned long long e0 = (unsigned long long)args.drop.idx_offset +
+                                                (unsigned long long)row * args.N + (col0 + c * 32 + j * 4);
+                  float m0, m1, m2, m3;
+                  pn_drop_mul2(args.drop, e0, m0, m1);
+                  pn_drop_mul2(args.drop, e0 + 2, m2, m3);
+                  f.x *= m0; f.y *= m1; f.z *= m2; f.w *= m3;
+                }
                 *reinterpret_cast<float4*>(bufg + lane * 128 + ((j ^ swz) << 4)) = f;
               }
               __syncwarp();
@@ -703,6 +728,7 @@ int pn_gemm_tn_batched(const void* A, int lda, const void* B, int ldb, float* ou
     return pn_fail(PN_E_BADARG, "pn_gemm_tn_batched: operands must be 16-byte aligned");
   GemmArgs a = {};
   a.M = M; a.N = N; a.K = Kper * batches; a.out = out; a.ldc = ldc; a.mode = PN_EPI_ATOMIC_F32; a.norm_dim = 1;
+  a.out_scale = 1.0f;
   a.batches = batches; a.batch_stride = (long long)M * ldc;
   return (N % 256) == 0 ? launch_gemm<1, 256, true>(A, lda, B, ldb, a, st)
                         : launch_gemm<1, 128, true>(A, lda, B, ldb, a, st);
@@ -717,6 +743,7 @@ int pn_gemm_wgrad(const void* A, int lda, const void* B, int ldb, float* out, in
     return pn_fail(PN_E_BADARG, "pn_gemm_wgrad: operands must be 16-byte aligned");
   GemmArgs a = {};
   a.M = M; a.N = N; a.K = K; a.out = out; a.ldc = ldc; a.mode = PN_EPI_ATOMIC_F32; a.norm_dim = 1;
+  a.out_scale = 1.0f;
   const bool n256 = (N % 256) == 0;
   if (cta_group == 2)
     return n256 ? launch_gemm<2, 256, true>(A, lda, B, ldb, a, st) : launch_gemm<2, 128, true>(A, lda, B, ldb, a, st);
@@ -756,6 +783,10 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   a.group_b_rows = ex ? ex->group_b_rows : 0;
   a.mask = ex ? ex->relu_mask : nullptr;
   a.ld_mask = ex ? ex->ld_mask : 0;
+  a.out_scale = ex && ex->out_scale != 0.0f ? ex->out_scale : 1.0f;
+  if (ex) a.drop = ex->drop;
+  if (a.drop.thresh && (mode == PN_EPI_F32 || (N & 1)))
+    return pn_fail(PN_E_BADARG, "pn_gemm: dropout is built into the bf16 and the residual epilogues only");
   if (a.mask && (mode != PN_EPI_BF16 || (a.ld_mask % 8) || ((uintptr_t)a.mask & 15)))
     return pn_fail(PN_E_BADARG, "pn_gemm: relu mask needs the bf16 epilogue, 16-byte alignment and ld %% 8 == 0");
   if (a.copy_out && ((a.ld_copy % 4) || ((uintptr_t)a.copy_out & 7)))
@@ -770,7 +801,7 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   // PN_GEMM_SLAB = rows per slab (0 = one launch).
   static const int slab_rows = [] { const char* e = getenv("PN_GEMM_SLAB"); return e ? atoi(e) : 0; }();
   if (slab_rows >= 256 && mode == PN_EPI_RESID_F32 && cta_group == 2 && K >= 2048 && M >= 2 * slab_rows &&
-      !a.row_scale && !a.sumsq_in && a.group_rows == 0) {
+      !a.row_scale && !a.sumsq_in && a.group_rows == 0 && !a.drop.thresh) {
     const int step = slab_rows / 256 * 256;
     for (int r0 = 0; r0 < M; r0 += step) {
       GemmArgs b = a;

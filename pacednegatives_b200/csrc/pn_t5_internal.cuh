@@ -13,6 +13,7 @@ int pn_gemm_bf16_internal(const void* A, int lda, const void* B, int ldb, void* 
                           cudaStream_t st);
 
 #include <cuda_bf16.h>
+#include "pn_dropout.cuh"
 // optional epilogue extras of the tcgen05 GEMM (all nullable)
 struct PnGemmExtra {
   const float* row_scale;     // acc *= row_scale[row]
@@ -26,6 +27,11 @@ struct PnGemmExtra {
   const __nv_bfloat16* relu_mask;   // bf16 mode: out = relu_mask[row, col] > 0 ? acc : 0 (ReLU backward), [M, ld_mask]
   int ld_mask;
   int group_rows, group_b_rows;     // block-diagonal B: A rows [g*group_rows, ..) use the B rows from g*group_b_rows
+  // training-mode dropout on the produced values (thresh 0 = off): element (row, col) has index row * N + col.
+  //   bf16 mode: out = dropout(relu?(acc * scales))           (FFN hidden, HF:103)
+  //   residual mode: out += dropout(acc * scales)              (sub-layer output before the residual add)
+  PnDrop drop;
+  float out_scale;                  // extra scalar factor on acc (0 = 1): 1/(1-p) of a dropped ReLU-backward mask
 };
 int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
                     int mode, int relu, const PnGemmExtra* ex, int cta_group, cudaStream_t st);
@@ -48,6 +54,11 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
 int pn_t5_self_attn(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
                     int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
                     cudaStream_t st);
+// training forward: dropout of the attention probabilities (HF:331), masks indexed [doc, head, i, j] with an even
+// row pitch; the logsumexp it emits is that of the un-dropped softmax
+int pn_t5_self_attn_drop(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
+                         int S, int n_heads, const float* bias, __nv_bfloat16* out, int ld_out, float* lse_out,
+                         PnDrop drop, cudaStream_t st);
 // Same with a key-padding mask: keys at positions >= klen[doc] (nullable, [docs]) are excluded from every row's
 // softmax — HF's attention_mask for right-padded prompts (the re-rank path, eval.py:14,23 / distill/wrapper.py:36).
 int pn_t5_self_attn_masked(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k_col, int v_col, int docs,
@@ -60,14 +71,15 @@ int pn_t5_self_attn_masked(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int 
 int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, int v_col, int docs, int S,
                         int n_heads, const float* bias, const __nv_bfloat16* ctx, const __nv_bfloat16* dctx,
                         int ld_ctx, const float* lse2, float* dvec, const float* row_scale,
-                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st);
+                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st, PnDrop drop = PnDrop());
 int pn_t5_rel_bias_grad(const float* dbias_diag, const int* bucket_of, int n_heads, int buckets, float* grad,
                         cudaStream_t st);
 // decoder self / cross attention for T <= 2 query tokens per document
 int pn_t5_dec_attn(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_bfloat16* k,
                    const __nv_bfloat16* v, int ld_kv, int k_col, int v_col, int docs, int T, int Sk,
                    int n_heads, int causal, const float* bias, __nv_bfloat16* out, int ld_out,
-                   cudaStream_t st, const int32_t* klen = nullptr);   // klen [docs]: keys >= klen[doc] are padding
+                   cudaStream_t st, const int32_t* klen = nullptr,   // klen [docs]: keys >= klen[doc] are padding
+                   PnDrop drop = PnDrop());                        // dropout of the probabilities (training)
 
 // Backward of pn_t5_dec_attn (pn_t5_dec_attn_bwd.cu).  dq rows are scaled by rs_q, dk / dv rows by rs_kv (both
 // nullable); grad_rel (nullable) accumulates the decoder relative_attention_bias gradient [buckets, H].
@@ -76,4 +88,4 @@ int pn_t5_dec_attn_bwd(const __nv_bfloat16* q, int ld_q, int q_col, const __nv_b
                        int ld_do, int docs, int T, int Sk, int n_heads, int causal, const float* bias,
                        const float* rs_q, const float* rs_kv, __nv_bfloat16* dq, int ld_dq, int dq_col,
                        __nv_bfloat16* dkv, int ld_dkv, int dk_col, int dv_col, float* grad_rel,
-                       cudaStream_t st);
+                       cudaStream_t st, PnDrop drop = PnDrop());

@@ -71,7 +71,12 @@ struct PnT5 {
   // the work enqueued so far has run (data-parallel callers start that range's all-reduce on a side stream)
   void (*grad_hook)(void* user, int64_t offset, int64_t numel) = nullptr;
   void* grad_hook_user = nullptr;
-  std::map<const void*, std::array<int64_t, 3>> fwd_ws;   // training workspaces holding a forward pass: docs, S, T
+  // training workspaces holding a forward pass: docs, S, T, dropout seed, dropout p (float bits), doc offset
+  std::map<const void*, std::array<int64_t, 6>> fwd_ws;
+  // dropout of the NEXT training forward (pn_t5_set_dropout); 0 = eval-mode arithmetic
+  float drop_p = 0.0f;
+  uint64_t drop_seed = 0;
+  int64_t drop_doc_offset = 0;
   bool finalized = false;
   bool xattn = true;                 // projection-free cross-attention where the shapes allow ("xattn" option)
   bool want_train = false;           // also keep packedT / embT (pn_t5_set_option "train")
@@ -92,18 +97,19 @@ static inline int pn_dev_alloc(PnT5* m, T** p, size_t n) {
 
 // pn_t5_ops.cu
 int pn_t5_embed(const int32_t* ids, const float* table, int64_t rows, int d, int vocab, float* hidden,
-                __nv_bfloat16* copy, float* sumsq, cudaStream_t st);
+                __nv_bfloat16* copy, float* sumsq, cudaStream_t st, PnDrop drop = PnDrop());
+int pn_t5_mask_copy(const __nv_bfloat16* src, __nv_bfloat16* dst, int64_t n, PnDrop drop, cudaStream_t st);
 int pn_t5_pack_weight(const float* master, const float* colscale, int64_t rows, int cols,
                       __nv_bfloat16* packed, __nv_bfloat16* packedT, int ldT, cudaStream_t st);
 int pn_t5_rmsnorm(const float* x, const float* w, int64_t rows, int d, float eps, __nv_bfloat16* out,
                   cudaStream_t st);
 int pn_t5_f32_to_bf16(const float* src, __nv_bfloat16* dst, int64_t n, cudaStream_t st);
 int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, int d, float eps,
-                int rel_id, int nrel_id, float* score, float* z2, cudaStream_t st);
+                int rel_id, int nrel_id, float* score, float* z2, cudaStream_t st, PnDrop drop = PnDrop());
 int pn_t5_head2_bwd(const float* x, const float* w, const float* emb, const float* dz2, int64_t rows, int d, float eps,
-                    int rel_id, int nrel_id, float* dhead_in, float* grad_emb, cudaStream_t st);
+                    int rel_id, int nrel_id, float* dhead_in, float* grad_emb, cudaStream_t st, PnDrop drop = PnDrop());
 int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float eps,
-                    __nv_bfloat16* out, cudaStream_t st);
+                    __nv_bfloat16* out, cudaStream_t st, PnDrop drop = PnDrop());
 
 // cross-attention without the K/V projection (pn_t5_ops.cu)
 int pn_t5_cross_expand_q(const __nv_bfloat16* q, int ld_q, int64_t docs, int T, int H, int Mp, __nv_bfloat16* qexp,
@@ -126,14 +132,19 @@ int pn_t5_rs(const float* ss, int parts, int64_t rows, int d, float eps, float* 
 int pn_t5_relu_mask_scale(__nv_bfloat16* y, const __nv_bfloat16* act, const float* rs, int64_t rows, int cols,
                           cudaStream_t st);
 int pn_t5_row_scale(__nv_bfloat16* y, int ld, const float* rs, int64_t rows, int cols, cudaStream_t st);
+// gdrop: mask applied to G as it is read (the sub-layer's input was dropped: encoder final norm); odrop: mask applied
+// to the bf16 copy dhb only (the NEXT consumer of dhb is the output projection of a sub-layer whose output was dropped)
 int pn_t5_norm_bwd(const void* G, int g_bf16, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d,
-                   int accumulate, float* dh, __nv_bfloat16* dhb, cudaStream_t st);
+                   int accumulate, float* dh, __nv_bfloat16* dhb, cudaStream_t st, PnDrop gdrop = PnDrop(),
+                   PnDrop odrop = PnDrop());
 int pn_t5_unfold(const float* dWp, const float* W, const float* g, int64_t rows, int cols, float* gradW,
                  float* gradg, cudaStream_t st);
 int pn_t5_embed_bwd(const int32_t* ids, const float* dh, int64_t rows, int d, int vocab, float* grad_table,
-                    cudaStream_t st);
+                    cudaStream_t st, PnDrop drop = PnDrop());
+// ydrop: the norm's output was dropped (dy is masked on load); odrop: mask on the bf16 copy dxb only (see norm_bwd)
 int pn_t5_final_norm_bwd(const float* dy, const float* x, const float* w, int64_t rows, int d, float eps,
-                         float* dx, __nv_bfloat16* dxb, float* dw, cudaStream_t st);
+                         float* dx, __nv_bfloat16* dxb, float* dw, cudaStream_t st, PnDrop ydrop = PnDrop(),
+                         PnDrop odrop = PnDrop());
 int pn_t5_sgd(float* p, const float* g, int64_t n, float lr, cudaStream_t st);
 int pn_t5_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                 float wd, int64_t step, float gscale, cudaStream_t st);

@@ -12,7 +12,7 @@ constexpr int kThreads = 256;
 __global__ void __launch_bounds__(kThreads)
 embed_kernel(const int32_t* __restrict__ ids, const float* __restrict__ table, int64_t rows, int d,
              int vocab, float* __restrict__ hidden, __nv_bfloat16* __restrict__ copy,
-             float* __restrict__ sumsq) {
+             float* __restrict__ sumsq, const PnDrop drop) {
   const int lane = threadIdx.x & 31;
   const int64_t w = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
@@ -23,7 +23,14 @@ embed_kernel(const int32_t* __restrict__ ids, const float* __restrict__ table, i
     float4* dst = reinterpret_cast<float4*>(hidden + (size_t)r * d);
     float ss = 0.0f;
     for (int i = lane; i < d / 4; i += 32) {
-      const float4 v = src[i];
+      float4 v = src[i];
+      if (drop.thresh) {   // dropout of the embedding output (T5Stack: self.dropout(inputs_embeds))
+        const unsigned long long e0 = (unsigned long long)drop.idx_offset + (unsigned long long)r * d + 4 * i;
+        float m0, m1, m2, m3;
+        pn_drop_mul2(drop, e0, m0, m1);
+        pn_drop_mul2(drop, e0 + 2, m2, m3);
+        v.x *= m0; v.y *= m1; v.z *= m2; v.w *= m3;
+      }
       dst[i] = v;
       ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
       if (copy) {
@@ -125,7 +132,7 @@ f32_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ ds
 __global__ void __launch_bounds__(kThreads)
 head2_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ emb,
              int64_t rows, int d, float eps, int rel_id, int nrel_id, float* __restrict__ score,
-             float* __restrict__ z2) {
+             float* __restrict__ z2, const PnDrop drop) {
   const int lane = threadIdx.x & 31;
   const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   if (r >= rows) return;
@@ -136,7 +143,7 @@ head2_kernel(const float* __restrict__ x, const float* __restrict__ w, const flo
   for (int i = lane; i < d; i += 32) {
     const float v = xr[i];
     ss += v * v;
-    const float y = v * w[i];
+    const float y = v * w[i] * pn_drop_mul(drop, (unsigned long long)drop.idx_offset + (unsigned long long)r * d + i);
     zt += y * et[i];
     zf += y * ef[i];
   }
@@ -159,7 +166,7 @@ head2_kernel(const float* __restrict__ x, const float* __restrict__ w, const flo
 __global__ void __launch_bounds__(kThreads)
 head2_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ emb,
                  const float* __restrict__ dz2, int64_t rows, int d, float eps, int rel_id, int nrel_id,
-                 float* __restrict__ dhead_in, float* __restrict__ grad_emb) {
+                 float* __restrict__ dhead_in, float* __restrict__ grad_emb, const PnDrop drop) {
   const int lane = threadIdx.x & 31;
   const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   if (r >= rows) return;
@@ -173,7 +180,7 @@ head2_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const
   const float g0 = dz2[2 * r], g1 = dz2[2 * r + 1];
   for (int i = lane; i < d; i += 32) {
     dhead_in[(size_t)r * d + i] = g0 * et[i] + g1 * ef[i];
-    const float hi = xr[i] * w[i] * k;
+    const float hi = xr[i] * w[i] * k * pn_drop_mul(drop, (unsigned long long)drop.idx_offset + (unsigned long long)r * d + i);
     atomicAdd(grad_emb + (size_t)rel_id * d + i, g0 * hi);
     atomicAdd(grad_emb + (size_t)nrel_id * d + i, g1 * hi);
   }
@@ -182,7 +189,7 @@ head2_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const
 // bf16 y = rmsnorm(x) * w * d^-0.5 for the full-vocabulary head GEMM
 __global__ void __launch_bounds__(kThreads)
 head_prep_kernel(const float* __restrict__ x, const float* __restrict__ w, int64_t rows, int d,
-                 float eps, __nv_bfloat16* __restrict__ out) {
+                 float eps, __nv_bfloat16* __restrict__ out, const PnDrop drop) {
   const int lane = threadIdx.x & 31;
   const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   if (r >= rows) return;
@@ -191,18 +198,32 @@ head_prep_kernel(const float* __restrict__ x, const float* __restrict__ w, int64
   for (int i = lane; i < d; i += 32) ss += xr[i] * xr[i];
   ss = pn_warp_sum(ss);
   const float k = rsqrtf(ss / (float)d + eps) * rsqrtf((float)d);
-  for (int i = lane; i < d; i += 32) out[(size_t)r * d + i] = __float2bfloat16_rn(xr[i] * w[i] * k);
+  for (int i = lane; i < d; i += 32)   // dropout of the final decoder norm's output (T5Stack: dropout(final_layer_norm))
+    out[(size_t)r * d + i] = __float2bfloat16_rn(
+        xr[i] * w[i] * k * pn_drop_mul(drop, (unsigned long long)drop.idx_offset + (unsigned long long)r * d + i));
+}
+
+// dst = bf16(src (.) mask): the dropped copy of the encoder output the cross K/V projections read.  The fused norm
+// scales rows in the GEMM epilogue and dropout is elementwise, so dropout(rs h g) W^T = rs ((h (.) M) (g W)^T).
+__global__ void __launch_bounds__(kThreads)
+mask_copy_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n, const PnDrop drop) {
+  for (int64_t i = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 2; i < n; i += (int64_t)gridDim.x * kThreads * 2) {
+    float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(src + i));
+    float m0, m1;
+    pn_drop_mul2(drop, (unsigned long long)drop.idx_offset + (unsigned long long)i, m0, m1);
+    *reinterpret_cast<__nv_bfloat162*>(dst + i) = __floats2bfloat162_rn(f.x * m0, f.y * m1);
+  }
 }
 
 // hidden[row, :] = table[ids[row], :] for the decoder inputs (ids int32 [rows])
 }  // namespace
 
 int pn_t5_embed(const int32_t* ids, const float* table, int64_t rows, int d, int vocab, float* hidden,
-                __nv_bfloat16* copy, float* sumsq, cudaStream_t st) {
+                __nv_bfloat16* copy, float* sumsq, cudaStream_t st, PnDrop drop) {
   if (rows == 0) return PN_OK;
   if (d % 4) return pn_fail(PN_E_UNSUPPORTED, "embed: d_model %% 4 != 0");
   embed_kernel<<<pn_grid(rows * 32, kThreads, 1, 8), kThreads, 0, st>>>(ids, table, rows, d, vocab,
-                                                                        hidden, copy, sumsq);
+                                                                        hidden, copy, sumsq, drop);
   PN_LAUNCHED();
   return PN_OK;
 }
@@ -240,28 +261,36 @@ int pn_t5_f32_to_bf16(const float* src, __nv_bfloat16* dst, int64_t n, cudaStrea
 }
 
 int pn_t5_head2(const float* x, const float* w, const float* emb, int64_t rows, int d, float eps,
-                int rel_id, int nrel_id, float* score, float* z2, cudaStream_t st) {
+                int rel_id, int nrel_id, float* score, float* z2, cudaStream_t st, PnDrop drop) {
   if (rows == 0) return PN_OK;
   head2_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(
-      x, w, emb, rows, d, eps, rel_id, nrel_id, score, z2);
+      x, w, emb, rows, d, eps, rel_id, nrel_id, score, z2, drop);
   PN_LAUNCHED();
   return PN_OK;
 }
 
 int pn_t5_head2_bwd(const float* x, const float* w, const float* emb, const float* dz2, int64_t rows, int d, float eps,
-                    int rel_id, int nrel_id, float* dhead_in, float* grad_emb, cudaStream_t st) {
+                    int rel_id, int nrel_id, float* dhead_in, float* grad_emb, cudaStream_t st, PnDrop drop) {
   if (rows == 0) return PN_OK;
   head2_bwd_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(
-      x, w, emb, dz2, rows, d, eps, rel_id, nrel_id, dhead_in, grad_emb);
+      x, w, emb, dz2, rows, d, eps, rel_id, nrel_id, dhead_in, grad_emb, drop);
   PN_LAUNCHED();
   return PN_OK;
 }
 
 int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float eps,
-                    __nv_bfloat16* out, cudaStream_t st) {
+                    __nv_bfloat16* out, cudaStream_t st, PnDrop drop) {
   if (rows == 0) return PN_OK;
   head_prep_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(
-      x, w, rows, d, eps, out);
+      x, w, rows, d, eps, out, drop);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+int pn_t5_mask_copy(const __nv_bfloat16* src, __nv_bfloat16* dst, int64_t n, PnDrop drop, cudaStream_t st) {
+  if (n == 0) return PN_OK;
+  if ((n & 1) || !drop.thresh) return pn_fail(PN_E_BADARG, "mask_copy: even element count and an enabled mask");
+  mask_copy_kernel<<<pn_grid(n / 2, kThreads, 4, 8), kThreads, 0, st>>>(src, dst, n, drop);
   PN_LAUNCHED();
   return PN_OK;
 }

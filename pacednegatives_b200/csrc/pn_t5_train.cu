@@ -53,10 +53,11 @@ struct TrainWs {
   std::vector<__nv_bfloat16*> qk, Pp, cpb;   // per decoder layer: QK [R, d], P*rs [rows, Mp], C' [R, d]
   float *scores, *cprime;                   // [rows, 128], [R, d]
   __nv_bfloat16 *qexp, *ctxfull, *dOfull, *dCp, *V2, *dQKb, *A_all, *B_all;
+  __nv_bfloat16* xdrop;   // dropped bf16 copy of the encoder output (dropout of the encoder's final norm), or null
   int64_t* header;   // reserved
 };
 
-size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, TrainWs* w) {
+size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, TrainWs* w, bool dropping) {
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
   const size_t L = m->enc.size(), Ld = m->dec.size();
   const size_t rows = (size_t)docs * S, drows = (size_t)docs * T;
@@ -76,7 +77,10 @@ size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, Tra
   for (auto& p : w->act) p = (__nv_bfloat16*)take(rows * ff * 2);
   for (auto& p : w->lse) p = (float*)take(rows * H * 4);
   w->Mp = (T * H + 7) & ~7;
-  w->xattn = m->xattn && (S % 128) == 0 && w->Mp <= 32;
+  // dropout of the cross-attention probabilities needs them as [T, S] rows per head: the projection-free form is
+  // the eval / p = 0 path
+  w->xattn = m->xattn && (S % 128) == 0 && w->Mp <= 32 && !dropping;
+  w->xdrop = dropping ? (__nv_bfloat16*)take(rows * d * 2) : nullptr;
   const size_t Mp = (size_t)w->Mp, R = (size_t)docs * Mp;
   if (!w->xattn) {
     for (auto& p : w->ckv) p = (__nv_bfloat16*)take(rows * 2 * di * 2);
@@ -140,16 +144,17 @@ __global__ void shift_right_train_kernel(const int64_t* labels, int64_t docs, in
 
 // y = rs (.) (hb W'^T), bf16 out
 int lin_fwd(const PnT5* m, const __nv_bfloat16* hb, const float* rs, const PnLin& W, __nv_bfloat16* out, int M,
-            int relu, cudaStream_t st) {
+            int relu, cudaStream_t st, PnDrop drop = PnDrop()) {
   PnGemmExtra ex = {};
-  ex.row_scale = rs;
+  ex.row_scale = rs; ex.drop = drop;
   return pn_gemm_bf16_ex(hb, W.cols, W.packed, W.cols, out, (int)W.rows, M, (int)W.rows, W.cols, PN_EPI_BF16, relu,
                          &ex, m->cta_group, st);
 }
 // h += x W^T; hb_next = bf16(h); rs_next from the epilogue's row sums of squares
 int lin_resid(const PnT5* m, const __nv_bfloat16* x, const PnLin& W, float* h, __nv_bfloat16* hb_next, float* ss,
-              float* rs_next, int M, cudaStream_t st) {
+              float* rs_next, int M, cudaStream_t st, PnDrop drop = PnDrop()) {
   PnGemmExtra ex = {};
+  ex.drop = drop;
   ex.copy_out = hb_next; ex.ld_copy = (int)W.rows; ex.sumsq_out = ss;
   RC(pn_gemm_bf16_ex(x, W.cols, W.packed, W.cols, h, (int)W.rows, M, (int)W.rows, W.cols, PN_EPI_RESID_F32, 0, &ex,
                      m->cta_group, st));
@@ -164,10 +169,11 @@ int dgrad(const PnT5* m, const __nv_bfloat16* dY, int ld_dy, const PnLin& W, voi
 }
 // data gradient through Wo of the FFN with the ReLU backward and the fused-norm row scale in the epilogue:
 // Ys = rs (.) (dY Wo (.) [act > 0])
+// (with dropout of the hidden activation the saved act is m s relu(u): [act > 0] = m [u > 0], times the scale s)
 int dgrad_relu(const PnT5* m, const __nv_bfloat16* dY, const PnLin& W, const __nv_bfloat16* act, const float* rs,
-               __nv_bfloat16* out, int M, cudaStream_t st) {
+               __nv_bfloat16* out, int M, cudaStream_t st, float act_scale = 1.0f) {
   PnGemmExtra ex = {};
-  ex.row_scale = rs; ex.relu_mask = act; ex.ld_mask = W.cols;
+  ex.row_scale = rs; ex.relu_mask = act; ex.ld_mask = W.cols; ex.out_scale = act_scale;
   return pn_gemm_bf16_ex(dY, (int)W.rows, W.packedT, (int)W.rows, out, W.cols, M, W.cols, (int)W.rows, PN_EPI_BF16, 0,
                          &ex, m->cta_group, st);
 }
@@ -189,7 +195,7 @@ int wgrad_folded(const PnT5* m, const __nv_bfloat16* Ys, int ld_ys, const __nv_b
 extern "C" int64_t pn_t5_train_workspace_bytes(const PnT5* m, int64_t docs, int32_t S, int32_t T) {
   if (!m || docs < 0 || S < 1 || T < 1) return -1;
   TrainWs w;
-  return (int64_t)carve_train(m, docs, S, T, nullptr, &w);
+  return (int64_t)carve_train(m, docs, S, T, nullptr, &w, m->drop_p > 0.0f);
 }
 
 extern "C" int pn_t5_set_train_buffers(PnT5* m, float* grads, float* adam_m, float* adam_v) {
@@ -211,39 +217,67 @@ static int train_forward_impl(PnT5* m, const int32_t* ids, const int64_t* labels
   PN_CHECK_ARG(ids && labels && (logits_out || z2_out) && workspace);
   PN_CHECK_ARG(docs * (int64_t)S < (1ll << 31));
   if (z2_out) PN_CHECK_ARG(rel_id >= 0 && rel_id < m->cfg.vocab && nrel_id >= 0 && nrel_id < m->cfg.vocab);
+  const float dp = m->drop_p;
+  const uint64_t dseed = m->drop_seed;
+  const long long doff = m->drop_doc_offset;
   TrainWs w;
-  const size_t need = carve_train(m, docs, S, T, (uint8_t*)workspace, &w);
+  const size_t need = carve_train(m, docs, S, T, (uint8_t*)workspace, &w, dp > 0.0f);
   if ((int64_t)need > workspace_bytes)
     return pn_fail(PN_E_BADARG, "pn_t5_train_forward: workspace %lld < %zu bytes", (long long)workspace_bytes, need);
   cudaStream_t st = (cudaStream_t)stream;
   const int d = m->cfg.d_model, di = m->d_inner, H = m->cfg.n_heads;
   const int rows = (int)(docs * S), drows = (int)(docs * T);
   const size_t L = m->enc.size(), Ld = m->dec.size();
-  m->fwd_ws[workspace] = {docs, (int64_t)S, (int64_t)T};   // host-side record: backward checks it without a sync
+  int32_t dp_bits;
+  memcpy(&dp_bits, &dp, 4);
+  // host-side record: backward checks it without a sync and regenerates the same dropout masks
+  m->fwd_ws[workspace] = {docs, (int64_t)S, (int64_t)T, (int64_t)dseed, (int64_t)dp_bits, (int64_t)doff};
+  const int ff = m->cfg.d_ff;
+  const long long Sp = S + (S & 1), Tp = T + (T & 1);
+  // mask of dropout call (stack, layer, kind) over `per_doc` elements per document (pn_dropout.cuh)
+  auto D = [&](int stack, int layer, int kind, long long per_doc) {
+    return dp > 0.0f ? pn_drop_make(dseed, pn_drop_site(stack, layer, kind), dp, doff, per_doc) : PnDrop();
+  };
+  auto DR = D;   // the decoder loops name their layer `D`
 
   // ---- encoder
-  RC(pn_t5_embed(ids, m->emb, rows, d, m->cfg.vocab, w.hidden, w.hb[0], w.ss, st));
+  RC(pn_t5_embed(ids, m->emb, rows, d, m->cfg.vocab, w.hidden, w.hb[0], w.ss, st, D(0, 0, PN_DROP_EMBED, (long long)S * d)));
   RC(pn_t5_rs(w.ss, 1, rows, d, m->cfg.eps, w.rs[0], st));
   for (size_t l = 0; l < L; ++l) {
     const PnEncLayer& E = m->enc[l];
+    const int li = (int)l;
     RC(lin_fwd(m, w.hb[2 * l], w.rs[2 * l], E.wqkv, w.qkv[l], rows, 0, st));
-    RC(pn_t5_self_attn(w.qkv[l], 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx[l], di, w.lse[l], st));
-    RC(lin_resid(m, w.ctx[l], E.wo, w.hidden, w.hb[2 * l + 1], w.ss, w.rs[2 * l + 1], rows, st));
-    RC(lin_fwd(m, w.hb[2 * l + 1], w.rs[2 * l + 1], E.wi, w.act[l], rows, 1, st));
-    RC(lin_resid(m, w.act[l], E.wo2, w.hidden, w.hb[2 * l + 2], w.ss, w.rs[2 * l + 2], rows, st));
+    RC(pn_t5_self_attn_drop(w.qkv[l], 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx[l], di, w.lse[l],
+                            D(0, li, PN_DROP_SELF_P, (long long)H * S * Sp), st));
+    RC(lin_resid(m, w.ctx[l], E.wo, w.hidden, w.hb[2 * l + 1], w.ss, w.rs[2 * l + 1], rows, st,
+                 D(0, li, PN_DROP_SELF_OUT, (long long)S * d)));
+    RC(lin_fwd(m, w.hb[2 * l + 1], w.rs[2 * l + 1], E.wi, w.act[l], rows, 1, st,
+               D(0, li, PN_DROP_FF_HID, (long long)S * ff)));
+    RC(lin_resid(m, w.act[l], E.wo2, w.hidden, w.hb[2 * l + 2], w.ss, w.rs[2 * l + 2], rows, st,
+                 D(0, li, PN_DROP_FF_OUT, (long long)S * d)));
+  }
+  // dropout of the encoder's final norm: a dropped copy of the bf16 encoder output is what the cross K/V projections
+  // read (the norm's row scale and weight stay in the GEMM, see mask_copy_kernel)
+  const __nv_bfloat16* xsrc = w.hb[2 * L];
+  if (dp > 0.0f) {
+    RC(pn_t5_mask_copy(w.hb[2 * L], w.xdrop, (int64_t)rows * d, D(0, 0, PN_DROP_FINAL, (long long)S * d), st));
+    xsrc = w.xdrop;
   }
   // ---- decoder over shift_right(labels)
   shift_right_train_kernel<<<pn_grid(docs * T, 256, 1, 4), 256, 0, st>>>(labels, docs, T, m->cfg.pad_id,
                                                                         m->cfg.pad_id, w.dec_ids);
   PN_LAUNCHED();
-  RC(pn_t5_embed(w.dec_ids, m->emb, drows, d, m->cfg.vocab, w.dec_hidden, w.dhb[0], w.dss, st));
+  RC(pn_t5_embed(w.dec_ids, m->emb, drows, d, m->cfg.vocab, w.dec_hidden, w.dhb[0], w.dss, st,
+                 D(1, 0, PN_DROP_EMBED, (long long)T * d)));
   RC(pn_t5_rs(w.dss, 1, drows, d, m->cfg.eps, w.drs[0], st));
   for (size_t l = 0; l < Ld; ++l) {
     const PnDecLayer& D = m->dec[l];
+    const int li = (int)l;
     RC(lin_fwd(m, w.dhb[3 * l], w.drs[3 * l], D.wqkv, w.dqkv[l], drows, 0, st));
     RC(pn_t5_dec_attn(w.dqkv[l], 3 * di, 0, w.dqkv[l], w.dqkv[l], 3 * di, di, 2 * di, (int)docs, T, T, H, 1,
-                      m->dec_bias, w.dctx_s[l], di, st));
-    RC(lin_resid(m, w.dctx_s[l], D.wo, w.dec_hidden, w.dhb[3 * l + 1], w.dss, w.drs[3 * l + 1], drows, st));
+                      m->dec_bias, w.dctx_s[l], di, st, nullptr, DR(1, li, PN_DROP_SELF_P, (long long)H * T * Tp)));
+    RC(lin_resid(m, w.dctx_s[l], D.wo, w.dec_hidden, w.dhb[3 * l + 1], w.dss, w.drs[3 * l + 1], drows, st,
+                 DR(1, li, PN_DROP_SELF_OUT, (long long)T * d)));
     RC(lin_fwd(m, w.dhb[3 * l + 1], w.drs[3 * l + 1], D.cq, w.cq[l], drows, 0, st));
     if (w.xattn) {
       // scores = X (Wk^T q), out = Wv (P^T X): no K/V projection of the encoder rows (pn_t5_ops.cu)
@@ -263,20 +297,25 @@ static int train_forward_impl(PnT5* m, const int32_t* ids, const int64_t* labels
                                nullptr, m->cta_group, st));
       RC(pn_t5_cross_gather(w.ctxfull, Mp, docs, T, H, w.dctx_c[l], di, st));
     } else {
-      RC(lin_fwd(m, w.hb[2 * L], w.rs[2 * L], D.ckv, w.ckv[l], rows, 0, st));
+      RC(lin_fwd(m, xsrc, w.rs[2 * L], D.ckv, w.ckv[l], rows, 0, st));
       RC(pn_t5_dec_attn(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, (int)docs, T, S, H, 0, nullptr,
-                        w.dctx_c[l], di, st));
+                        w.dctx_c[l], di, st, nullptr, DR(1, li, PN_DROP_CROSS_P, (long long)H * T * Sp)));
     }
-    RC(lin_resid(m, w.dctx_c[l], D.co, w.dec_hidden, w.dhb[3 * l + 2], w.dss, w.drs[3 * l + 2], drows, st));
-    RC(lin_fwd(m, w.dhb[3 * l + 2], w.drs[3 * l + 2], D.wi, w.dact[l], drows, 1, st));
-    RC(lin_resid(m, w.dact[l], D.wo2, w.dec_hidden, w.dhb[3 * l + 3], w.dss, w.drs[3 * l + 3], drows, st));
+    RC(lin_resid(m, w.dctx_c[l], D.co, w.dec_hidden, w.dhb[3 * l + 2], w.dss, w.drs[3 * l + 2], drows, st,
+                 DR(1, li, PN_DROP_CROSS_OUT, (long long)T * d)));
+    RC(lin_fwd(m, w.dhb[3 * l + 2], w.drs[3 * l + 2], D.wi, w.dact[l], drows, 1, st,
+               DR(1, li, PN_DROP_FF_HID, (long long)T * ff)));
+    RC(lin_resid(m, w.dact[l], D.wo2, w.dec_hidden, w.dhb[3 * l + 3], w.dss, w.drs[3 * l + 3], drows, st,
+                 DR(1, li, PN_DROP_FF_OUT, (long long)T * d)));
   }
   // ---- tied head: logits = (RMSNorm(h) * d^-0.5) E^T  (HF:1107-1110); restricted mode: only the two rows of E
   // the re-rank score reads (distill/wrapper.py:34-38), in fp32
   if (z2_out)
-    RC(pn_t5_head2(w.dec_hidden, m->dec_final, m->emb, drows, d, m->cfg.eps, rel_id, nrel_id, nullptr, z2_out, st));
+    RC(pn_t5_head2(w.dec_hidden, m->dec_final, m->emb, drows, d, m->cfg.eps, rel_id, nrel_id, nullptr, z2_out, st,
+                   DR(1, 0, PN_DROP_FINAL, (long long)T * d)));
   if (logits_out) {
-    RC(pn_t5_head_prep(w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.head_in, st));
+    RC(pn_t5_head_prep(w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.head_in, st,
+                       DR(1, 0, PN_DROP_FINAL, (long long)T * d)));
     RC(pn_gemm_bf16_internal(w.head_in, d, m->emb_bf16, d, logits_out, m->vocab_pad, drows, m->vocab_pad, d,
                              PN_EPI_F32, 0, nullptr, m->cta_group, st));
   }
@@ -296,6 +335,17 @@ extern "C" int pn_t5_train_forward_z2(PnT5* m, const int32_t* ids, const int64_t
   PN_CHECK_ARG(z2_out);
   return train_forward_impl(m, ids, labels, docs, S, T, nullptr, z2_out, rel_id, nrel_id, workspace, workspace_bytes,
                             stream);
+}
+
+// Dropout of the NEXT pn_t5_train_forward (and of the backward that consumes its workspace): p = the checkpoint's
+// dropout_rate (HF T5 in train mode, as Lightning runs LCEModel), seed names the forward call, doc_offset = index of
+// this call's first document inside the whole step's batch (masks are a function of the global document index)
+extern "C" int pn_t5_set_dropout(PnT5* m, float p, uint64_t seed, int64_t doc_offset) {
+  PN_CHECK_ARG(m && p >= 0.0f && p < 1.0f && doc_offset >= 0);
+  m->drop_p = p;
+  m->drop_seed = seed;
+  m->drop_doc_offset = doc_offset;
+  return PN_OK;
 }
 
 extern "C" int pn_t5_set_grad_hook(PnT5* m, void (*fn)(void*, int64_t, int64_t), void* user) {
@@ -327,17 +377,30 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
   if (dz2) PN_CHECK_ARG(rel_id >= 0 && rel_id < m->cfg.vocab && nrel_id >= 0 && nrel_id < m->cfg.vocab);
   if (m->cfg.vocab % 8)
     return pn_fail(PN_E_UNSUPPORTED, "pn_t5_train_backward: vocab=%d must be a multiple of 8", m->cfg.vocab);
-  TrainWs w;
-  const size_t need = carve_train(m, docs, S, T, (uint8_t*)workspace, &w);
-  if ((int64_t)need > workspace_bytes)
-    return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace %lld < %zu bytes", (long long)workspace_bytes, need);
   cudaStream_t st = (cudaStream_t)stream;
+  // the forward this workspace holds: its shape and the dropout (seed, p, document offset) it ran with
+  uint64_t dseed = 0;
+  float dp = 0.0f;
+  long long doff = 0;
   {
     auto it = m->fwd_ws.find(workspace);
     if (it == m->fwd_ws.end() || it->second[0] != docs || it->second[1] != S || it->second[2] != T)
       return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace does not hold a forward pass of this shape");
+    dseed = (uint64_t)it->second[3];
+    const int32_t bits = (int32_t)it->second[4];
+    memcpy(&dp, &bits, 4);
+    doff = it->second[5];
     m->fwd_ws.erase(it);
   }
+  TrainWs w;
+  const size_t need = carve_train(m, docs, S, T, (uint8_t*)workspace, &w, dp > 0.0f);
+  if ((int64_t)need > workspace_bytes)
+    return pn_fail(PN_E_BADARG, "pn_t5_train_backward: workspace %lld < %zu bytes", (long long)workspace_bytes, need);
+  const long long Sp = S + (S & 1), Tp = T + (T & 1);
+  auto DR = [&](int stack, int layer, int kind, long long per_doc) {
+    return dp > 0.0f ? pn_drop_make(dseed, pn_drop_site(stack, layer, kind), dp, doff, per_doc) : PnDrop();
+  };
+  const float act_scale = dp > 0.0f ? 1.0f / (1.0f - dp) : 1.0f;
   const int d = m->cfg.d_model, di = m->d_inner, ff = m->cfg.d_ff, H = m->cfg.n_heads;
   const int rows = (int)(docs * S), drows = (int)(docs * T);
   const int L = (int)m->enc.size(), Ld = (int)m->dec.size();
@@ -349,15 +412,18 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
   if (dz2) {
     // restricted head: z[r, c] = head_in[r, :] . E[id_c, :]  ->  d head_in = dz E[(rel, nrel)], dE[id_c] += dz^T head_in
     RC(pn_t5_head2_bwd(w.dec_hidden, m->dec_final, m->emb, dz2, drows, d, m->cfg.eps, rel_id, nrel_id, w.dgbuf,
-                       G + m->emb_off, st));
+                       G + m->emb_off, st, DR(1, 0, PN_DROP_FINAL, (long long)T * d)));
   } else {
     RC(pn_t5_f32_to_bf16(dlogits, w.dlb, (int64_t)drows * Vp, st));
     RC(pn_gemm_wgrad(w.dlb, Vp, w.head_in, d, G + m->emb_off, d, m->cfg.vocab, d, drows, m->cta_group, st));
     RC(pn_gemm_bf16_internal(w.dlb, Vp, m->embT_bf16, Vp, w.dgbuf, d, drows, d, Vp, PN_EPI_F32, 0, nullptr,
                              m->cta_group, st));
   }
+  // every bf16 copy of the residual-stream gradient is written for ONE consumer — the output projection of the next
+  // sub-layer down — whose forward output was dropped: the copy carries that sub-layer's mask (`odrop`)
   RC(pn_t5_final_norm_bwd(w.dgbuf, w.dec_hidden, m->dec_final, drows, d, m->cfg.eps, w.ddH, w.ddHb,
-                          G + m->dec_final_off, st));
+                          G + m->dec_final_off, st, DR(1, 0, PN_DROP_FINAL, (long long)T * d),
+                          DR(1, Ld - 1, PN_DROP_FF_OUT, (long long)T * d)));
 
   // ---- decoder layers, last to first.  ddH / ddHb = gradient of the decoder residual stream
   for (int l = Ld - 1; l >= 0; --l) {
@@ -366,10 +432,11 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
     const float *rs0 = w.drs[3 * l], *rs1 = w.drs[3 * l + 1], *rs2 = w.drs[3 * l + 2];
     // FFN: h3 = h2 + relu(norm(h2) Wi^T) Wo^T
     RC(wgrad_plain(m, w.ddHb, d, w.dact[l], D.wo2, drows, st));
-    RC(dgrad_relu(m, w.ddHb, D.wo2, w.dact[l], rs2, w.ddbig, drows, st));
+    RC(dgrad_relu(m, w.ddHb, D.wo2, w.dact[l], rs2, w.ddbig, drows, st, act_scale));
     RC(wgrad_folded(m, w.ddbig, ff, hb2, D.wi, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, ff, D.wi, w.dgbuf, PN_EPI_F32, drows, st));
-    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb2, rs2, drows, d, 1, w.ddH, w.ddHb, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb2, rs2, drows, d, 1, w.ddH, w.ddHb, st, PnDrop(),
+                      DR(1, l, PN_DROP_CROSS_OUT, (long long)T * d)));
     // cross-attention: h2 = h1 + attn(norm(h1) Cq^T, norm_f(enc) Ckv^T) Co^T
     RC(wgrad_plain(m, w.ddHb, d, w.dctx_c[l], D.co, drows, st));
     RC(dgrad(m, w.ddHb, d, D.co, w.ddctx, PN_EPI_BF16, drows, st));
@@ -405,29 +472,33 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
       RC(pn_t5_row_scale(w.ddbig, di, rs1, drows, di, st));
     } else {
       RC(pn_t5_dec_attn_bwd(w.cq[l], di, 0, w.ckv[l], w.ckv[l], 2 * di, 0, di, w.ddctx, di, (int)docs, T, S, H, 0,
-                            nullptr, rs1, w.rs[2 * L], w.ddbig, di, 0, w.dbig, 2 * di, 0, di, nullptr, st));
-      RC(wgrad_folded(m, w.dbig, 2 * di, w.hb[2 * L], D.ckv, w.dWtmp, rows, st));
+                            nullptr, rs1, w.rs[2 * L], w.ddbig, di, 0, w.dbig, 2 * di, 0, di, nullptr, st,
+                            DR(1, l, PN_DROP_CROSS_P, (long long)H * T * Sp)));
+      RC(wgrad_folded(m, w.dbig, 2 * di, w.xdrop ? w.xdrop : w.hb[2 * L], D.ckv, w.dWtmp, rows, st));
       // every decoder layer reads the same normalised encoder output: their data gradients add up in `hidden`
       RC(dgrad(m, w.dbig, 2 * di, D.ckv, w.hidden, l == Ld - 1 ? PN_EPI_F32 : PN_EPI_RESID_F32, rows, st));
     }
     RC(wgrad_folded(m, w.ddbig, di, hb1, D.cq, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, di, D.cq, w.dgbuf, PN_EPI_F32, drows, st));
-    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb1, rs1, drows, d, 1, w.ddH, w.ddHb, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb1, rs1, drows, d, 1, w.ddH, w.ddHb, st, PnDrop(),
+                      DR(1, l, PN_DROP_SELF_OUT, (long long)T * d)));
     // self-attention: h1 = h0 + attn(norm(h0) Wqkv^T) Wo^T
     RC(wgrad_plain(m, w.ddHb, d, w.dctx_s[l], D.wo, drows, st));
     RC(dgrad(m, w.ddHb, d, D.wo, w.ddctx, PN_EPI_BF16, drows, st));
     RC(pn_t5_dec_attn_bwd(w.dqkv[l], 3 * di, 0, w.dqkv[l], w.dqkv[l], 3 * di, di, 2 * di, w.ddctx, di, (int)docs, T,
                           T, H, 1, m->dec_bias, rs0, rs0, w.ddbig, 3 * di, 0, w.ddbig, 3 * di, di, 2 * di,
-                          G + m->dec_rel_off, st));
+                          G + m->dec_rel_off, st, DR(1, l, PN_DROP_SELF_P, (long long)H * T * Tp)));
     RC(wgrad_folded(m, w.ddbig, 3 * di, hb0, D.wqkv, w.dWtmp, drows, st));
     RC(dgrad(m, w.ddbig, 3 * di, D.wqkv, w.dgbuf, PN_EPI_F32, drows, st));
-    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st));
+    RC(pn_t5_norm_bwd(w.dgbuf, 0, hb0, rs0, drows, d, 1, w.ddH, w.ddHb, st, PnDrop(),
+                      l > 0 ? DR(1, l - 1, PN_DROP_FF_OUT, (long long)T * d) : PnDrop()));
     if (m->grad_hook && Ld >= 2 && l == Ld / 2) {   // decoder layers [Ld/2, Ld) and the final decoder norm are done
       const int64_t dmid = first_offset(m, "decoder.block." + std::to_string(l) + ".");
       m->grad_hook(m->grad_hook_user, dmid, m->n_params - dmid);
     }
   }
-  RC(pn_t5_embed_bwd(w.dec_ids, w.ddH, drows, d, m->cfg.vocab, G + m->emb_off, st));
+  RC(pn_t5_embed_bwd(w.dec_ids, w.ddH, drows, d, m->cfg.vocab, G + m->emb_off, st,
+                     DR(1, 0, PN_DROP_EMBED, (long long)T * d)));
   // Gradient ranges in the order they become final (flat buffer = HF order: shared | encoder.block.* |
   // encoder.final_layer_norm | decoder.block.* | decoder.final_layer_norm): the upper decoder half (+ its final
   // norm) left above when decoder layer Ld/2 was done, the lower half now (decoder.block.0 holds the relative bias
@@ -453,24 +524,28 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
   }
 
   // ---- encoder: the final norm (folded into every Ckv), then the layers last to first
-  RC(pn_t5_norm_bwd(w.hidden, 0, w.hb[2 * L], w.rs[2 * L], rows, d, 0, w.dH, w.dHb, st));
+  RC(pn_t5_norm_bwd(w.hidden, 0, w.hb[2 * L], w.rs[2 * L], rows, d, 0, w.dH, w.dHb, st,
+                    DR(0, 0, PN_DROP_FINAL, (long long)S * d), DR(0, L - 1, PN_DROP_FF_OUT, (long long)S * d)));
   PN_CUDA(cudaMemsetAsync(w.diag, 0, (size_t)H * 1023 * 4, st));
   for (int l = L - 1; l >= 0; --l) {
     const PnEncLayer& E = m->enc[l];
     const __nv_bfloat16 *hb0 = w.hb[2 * l], *hb1 = w.hb[2 * l + 1];
     const float *rs0 = w.rs[2 * l], *rs1 = w.rs[2 * l + 1];
     RC(wgrad_plain(m, w.dHb, d, w.act[l], E.wo2, rows, st));
-    RC(dgrad_relu(m, w.dHb, E.wo2, w.act[l], rs1, w.dbig, rows, st));
+    RC(dgrad_relu(m, w.dHb, E.wo2, w.act[l], rs1, w.dbig, rows, st, act_scale));
     RC(wgrad_folded(m, w.dbig, ff, hb1, E.wi, w.dWtmp, rows, st));
     RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, PN_EPI_F32, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, 0, hb1, rs1, rows, d, 1, w.dH, w.dHb, st));
+    RC(pn_t5_norm_bwd(w.gbuf, 0, hb1, rs1, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
+                      DR(0, l, PN_DROP_SELF_OUT, (long long)S * d)));
     RC(wgrad_plain(m, w.dHb, d, w.ctx[l], E.wo, rows, st));
     RC(dgrad(m, w.dHb, d, E.wo, w.dctx, PN_EPI_BF16, rows, st));
     RC(pn_t5_self_attn_bwd(w.qkv[l], 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx[l], w.dctx, di,
-                           w.lse[l], w.dvec, rs0, w.dbig, w.diag, st));
+                           w.lse[l], w.dvec, rs0, w.dbig, w.diag, st,
+                           DR(0, l, PN_DROP_SELF_P, (long long)H * S * Sp)));
     RC(wgrad_folded(m, w.dbig, 3 * di, hb0, E.wqkv, w.dWtmp, rows, st));
     RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, PN_EPI_F32, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, 0, hb0, rs0, rows, d, 1, w.dH, w.dHb, st));
+    RC(pn_t5_norm_bwd(w.gbuf, 0, hb0, rs0, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
+                      l > 0 ? DR(0, l - 1, PN_DROP_FF_OUT, (long long)S * d) : PnDrop()));
     if (m->grad_hook && l > 0)
       for (int g = groups - 1; g >= 1; --g)
         if (group_lo(g) == l) {   // layers [l, top of group g) are done
@@ -479,7 +554,7 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
           m->grad_hook(m->grad_hook_user, lo, hi - lo);
         }
   }
-  RC(pn_t5_embed_bwd(ids, w.dH, rows, d, m->cfg.vocab, G + m->emb_off, st));
+  RC(pn_t5_embed_bwd(ids, w.dH, rows, d, m->cfg.vocab, G + m->emb_off, st, DR(0, 0, PN_DROP_EMBED, (long long)S * d)));
   RC(pn_t5_rel_bias_grad(w.diag, bucket_of, H, m->cfg.rel_buckets, G + m->enc_rel_off, st));
   if (m->grad_hook) {
     const int64_t rest = groups > 1 && group_lo(1) > 0 ? enc_layer_off(group_lo(1)) : dec_off;

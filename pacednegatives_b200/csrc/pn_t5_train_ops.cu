@@ -73,7 +73,8 @@ row_scale_kernel(__nv_bfloat16* __restrict__ y, int ld, const float* __restrict_
 template <int MAXV, bool kG16>
 __global__ void __launch_bounds__(kThreads)
 norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ hb, const float* __restrict__ rs,
-                int64_t rows, int d, int accumulate, float* __restrict__ dh, __nv_bfloat16* __restrict__ dhb) {
+                int64_t rows, int d, int accumulate, float* __restrict__ dh, __nv_bfloat16* __restrict__ dhb,
+                const PnDrop gdrop, const PnDrop odrop) {
   const float* G = reinterpret_cast<const float*>(Gv);
   const __nv_bfloat16* G16 = reinterpret_cast<const __nv_bfloat16*>(Gv);
   const int lane = threadIdx.x & 31;
@@ -96,6 +97,13 @@ norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ h
         } else {
           g[i] = reinterpret_cast<const float4*>(G + (size_t)r * d)[c];
         }
+        if (gdrop.thresh) {
+          const unsigned long long e0 = (unsigned long long)gdrop.idx_offset + (unsigned long long)r * d + 4 * c;
+          float m0, m1, m2, m3;
+          pn_drop_mul2(gdrop, e0, m0, m1);
+          pn_drop_mul2(gdrop, e0 + 2, m2, m3);
+          g[i].x *= m0; g[i].y *= m1; g[i].z *= m2; g[i].w *= m3;
+        }
         const uint2 raw = reinterpret_cast<const uint2*>(hb + (size_t)r * d)[c];
         const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
         const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
@@ -116,6 +124,13 @@ norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ h
         o.x += pv[i].x; o.y += pv[i].y; o.z += pv[i].z; o.w += pv[i].w;
         *dst = o;
         if (dhb) {
+          if (odrop.thresh) {
+            const unsigned long long e0 = (unsigned long long)odrop.idx_offset + (unsigned long long)r * d + 4 * c;
+            float m0, m1, m2, m3;
+            pn_drop_mul2(odrop, e0, m0, m1);
+            pn_drop_mul2(odrop, e0 + 2, m2, m3);
+            o.x *= m0; o.y *= m1; o.z *= m2; o.w *= m3;
+          }
           __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
           reinterpret_cast<uint2*>(dhb + (size_t)r * d)[c] =
               make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
@@ -171,7 +186,7 @@ unfold_kernel(const float* __restrict__ dWp, const float* __restrict__ W, const 
 // grad_table[ids[r], :] += dh[r, :]  (tied input embeddings), one warp per row, vector atomics
 __global__ void __launch_bounds__(kThreads)
 embed_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ dh, int64_t rows, int d, int vocab,
-                 float* __restrict__ grad_table) {
+                 float* __restrict__ grad_table, const PnDrop drop) {
   const int lane = threadIdx.x & 31;
   const int64_t w = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   const int64_t nw = ((int64_t)gridDim.x * kThreads) >> 5;
@@ -180,7 +195,17 @@ embed_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ dh, 
     id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
     const float4* src = reinterpret_cast<const float4*>(dh + (size_t)r * d);
     float4* dst = reinterpret_cast<float4*>(grad_table + (size_t)id * d);
-    for (int i = lane; i < d / 4; i += 32) atomicAdd(dst + i, src[i]);
+    for (int i = lane; i < d / 4; i += 32) {
+      float4 v = src[i];
+      if (drop.thresh) {   // the embedding output was dropped: its gradient passes through the same mask
+        const unsigned long long e0 = (unsigned long long)drop.idx_offset + (unsigned long long)r * d + 4 * i;
+        float m0, m1, m2, m3;
+        pn_drop_mul2(drop, e0, m0, m1);
+        pn_drop_mul2(drop, e0 + 2, m2, m3);
+        v.x *= m0; v.y *= m1; v.z *= m2; v.w *= m3;
+      }
+      atomicAdd(dst + i, v);
+    }
   }
 }
 
@@ -189,16 +214,17 @@ embed_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ dh, 
 __global__ void __launch_bounds__(kThreads)
 final_norm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ w,
                       int64_t rows, int d, float eps, float* __restrict__ dx, __nv_bfloat16* __restrict__ dxb,
-                      float* __restrict__ dw) {
+                      float* __restrict__ dw, const PnDrop ydrop, const PnDrop odrop) {
   const int lane = threadIdx.x & 31;
   const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   if (r >= rows) return;
   const float* xr = x + (size_t)r * d;
   const float* gr = dy + (size_t)r * d;
   float ss = 0.0f, dot = 0.0f;
+  const unsigned long long yb = (unsigned long long)ydrop.idx_offset + (unsigned long long)r * d;
   for (int i = lane; i < d; i += 32) {
     ss += xr[i] * xr[i];
-    dot += xr[i] * w[i] * gr[i];
+    dot += xr[i] * w[i] * gr[i] * pn_drop_mul(ydrop, yb + i);
   }
   ss = pn_warp_sum(ss);
   dot = pn_warp_sum(dot);
@@ -206,10 +232,13 @@ final_norm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x,
   const float sc = rsqrtf((float)d);
   const float m = dot * rs * rs / (float)d;     // mean(x_hat w dy) * rs, folded for the x (not x_hat) product
   for (int i = lane; i < d; i += 32) {
-    const float v = sc * rs * (w[i] * gr[i] - xr[i] * m);
+    const float gi = gr[i] * pn_drop_mul(ydrop, yb + i);
+    const float v = sc * rs * (w[i] * gi - xr[i] * m);
     dx[(size_t)r * d + i] = v;
-    if (dxb) dxb[(size_t)r * d + i] = __float2bfloat16_rn(v);
-    atomicAdd(dw + i, sc * gr[i] * xr[i] * rs);
+    if (dxb)
+      dxb[(size_t)r * d + i] = __float2bfloat16_rn(
+          v * pn_drop_mul(odrop, (unsigned long long)odrop.idx_offset + (unsigned long long)r * d + i));
+    atomicAdd(dw + i, sc * gi * xr[i] * rs);
   }
 }
 
@@ -298,11 +327,11 @@ int pn_t5_row_scale(__nv_bfloat16* y, int ld, const float* rs, int64_t rows, int
 }
 
 int pn_t5_norm_bwd(const void* G, int g_bf16, const __nv_bfloat16* hb, const float* rs, int64_t rows, int d,
-                   int accumulate, float* dh, __nv_bfloat16* dhb, cudaStream_t st) {
+                   int accumulate, float* dh, __nv_bfloat16* dhb, cudaStream_t st, PnDrop gdrop, PnDrop odrop) {
   if (rows == 0) return PN_OK;
   if (d % 4 || d > 32 * 4 * 16) return pn_fail(PN_E_UNSUPPORTED, "norm_bwd: d_model=%d unsupported", d);
   const int grid = pn_grid(rows * 32, kThreads, 1, 8);
-#define PN_NB(V, B) norm_bwd_kernel<V, B><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb)
+#define PN_NB(V, B) norm_bwd_kernel<V, B><<<grid, kThreads, 0, st>>>(G, hb, rs, rows, d, accumulate, dh, dhb, gdrop, odrop)
   if (d <= 32 * 4 * 4) { if (g_bf16) PN_NB(4, true); else PN_NB(4, false); }
   else if (d <= 32 * 4 * 6) { if (g_bf16) PN_NB(6, true); else PN_NB(6, false); }
   else if (d <= 32 * 4 * 8) { if (g_bf16) PN_NB(8, true); else PN_NB(8, false); }
@@ -325,18 +354,19 @@ int pn_t5_unfold(const float* dWp, const float* W, const float* g, int64_t rows,
 }
 
 int pn_t5_embed_bwd(const int32_t* ids, const float* dh, int64_t rows, int d, int vocab, float* grad_table,
-                    cudaStream_t st) {
+                    cudaStream_t st, PnDrop drop) {
   if (rows == 0) return PN_OK;
-  embed_bwd_kernel<<<pn_grid(rows * 32, kThreads, 1, 8), kThreads, 0, st>>>(ids, dh, rows, d, vocab, grad_table);
+  embed_bwd_kernel<<<pn_grid(rows * 32, kThreads, 1, 8), kThreads, 0, st>>>(ids, dh, rows, d, vocab, grad_table, drop);
   PN_LAUNCHED();
   return PN_OK;
 }
 
 int pn_t5_final_norm_bwd(const float* dy, const float* x, const float* w, int64_t rows, int d, float eps,
-                         float* dx, __nv_bfloat16* dxb, float* dw, cudaStream_t st) {
+                         float* dx, __nv_bfloat16* dxb, float* dw, cudaStream_t st, PnDrop ydrop, PnDrop odrop) {
   if (rows == 0) return PN_OK;
   final_norm_bwd_kernel<<<(unsigned)((rows * 32 + kThreads - 1) / kThreads), kThreads, 0, st>>>(dy, x, w, rows, d,
-                                                                                               eps, dx, dxb, dw);
+                                                                                               eps, dx, dxb, dw,
+                                                                                               ydrop, odrop);
   PN_LAUNCHED();
   return PN_OK;
 }

@@ -116,13 +116,15 @@ class _ModelFn(torch.autograd.Function):
         N, S = ids.shape
         T = labels.shape[1]
         lib = _lib.lib()
+        model._apply_dropout_state()
         need = int(lib.pn_t5_train_workspace_bytes(model._h, N, S, T))
         ws = torch.empty(need, dtype=torch.uint8, device="cuda")
         logits = torch.empty(N * T, model.vocab_pad, dtype=torch.float32, device="cuda")
         _lib.check(lib.pn_t5_train_forward(model._h, _lib.ptr(ids), _lib.ptr(labels), N, S, T, _lib.ptr(logits),
                                            _lib.ptr(ws), need, _lib.stream()))
-        ctx.model, ctx.ws, ctx.ids, ctx.shape = model, ws, ids, (N, S, T)
-        model._pending += 1
+        if ctx.needs_input_grad[0]:      # under torch.no_grad() (the train-mode meta forward) nothing is kept
+            ctx.model, ctx.ws, ctx.ids, ctx.shape = model, ws, ids, (N, S, T)
+            model._pending += 1
         return logits.view(N, T, model.vocab_pad)
 
     @staticmethod
@@ -154,13 +156,15 @@ class _ModelZ2Fn(torch.autograd.Function):
         N, S = ids.shape
         T = labels.shape[1]
         lib = _lib.lib()
+        model._apply_dropout_state()
         need = int(lib.pn_t5_train_workspace_bytes(model._h, N, S, T))
         ws = torch.empty(need, dtype=torch.uint8, device="cuda")
         z2 = torch.empty(N * T, 2, dtype=torch.float32, device="cuda")
         _lib.check(lib.pn_t5_train_forward_z2(model._h, _lib.ptr(ids), _lib.ptr(labels), N, S, T, model.rel_id,
                                               model.nrel_id, _lib.ptr(z2), _lib.ptr(ws), need, _lib.stream()))
-        ctx.model, ctx.ws, ctx.ids, ctx.shape = model, ws, ids, (N, S, T)
-        model._pending += 1
+        if ctx.needs_input_grad[0]:
+            ctx.model, ctx.ws, ctx.ids, ctx.shape = model, ws, ids, (N, S, T)
+            model._pending += 1
         return z2.view(N, T, 2)
 
     @staticmethod
@@ -198,6 +202,9 @@ class MonoT5Model(MonoT5Scorer):
                                                _lib.ptr(self.exp_avg_sq)))
         self._anchor = torch.zeros(1, device="cuda", requires_grad=True)
         self.opt_steps = 0
+        # train-mode dropout of the next forward(s): rate, seed of the forward call, index of the call's first
+        # document inside the step's batch (csrc/pn_dropout.cuh).  0.0 = eval-mode arithmetic.
+        self.dropout_rate, self.dropout_seed, self.dropout_doc_offset = 0.0, 0, 0
         # gradient all-reduce overlapped with the backward pass (DDP's bucketing): libpn_b200 calls _on_grad_range
         # while it enqueues the backward; ranges go out on a side stream behind an event
         self.overlap_grad_reduce = True
@@ -216,6 +223,10 @@ class MonoT5Model(MonoT5Scorer):
                 obj._on_grad_range(off, numel)
         self._hook_c = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64)(hook)
         _lib.check(lib.pn_t5_set_grad_hook(self._h, C.cast(self._hook_c, C.c_void_p), None))
+
+    def _apply_dropout_state(self):
+        _lib.check(_lib.lib().pn_t5_set_dropout(self._h, float(self.dropout_rate), int(self.dropout_seed) & (2 ** 64 - 1),
+                                                int(self.dropout_doc_offset)))
 
     def __call__(self, input_ids, labels, attention_mask=None):
         if attention_mask is not None and not bool(torch.as_tensor(attention_mask).all()):
@@ -455,7 +466,17 @@ class LCEModel(_LightningBase):
         self.automatic_optimization = False
         if _pl is not None:
             self.save_hyperparameters()
-        self.elide = bool(elide_no_grad_forward) if elide_no_grad_forward is not None else True
+        # dropout: hparams['dropout_rate'], else the checkpoint's config.json value when the model came from
+        # model_name (t5-* / monot5-*: 0.1, what the reference trains with under Lightning's train mode), else 0
+        cfg_base = getattr(self.model, "hf_config_base", None) or {}
+        self.dropout_rate = float(self.hparams.get("dropout_rate", cfg_base.get("dropout_rate", 0.0) if name else 0.0))
+        self.dropout_seed = int(self.hparams.get("seed", 0))
+        self.model.dropout_rate = self.dropout_rate
+        if self.dropout_rate > 0.0 and elide_no_grad_forward:
+            raise ValueError("elide_no_grad_forward needs dropout_rate 0: with dropout the two forwards of "
+                             "lceT5.py:131-133 / 149-150 see different masks")
+        self.elide = (bool(elide_no_grad_forward) if elide_no_grad_forward is not None else True) \
+            and self.dropout_rate == 0.0
         self.difficulty = self.weights.eta.item()
         self._pn_step = 0
         self.logged = {}
@@ -498,18 +519,39 @@ class LCEModel(_LightningBase):
         sched = _linear_schedule(opt, int(self.hparams.warmup_steps), int(self.hparams.total_steps))
         return [meta_opt, opt], [meta_sched, sched]
 
-    def _forward_pn(self, p, n, k, V):
+    def _forward_pn(self, p, n, k, V, doc_offset=0):
         """`self.model(**p).logits`, `self.model(**n).logits` (lceT5.py:149-150).  Documents are independent, so
         when both batches have the same sequence and label lengths they go through the model as ONE batch (half
         the kernel launches, fuller GEMM tiles); the logits are the same numbers either way."""
         pi, ni = torch.as_tensor(p["input_ids"]), torch.as_tensor(n["input_ids"])
         pl, nl = torch.as_tensor(p["labels"]), torch.as_tensor(n["labels"])
+        Q = pi.shape[0]
+        # dropout masks are a function of the document's index in the step's batch: positives doc_offset ..,
+        # then the negatives (the same numbering whether the two halves run as one batch or two)
+        self.model.dropout_doc_offset = doc_offset
         if pi.shape[1] == ni.shape[1] and pl.shape[1] == nl.shape[1]:
             dev = "cuda"
             logits = self.model(torch.cat([pi.to(dev), ni.to(dev)]), torch.cat([pl.to(dev), nl.to(dev)]))
-            Q = pi.shape[0]
             return logits[:Q], logits[Q:].reshape(-1, k, V)
-        return self.model(pi, pl), self.model(ni, nl).view(-1, k, V)
+        plog = self.model(pi, pl)
+        self.model.dropout_doc_offset = doc_offset + Q
+        nlog = self.model(ni, nl).view(-1, k, V)
+        self.model.dropout_doc_offset = doc_offset
+        return plog, nlog
+
+    def _forward_seed(self, which):
+        """seed of forward `which` (0 = the no-grad meta forward, 1 = the gradient forward) of this step"""
+        self.model.dropout_seed = (self.dropout_seed << 32) + 2 * self._pn_step + which
+
+    def _no_grad_logits(self, p, n, k, V, doc_offset):
+        """`with torch.no_grad(): self.model(**p) ... self.model(**n)` (lceT5.py:131-133).  Lightning keeps the module
+        in train mode there, so with dropout this is a train-mode forward with its own masks (nothing saved for a
+        backward); without dropout it is the scorer's forward."""
+        if self.dropout_rate > 0.0:
+            return self._forward_pn(p, n, k, V, doc_offset)
+        p0, _ = self.model.logits(p["input_ids"], p["labels"])
+        n0, _ = self.model.logits(n["input_ids"], n["labels"])
+        return p0, n0.reshape(-1, k, V)
 
     @staticmethod
     def _raw(opt):
@@ -544,17 +586,26 @@ class LCEModel(_LightningBase):
         Q, T = pi.shape[0], pl.shape[1]
         if not self.elide:
             with torch.no_grad():
-                p0, _ = self.model.logits(pi, pl)
-                n0, _ = self.model.logits(ni, nl)
-                loss0 = self.pair_loss(p0.contiguous(), n0.reshape(-1, k, V).contiguous(), pl.cuda(), nl.cuda())
+                loss0 = []
+                self._forward_seed(0)
+                for a in range(0, Q, mq):
+                    b = min(Q, a + mq)
+                    pc = {"input_ids": pi[a:b], "labels": pl[a:b]}
+                    nc = {"input_ids": ni[a * k:b * k], "labels": nl[a * k:b * k]}
+                    p0, n0 = self._no_grad_logits(pc, nc, k, V, a * (1 + k))
+                    loss0.append(self.pair_loss(p0.contiguous(), n0.contiguous(), pc["labels"].cuda(),
+                                                nc["labels"].cuda()))
+                    del p0, n0
+                loss0 = torch.cat(loss0)
         opt.zero_grad()
         parts = []
+        self._forward_seed(1)
         try:
             for a in range(0, Q, mq):
                 b = min(Q, a + mq)
                 pc = {"input_ids": pi[a:b], "labels": pl[a:b]}
                 nc = {"input_ids": ni[a * k:b * k], "labels": nl[a * k:b * k]}
-                plogits, nlogits = self._forward_pn(pc, nc, k, V)
+                plogits, nlogits = self._forward_pn(pc, nc, k, V, a * (1 + k))
                 main = self.pair_loss(plogits.contiguous(), nlogits.contiguous(), pc["labels"].cuda(),
                                       nc["labels"].cuda())
                 parts.append(main.detach())
@@ -594,6 +645,8 @@ class LCEModel(_LightningBase):
             S = max(pi.shape[1], ni.shape[1])      # pad tokens are attended on this path (no mask, lceT5.py:53)
             pi = torch.nn.functional.pad(pi, (0, S - pi.shape[1]), value=self.model.dims.pad_id)
             ni = torch.nn.functional.pad(ni, (0, S - ni.shape[1]), value=self.model.dims.pad_id)
+        self._forward_seed(1)
+        self.model.dropout_doc_offset = 0
         z2 = self.model.z2(torch.cat([pi, ni]))[:, 0]                      # [Q + Q*k, 2]
         grouped = torch.cat([z2[:Q].unsqueeze(1), z2[Q:].view(Q, k, 2)], dim=1)   # [Q, G, 2], positive first
         main_loss, _ = lce_restricted(grouped.reshape(-1, 2), G)
@@ -620,13 +673,13 @@ class LCEModel(_LightningBase):
             return self._training_step_micro(p, n, mq, meta_opt, opt, meta_scheduler, scheduler)
 
         if self.elide:
+            self._forward_seed(1)
             plogits, nlogits = self._forward_pn(p, n, k, V)
             p0, n0 = plogits.detach(), nlogits.detach()
         else:
             with torch.no_grad():
-                p0, _ = self.model.logits(p["input_ids"], p["labels"])
-                n0, _ = self.model.logits(n["input_ids"], n["labels"])
-                n0 = n0.reshape(-1, k, V)
+                self._forward_seed(0)
+                p0, n0 = self._no_grad_logits(p, n, k, V, 0)
         op = torch.as_tensor(p["labels"]).cuda()
         on = torch.as_tensor(n["labels"]).cuda()
         with torch.no_grad():
@@ -635,6 +688,7 @@ class LCEModel(_LightningBase):
         weights, meta_loss = self._meta_step(loss, meta_opt, meta_scheduler)
 
         if not self.elide:
+            self._forward_seed(1)
             plogits, nlogits = self._forward_pn(p, n, k, V)
         main_loss = self.pair_loss(plogits.contiguous(), nlogits.contiguous(), op, on)
 

@@ -301,8 +301,10 @@ class MonoT5Scorer:
         .from_pretrained(path)`` loads — train/train_lce.py:103 calls this on the trained model."""
         os.makedirs(path, exist_ok=True)
         with open(os.path.join(path, "config.json"), "w") as f:
-            json.dump(hf_config(self.dims, self.hf_config_base, getattr(self, "dropout_rate", None)
-                                if self.hf_config_base is None else None), f, indent=2)
+            # no source config (weights given directly): HF's t5 default rate unless this model trained with one
+            rate = getattr(self, "dropout_rate", None) or None
+            json.dump(hf_config(self.dims, self.hf_config_base, rate if self.hf_config_base is None else None), f,
+                      indent=2)
         sd = {k: v.contiguous() for k, v in self.state_dict().items()}
         if safe_serialization:
             from safetensors.torch import save_file

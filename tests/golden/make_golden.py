@@ -457,7 +457,7 @@ def _sample_index(name, numel, count=8192):
 
 
 def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_id=1176, nrel_id=6136, steps=1,
-                    lr=1e-3, meta_lr=1e-2):
+                    lr=1e-3, meta_lr=1e-2, dropout=None, S_neg=None):
     """The reference's own LCEModel.training_step (lceT5.py:124-167), unmodified, on HF T5 fp32 CPU at the widths
     the bench runs: per parameter the gradient norm, a seeded element sample (all elements for
     tensors <= 65536) and, for matrices, the row / column sums and the norm of every 64 x 64 block (a wrong head /
@@ -466,9 +466,13 @@ def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_i
     from oracle import t5 as ot
     from transformers import T5Config, T5ForConditionalGeneration, get_linear_schedule_with_warmup
     w = ot.init_weights(dims, seed=seed)
+    # dropout = (p, base_seed): HF in train mode WITH dropout_rate p, as Lightning runs the reference; the masks of
+    # every dropout call are the counter-hash masks of csrc/pn_dropout.cuh, replayed inside HF (oracle/dropout.py)
+    from oracle import dropout as od
+    drop_p, drop_base = dropout if dropout else (0.0, 0)
     cfg = T5Config(vocab_size=dims.vocab, d_model=dims.d_model, d_kv=dims.d_kv, d_ff=dims.d_ff,
                    num_layers=dims.n_layers, num_decoder_layers=dims.n_dec_layers,
-                   num_heads=dims.n_heads, dropout_rate=0.0, decoder_start_token_id=0,
+                   num_heads=dims.n_heads, dropout_rate=drop_p, decoder_start_token_id=0,
                    pad_token_id=0, eos_token_id=1, feed_forward_proj="relu", tie_word_embeddings=True)
     m = T5ForConditionalGeneration(cfg).train()
     sd = {k_: torch.tensor(v) for k_, v in w.items()}
@@ -476,10 +480,19 @@ def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_i
     sd["lm_head.weight"] = sd["shared.weight"]
     missing = m.load_state_dict(sd, strict=False)
     assert not missing.missing_keys and not missing.unexpected_keys, missing
+
+    def replay(step, forwards=(0, 1)):
+        """masks of the step's forwards: the no-grad pair (p, n) then the gradient pair, seeds (base << 32) + 2 *
+        step + which, positives numbered from document 0 and negatives from Q"""
+        sched = []
+        for which in forwards:
+            sd_ = (drop_base << 32) + 2 * step + which
+            sched += [(sd_, 0), (sd_, Q)]
+        return od.HFDropoutReplay(drop_p, dims.n_layers, dims.n_dec_layers, sched)
     rng = np.random.RandomState(ids_seed)
     hi = min(dims.vocab, 32100)
     pids = rng.randint(2, hi, size=(Q, S)).astype(np.int64)
-    nids = rng.randint(2, hi, size=(Q * k, S)).astype(np.int64)
+    nids = rng.randint(2, hi, size=(Q * k, S_neg or S)).astype(np.int64)
     pids[:, -1] = 1
     nids[:, -1] = 1
     plab = np.tile([[rel_id, 1]], (Q, 1)).astype(np.int64)
@@ -489,7 +502,7 @@ def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_i
     loss_fn = torch.nn.CrossEntropyLoss(ignore_index=-100, reduction="none")
     if eta is None:
         probe = types.SimpleNamespace(loss_fn=loss_fn, hparams=types.SimpleNamespace(use_mean=True))
-        with torch.no_grad():
+        with torch.no_grad(), replay(0, (0,)):      # the losses eta is compared with: step 0's no-grad forward
             pl = m(**batch[0]).logits
             nl = m(**batch[1]).logits.view(-1, k, dims.vocab)
             ls = np.sort(rt.LCEModel.pair_loss(probe, pl, nl, batch[0]["labels"], batch[1]["labels"]).numpy())
@@ -515,7 +528,10 @@ def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_i
     names = [n_ for n_, _ in m.named_parameters()]
     res = {}
     for step in range(steps):
-        o = rt.LCEModel.training_step(self, batch, step)
+        with replay(step) as rp_:
+            o = rt.LCEModel.training_step(self, batch, step)
+        if drop_p > 0.0:
+            assert rp_.calls == 4 * len(rp_.sites), (rp_.calls, len(rp_.sites))
         res[f"main_loss{step}"] = float(o["main_loss"])
         res[f"meta_loss{step}"] = float(o["meta_loss"])
         res[f"eta{step}"] = float(self.weights.eta.item())
@@ -539,7 +555,26 @@ def gold_train_wide(rt, out, dims, Q, k, S, seed, eta=None, ids_seed=4321, rel_i
                             dims.n_heads]), seed=np.array(seed), pids=pids, nids=nids, plab=plab, nlab=nlab,
         hp=np.array([hp.n, int(hp.use_mean), hp.lr, hp.meta_lr, hp.warmup_steps, hp.total_steps, hp.eta],
                     dtype=np.float64),
-        steps=np.array(steps), names=np.array(names), **{k_: np.asarray(v) for k_, v in res.items()})
+        steps=np.array(steps), dropout=np.array([drop_p, drop_base], dtype=np.float64), names=np.array(names),
+        **{k_: np.asarray(v) for k_, v in res.items()})
+
+
+def gold_train_dropout(rt):
+    """a10 with the reference's train-mode dropout (0.1): tiny model for two steps (the seeds advance), and the
+    t5-base width (12 heads, S 512) for one."""
+    sys.path.insert(0, ROOT)
+    from oracle import t5 as ot
+    gold_train_wide(rt, os.path.join(HERE, "train_golden_dropout_tiny.npz"),
+                    ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2),
+                    Q=2, k=3, S=128, seed=23, steps=2, rel_id=117, nrel_id=213, dropout=(0.1, 7))
+    gold_train_wide(rt, os.path.join(HERE, "train_golden_dropout_base.npz"),
+                    ot.T5Dims(vocab=32128, d_model=768, d_kv=64, d_ff=3072, n_layers=2, n_dec_layers=2, n_heads=12),
+                    Q=2, k=3, S=512, seed=31, steps=1, dropout=(0.1, 11))
+    # ragged S (odd key pitch is padded to even) and the un-concatenated path (positives and negatives of different
+    # lengths run as two model calls): positives 77 tokens, negatives 90
+    gold_train_wide(rt, os.path.join(HERE, "train_golden_dropout_ragged.npz"),
+                    ot.T5Dims(vocab=384, d_model=128, d_kv=64, d_ff=256, n_layers=2, n_dec_layers=2, n_heads=2),
+                    Q=2, k=3, S=77, seed=29, steps=1, rel_id=117, nrel_id=213, dropout=(0.1, 13), S_neg=90)
 
 
 def gold_train_widths(rt):
@@ -980,6 +1015,7 @@ def main():
     gold_train(rt, os.path.join(HERE, "train_golden.npz"))
     if "--wide" in sys.argv or "--all" in sys.argv:   # minutes of CPU: only on request
         gold_train_widths(rt)
+        gold_train_dropout(rt)
     gold_newwrapper(rp, rw, os.path.join(HERE, "newwrapper_golden.npz"))
     gold_stdwrapper(rp, rw, os.path.join(HERE, "stdwrapper_golden.npz"))
     gold_scalar_wrappers(rp, rw, os.path.join(HERE, "scalar_wrappers_golden.npz"))
