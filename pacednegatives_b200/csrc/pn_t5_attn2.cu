@@ -92,7 +92,36 @@ __device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
+// 2^x for a pair on the FMA pipe instead of MUFU.EX2 (the exponential unit is the busiest pipe of this kernel:
+// 16 lanes / clk / SM against 128 for FFMA): Cody-Waite split x = n + f with the round-to-nearest magic constant
+// (n in the low mantissa bits of t = x + 1.5 * 2^23), a cubic minimax polynomial for 2^f on [-0.5, 0.5] (relative
+// error 7.5e-5, far below the bf16 rounding of P) and n added into the exponent field.  x is clamped at -125 (2^-125
+// is 0 for every purpose here and keeps the exponent arithmetic in range); x <= ~+60 by the redo threshold.
+#ifndef PN_ATTN_POLY
+// Measured (same box, profiles/r4h_attn_poly_ab.txt; 250 docs x 12 heads x 512): 0 -> 496.7 TFLOP/s, 1 -> 501.5 (+1 %),
+// 2 -> 434.7 (-12 %); re-rank step 8 581 / 8 575 / 8 352 pairs/s.  The kernel is not MUFU-bound (two softmax warps per
+// scheduler: issue + dependency latency), so the default stays 0.
+#define PN_ATTN_POLY 0     // 0: every exponential on MUFU; 1: one pair in four on the FMA pipe; 2: one in two
+#endif
+__device__ __forceinline__ void ex2_poly2(float x0, float x1, float& p0, float& p1) {
+  const uint64_t magic = f2pack(12582912.0f, 12582912.0f), nmagic = f2pack(-12582912.0f, -12582912.0f);
+  const uint64_t x = f2pack(fmaxf(x0, -125.0f), fmaxf(x1, -125.0f));
+  const uint64_t t = add2(x, magic);
+  const uint64_t n = add2(t, nmagic);
+  const uint64_t f = fma2(n, f2pack(-1.0f, -1.0f), x);
+  uint64_t p = fma2(f, f2pack(0.055171459913253784f, 0.055171459913253784f), f2pack(0.2426108568906784f, 0.2426108568906784f));
+  p = fma2(p, f, f2pack(0.6932609677314758f, 0.6932609677314758f));
+  p = fma2(p, f, f2pack(0.9999281167984009f, 0.9999281167984009f));
+  float t0, t1, q0, q1;
+  f2unpack(t, t0, t1);
+  f2unpack(p, q0, q1);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+}
 
+// kDrop: training forward with dropout of the probabilities; the eval instantiation carries none of that code (its
+// registers are all spoken for: 168 per thread at 384 threads)
+template <bool kDrop>
 __global__ void __launch_bounds__(kThreads, 1)
 t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args a) {
   extern __shared__ uint8_t smem_raw[];
@@ -330,10 +359,12 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
       // single pass: bias (columns 32..127), running max, p = 2^(x - m_used) against the STALE max so that the
       // exponentials do not wait for the row max; P -> its own TMEM buffer as packed bf16 (64 columns)
       // dropout mask of this row's chunk: element [doc, head, qi, c*KC + jj] at an even row pitch
-      const bool dropping = a.drop.thresh != 0;
-      const unsigned long long dbase =
-          (unsigned long long)a.drop.idx_offset +
-          ((unsigned long long)((doc0 + it * a.cph) * a.n_heads + head) * S + (qi < S ? qi : 0)) * (S + (S & 1)) + c * KC;
+      constexpr bool dropping = kDrop;
+      unsigned long long dbase = 0;
+      if (kDrop)
+        dbase = (unsigned long long)a.drop.idx_offset +
+                ((unsigned long long)((doc0 + it * a.cph) * a.n_heads + head) * S + (qi < S ? qi : 0)) * (S + (S & 1)) +
+                c * KC;
       float nm = -m_used;
       uint64_t nm2 = f2pack(nm, nm);
       uint64_t lsa = f2pack(0.0f, 0.0f), lsb = lsa;
@@ -363,8 +394,13 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
           f2unpack(add2(xb, nm2), e2, e3);
           const float p0 = ex2_approx(e0);
           const float p1 = ex2_approx(e1);
-          const float p2 = ex2_approx(e2);
-          const float p3 = ex2_approx(e3);
+          float p2, p3;
+          if (PN_ATTN_POLY == 2 || (PN_ATTN_POLY == 1 && (e & 2))) {
+            ex2_poly2(e2, e3, p2, p3);
+          } else {
+            p2 = ex2_approx(e2);
+            p3 = ex2_approx(e3);
+          }
           lsa = add2(lsa, f2pack(p0, p1));
           lsb = add2(lsb, f2pack(p2, p3));
           if (dropping) {
@@ -566,12 +602,15 @@ static int self_attn_impl(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int k
   }
   static bool attr_done = false;
   if (!attr_done) {
-    PN_CUDA(cudaFuncSetAttribute(t5_self_attn2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PN_CUDA(cudaFuncSetAttribute(t5_self_attn2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 ATTN2_SMEM));
+    PN_CUDA(cudaFuncSetAttribute(t5_self_attn2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  ATTN2_SMEM));
     attr_done = true;
   }
   PnProfScope prof(PN_PROF_ATTN, 4.0 * docs * n_heads * (double)S * S * DK, st);
-  t5_self_attn2_kernel<<<n_heads * a.cph, kThreads, ATTN2_SMEM, st>>>(tm, a);
+  if (drop.thresh) t5_self_attn2_kernel<true><<<n_heads * a.cph, kThreads, ATTN2_SMEM, st>>>(tm, a);
+  else t5_self_attn2_kernel<false><<<n_heads * a.cph, kThreads, ATTN2_SMEM, st>>>(tm, a);
   PN_LAUNCHED();
   return PN_OK;
 }

@@ -527,6 +527,11 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
   RC(pn_t5_norm_bwd(w.hidden, 0, w.hb[2 * L], w.rs[2 * L], rows, d, 0, w.dH, w.dHb, st,
                     DR(0, 0, PN_DROP_FINAL, (long long)S * d), DR(0, L - 1, PN_DROP_FF_OUT, (long long)S * d)));
   PN_CUDA(cudaMemsetAsync(w.diag, 0, (size_t)H * 1023 * 4, st));
+  // G = Ys W' of the encoder's two normed linears goes to norm_bwd as bf16 ("dgrad_bf16", default): the bf16 epilogue
+  // leaves by TMA store (the fp32 one through registers) and norm_bwd reads 2 B instead of 4 B per element; dh itself
+  // stays fp32.  Parity at the bench widths: tests/test_gpu_train.py::test_training_step_at_bench_widths.
+  const int g16 = m->dgrad_bf16 ? 1 : 0;
+  const int gmode = g16 ? PN_EPI_BF16 : PN_EPI_F32;
   for (int l = L - 1; l >= 0; --l) {
     const PnEncLayer& E = m->enc[l];
     const __nv_bfloat16 *hb0 = w.hb[2 * l], *hb1 = w.hb[2 * l + 1];
@@ -534,8 +539,8 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
     RC(wgrad_plain(m, w.dHb, d, w.act[l], E.wo2, rows, st));
     RC(dgrad_relu(m, w.dHb, E.wo2, w.act[l], rs1, w.dbig, rows, st, act_scale));
     RC(wgrad_folded(m, w.dbig, ff, hb1, E.wi, w.dWtmp, rows, st));
-    RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, PN_EPI_F32, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, 0, hb1, rs1, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
+    RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, gmode, rows, st));
+    RC(pn_t5_norm_bwd(w.gbuf, g16, hb1, rs1, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
                       DR(0, l, PN_DROP_SELF_OUT, (long long)S * d)));
     RC(wgrad_plain(m, w.dHb, d, w.ctx[l], E.wo, rows, st));
     RC(dgrad(m, w.dHb, d, E.wo, w.dctx, PN_EPI_BF16, rows, st));
@@ -543,8 +548,8 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
                            w.lse[l], w.dvec, rs0, w.dbig, w.diag, st,
                            DR(0, l, PN_DROP_SELF_P, (long long)H * S * Sp)));
     RC(wgrad_folded(m, w.dbig, 3 * di, hb0, E.wqkv, w.dWtmp, rows, st));
-    RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, PN_EPI_F32, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, 0, hb0, rs0, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
+    RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, gmode, rows, st));
+    RC(pn_t5_norm_bwd(w.gbuf, g16, hb0, rs0, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
                       l > 0 ? DR(0, l - 1, PN_DROP_FF_OUT, (long long)S * d) : PnDrop()));
     if (m->grad_hook && l > 0)
       for (int g = groups - 1; g >= 1; --g)

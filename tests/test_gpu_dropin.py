@@ -117,6 +117,7 @@ def test_reference_driver_runs_against_the_drop_in(tmp_path, aliased):
     from pacednegatives_b200.lceT5 import LCEModel, TokenCELoss
     assert isinstance(model, LCEModel) and model.tokenizer is not None and isinstance(model.loss_fn, TokenCELoss)
     assert model.automatic_optimization is False and model.hparams.model_name == ckpt
+    assert model.dropout_rate == 0.1            # the checkpoint's config.json value: the reference's train-mode regime
     assert model.hparams.total_steps == 16 and model.hparams.warmup_steps == 2
     assert len(trainer.outputs) == 3
     for o in trainer.outputs:
@@ -148,7 +149,9 @@ def test_first_step_loss_matches_hf_on_the_tokenised_batch(tmp_path, aliased):
     dims, w0 = make_checkpoint(ckpt)
     from pacednegatives_b200.lceT5 import LCEModel, LCEDataModule
     model = LCEModel({"model_name": ckpt, "total_steps": 10, "eta": 20.0, "batch_size": 4, "lr": 1e-3,
-                      "meta_lr": 1e-2, "n": 3, "warmup_steps": 0, "use_mean": True, "ignore_index": -100})
+                      "meta_lr": 1e-2, "n": 3, "warmup_steps": 0, "use_mean": True, "ignore_index": -100,
+                      "dropout_rate": 0.0})     # HF below runs in eval mode; the default is the checkpoint's 0.1
+    assert model.dropout_rate == 0.0
     rng = np.random.RandomState(5)
     rows = [{"query_id": str(q), "doc_id_a": str(int(rng.randint(64))),
              "doc_id_b": [str(int(x)) for x in rng.permutation(64)[:40]]} for q in range(4)]
