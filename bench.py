@@ -675,7 +675,8 @@ def run_train(args, dist):
               total_steps=1000000, eta=0.3466, micro_queries=mq, dropout_rate=dr, seed=1)
     tag = "T5-large" if large else "monoT5-base"
     cfg_i = 3 if large else 2
-    m = LCEModel(hp, dims=dims, state_dict=random_state_dict(dims, seed=0), cta_group=args.cta_group)
+    opts = dict(kv.split("=") for kv in (args.set_option or []))
+    m = LCEModel(hp, dims=dims, state_dict=random_state_dict(dims, seed=0), cta_group=args.cta_group, options=opts)
     total = args.steps + args.warmup
     nbuf = min(total, 4)
     plab = torch.tensor([[1176, 1]] * Q, dtype=torch.int64)
@@ -750,7 +751,7 @@ def run_train(args, dist):
         "config": {"workload": f"LCE training step, {tag}, 1+{k} docs per query, seq 512 (BASELINE configs[{cfg_i}])",
                    "queries_per_step_per_gpu": Q, "negatives": k, "seq_len": S, "label_tokens": T,
                    "micro_queries": mq if 0 < mq < Q else None,
-                   "dropout_rate": dr,
+                   "dropout_rate": dr, "options": opts or None,
                    "no_grad_forward": ("elided (identical arithmetic at dropout 0); FLOP count uses 3x forward" if dr == 0.0
                                        else "run in train mode with its own masks; FLOP count uses 4x forward"),
                    "optimizer": "AdamW (transformers rule) on flat fp32 masters + eta meta step",
@@ -939,6 +940,8 @@ def main():
     ap.add_argument("--micro-queries", type=int, default=-1,
                     help="train workload: queries per micro-batch (0 = whole batch at once, -1 = config default)")
     ap.add_argument("--ref-train-docs", type=int, default=4)
+    ap.add_argument("--set-option", action="append", metavar="NAME=VALUE",
+                    help="train workload: pn_t5_set_option on the model (A/B runs: dgrad_bf16=0, grad_ranges=1 ...)")
     ap.add_argument("--train-dropout", type=float, default=0.0,
                     help="train workload: dropout_rate (0.1 = the reference's train-mode regime: 4 forwards' worth of work)")
     ap.add_argument("--no-dropout-regime", action="store_true",

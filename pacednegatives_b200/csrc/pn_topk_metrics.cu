@@ -9,6 +9,7 @@
 // C*(4+4+1) input bytes once.  K <= 32 (the nDCG@10 / MRR@10 case) takes the sort-free topk_count_kernel below;
 // larger K sorts the keys with a bitonic network.
 #include "pn_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -331,6 +332,157 @@ topk_count_kernel(const float* __restrict__ scores, const int32_t* __restrict__ 
   }
 }
 
+// ---- K <= 32 and C <= 1024 (the BM25 top-1000 / nDCG@10 case): ONE WARP per query, no block barriers.
+// A lane keeps its 32 candidates' 64-bit keys in registers (coalesced loads, 32 independent loads in flight per lane):
+//   ranks of the relevant documents: rank(d) = #{keys > key_d}: 32 register compares per lane + one REDUX per document
+//   the K best in order: K rounds of {lane-local max over 32 registers, two REDUX for the warp arg-max, winner zeroed}
+//   AP / RR from the ranks, DCG from the winners' grades, ideal DCG from a per-warp grade histogram
+// Per-warp shared memory (12.4 KB): the relevant documents' keys and ranks, the grades by position, the winners.
+// Measured (200 000 queries x 1 000 candidates, 5 % relevant, K = 10; tools/gpu_topk.sh): 3.92 ms against 4.87 ms for
+// the block-per-query kernel above — 464 GB/s of algorithmic bytes.  The pass is instruction-bound, not HBM-bound:
+// ~10 k warp instructions per query, most of them the 64-bit compare-adds of the exact ranks average precision needs
+// (R x C / 32 x 4); giving the compares more instruction-level parallelism (4 documents per pass, tree-shaped local
+// maximum) made it slower (4.40 ms).
+constexpr int kWarpMaxC = 1024;
+constexpr int kWarpsPerCta = 8;
+struct __align__(16) TopkWarpSmem {
+  uint64_t relkey[kWarpMaxC];
+  uint16_t rel_rank[kWarpMaxC];
+  uint8_t srel[kWarpMaxC];
+  uint64_t top[kFastMaxK];
+  int toprel[kFastMaxK];
+  int hist[256];
+};
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 2)
+topk_warp_kernel(const float* __restrict__ scores, const int32_t* __restrict__ docids,
+                 const uint8_t* __restrict__ rels, int64_t Q, int32_t C, int32_t K,
+                 int32_t* __restrict__ top_ids, float* __restrict__ top_scores, float* __restrict__ metrics,
+                 const int32_t* __restrict__ qrel_num, const double* __restrict__ qrel_idcg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  TopkWarpSmem& sm = reinterpret_cast<TopkWarpSmem*>(smem_raw)[warp];
+  for (int i = lane; i < 256; i += 32) sm.hist[i] = 0;
+  __syncwarp();
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  for (int64_t q = (int64_t)blockIdx.x * kWarpsPerCta + warp; q < Q; q += (int64_t)gridDim.x * kWarpsPerCta) {
+    const float* sc = scores + q * (int64_t)C;
+    const int32_t* ids = docids ? docids + q * (int64_t)C : nullptr;
+    const uint8_t* rl = rels ? rels + q * (int64_t)C : nullptr;
+    uint64_t k[32];
+    uint32_t rr[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int i = lane + 32 * j;
+      k[j] = 0ull;
+      rr[j] = 0u;
+      if (i < C) {
+        const int32_t id = ids ? __ldg(ids + i) : i;
+        k[j] = ((uint64_t)orderable(__ldg(sc + i)) << 32) | (uint32_t)(id ^ 0x80000000);
+        rr[j] = rl ? (uint32_t)__ldg(rl + i) : 0u;
+      }
+    }
+    // grades by position, the list of relevant documents (ballot prefix: list order = candidate order), histogram
+    int R = 0;
+    uint32_t gmax = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int i = lane + 32 * j;
+      if (i < C) sm.srel[i] = (uint8_t)rr[j];
+      const uint32_t m = __ballot_sync(0xffffffffu, rr[j] != 0u);
+      if (rr[j] != 0u) {
+        sm.relkey[R + __popc(m & lt_mask)] = k[j];
+        atomicAdd(&sm.hist[rr[j]], 1);
+        gmax = max(gmax, rr[j]);
+      }
+      R += __popc(m);
+    }
+    gmax = __reduce_max_sync(0xffffffffu, gmax);
+    __syncwarp();
+
+    // ranks of the relevant documents (before the winners are zeroed in the registers)
+    if (metrics) {
+      for (int t = 0; t < R; ++t) {
+        const uint64_t kr = sm.relkey[t];
+        int cnt = 0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) cnt += k[j] > kr ? 1 : 0;
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0) sm.rel_rank[t] = (uint16_t)cnt;
+      }
+    }
+
+    // the K best, in order
+    const int rounds = K < C ? K : C;
+    if (lane < kFastMaxK) { sm.top[lane] = 0ull; sm.toprel[lane] = 0; }
+    __syncwarp();
+    for (int rnd = 0; rnd < rounds; ++rnd) {
+      uint64_t lb = 0ull;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) lb = k[j] > lb ? k[j] : lb;
+      const uint32_t whi = __reduce_max_sync(0xffffffffu, (uint32_t)(lb >> 32));
+      const uint32_t wlo = __reduce_max_sync(0xffffffffu, (uint32_t)(lb >> 32) == whi ? (uint32_t)lb : 0u);
+      const uint64_t best = ((uint64_t)whi << 32) | wlo;
+      if (best == 0ull) break;    // fewer than K candidates
+      if (lb == best) {           // exactly one lane: keys are unique (the low word is the document id)
+        int wpos = 0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (k[j] == best) { k[j] = 0ull; wpos = lane + 32 * j; }
+        sm.top[rnd] = best;
+        sm.toprel[rnd] = sm.srel[wpos];
+      }
+    }
+    __syncwarp();
+    if (lane < K) {
+      const uint64_t kk = lane < kFastMaxK ? sm.top[lane] : 0ull;
+      const bool live = kk != 0ull;
+      if (top_ids) top_ids[q * K + lane] = live ? (int32_t)((uint32_t)kk ^ 0x80000000u) : -1;
+      if (top_scores) top_scores[q * K + lane] = live ? unorderable((uint32_t)(kk >> 32)) : 0.0f;
+    }
+    if (metrics) {
+      // average precision and the first relevant rank, lanes over the relevant documents
+      double ap = 0.0;
+      int first = 0x7fffffff;
+      for (int j = lane; j < R; j += 32) {
+        const int rk = sm.rel_rank[j];
+        int upto = 0;
+        for (int t = 0; t < R; ++t) upto += sm.rel_rank[t] <= rk ? 1 : 0;
+        ap += (double)upto / (double)(rk + 1);
+        first = min(first, rk);
+      }
+      ap = pn_warp_sum(ap);
+      first = __reduce_min_sync(0xffffffffu, first);
+      // DCG@K from the winners' grades; ideal DCG@K from the grade histogram, high to low: lane = slot
+      double dcg = 0.0, idcg = 0.0;
+      if (lane < K) {
+        const double disc = 1.0 / log2((double)(lane + 2));
+        if (sm.toprel[lane]) dcg = (double)sm.toprel[lane] * disc;
+        int cum = 0, grade = 0;
+        for (int g = (int)gmax; g >= 1; --g) {
+          cum += sm.hist[g];
+          if (cum > lane) { grade = g; break; }
+        }
+        idcg = (double)grade * disc;
+      }
+      dcg = pn_warp_sum(dcg);
+      idcg = pn_warp_sum(idcg);
+      if (lane == 0) {
+        if (qrel_idcg) idcg = qrel_idcg[q];
+        const int nrel = qrel_num ? qrel_num[q] : R;
+        float* m = metrics + q * 4;
+        m[0] = idcg > 0.0 ? (float)(dcg / idcg) : 0.0f;
+        m[1] = first < C ? (float)(1.0 / (double)(first + 1)) : 0.0f;
+        m[2] = first < K ? (float)(1.0 / (double)(first + 1)) : 0.0f;
+        m[3] = nrel > 0 ? (float)(ap / (double)nrel) : 0.0f;
+      }
+    }
+    __syncwarp();
+    for (int g = 1 + lane; g <= (int)gmax; g += 32) sm.hist[g] = 0;   // only the touched entries
+    __syncwarp();
+  }
+}
+
 }  // namespace
 
 extern "C" int pn_topk_metrics(const float* scores, const int32_t* docids, const uint8_t* rels,
@@ -347,6 +499,21 @@ extern "C" int pn_topk_metrics_qrels(const float* scores, const int32_t* docids,
   PN_CHECK_ARG(Q >= 0 && C >= 1 && C <= 4096 && K >= 1);
   if (Q == 0) return PN_OK;
   PN_CHECK_ARG(scores != nullptr);
+  static const int want_warp = [] { const char* e = getenv("PN_TOPK_WARP"); return e ? atoi(e) : 1; }();
+  if (K <= kFastMaxK && C <= kWarpMaxC && want_warp) {
+    const size_t smem = sizeof(TopkWarpSmem) * kWarpsPerCta;
+    static bool attr_done = false;
+    if (!attr_done) {
+      PN_CUDA(cudaFuncSetAttribute(topk_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_done = true;
+    }
+    const int64_t want = (Q + kWarpsPerCta - 1) / kWarpsPerCta;
+    const int grid = (int)(want < PN_SM_COUNT * 2 ? want : PN_SM_COUNT * 2);
+    topk_warp_kernel<<<grid, kWarpsPerCta * 32, smem, (cudaStream_t)stream>>>(scores, docids, rels, Q, C, K, top_ids,
+                                                                              top_scores, metrics_out, qrel_num, qrel_idcg);
+    PN_LAUNCHED();
+    return PN_OK;
+  }
   if (K <= kFastMaxK) {
     const int Cp = (C + 3) & ~3;
     const size_t smem = (size_t)Cp * (8 + 2 + 2 + 1);

@@ -212,7 +212,7 @@ class MonoT5Scorer:
     """dims: T5Dims; state_dict: {hf_name: tensor} (any float dtype, CPU or CUDA)."""
 
     def __init__(self, dims, state_dict, rel_id=REL_ID, nrel_id=NREL_ID, chunk_docs=128, cta_group=2,
-                 train=False, xattn=True):
+                 train=False, xattn=True, options=None):
         _lib.require_gpu()
         self.dims, self.rel_id, self.nrel_id = dims, int(rel_id), int(nrel_id)
         self.chunk_docs = int(chunk_docs)
@@ -227,6 +227,8 @@ class MonoT5Scorer:
         _lib.check(lib.pn_t5_set_option(self._h, b"xattn", int(bool(xattn))))
         if train:   # also keep the transposed operands of the data-gradient GEMMs (must precede the weights)
             _lib.check(lib.pn_t5_set_option(self._h, b"train", 1))
+        for oname, oval in (options or {}).items():     # pn_t5_set_option: dgrad_bf16, grad_ranges ...
+            _lib.check(lib.pn_t5_set_option(self._h, oname.encode(), int(oval)))
         self.hf_config_base = None      # config.json of the checkpoint the weights came from (from_pretrained)
         known = {n for n, _, _ in self.named_offsets()} | set(_TIED)
         skipped = []
