@@ -80,6 +80,7 @@ struct GemmArgs {
   int batches;
   PnDrop drop;             // dropout on the produced values (thresh 0 = off), see PnGemmExtra
   float out_scale;         // scalar factor folded into the row scale
+  int m_major;             // tile walk: 1 = a CTA (pair) takes whole m-blocks and walks their n-tiles back to back
 };
 
 // kTN = false: C[M,N] = A[M,K] . B[N,K]^T   (both operands K-major: forward and data-gradient GEMMs)
@@ -87,12 +88,15 @@ struct GemmArgs {
 //              the K range is split over args.splits work items per tile, accumulated with fp32 atomics
 // kTmaRes  : PN_EPI_RESID_F32 with the residual tiles moved by TMA (tmC = the fp32 output as 32 x 32 boxes, tmY = the
 //              bf16 copy as 32 x 32 boxes); trades pipeline stages for the 64 KB of epilogue tiles
-template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes>
+// kTmaMask : PN_EPI_BF16 with a ReLU-backward mask (tmY = the mask as 32 x 64 boxes): each epilogue warp receives the
+//              mask tile of its next chunk by TMA while it works on the current one and applies it thread-per-row
+//              while packing (no per-thread global loads, no second pass over the staged tile); costs one stage
+template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes, bool kTmaMask = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmY,
                  const GemmArgs args) {
-  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : EPI_BYTES>;
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES)>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -121,6 +125,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int num_tiles = num_out_tiles * args.splits;            // work items: (k-split, output tile)
   const int total_kb = (args.K + BLOCK_K - 1) / BLOCK_K;
   const int kb_per_split = (total_kb + args.splits - 1) / args.splits;
+  // Work item -> output tile.  Round-robin over tiles (item % num_out_tiles) hands the n-tiles of one 256 x K block
+  // of A to different CTA pairs, which drift apart over the ~80 waves of an M = 512 000 launch until the block has left
+  // L2 between their reads (1.38x the DRAM bytes of the K = 3072 projection, profiles/r1t_ncu_full_summary.md).
+  // m_major: the it-th item of pair g is n-tile (it % n_tiles) of m-block (it / n_tiles) * groups + g, so one pair
+  // reads an A block n_tiles times back to back (and all pairs sweep the B tiles in step); the m-blocks left over
+  // after the full rounds are dealt out tile by tile for balance.  A bijection on [0, num_out_tiles).
+  const int mm_full_rounds = m_tiles / num_groups;
+  const int mm_full_items = mm_full_rounds * n_tiles;              // items per pair in the full rounds
+  auto tile_of = [&](int item) -> int {
+    if (!args.m_major) return item % num_out_tiles;
+    const int it_ = item / num_groups, g_ = item - it_ * num_groups;
+    if (it_ < mm_full_items) return ((it_ / n_tiles) * num_groups + g_) * n_tiles + it_ % n_tiles;
+    return item;   // tail: item >= mm_full_items * num_groups = first tile of the left-over m-blocks
+  };
   auto kb_range = [&](int item, int& kb0, int& kb1) {
     const int sp = item / num_out_tiles;
     kb0 = sp * kb_per_split;
@@ -131,7 +149,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
-    if (kTmaRes) tma_prefetch_desc(&tmY);
+    if (kTmaRes || kTmaMask) tma_prefetch_desc(&tmY);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -142,7 +160,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), 4 * kCtaGroup);  // one arrive per epilogue warp per CTA
     }
-    if (kTmaRes)
+    if (kTmaRes || kTmaMask)
       for (int w = 0; w < 4; ++w)
         for (int b = 0; b < kResBufs; ++b) mbar_init(res_bar(w, b), 1);
     fence_mbar_init();
@@ -161,7 +179,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int s = 0;
     uint32_t ph = 0;
     for (int item = group_id; item < num_tiles; item += num_groups) {
-      const int tile = item % num_out_tiles;
+      const int tile = tile_of(item);
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
       const int m0 = m_blk * tile_m + (int)cta_rank * BLOCK_M;
       int n0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;
@@ -257,7 +275,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tma_load_2d(wbase + b * EPI_BUF_BYTES, &tmC, res_bar(ew, b), c0, r0);
     };
     auto tile_origin = [&](int item, int& r0, int& c0) {
-      const int tile = item % num_out_tiles;
+      const int tile = tile_of(item);
       r0 = (tile / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
       c0 = (tile % n_tiles) * BLOCK_N;
     };
@@ -270,7 +288,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int it = 0;
     uint32_t q = 0;
     for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
-      const int tile = item % num_out_tiles;
+      const int tile = tile_of(item);
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
@@ -373,8 +391,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int rrow = lane >> 3, rj = lane & 7;        // read-back mapping: iteration i -> row 4*i + rrow, chunk rj
     int it = 0;
     uint32_t cc = 0;                                  // chunks staged so far (buffer = cc & 1)
+    // kTmaMask: two 4 KB mask tiles per warp behind the staging tiles; the tile of chunk cc + 1 is requested while
+    // chunk cc is processed (its mbarrier: res_bar(ew, (cc + 1) & 1), phase ((cc + 1) >> 1) & 1)
+    const uint32_t mstage0 = epi_smem + 4 * (2 * EPI_BUF_BYTES) + ew * (2 * EPI_BUF_BYTES);
+    auto load_mask_tile = [&](uint32_t b, int r0, int c0) {
+      mbar_arrive_expect_tx(res_bar(ew, b), EPI_BUF_BYTES);
+      tma_load_2d(mstage0 + b * EPI_BUF_BYTES, &tmY, res_bar(ew, b), c0, r0);
+    };
+    auto warp_origin = [&](int item_, int& r0, int& c0) {
+      const int t_ = tile_of(item_);
+      r0 = (t_ / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
+      c0 = (t_ % n_tiles) * BLOCK_N;
+    };
+    if (kTmaMask && lane == 0 && group_id < num_tiles) {
+      int r0, c0;
+      warp_origin(group_id, r0, c0);
+      load_mask_tile(0, r0, c0);
+    }
     for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
-      const int tile = item % num_out_tiles;
+      const int tile = tile_of(item);
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
@@ -392,7 +427,57 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
       const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N;
-      if (args.mode == PN_EPI_BF16) {
+      if (kTmaMask) {
+        int nrow0 = 0, ncol0 = 0;
+        const bool nvalid = item + num_groups < num_tiles;
+        if (nvalid) warp_origin(item + num_groups, nrow0, ncol0);
+        mbar_wait(tfull_bar(as), aph);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 64; ++c, ++cc) {
+          const uint32_t buf = stage0 + (cc & 1) * EPI_BUF_BYTES;
+          const uint32_t mbuf = mstage0 + (cc & 1) * EPI_BUF_BYTES + lane * 128;
+          uint32_t v0[32], v1[32];
+          tmem_ld_32x32(t_row + c * 64, v0);
+          tmem_ld_32x32(t_row + c * 64 + 32, v1);
+          if (lane == 0) tma_store_wait_read<1>();   // the store that used this staging buffer two chunks ago has drained
+          __syncwarp();                              // ... and every lane is done with the other mask tile (chunk cc - 1)
+          if (lane == 0) {
+            if (c + 1 < BLOCK_N / 64) load_mask_tile((cc + 1) & 1, row0, col0 + (c + 1) * 64);
+            else if (nvalid) load_mask_tile((cc + 1) & 1, nrow0, ncol0);
+          }
+          mbar_wait(res_bar(ew, cc & 1), (cc >> 1) & 1);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t(&v)[32] = j < 4 ? v0 : v1;
+            uint32_t mk0, mk1, mk2, mk3;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(mk0), "=r"(mk1), "=r"(mk2), "=r"(mk3)
+                         : "r"(mbuf + ((j ^ swz) << 4)));
+            const uint32_t mk[4] = {mk0, mk1, mk2, mk3};
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float x0 = __uint_as_float(v[(j & 3) * 8 + 2 * e]) * rs;
+              const float x1 = __uint_as_float(v[(j & 3) * 8 + 2 * e + 1]) * rs;
+              __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+              // the mask holds ReLU outputs (>= 0): positive <=> any magnitude bit set
+              pk[e] = *reinterpret_cast<uint32_t*>(&h) &
+                      (((mk[e] & 0x00007fffu) ? 0x0000ffffu : 0u) | ((mk[e] & 0x7fff0000u) ? 0xffff0000u : 0u));
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * 128 + ((j ^ swz) << 4)),
+                         "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                         : "memory");
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC, buf, col0 + c * 64, row0);   // rows beyond M are clipped by the tensor map
+            tma_store_commit();
+          }
+        }
+      } else if (args.mode == PN_EPI_BF16) {
         // ReLU-backward mask: read with the coalesced mapping (lanes 0..7 = the eight 16-byte pieces of one 128-byte
         // row, four rows per instruction: 4 L1 wavefronts instead of the 32 of a thread-per-row read) and applied to
         // the staged tile in shared memory just before the TMA store.  The mask of the NEXT chunk is requested a
@@ -629,9 +714,9 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
                       row_stride_elems, box_rows, box_cols);
 }
 
-template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes = false>
+template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes = false, bool kTmaMask = false>
 static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs args, cudaStream_t st) {
-  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : EPI_BYTES>;
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES)>;
   CUtensorMap tmA, tmB;
   int rc;
   if (!kTN) {
@@ -667,7 +752,11 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
       if (rc) return rc;
     }
   }
-  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N, kTN, kTmaRes>;
+  if (kTmaMask) {   // the ReLU-backward mask as 32-row x 64-column boxes (the layout of the staged output tile)
+    rc = pn_make_tmap_bf16_2d(&tmY, args.mask, args.M, args.N, args.ld_mask, 32, 64);
+    if (rc) return rc;
+  }
+  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N, kTN, kTmaRes, kTmaMask>;
   static bool attr_done = false;
   if (!attr_done) {
     PN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -690,6 +779,11 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
   }
   int groups = max_groups;
   if (tiles * args.splits < groups) groups = tiles * args.splits;
+  // measured and left OFF (profiles/r4o_gemm_ab.txt, same box): re-rank 8 087 against 8 523 pairs/s, training 110.3
+  // against 108.0 ms — with every pair sweeping the same B tile at the same moment the weight tiles become an L2 hot
+  // spot, which costs more than the A re-reads it removes
+  static const int want_mmajor = [] { const char* e = getenv("PN_GEMM_MMAJOR"); return e ? atoi(e) : 0; }();
+  args.m_major = (!kTN && args.splits == 1 && want_mmajor) ? 1 : 0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(groups * kCtaGroup);
   cfg.blockDim = dim3(kGemmThreads);
@@ -824,6 +918,13 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   if (tma_res && (epi_bound || tma_res == 2) && mode == PN_EPI_RESID_F32 && cta_group == 2 && n256 && (ldc % 4) == 0 &&
       (!a.copy_out || ((a.ld_copy % 8) == 0 && ((uintptr_t)a.copy_out & 15) == 0)))
     return launch_gemm<2, 256, false, true>(A, lda, B, ldb, a, st);
+  // masked (ReLU-backward) epilogue with the mask tile moved by TMA: the FFN data gradient [131072 x 768] x [768 x 3072]
+  // took 704 us with the register path against 443 us for the same-shape forward GEMM (profiles/r4n_train_launches*);
+  // same-box A/B of the training step: 110.1 / 110.4 ms with it, 113.1 / 112.0 ms without (profiles/r4o_gemm_ab.txt).
+  // PN_GEMM_TMA_MASK=0 keeps the register path.
+  static const int tma_mask = [] { const char* e = getenv("PN_GEMM_TMA_MASK"); return e ? atoi(e) : 1; }();
+  if (tma_mask && a.mask && mode == PN_EPI_BF16 && cta_group == 2 && n256 && !relu && !a.drop.thresh)
+    return launch_gemm<2, 256, false, false, true>(A, lda, B, ldb, a, st);
   if (cta_group == 2) {
     return n256 ? launch_gemm<2, 256, false>(A, lda, B, ldb, a, st) : launch_gemm<2, 128, false>(A, lda, B, ldb, a, st);
   } else if (cta_group == 1) {
