@@ -1,13 +1,10 @@
 #!/bin/bash
-# Round-end check: every GPU test, smoke, and the bench lines of BASELINE configs[1..4].  Usage: tools/gpu_final.sh <tag>
-TAG=${1:-r2d}
+# what the driver runs at round end: pytest -m gpu -x, smoke(), default bench, reference arm
+TAG=${1:-r4p}
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -q > gpurun_out/${TAG}_tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/${TAG}_tests.log
-tail -3 gpurun_out/${TAG}_tests.log
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/${TAG}_smoke.log
-python bench.py --steps 5 --warmup 3 > gpurun_out/${TAG}_bench_rerank.json 2> gpurun_out/${TAG}_bench_rerank.err; echo "rerank rc=$?"
-python bench.py --workload train --steps 10 --warmup 3 > gpurun_out/${TAG}_bench_train.json 2> gpurun_out/${TAG}_bench_train.err; echo "train rc=$?"
-python bench.py --workload train --model large --steps 3 --warmup 3 > gpurun_out/${TAG}_bench_train_large.json 2> gpurun_out/${TAG}_bench_train_large.err; echo "large rc=$?"
-python bench.py --impl reference --steps 1 --warmup 1 > gpurun_out/${TAG}_bench_rerank_reference.json 2> gpurun_out/${TAG}_bench_rerank_reference.err; echo "ref rc=$?"
-python bench.py --workload select --steps 5 --warmup 3 > gpurun_out/${TAG}_bench_select.json 2> gpurun_out/${TAG}_bench_select.err; echo "select rc=$?"
-for f in rerank train train_large rerank_reference select; do head -c 330 gpurun_out/${TAG}_bench_$f.json; echo; done
+timeout 1200 python -m pytest tests -x -q -m gpu > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/${TAG}_pytest.log | cut -c1-300
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/${TAG}_smoke.log
+timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench rc=$?"
+head -c 1500 gpurun_out/${TAG}_bench.json; echo
+timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err; echo "reference rc=$?"
+head -c 700 gpurun_out/${TAG}_bench_reference.json; echo
