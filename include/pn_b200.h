@@ -215,6 +215,28 @@ int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* o
 int pn_gemm_bf16_wgrad(const void* A, int64_t lda, const void* B, int64_t ldb, float* out, int64_t ldc,
                        int64_t M, int64_t N, int64_t K, int cta_group, void* stream);
 
+/* Building blocks of the fused RMSNorm backward of the encoder's normed linears (autograd of HF modeling_t5.py:55-69
+ * followed by :298-299 / :92-95 under lceT5.py:155 manual_backward; DESIGN.md section 4 "norm backward").
+ * With y = rs h W'^T the forward output of a normed linear and Ys its scaled output gradient,
+ *   dh = Ys W' - coef h,   coef[row] = rs^2 <Ys W', h> / d = rs <Ys, y> / d :
+ * the row dot is known before the data-gradient product is formed, from the kernels that produce Ys.
+ *
+ * pn_gemm_bf16_relu_bwd: out bf16 [M, ldc] = row_scale[row]? * (dY[M,K] . Wt[N,K]^T) where act[row, col] > 0, else 0
+ *   (ReLU backward of the FFN's first linear; act = the saved forward activation, bf16 [M, ld_act]); dot_out
+ *   (nullable) fp32 [N / 256][M] receives the per-256-column partial sums of out[row, col] * act[row, col].
+ *   2-CTA tiles only: N % 256 == 0, K % 64 == 0, 16-byte aligned operands. */
+int pn_gemm_bf16_relu_bwd(const void* dY, int64_t ld_dy, const void* Wt, int64_t ldw, const void* act, int64_t ld_act,
+                          const float* row_scale, void* out, int64_t ldc, float* dot_out, int64_t M, int64_t N,
+                          int64_t K, void* stream);
+/* pn_gemm_bf16_norm_bwd: dh fp32 [M, ld_dh] += Ys[M,K] . Wt[N,K]^T - coef[row] * hb[row, col]; dhb bf16 [M, ld_dhb] =
+ *   the updated dh.  hb bf16 [M, ld_hb] is the residual stream the norm read.  Same shape limits. */
+int pn_gemm_bf16_norm_bwd(const void* Ys, int64_t ld_ys, const void* Wt, int64_t ldw, const void* hb, int64_t ld_hb,
+                          const float* coef, float* dh, int64_t ld_dh, void* dhb, int64_t ld_dhb, int64_t M, int64_t N,
+                          int64_t K, void* stream);
+/* coef[row] = rs[row] * sum_p part[p * rows + row] / d */
+int pn_t5_norm_coef(const float* part, int32_t parts, const float* rs, int64_t rows, int32_t d, float* coef,
+                    void* stream);
+
 /* T5 encoder self-attention (HF modeling_t5.py:308-336): out = softmax(Q K^T + bias[h, j-i]) V per
  * (document, head), no 1/sqrt(d) scaling, d_kv = 64, S <= 512, no mask.  qkv bf16 [docs*S, 3*H*64] holds
  * q | k | v column blocks; bias fp32 [H, 1023] indexed by (j - i + 511); out bf16 [docs*S, H*64]. */
@@ -234,6 +256,12 @@ int pn_t5_self_attention_lse(const void* qkv, int32_t docs, int32_t S, int32_t n
 int pn_t5_self_attention_bwd(const void* qkv, int32_t docs, int32_t S, int32_t n_heads, const float* bias,
                              const void* ctx, const void* dctx, const float* lse2, const float* row_scale,
                              void* dqkv, float* dbias_diag, float* dvec_ws, void* stream);
+
+/* pn_t5_self_attention_bwd that also leaves, in dot_out fp32 [4 * n_heads][docs * S], partial row sums of
+ * dqkv[row, :] * qkv[row, :] (the row dot of the RMSNorm backward behind the qkv projection; sum the planes). */
+int pn_t5_self_attention_bwd_dot(const void* qkv, int32_t docs, int32_t S, int32_t n_heads, const float* bias,
+                                 const void* ctx, const void* dctx, const float* lse2, const float* row_scale,
+                                 void* dqkv, float* dbias_diag, float* dvec_ws, float* dot_out, void* stream);
 
 /* Allocation-free variant of pn_t5_self_attention_bwd.  It has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight

@@ -44,6 +44,13 @@ SIGNATURES = {
     "pn_gemm_bf16": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_int,
                              c_vp, c_int, c_vp]),
     "pn_gemm_bf16_wgrad": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_vp]),
+    "pn_gemm_bf16_relu_bwd": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_i64,
+                                      c_i64, c_vp]),
+    "pn_gemm_bf16_norm_bwd": (c_int, [c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_i64,
+                                      c_i64, c_i64, c_vp]),
+    "pn_t5_norm_coef": (c_int, [c_vp, c_i32, c_vp, c_i64, c_i32, c_vp, c_vp]),
+    "pn_t5_self_attention_bwd_dot": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                             c_vp, c_vp, c_vp]),
     "pn_t5_self_attention": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "pn_t5_self_attention_lse": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "pn_t5_self_attention_bwd": (c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,

@@ -74,4 +74,26 @@ __device__ __forceinline__ void pn_drop_mul2(const PnDrop& d, unsigned long long
   m0 = (h & 0xffffu) < d.thresh ? d.scale : 0.0f;
   m1 = (h >> 16) < d.thresh ? d.scale : 0.0f;
 }
+// Row form for kernels that walk a run of consecutive elements (an attention row chunk): when the run's pair indices
+// [pair0, pair0 + n_pairs) share their high 32 bits — always, except for one run in 2^32 pairs — the inner hash of
+// pn_drop_bits is the same for the whole run and is folded into the key once.  Same bits as pn_drop_mul2.
+struct PnDropRun {
+  uint32_t k;        // key_lo ^ mix32(hi32(pair0) ^ key_hi)
+  uint32_t lo0;      // lo32(pair0)
+  bool fast;         // false: the run crosses a 2^32 pair boundary, use pn_drop_mul2 on the full index
+};
+__device__ __forceinline__ PnDropRun pn_drop_run(const PnDrop& d, unsigned long long idx_even0, uint32_t n_pairs) {
+  const unsigned long long pair0 = idx_even0 >> 1;
+  PnDropRun r;
+  r.lo0 = (uint32_t)pair0;
+  r.k = d.key_lo ^ pn_mix32((uint32_t)(pair0 >> 32) ^ d.key_hi);
+  r.fast = r.lo0 <= 0xffffffffu - n_pairs;
+  return r;
+}
+// multipliers of elements (idx_even0 + 2 t, idx_even0 + 2 t + 1) of a fast run
+__device__ __forceinline__ void pn_drop_run_mul2(const PnDrop& d, const PnDropRun& r, uint32_t t, float& m0, float& m1) {
+  const uint32_t h = pn_mix32((r.lo0 + t) ^ r.k);
+  m0 = (h & 0xffffu) < d.thresh ? d.scale : 0.0f;
+  m1 = (h >> 16) < d.thresh ? d.scale : 0.0f;
+}
 #endif

@@ -365,6 +365,10 @@ extern "C" int pn_t5_set_option(PnT5* m, const char* name, int64_t value) {
     m->dgrad_bf16 = value != 0;
     return PN_OK;
   }
+  if (!strcmp(name, "fuse_norm_bwd")) {   // 0: the encoder's RMSNorm backward runs as its own bandwidth pass
+    m->fuse_norm_bwd = value != 0;
+    return PN_OK;
+  }
   if (!strcmp(name, "grad_ranges")) {   // encoder layer groups handed to the gradient hook separately
     PN_CHECK_ARG(value >= 1 && value <= 64);
     m->grad_ranges = (int)value;

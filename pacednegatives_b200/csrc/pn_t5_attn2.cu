@@ -365,6 +365,13 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
         dbase = (unsigned long long)a.drop.idx_offset +
                 ((unsigned long long)((doc0 + it * a.cph) * a.n_heads + head) * S + (qi < S ? qi : 0)) * (S + (S & 1)) +
                 c * KC;
+      // the chunk's KC / 2 index pairs share their inner hash (pn_drop_run); one row in 2^32 pairs does not
+      PnDropRun drun = {};
+      bool dfast = true;
+      if (kDrop) {
+        drun = pn_drop_run(a.drop, dbase, KC / 2);
+        dfast = __all_sync(0xffffffffu, drun.fast);
+      }
       float nm = -m_used;
       uint64_t nm2 = f2pack(nm, nm);
       uint64_t lsa = f2pack(0.0f, 0.0f), lsb = lsa;
@@ -405,8 +412,13 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
           lsb = add2(lsb, f2pack(p2, p3));
           if (dropping) {
             float m0, m1, m2, m3;
-            pn_drop_mul2(a.drop, dbase + jj, m0, m1);
-            pn_drop_mul2(a.drop, dbase + jj + 2, m2, m3);
+            if (dfast) {
+              pn_drop_run_mul2(a.drop, drun, jj >> 1, m0, m1);
+              pn_drop_run_mul2(a.drop, drun, (jj >> 1) + 1, m2, m3);
+            } else {
+              pn_drop_mul2(a.drop, dbase + jj, m0, m1);
+              pn_drop_mul2(a.drop, dbase + jj + 2, m2, m3);
+            }
             pk[e] = pack_bf16x2(p0 * m0, p1 * m1);
             pk[e + 1] = pack_bf16x2(p2 * m2, p3 * m3);
           } else {

@@ -59,6 +59,9 @@ struct BwdArgs {
   int ld;
   float* dbias_diag;                // [H, 1023] += per-diagonal sums (MODE 0 only)
   PnDrop drop;                      // dropout of the probabilities in the forward (HF:331), regenerated here
+  const __nv_bfloat16* qkv;         // the forward's q | k | v rows (same layout as dqkv), read only when dot_out is set
+  float* dot_out;                   // nullable [4 * H][dot_stride]: partial row sums of dqkv * qkv (see internal.cuh)
+  long long dot_stride;
 };
 
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
@@ -116,7 +119,7 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
     mbar_init(bar(B_RES_FULL), 1);
-    mbar_init(bar(B_RES_FREE), 1);
+    mbar_init(bar(B_RES_FREE), a.dot_out ? 8 : 1);   // row dots: the compute warps read the resident tiles last
     mbar_init(bar(B_STR_FULL0), 1);
     mbar_init(bar(B_STR_FULL1), 1);
     mbar_init(bar(B_STR_EMPTY0), 1);
@@ -250,7 +253,7 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         umma_commit<1>(bar(B_STR_EMPTY0 + (g & 1)));
         if (t == nb - 1) {
           umma_commit<1>(bar(B_ACC_FULL));
-          umma_commit<1>(bar(B_RES_FREE));
+          if (!a.dot_out) umma_commit<1>(bar(B_RES_FREE));
         }
       }
       __syncwarp();
@@ -309,6 +312,12 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const unsigned long long dbase =
             (unsigned long long)a.drop.idx_offset +
             ((unsigned long long)(item_doc(it) * a.n_heads + head) * S + (qi < S ? qi : 0)) * (S + (S & 1)) + k0;
+        PnDropRun drun = {};
+        bool dfast = true;
+        if (dropping) {   // the 32 index pairs of this thread's 64 keys share their inner hash (pn_drop_run)
+          drun = pn_drop_run(a.drop, dbase, 32);
+          dfast = __all_sync(0xffffffffu, drun.fast);
+        }
         mbar_wait(bar(B_SP_FULL), g & 1);
         tc_fence_after();
         uint32_t pp[32], pd[32];                    // P and dS of this thread's 64 columns, packed bf16
@@ -344,7 +353,8 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 uint64_t dpv = f2pack(__uint_as_float(dp[j + 2 * h2]), __uint_as_float(dp[j + 2 * h2 + 1]));
                 float m0 = 1.0f, m1 = 1.0f;
                 if (dropping) {
-                  pn_drop_mul2(a.drop, dbase + c2 * 32 + j + 2 * h2, m0, m1);
+                  if (dfast) pn_drop_run_mul2(a.drop, drun, (c2 * 32 + j + 2 * h2) >> 1, m0, m1);
+                  else pn_drop_mul2(a.drop, dbase + c2 * 32 + j + 2 * h2, m0, m1);
                   dpv = mul2(dpv, f2pack(m0, m1));
                 }
                 const uint64_t dsv = mul2(f2pack(p0, p1), add2(dpv, ndv2));
@@ -398,6 +408,25 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
 
         if (t == nb - 1) {
           // ---- item epilogue: dV, dK of key block ob (MODE 0) or dQ of query block ob (MODE 1)
+          // row-dot operands: the forward's v | k (MODE 0) or q (MODE 1) values of this thread's 32 columns, read from
+          // the resident tiles (row r, 16-byte chunks half*4 .. half*4+3 under the 128-byte swizzle: conflict-free,
+          // where the same bytes from global memory would be 32 sectors per instruction).  With dot_out set the
+          // resident pair is released by these warps instead of by the last MMA's commit.
+          uint4 xq[4], yq[4];
+          if (a.dot_out) {
+            mbar_wait(bar(B_RES_FULL), it & 1);   // completed long ago: orders these reads after the TMA writes
+            const uint32_t t0 = base + SM_RES + (MODE == 0 ? TILE_BYTES : 0) + r * 128;
+            const uint32_t t1 = base + SM_RES + r * 128;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t ch = (uint32_t)(((half * 4 + j) ^ (r & 7)) << 4);
+              asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(xq[j].x), "=r"(xq[j].y), "=r"(xq[j].z), "=r"(xq[j].w) : "r"(t0 + ch));
+              if (MODE == 0)
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(yq[j].x), "=r"(yq[j].y), "=r"(yq[j].z), "=r"(yq[j].w) : "r"(t1 + ch));
+            }
+          }
           mbar_wait(bar(B_ACC_FULL), it & 1);
           tc_fence_after();
           uint32_t a0[32], a1[32];
@@ -406,13 +435,41 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           tmem_ld_wait();
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(bar(B_ACC_FREE));
+          if (lane == 0) {
+            mbar_arrive(bar(B_ACC_FREE));
+            if (a.dot_out) mbar_arrive(bar(B_RES_FREE));   // MMAs done (B_ACC_FULL) and this warp's reads too
+          }
           const int oi = ob * BLK + r;
           if (oi < S) {
             const size_t grow = (size_t)(row0 + oi);
             const float sc = a.row_scale ? a.row_scale[grow] : 1.0f;
             __nv_bfloat16* dst0 = a.dqkv + grow * a.ld + (MODE == 0 ? a.v_col : a.q_col) + head * DK + half * 32;
             __nv_bfloat16* dst1 = a.dqkv + grow * a.ld + a.k_col + head * DK + half * 32;
+            if (a.dot_out) {
+              // <dq, q> (MODE 1) or <dv, v> + <dk, k> (MODE 0) over this thread's 32 columns: with the forward's
+              // q | k | v = rs h W'^T these sums are the row dot <G, h> of the norm behind the projection
+              float ds = 0.0f;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const uint4 x = xq[j];
+                const uint32_t xw[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  ds = fmaf(__uint_as_float(a0[8 * j + 2 * e]), __uint_as_float(xw[e] << 16), ds);
+                  ds = fmaf(__uint_as_float(a0[8 * j + 2 * e + 1]), __uint_as_float(xw[e] & 0xffff0000u), ds);
+                }
+                if (MODE == 0) {
+                  const uint4 y = yq[j];
+                  const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    ds = fmaf(__uint_as_float(a1[8 * j + 2 * e]), __uint_as_float(yw[e] << 16), ds);
+                    ds = fmaf(__uint_as_float(a1[8 * j + 2 * e + 1]), __uint_as_float(yw[e] & 0xffff0000u), ds);
+                  }
+                }
+              }
+              a.dot_out[(size_t)((MODE * a.n_heads + head) * 2 + half) * a.dot_stride + grow] = ds * sc;
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint4 u;
@@ -582,7 +639,7 @@ __global__ void rel_bias_grad_kernel(const float* __restrict__ diag, const int* 
 int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, int v_col, int docs, int S,
                         int n_heads, const float* bias, const __nv_bfloat16* ctx, const __nv_bfloat16* dctx,
                         int ld_ctx, const float* lse2, float* dvec, const float* row_scale,
-                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st, PnDrop drop) {
+                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st, PnDrop drop, float* dot_out) {
   if (S < 1 || S > MAX_S) return pn_fail(PN_E_UNSUPPORTED, "self-attention backward: S=%d not in [1,512]", S);
   if (docs <= 0) return PN_OK;
   const int64_t rows = (int64_t)docs * S;
@@ -612,6 +669,7 @@ int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, 
   a.bias = bias; a.lse2 = lse2; a.dvec = dvec; a.row_scale = row_scale;
   a.dqkv = dqkv; a.ld = ld; a.dbias_diag = dbias_diag;
   a.drop = drop;
+  a.qkv = qkv; a.dot_out = dot_out; a.dot_stride = rows;
   // five [128 x 128 x 64] products per (query block, key block) pair, S and dP formed twice
   PnProfScope prof(PN_PROF_ATTN_BWD, 14.0 * docs * n_heads * (double)S * S * DK, st);
   auto launched = [&](const void* fn, const char* which) -> int {
@@ -659,6 +717,18 @@ extern "C" int pn_t5_self_attention_bwd(const void* qkv, int32_t docs, int32_t S
   return pn_t5_self_attn_bwd((const __nv_bfloat16*)qkv, 3 * di, 0, di, 2 * di, docs, S, n_heads, bias,
                              (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, di, lse2, dvec_ws,
                              row_scale, (__nv_bfloat16*)dqkv, dbias_diag, (cudaStream_t)stream);
+}
+
+extern "C" int pn_t5_self_attention_bwd_dot(const void* qkv, int32_t docs, int32_t S, int32_t n_heads,
+                                            const float* bias, const void* ctx, const void* dctx,
+                                            const float* lse2, const float* row_scale, void* dqkv,
+                                            float* dbias_diag, float* dvec_ws, float* dot_out, void* stream) {
+  PN_CHECK_ARG(qkv && bias && ctx && dctx && lse2 && dqkv && dbias_diag && dvec_ws && dot_out && docs >= 0 &&
+               n_heads > 0);
+  const int di = n_heads * DK;
+  return pn_t5_self_attn_bwd((const __nv_bfloat16*)qkv, 3 * di, 0, di, 2 * di, docs, S, n_heads, bias,
+                             (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, di, lse2, dvec_ws,
+                             row_scale, (__nv_bfloat16*)dqkv, dbias_diag, (cudaStream_t)stream, PnDrop(), dot_out);
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -35,6 +35,11 @@ constexpr int RES_Y_BYTES = 32 * 64;
 constexpr int RES_WARP_BYTES = kResBufs * EPI_BUF_BYTES + 2 * RES_Y_BYTES;   // 24 KB
 constexpr int EPI_BYTES_TMA = 4 * RES_WARP_BYTES;                             // 96 KB: 4 pipeline stages left
 static_assert(8 * (2 * 8 + 5 + 4 * kResBufs) <= 512, "barrier area");
+// Norm-backward residual epilogue (kNormRes = ring depth): per warp kNormRes fp32 tiles + as many bf16 tiles of the
+// normed stream + the two bf16 copy tiles.  3 buffers = 22 KB per warp, 88 KB: 4 pipeline stages, as the plain TMA
+// residual path; 4 buffers = 28 KB per warp, 112 KB: 3 stages.  PN_NORM_BUFS (environment) picks, default 3.
+__host__ __device__ constexpr int norm_warp_bytes(int bufs) { return bufs * (EPI_BUF_BYTES + RES_Y_BYTES) + 2 * RES_Y_BYTES; }
+static_assert(4 <= kResBufs && norm_warp_bytes(3) % 1024 == 0 && norm_warp_bytes(4) % 1024 == 0, "norm-backward epilogue tiles");
 
 template <int kCtaGroup, int BLOCK_N, int kEpiBytes = EPI_BYTES>
 struct GemmCfg {
@@ -81,6 +86,10 @@ struct GemmArgs {
   PnDrop drop;             // dropout on the produced values (thresh 0 = off), see PnGemmExtra
   float out_scale;         // scalar factor folded into the row scale
   int m_major;             // tile walk: 1 = a CTA (pair) takes whole m-blocks and walks their n-tiles back to back
+  float* dot_out;          // masked bf16 epilogue, nullable: [N / BLOCK_N][ss_stride] row sums of out * mask
+  const float* nb_coef;    // kNormRes: out += acc - nb_coef[row] * hb[row, col]
+  const __nv_bfloat16* nb_hb;
+  int ld_hb;
 };
 
 // kTN = false: C[M,N] = A[M,K] . B[N,K]^T   (both operands K-major: forward and data-gradient GEMMs)
@@ -91,12 +100,16 @@ struct GemmArgs {
 // kTmaMask : PN_EPI_BF16 with a ReLU-backward mask (tmY = the mask as 32 x 64 boxes): each epilogue warp receives the
 //              mask tile of its next chunk by TMA while it works on the current one and applies it thread-per-row
 //              while packing (no per-thread global loads, no second pass over the staged tile); costs one stage
-template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes, bool kTmaMask = false>
+// kNormRes : PN_EPI_RESID_F32 of the data gradient of a normed linear with the RMSNorm backward folded in (tmC, tmY as
+//              kTmaRes, tmH = the bf16 stream the norm read as 32 x 32 boxes): out += acc - coef[row] * hb[row, col]
+template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes, bool kTmaMask = false, int kNormRes = 0>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmY,
-                 const GemmArgs args) {
-  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES)>;
+                 const __grid_constant__ CUtensorMap tmH, const GemmArgs args) {
+  static_assert(!(kNormRes && (kTmaRes || kTmaMask)), "one epilogue variant per instantiation");
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N,
+                      kNormRes ? 4 * norm_warp_bytes(kNormRes) : (kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES))>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -149,7 +162,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
-    if (kTmaRes || kTmaMask) tma_prefetch_desc(&tmY);
+    if (kTmaRes || kTmaMask || kNormRes) tma_prefetch_desc(&tmY);
+    if (kNormRes) tma_prefetch_desc(&tmH);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -160,7 +174,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), 4 * kCtaGroup);  // one arrive per epilogue warp per CTA
     }
-    if (kTmaRes || kTmaMask)
+    if (kTmaRes || kTmaMask || kNormRes)
       for (int w = 0; w < 4; ++w)
         for (int b = 0; b < kResBufs; ++b) mbar_init(res_bar(w, b), 1);
     fence_mbar_init();
@@ -254,6 +268,135 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       umma_commit<kCtaGroup>(tfull_bar(as));   // accumulator ready (signalled in both CTAs)
     }
+  } else if (warp >= 4 && kNormRes) {
+    // ===================== norm-backward residual epilogue =====================
+    // dh[row, col] += acc - coef[row] * hb[row, col] and the bf16 copy of the updated dh: the RMSNorm backward of a
+    // normed linear finished inside its data-gradient GEMM.  Structure of the TMA residual epilogue below; every
+    // ring slot holds the fp32 dh tile and the bf16 tile of the stream the norm read, both on the slot's mbarrier.
+    const int ew = warp - 4;
+    constexpr int kChunks = BLOCK_N / 32;
+    constexpr int RB = kNormRes ? kNormRes : 1;
+    const uint32_t wbase = epi_smem + ew * norm_warp_bytes(RB);
+    const uint32_t hbase = wbase + RB * EPI_BUF_BYTES;
+    const uint32_t ybase = hbase + RB * RES_Y_BYTES;
+    const uint32_t swz = (uint32_t)(lane & 7), yswz = (uint32_t)((lane >> 1) & 3);
+    static_assert(RB - 1 <= kChunks, "prefetch distance reaches at most into the next tile");
+    auto load_tile = [&](uint32_t b, int r0, int c0) {
+      mbar_arrive_expect_tx(res_bar(ew, b), EPI_BUF_BYTES + RES_Y_BYTES);
+      tma_load_2d(wbase + b * EPI_BUF_BYTES, &tmC, res_bar(ew, b), c0, r0);
+      tma_load_2d(hbase + b * RES_Y_BYTES, &tmH, res_bar(ew, b), c0, r0);
+    };
+    auto tile_origin = [&](int item, int& r0, int& c0) {
+      const int tile = tile_of(item);
+      r0 = (tile / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
+      c0 = (tile % n_tiles) * BLOCK_N;
+    };
+    if (lane == 0 && group_id < num_tiles) {
+      int r0, c0;
+      tile_origin(group_id, r0, c0);
+      for (int i = 0; i + 1 < RB; ++i) load_tile(i, r0, c0 + i * 32);
+    }
+    uint32_t rb = 0, rph = 0;
+    int it = 0;
+    uint32_t q = 0;
+    for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
+      const int tile = tile_of(item);
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int row0 = m_blk * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
+      const int row = row0 + lane;
+      const int col0 = n_blk * BLOCK_N;
+      const bool live = row < args.M;
+      float rs = args.out_scale;
+      if (live && args.row_scale) rs *= args.row_scale[row];
+      const float nk = live ? -args.nb_coef[row] : 0.0f;
+      const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + as * BLOCK_N;
+      int nrow0 = 0, ncol0 = 0;
+      const bool nvalid = item + num_groups < num_tiles;
+      if (nvalid) tile_origin(item + num_groups, nrow0, ncol0);
+      mbar_wait(tfull_bar(as), aph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < kChunks; ++c, ++q) {
+        const uint32_t rbuf = wbase + rb * EPI_BUF_BYTES + lane * 128;
+        const uint32_t hbuf = hbase + rb * RES_Y_BYTES + lane * 64;
+        const uint32_t ybuf = ybase + (q & 1) * RES_Y_BYTES + lane * 64;
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + c * 32, v);
+        mbar_wait(res_bar(ew, rb), rph);
+        tmem_ld_wait();
+        __syncwarp();   // lane 0 has seen the store of chunk q - 2 drain before ybuf is rewritten
+        // args.drop: dropout mask of the PREVIOUS sub-layer's output, applied to the bf16 copy only (the copy is the
+        // gradient of that sub-layer's linear output; dh itself is the gradient of the stream and stays unmasked)
+        PnDropRun drun = {};
+        unsigned long long dbase = 0;
+        if (args.drop.thresh) {
+          dbase = (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N + (col0 + c * 32);
+          drun = pn_drop_run(args.drop, dbase, 16);
+        }
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          uint32_t hw[4];   // 8 bf16 of the normed stream: 64-byte rows, piece p of row r at p ^ ((r >> 1) & 3)
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(hw[0]), "=r"(hw[1]), "=r"(hw[2]), "=r"(hw[3])
+                       : "r"(hbuf + ((p ^ yswz) << 4)));
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {
+            const int j = 2 * p + jj;
+            const uint32_t addr = rbuf + ((j ^ swz) << 4);
+            float4 h;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(h.x), "=f"(h.y), "=f"(h.z), "=f"(h.w) : "r"(addr));
+            const uint32_t w0 = hw[2 * jj], w1 = hw[2 * jj + 1];
+            h.x = fmaf(__uint_as_float(v[j * 4 + 0]), rs, fmaf(nk, __uint_as_float(w0 << 16), h.x));
+            h.y = fmaf(__uint_as_float(v[j * 4 + 1]), rs, fmaf(nk, __uint_as_float(w0 & 0xffff0000u), h.y));
+            h.z = fmaf(__uint_as_float(v[j * 4 + 2]), rs, fmaf(nk, __uint_as_float(w1 << 16), h.z));
+            h.w = fmaf(__uint_as_float(v[j * 4 + 3]), rs, fmaf(nk, __uint_as_float(w1 & 0xffff0000u), h.w));
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w)
+                         : "memory");
+            if (args.drop.thresh) {
+              float m0, m1, m2, m3;
+              if (drun.fast) {
+                pn_drop_run_mul2(args.drop, drun, 2 * j, m0, m1);
+                pn_drop_run_mul2(args.drop, drun, 2 * j + 1, m2, m3);
+              } else {
+                pn_drop_mul2(args.drop, dbase + 4 * j, m0, m1);
+                pn_drop_mul2(args.drop, dbase + 4 * j + 2, m2, m3);
+              }
+              h.x *= m0; h.y *= m1; h.z *= m2; h.w *= m3;
+            }
+            __nv_bfloat162 lo = __floats2bfloat162_rn(h.x, h.y), hi = __floats2bfloat162_rn(h.z, h.w);
+            v[j * 2 + 0] = *reinterpret_cast<uint32_t*>(&lo);   // v[0 .. 15] becomes the packed bf16 row
+            v[j * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
+          }
+        }
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ybuf + ((p ^ yswz) << 4)), "r"(v[p * 4 + 0]),
+                       "r"(v[p * 4 + 1]), "r"(v[p * 4 + 2]), "r"(v[p * 4 + 3])
+                       : "memory");
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmC, wbase + rb * EPI_BUF_BYTES, col0 + c * 32, row0);
+          tma_store_2d(&tmY, ybase + (q & 1) * RES_Y_BYTES, col0 + c * 32, row0);
+          tma_store_commit();
+          tma_store_wait_read<1>();   // chunk q - 1 has left shared memory: its slot takes chunk q + RB - 1
+          const uint32_t bl = rb == 0 ? RB - 1 : rb - 1;
+          const int cn = c + RB - 1;
+          if (cn < kChunks) load_tile(bl, row0, col0 + cn * 32);
+          else if (nvalid) load_tile(bl, nrow0, ncol0 + (cn - kChunks) * 32);
+        }
+        if (++rb == RB) { rb = 0; rph ^= 1; }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (kCtaGroup == 1) mbar_arrive(tempty_bar(as));
+        else mbar_arrive_remote(tempty_bar(as), 0);
+      }
+    }
+    if (lane == 0) tma_store_wait_all<0>();
   } else if (warp >= 4 && kTmaRes) {
     // ===================== residual epilogue, tiles moved by TMA =====================
     // out[row, col] += acc * rs, plus the bf16 copy and the row sums of squares of the updated values.  Each warp
@@ -433,6 +576,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (nvalid) warp_origin(item + num_groups, nrow0, ncol0);
         mbar_wait(tfull_bar(as), aph);
         tc_fence_after();
+        float dsum = 0.0f;   // sum over the tile's columns of out * mask (the mask holds the forward activation)
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / 64; ++c, ++cc) {
           const uint32_t buf = stage0 + (cc & 1) * EPI_BUF_BYTES;
@@ -465,6 +609,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               // the mask holds ReLU outputs (>= 0): positive <=> any magnitude bit set
               pk[e] = *reinterpret_cast<uint32_t*>(&h) &
                       (((mk[e] & 0x00007fffu) ? 0x0000ffffu : 0u) | ((mk[e] & 0x7fff0000u) ? 0xffff0000u : 0u));
+              dsum = fmaf(x0, __uint_as_float(mk[e] << 16), dsum);          // a zero activation contributes nothing
+              dsum = fmaf(x1, __uint_as_float(mk[e] & 0xffff0000u), dsum);
             }
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * 128 + ((j ^ swz) << 4)),
                          "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
@@ -477,6 +623,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tma_store_commit();
           }
         }
+        if (args.dot_out && live) args.dot_out[(size_t)n_blk * args.ss_stride + row] = dsum;
       } else if (args.mode == PN_EPI_BF16) {
         // ReLU-backward mask: read with the coalesced mapping (lanes 0..7 = the eight 16-byte pieces of one 128-byte
         // row, four rows per instruction: 4 L1 wavefronts instead of the 32 of a thread-per-row read) and applied to
@@ -714,9 +861,10 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
                       row_stride_elems, box_rows, box_cols);
 }
 
-template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes = false, bool kTmaMask = false>
+template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes = false, bool kTmaMask = false, int kNormRes = 0>
 static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs args, cudaStream_t st) {
-  using Cfg = GemmCfg<kCtaGroup, BLOCK_N, kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES)>;
+  using Cfg = GemmCfg<kCtaGroup, BLOCK_N,
+                      kNormRes ? 4 * norm_warp_bytes(kNormRes) : (kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES))>;
   CUtensorMap tmA, tmB;
   int rc;
   if (!kTN) {
@@ -741,8 +889,13 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
     rc = pn_make_tmap_bf16_2d(&tmC, args.out, args.M, args.N, args.ldc, 32, 64);
     if (rc) return rc;
   }
-  CUtensorMap tmY = tmA;
-  if (kTmaRes) {   // fp32 residual stream and its bf16 copy as 32-row x 32-column boxes (128 / 64 bytes per box row)
+  CUtensorMap tmY = tmA, tmH = tmA;
+  if (kNormRes) {
+    rc = make_tmap_2d(&tmH, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, CU_TENSOR_MAP_SWIZZLE_64B, args.nb_hb, args.M, args.N,
+                      args.ld_hb, 32, 32);
+    if (rc) return rc;
+  }
+  if (kTmaRes || kNormRes) {   // fp32 residual stream and its bf16 copy as 32-row x 32-column boxes (128 / 64 bytes per box row)
     rc = make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, CU_TENSOR_MAP_SWIZZLE_128B, args.out, args.M, args.N,
                       args.ldc, 32, 32);
     if (rc) return rc;
@@ -756,7 +909,7 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
     rc = pn_make_tmap_bf16_2d(&tmY, args.mask, args.M, args.N, args.ld_mask, 32, 64);
     if (rc) return rc;
   }
-  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N, kTN, kTmaRes, kTmaMask>;
+  auto kern = gemm_bf16_kernel<kCtaGroup, BLOCK_N, kTN, kTmaRes, kTmaMask, kNormRes>;
   static bool attr_done = false;
   if (!attr_done) {
     PN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -802,10 +955,11 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
   const double out_b = args.mode == PN_EPI_BF16 ? 2.0 : (args.mode == PN_EPI_RESID_F32 ? 8.0 : 4.0);
   const double bytes = 2.0 * ((double)args.M * args.K + (double)(args.group_rows > 0 ? args.M / args.group_rows : 1) *
                                                             args.N * args.K) +
-                       (double)args.M * args.N * (out_b + (args.copy_out ? 2.0 : 0.0) + (args.mask ? 2.0 : 0.0));
+                       (double)args.M * args.N *
+                           (out_b + (args.copy_out ? 2.0 : 0.0) + (args.mask ? 2.0 : 0.0) + (kNormRes ? 2.0 : 0.0));
   const bool hbm_bound = flops < 200.0 * bytes;
   PnProfScope prof(hbm_bound ? PN_PROF_GEMM_HBM : (kTN ? PN_PROF_WGRAD : PN_PROF_GEMM), hbm_bound ? bytes : flops, st);
-  PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmY, args));
+  PN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmY, tmH, args));
   g_pn_launches.fetch_add(1, std::memory_order_relaxed);
   return PN_OK;
 }
@@ -879,6 +1033,10 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   a.ld_mask = ex ? ex->ld_mask : 0;
   a.out_scale = ex && ex->out_scale != 0.0f ? ex->out_scale : 1.0f;
   if (ex) a.drop = ex->drop;
+  a.dot_out = ex ? ex->dot_out : nullptr;
+  a.nb_coef = ex ? ex->nb_coef : nullptr;
+  a.nb_hb = ex ? ex->nb_hb : nullptr;
+  a.ld_hb = ex ? ex->ld_hb : 0;
   if (a.drop.thresh && (mode == PN_EPI_F32 || (N & 1)))
     return pn_fail(PN_E_BADARG, "pn_gemm: dropout is built into the bf16 and the residual epilogues only");
   if (a.mask && (mode != PN_EPI_BF16 || (a.ld_mask % 8) || ((uintptr_t)a.mask & 15)))
@@ -889,6 +1047,19 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
     return pn_fail(PN_E_BADARG, "pn_gemm: copy/sumsq outputs need an fp32 epilogue mode");
   a.ss_stride = M;
   const bool n256 = (N % 256) == 0;
+  static const int tma_mask = [] { const char* e = getenv("PN_GEMM_TMA_MASK"); return e ? atoi(e) : 1; }();
+  if (a.dot_out && !(tma_mask && a.mask && mode == PN_EPI_BF16 && cta_group == 2 && n256 && !relu && !a.drop.thresh))
+    return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: dot_out needs the TMA-masked bf16 epilogue (2-CTA, N %% 256 == 0)");
+  if (a.nb_coef) {   // RMSNorm backward folded into the data-gradient GEMM
+    if (mode != PN_EPI_RESID_F32 || cta_group != 2 || !n256 || !a.nb_hb || !a.copy_out || (N & 1) ||
+        a.sumsq_in || a.sumsq_out || a.group_rows || (ldc % 4) || (a.ld_copy % 8) || ((uintptr_t)a.copy_out & 15) ||
+        (a.ld_hb % 8) || ((uintptr_t)a.nb_hb & 15))
+      return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: the norm-backward epilogue needs the 2-CTA residual mode with "
+                                       "N %% 256 == 0, a bf16 copy output and 16-byte aligned operands");
+    static const int norm_bufs = [] { const char* e = getenv("PN_NORM_BUFS"); return e ? atoi(e) : 3; }();
+    return norm_bufs == 4 ? launch_gemm<2, 256, false, false, false, 4>(A, lda, B, ldb, a, st)
+                          : launch_gemm<2, 256, false, false, false, 3>(A, lda, B, ldb, a, st);
+  }
   // Deep-K residual launches over very many rows go out as row slabs: with the static tile order the CTA pairs that
   // share an A block drift apart over the ~80 waves of an M = 512 000 launch until the block has left L2 between
   // their reads (1.45x the DRAM reads, profiles/r2b_gemm_traffic.csv); at 131 072 rows per launch they do not.
@@ -922,7 +1093,6 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
   // took 704 us with the register path against 443 us for the same-shape forward GEMM (profiles/r4n_train_launches*);
   // same-box A/B of the training step: 110.1 / 110.4 ms with it, 113.1 / 112.0 ms without (profiles/r4o_gemm_ab.txt).
   // PN_GEMM_TMA_MASK=0 keeps the register path.
-  static const int tma_mask = [] { const char* e = getenv("PN_GEMM_TMA_MASK"); return e ? atoi(e) : 1; }();
   if (tma_mask && a.mask && mode == PN_EPI_BF16 && cta_group == 2 && n256 && !relu && !a.drop.thresh)
     return launch_gemm<2, 256, false, false, true>(A, lda, B, ldb, a, st);
   if (cta_group == 2) {
@@ -950,4 +1120,26 @@ extern "C" int pn_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t l
   PN_CHECK_ARG(A && B && out);
   return pn_gemm_bf16_internal(A, (int)lda, B, (int)ldb, out, (int)ldc, (int)M, (int)N, (int)K, mode,
                                relu, row_scale, cta_group, (cudaStream_t)stream);
+}
+
+/* building blocks of the fused norm backward: see include/pn_b200.h */
+extern "C" int pn_gemm_bf16_relu_bwd(const void* dY, int64_t ld_dy, const void* Wt, int64_t ldw, const void* act,
+                                     int64_t ld_act, const float* row_scale, void* out, int64_t ldc, float* dot_out,
+                                     int64_t M, int64_t N, int64_t K, void* stream) {
+  PN_CHECK_ARG(dY && Wt && act && out);
+  PnGemmExtra ex = {};
+  ex.row_scale = row_scale; ex.relu_mask = (const __nv_bfloat16*)act; ex.ld_mask = (int)ld_act; ex.dot_out = dot_out;
+  return pn_gemm_bf16_ex(dY, (int)ld_dy, Wt, (int)ldw, out, (int)ldc, (int)M, (int)N, (int)K, PN_EPI_BF16, 0, &ex, 2,
+                         (cudaStream_t)stream);
+}
+
+extern "C" int pn_gemm_bf16_norm_bwd(const void* Ys, int64_t ld_ys, const void* Wt, int64_t ldw, const void* hb,
+                                     int64_t ld_hb, const float* coef, float* dh, int64_t ld_dh, void* dhb,
+                                     int64_t ld_dhb, int64_t M, int64_t N, int64_t K, void* stream) {
+  PN_CHECK_ARG(Ys && Wt && hb && coef && dh && dhb);
+  PnGemmExtra ex = {};
+  ex.nb_coef = coef; ex.nb_hb = (const __nv_bfloat16*)hb; ex.ld_hb = (int)ld_hb;
+  ex.copy_out = (__nv_bfloat16*)dhb; ex.ld_copy = (int)ld_dhb;
+  return pn_gemm_bf16_ex(Ys, (int)ld_ys, Wt, (int)ldw, dh, (int)ld_dh, (int)M, (int)N, (int)K, PN_EPI_RESID_F32, 0, &ex,
+                         2, (cudaStream_t)stream);
 }

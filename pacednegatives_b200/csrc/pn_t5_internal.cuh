@@ -32,6 +32,16 @@ struct PnGemmExtra {
   //   residual mode: out += dropout(acc * scales)              (sub-layer output before the residual add)
   PnDrop drop;
   float out_scale;                  // extra scalar factor on acc (0 = 1): 1/(1-p) of a dropped ReLU-backward mask
+  // bf16 mode with relu_mask, nullable: [N / 256][M] per-n-tile row sums of out[row, col] * relu_mask[row, col]
+  // (the saved activation doubles as the forward output: the row dot of the RMSNorm backward, see nb_coef)
+  float* dot_out;
+  // residual mode, nullable: RMSNorm backward folded into the data-gradient GEMM of a normed linear,
+  //   out[row, col] += acc - nb_coef[row] * nb_hb[row, col]   (+ the bf16 copy of the updated stream in copy_out;
+  //   `drop` then masks the COPY only: the dropout of the sub-layer output below, whose gradient the copy is)
+  // nb_coef[row] = rs^2 * <G, h> / d, known BEFORE the product because <G, h> = <Ys, y> / rs with y the forward output
+  const float* nb_coef;
+  const __nv_bfloat16* nb_hb;       // [M, ld_hb] the bf16 residual stream the norm read
+  int ld_hb;
 };
 int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, int ldc, int M, int N, int K,
                     int mode, int relu, const PnGemmExtra* ex, int cta_group, cudaStream_t st);
@@ -71,7 +81,13 @@ int pn_t5_self_attn_masked(const __nv_bfloat16* qkv, int ld_qkv, int q_col, int 
 int pn_t5_self_attn_bwd(const __nv_bfloat16* qkv, int ld, int q_col, int k_col, int v_col, int docs, int S,
                         int n_heads, const float* bias, const __nv_bfloat16* ctx, const __nv_bfloat16* dctx,
                         int ld_ctx, const float* lse2, float* dvec, const float* row_scale,
-                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st, PnDrop drop = PnDrop());
+                        __nv_bfloat16* dqkv, float* dbias_diag, cudaStream_t st, PnDrop drop = PnDrop(),
+                        float* dot_out = nullptr);
+// dot_out (nullable): [4 * n_heads][docs * S] partial row sums of dqkv[row, :] * qkv[row, :] (plane = (pass * n_heads +
+// head) * 2 + column half), the row dot the RMSNorm backward of the qkv projection needs (pn_t5_norm_coef)
+// coef[row] = scale * rs[row] * sum_p part[p * rows + row] / d
+int pn_t5_norm_coef(const float* part, int parts, const float* rs, int64_t rows, int d, float* coef, cudaStream_t st,
+                    float scale = 1.0f);   // scale: extra factor on the sum (1 - p when the saved activation was dropped)
 int pn_t5_rel_bias_grad(const float* dbias_diag, const int* bucket_of, int n_heads, int buckets, float* grad,
                         cudaStream_t st);
 // decoder self / cross attention for T <= 2 query tokens per document

@@ -81,6 +81,7 @@ struct PnT5 {
   bool xattn = true;                 // projection-free cross-attention where the shapes allow ("xattn" option)
   bool want_train = false;           // also keep packedT / embT (pn_t5_set_option "train")
   int cta_group = 2;
+  bool fuse_norm_bwd = true;         // encoder RMSNorm backward inside the data-gradient GEMM ("fuse_norm_bwd" option)
   bool dgrad_bf16 = true;            // encoder data gradients reach norm_bwd as bf16 ("dgrad_bf16" option)
   int grad_ranges = 4;               // encoder layer groups whose gradients leave separately ("grad_ranges" option)
 };

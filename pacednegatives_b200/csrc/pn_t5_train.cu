@@ -171,11 +171,21 @@ int dgrad(const PnT5* m, const __nv_bfloat16* dY, int ld_dy, const PnLin& W, voi
 // Ys = rs (.) (dY Wo (.) [act > 0])
 // (with dropout of the hidden activation the saved act is m s relu(u): [act > 0] = m [u > 0], times the scale s)
 int dgrad_relu(const PnT5* m, const __nv_bfloat16* dY, const PnLin& W, const __nv_bfloat16* act, const float* rs,
-               __nv_bfloat16* out, int M, cudaStream_t st, float act_scale = 1.0f) {
+               __nv_bfloat16* out, int M, cudaStream_t st, float act_scale = 1.0f, float* dot_out = nullptr) {
   PnGemmExtra ex = {};
-  ex.row_scale = rs; ex.relu_mask = act; ex.ld_mask = W.cols; ex.out_scale = act_scale;
+  ex.row_scale = rs; ex.relu_mask = act; ex.ld_mask = W.cols; ex.out_scale = act_scale; ex.dot_out = dot_out;
   return pn_gemm_bf16_ex(dY, (int)W.rows, W.packedT, (int)W.rows, out, W.cols, M, W.cols, (int)W.rows, PN_EPI_BF16, 0,
                          &ex, m->cta_group, st);
+}
+// data gradient of a normed linear with the RMSNorm backward folded into the epilogue:
+//   dh += Ys W' - coef (.) hb,  dhb = bf16(dh)        (coef from pn_t5_norm_coef)
+int dgrad_norm(const PnT5* m, const __nv_bfloat16* Ys, int ld_ys, const PnLin& W, const __nv_bfloat16* hb,
+               const float* coef, float* dh, __nv_bfloat16* dhb, int M, cudaStream_t st, PnDrop copy_drop = PnDrop()) {
+  PnGemmExtra ex = {};
+  ex.drop = copy_drop;
+  ex.nb_coef = coef; ex.nb_hb = hb; ex.ld_hb = W.cols; ex.copy_out = dhb; ex.ld_copy = W.cols;
+  return pn_gemm_bf16_ex(Ys, ld_ys, W.packedT, (int)W.rows, dh, W.cols, M, W.cols, (int)W.rows, PN_EPI_RESID_F32, 0, &ex,
+                         m->cta_group, st);
 }
 // weight gradient of an un-normed linear: grads[W] += dY^T X
 int wgrad_plain(const PnT5* m, const __nv_bfloat16* dY, int ld_dy, const __nv_bfloat16* X, const PnLin& W, int K,
@@ -532,25 +542,48 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
   // stays fp32.  Parity at the bench widths: tests/test_gpu_train.py::test_training_step_at_bench_widths.
   const int g16 = m->dgrad_bf16 ? 1 : 0;
   const int gmode = g16 ? PN_EPI_BF16 : PN_EPI_F32;
+  // "fuse_norm_bwd" (default; 2-CTA tiles, widths in 256s): the row dot <G, h> of each norm's backward is
+  // <Ys, y> / rs with y the forward output of the normed linear (y = rs h W'^T, so <Ys W', h> = <Ys, h W'^T>), and the
+  // kernels that PRODUCE Ys hold y already: the masked FFN data gradient has the saved activation as its mask tile, the
+  // attention backward reads q | k | v.  They leave per-tile partial sums, pn_t5_norm_coef turns them into
+  // coef = rs^2 <G, h> / d, and the data-gradient GEMM finishes dh += G - coef h in its epilogue: no G round trip
+  // through HBM and no separate bandwidth pass (norm_bwd, 7 % of the step in profiles/r4n_train_launches_summary.txt).
+  const bool fuse = m->fuse_norm_bwd && m->cta_group == 2 && (d % 256) == 0 && (ff % 256) == 0 &&
+                    ((3 * di) % 256) == 0 && ff / 256 <= 64 && 4 * H <= 64 && d > 65;
+  float* part = w.gbuf;                          // [<= 64][rows] partial dots (G itself is never stored when fusing)
+  float* coef = w.gbuf + (size_t)64 * rows;      // [rows]
   for (int l = L - 1; l >= 0; --l) {
     const PnEncLayer& E = m->enc[l];
     const __nv_bfloat16 *hb0 = w.hb[2 * l], *hb1 = w.hb[2 * l + 1];
     const float *rs0 = w.rs[2 * l], *rs1 = w.rs[2 * l + 1];
     RC(wgrad_plain(m, w.dHb, d, w.act[l], E.wo2, rows, st));
-    RC(dgrad_relu(m, w.dHb, E.wo2, w.act[l], rs1, w.dbig, rows, st, act_scale));
+    RC(dgrad_relu(m, w.dHb, E.wo2, w.act[l], rs1, w.dbig, rows, st, act_scale, fuse ? part : nullptr));
     RC(wgrad_folded(m, w.dbig, ff, hb1, E.wi, w.dWtmp, rows, st));
-    RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, gmode, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, g16, hb1, rs1, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
-                      DR(0, l, PN_DROP_SELF_OUT, (long long)S * d)));
+    if (fuse) {
+      // with dropout the saved activation is m s relu(u), s = 1 / (1 - p): <Ys, u> = <Ys, act> / s
+      RC(pn_t5_norm_coef(part, ff / 256, rs1, rows, d, coef, st, 1.0f / act_scale));
+      RC(dgrad_norm(m, w.dbig, ff, E.wi, hb1, coef, w.dH, w.dHb, rows, st,
+                    DR(0, l, PN_DROP_SELF_OUT, (long long)S * d)));
+    } else {
+      RC(dgrad(m, w.dbig, ff, E.wi, w.gbuf, gmode, rows, st));
+      RC(pn_t5_norm_bwd(w.gbuf, g16, hb1, rs1, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
+                        DR(0, l, PN_DROP_SELF_OUT, (long long)S * d)));
+    }
     RC(wgrad_plain(m, w.dHb, d, w.ctx[l], E.wo, rows, st));
     RC(dgrad(m, w.dHb, d, E.wo, w.dctx, PN_EPI_BF16, rows, st));
     RC(pn_t5_self_attn_bwd(w.qkv[l], 3 * di, 0, di, 2 * di, (int)docs, S, H, m->enc_bias, w.ctx[l], w.dctx, di,
                            w.lse[l], w.dvec, rs0, w.dbig, w.diag, st,
-                           DR(0, l, PN_DROP_SELF_P, (long long)H * S * Sp)));
+                           DR(0, l, PN_DROP_SELF_P, (long long)H * S * Sp), fuse ? part : nullptr));
     RC(wgrad_folded(m, w.dbig, 3 * di, hb0, E.wqkv, w.dWtmp, rows, st));
-    RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, gmode, rows, st));
-    RC(pn_t5_norm_bwd(w.gbuf, g16, hb0, rs0, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
-                      l > 0 ? DR(0, l - 1, PN_DROP_FF_OUT, (long long)S * d) : PnDrop()));
+    if (fuse) {
+      RC(pn_t5_norm_coef(part, 4 * H, rs0, rows, d, coef, st));
+      RC(dgrad_norm(m, w.dbig, 3 * di, E.wqkv, hb0, coef, w.dH, w.dHb, rows, st,
+                    l > 0 ? DR(0, l - 1, PN_DROP_FF_OUT, (long long)S * d) : PnDrop()));
+    } else {
+      RC(dgrad(m, w.dbig, 3 * di, E.wqkv, w.gbuf, gmode, rows, st));
+      RC(pn_t5_norm_bwd(w.gbuf, g16, hb0, rs0, rows, d, 1, w.dH, w.dHb, st, PnDrop(),
+                        l > 0 ? DR(0, l - 1, PN_DROP_FF_OUT, (long long)S * d) : PnDrop()));
+    }
     if (m->grad_hook && l > 0)
       for (int g = groups - 1; g >= 1; --g)
         if (group_lo(g) == l) {   // layers [l, top of group g) are done

@@ -140,6 +140,17 @@ norm_bwd_kernel(const void* __restrict__ Gv, const __nv_bfloat16* __restrict__ h
   }
 }
 
+// coefficient of the RMSNorm backward folded into a data-gradient GEMM: coef[r] = rs[r] * sum_p part[p][r] / d
+__global__ void __launch_bounds__(kThreads)
+norm_coef_kernel(const float* __restrict__ part, int parts, const float* __restrict__ rs, int64_t rows, float inv_d,
+                 float* __restrict__ coef) {
+  for (int64_t r = (int64_t)blockIdx.x * kThreads + threadIdx.x; r < rows; r += (int64_t)gridDim.x * kThreads) {
+    float s = 0.0f;
+    for (int p = 0; p < parts; ++p) s += part[(size_t)p * rows + r];
+    coef[r] = rs[r] * s * inv_d;
+  }
+}
+
 // gradW[n,k] += dWp[n,k] * g[k];  gradg[k] += sum_n dWp[n,k] * W[n,k]   (W = fp32 master, dWp = d W')
 // A CTA owns 128 columns (one float4 per lane) x 32 rows; every load of a thread is independent and issued up front,
 // one atomic per column per CTA.
@@ -357,6 +368,21 @@ int pn_t5_embed_bwd(const int32_t* ids, const float* dh, int64_t rows, int d, in
                     cudaStream_t st, PnDrop drop) {
   if (rows == 0) return PN_OK;
   embed_bwd_kernel<<<pn_grid(rows * 32, kThreads, 1, 8), kThreads, 0, st>>>(ids, dh, rows, d, vocab, grad_table, drop);
+  PN_LAUNCHED();
+  return PN_OK;
+}
+
+extern "C" int pn_t5_norm_coef(const float* part, int32_t parts, const float* rs, int64_t rows, int32_t d,
+                               float* coef, void* stream) {
+  PN_CHECK_ARG(part && rs && coef && parts > 0 && d > 0);
+  return pn_t5_norm_coef(part, (int)parts, rs, rows, (int)d, coef, (cudaStream_t)stream, 1.0f);
+}
+
+int pn_t5_norm_coef(const float* part, int parts, const float* rs, int64_t rows, int d, float* coef, cudaStream_t st,
+                    float scale) {
+  if (rows <= 0) return PN_OK;
+  norm_coef_kernel<<<(unsigned)std::min<int64_t>((rows + kThreads - 1) / kThreads, 4 * PN_SM_COUNT), kThreads, 0, st>>>(
+      part, parts, rs, rows, scale / (float)d, coef);
   PN_LAUNCHED();
   return PN_OK;
 }

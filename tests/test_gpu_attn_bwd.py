@@ -80,3 +80,45 @@ def test_self_attention_backward_saturated_bias(docs, S, H, DC):
     from pacednegatives_b200 import _lib
     _lib.require_gpu()
     run_case(docs, S, H, True, seed=docs * 1000 + S + H + DC, DC=DC)
+
+
+@pytest.mark.parametrize("docs,S,H,with_scale", [(3, 512, 2, True), (1, 200, 2, True), (2, 77, 4, False),
+                                                 (5, 512, 12, True)])
+def test_self_attention_backward_row_dots(docs, S, H, with_scale):
+    """pn_t5_self_attention_bwd_dot: the 4*H planes summed = sum_col dqkv[row, col] * qkv[row, col] (the RMSNorm
+    backward's row dot), and dqkv itself is bit-identical to the plain entry point's.  The kernel sums the fp32
+    (unrounded) gradient entries, the check the stored bf16 ones: 1e-2 of the row's absolute-sum scale."""
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    lib = _lib.lib()
+    torch.manual_seed(7 * docs + S + H)
+    di, rows = H * 64, docs * S
+    qkv = (torch.randn(rows, 3 * di, device="cuda") * 0.5).bfloat16()
+    bias = torch.randn(H, 1023, device="cuda")
+    dctx = (torch.randn(rows, di, device="cuda") * 0.5).bfloat16()
+    rs = (torch.rand(rows, device="cuda") + 0.5) if with_scale else None
+    ctx = torch.zeros(rows, di, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(rows, H, device="cuda")
+    _lib.check(lib.pn_t5_self_attention_lse(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(ctx), _lib.ptr(lse),
+                                            _lib.stream()))
+    outs = []
+    for with_dot in (False, True):
+        dqkv = torch.full((rows, 3 * di), float("nan"), device="cuda").bfloat16()
+        diag = torch.zeros(H, 1023, device="cuda")
+        dvec = torch.zeros(rows, H, device="cuda")
+        dots = torch.full((4 * H, rows), float("nan"), device="cuda")
+        args = [_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(ctx), _lib.ptr(dctx), _lib.ptr(lse),
+                _lib.ptr(rs) if with_scale else None, _lib.ptr(dqkv), _lib.ptr(diag), _lib.ptr(dvec)]
+        if with_dot:
+            _lib.check(lib.pn_t5_self_attention_bwd_dot(*args, _lib.ptr(dots), _lib.stream()))
+        else:
+            _lib.check(lib.pn_t5_self_attention_bwd(*args, _lib.stream()))
+        torch.cuda.synchronize()
+        outs.append((dqkv, dots))
+    assert torch.equal(outs[0][0], outs[1][0])
+    dqkv, dots = outs[1]
+    assert torch.isfinite(dots).all()
+    prod = dqkv.float() * qkv.float()
+    ref = prod.sum(1)
+    scale = prod.abs().sum(1) + 1e-3
+    assert ((dots.sum(0) - ref).abs() / scale).max().item() < 1e-2

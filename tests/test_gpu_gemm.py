@@ -111,3 +111,70 @@ def test_wgrad_gemm_vs_torch(cta_group, K, M, N):
     err = (out - ref).abs().max().item()
     scale = ref.abs().max().item()
     assert err <= 2e-5 * scale + 1e-3, f"K={K} M={M} N={N}: max err {err} (scale {scale})"
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Building blocks of the fused RMSNorm backward (include/pn_b200.h: pn_gemm_bf16_relu_bwd / _norm_bwd / pn_t5_norm_coef)
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (1000, 768, 256), (148 * 256 + 77, 3072, 768)])
+def test_relu_backward_epilogue_and_its_row_dots(M, N, K):
+    """out = rs * (dY Wt^T) where act > 0; dot partials: sum over each 256-column tile of out * act.
+    Tolerance: bf16 output rounding (2^-8 relative) on the product; the dots are fp32 sums of the UNROUNDED products,
+    compared with the fp32 torch value at 2e-3 of the row's absolute-sum scale."""
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    import ctypes
+    torch.manual_seed(M + N)
+    dY = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    Wt = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    act = torch.relu(torch.randn(M, N, device="cuda")).bfloat16()
+    rs = torch.rand(M, device="cuda") + 0.5
+    out = torch.full((M, N), float("nan"), device="cuda").bfloat16()
+    parts = torch.full((N // 256, M), float("nan"), device="cuda")
+    vp = lambda t: ctypes.c_void_p(t.data_ptr())
+    _lib.check(_lib.lib().pn_gemm_bf16_relu_bwd(vp(dY), K, vp(Wt), K, vp(act), N, vp(rs), vp(out), N, vp(parts), M, N, K,
+                                                _lib.stream()))
+    torch.cuda.synchronize()
+    ref = ref_mm(dY, Wt) * rs[:, None] * (act > 0)
+    assert torch.allclose(out.float(), ref, rtol=1.6e-2, atol=2e-2)
+    prod = ref * act.float()
+    ref_parts = prod.view(M, N // 256, 256).sum(2).t()
+    scale = prod.abs().view(M, N // 256, 256).sum(2).t() + 1e-3
+    assert torch.isfinite(parts).all()
+    assert ((parts - ref_parts).abs() / scale).max().item() < 2e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (1000, 768, 2304), (148 * 256 + 77, 768, 3072), (4096 + 31, 1024, 1024)])
+def test_norm_backward_residual_epilogue(M, N, K):
+    """dh += Ys Wt^T - coef (.) hb and its bf16 copy, on a column slice of a wider buffer (margins untouched)."""
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    import ctypes
+    torch.manual_seed(M + K)
+    Ys = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    Wt = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    hb = torch.randn(M, N, device="cuda").bfloat16()
+    coef = torch.randn(M, device="cuda") * 0.3
+    wide = torch.randn(M, N + 64, device="cuda")
+    before = wide.clone()
+    dhb = torch.full((M, N), float("nan"), device="cuda").bfloat16()
+    vp = lambda t: ctypes.c_void_p(t.data_ptr())
+    dh = wide[:, 32:32 + N]
+    _lib.check(_lib.lib().pn_gemm_bf16_norm_bwd(vp(Ys), K, vp(Wt), K, vp(hb), N, vp(coef), vp(dh), wide.stride(0),
+                                                vp(dhb), N, M, N, K, _lib.stream()))
+    torch.cuda.synchronize()
+    ref = before[:, 32:32 + N] + ref_mm(Ys, Wt) - coef[:, None] * hb.float()
+    assert torch.allclose(dh, ref, rtol=1e-4, atol=2e-3)
+    assert torch.equal(wide[:, :32], before[:, :32]) and torch.equal(wide[:, 32 + N:], before[:, 32 + N:])
+    assert torch.equal(dhb, dh.bfloat16())
+
+
+def test_norm_coef_kernel():
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    rows, parts, d = 1000, 12, 768
+    part = torch.randn(parts, rows, device="cuda")
+    rs = torch.rand(rows, device="cuda") + 0.5
+    coef = torch.zeros(rows, device="cuda")
+    _lib.check(_lib.lib().pn_t5_norm_coef(_lib.ptr(part), parts, _lib.ptr(rs), rows, d, _lib.ptr(coef), _lib.stream()))
+    torch.cuda.synchronize()
+    assert torch.allclose(coef, rs * part.sum(0) / d, rtol=1e-5, atol=1e-6)

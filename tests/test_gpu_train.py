@@ -353,3 +353,30 @@ def test_restricted_mode_step_vs_oracle_and_hf_autograd(golden_dir, xattn):
     tot_ref = torch.cat([p_.grad.reshape(-1) for _, p_ in hf.named_parameters()]).cuda()
     tot_got = torch.cat([grads[n_] for n_, _ in hf.named_parameters()])
     assert (tot_got - tot_ref).norm().item() / tot_ref.norm().item() < 5e-2, worst
+
+
+def test_fused_norm_backward_matches_the_separate_pass(golden_dir):
+    """"fuse_norm_bwd" (default; RMSNorm backward inside the encoder's data-gradient GEMMs, row dot taken from the
+    kernels that produce the output gradient) against the separate norm_bwd pass ("fuse_norm_bwd" = 0) on the same
+    step at t5-small width (cfg1 golden inputs): same loss bits (the forward is shared), every gradient tensor within
+    1e-2 relative L2 — the two differ only in where the row dot is rounded (bf16 G . h against fp32 Ys . y) and in
+    dh taking G unrounded instead of through bf16."""
+    from pacednegatives_b200.lceT5 import LCEModel
+    from pacednegatives_b200.scorer import T5Dims
+    g, dims, hp, batch = _load_wide(golden_dir, "cfg1")
+    sd = {k: torch.as_tensor(v) for k, v in ot.init_weights(dims, seed=int(g["seed"])).items()}
+
+    def run(fuse):
+        m = LCEModel(hp, dims=T5Dims(**dims.__dict__), state_dict=sd, cta_group=2, options={"fuse_norm_bwd": fuse})
+        out = m.training_step(batch, 0)
+        return float(out["main_loss"].detach()), {k: v.clone() for k, v in m.model.named_grads().items()}
+    l1, g1 = run(1)
+    l0, g0 = run(0)
+    assert l0 == l1
+    worst = 0.0
+    for n in g0:
+        ref = g0[n].double()
+        if ref.norm().item() < 1e-12:
+            continue
+        worst = max(worst, ((g1[n].double() - ref).norm() / ref.norm()).item())
+    assert worst < 1e-2, worst
