@@ -440,53 +440,77 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             if (a.dot_out) mbar_arrive(bar(B_RES_FREE));   // MMAs done (B_ACC_FULL) and this warp's reads too
           }
           const int oi = ob * BLK + r;
-          if (oi < S) {
-            const size_t grow = (size_t)(row0 + oi);
-            const float sc = a.row_scale ? a.row_scale[grow] : 1.0f;
-            __nv_bfloat16* dst0 = a.dqkv + grow * a.ld + (MODE == 0 ? a.v_col : a.q_col) + head * DK + half * 32;
-            __nv_bfloat16* dst1 = a.dqkv + grow * a.ld + a.k_col + head * DK + half * 32;
-            if (a.dot_out) {
-              // <dq, q> (MODE 1) or <dv, v> + <dk, k> (MODE 0) over this thread's 32 columns: with the forward's
-              // q | k | v = rs h W'^T these sums are the row dot <G, h> of the norm behind the projection
-              float ds = 0.0f;
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const uint4 x = xq[j];
-                const uint32_t xw[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  ds = fmaf(__uint_as_float(a0[8 * j + 2 * e]), __uint_as_float(xw[e] << 16), ds);
-                  ds = fmaf(__uint_as_float(a0[8 * j + 2 * e + 1]), __uint_as_float(xw[e] & 0xffff0000u), ds);
-                }
-                if (MODE == 0) {
-                  const uint4 y = yq[j];
-                  const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
-#pragma unroll
-                  for (int e = 0; e < 4; ++e) {
-                    ds = fmaf(__uint_as_float(a1[8 * j + 2 * e]), __uint_as_float(yw[e] << 16), ds);
-                    ds = fmaf(__uint_as_float(a1[8 * j + 2 * e + 1]), __uint_as_float(yw[e] & 0xffff0000u), ds);
-                  }
-                }
-              }
-              a.dot_out[(size_t)((MODE * a.n_heads + head) * 2 + half) * a.dot_stride + grow] = ds * sc;
-            }
+          const bool live = oi < S;
+          const size_t grow = (size_t)(row0 + (live ? oi : 0));
+          const float sc = (live && a.row_scale) ? a.row_scale[grow] : 1.0f;
+          if (a.dot_out && live) {
+            // <dq, q> (MODE 1) or <dv, v> + <dk, k> (MODE 0) over this thread's 32 columns: with the forward's
+            // q | k | v = rs h W'^T these sums are the row dot <G, h> of the norm behind the projection
+            float ds = 0.0f;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              uint4 u;
-              u.x = pack2(__uint_as_float(a0[8 * j + 0]) * sc, __uint_as_float(a0[8 * j + 1]) * sc);
-              u.y = pack2(__uint_as_float(a0[8 * j + 2]) * sc, __uint_as_float(a0[8 * j + 3]) * sc);
-              u.z = pack2(__uint_as_float(a0[8 * j + 4]) * sc, __uint_as_float(a0[8 * j + 5]) * sc);
-              u.w = pack2(__uint_as_float(a0[8 * j + 6]) * sc, __uint_as_float(a0[8 * j + 7]) * sc);
-              reinterpret_cast<uint4*>(dst0)[j] = u;
+              const uint4 x = xq[j];
+              const uint32_t xw[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                ds = fmaf(__uint_as_float(a0[8 * j + 2 * e]), __uint_as_float(xw[e] << 16), ds);
+                ds = fmaf(__uint_as_float(a0[8 * j + 2 * e + 1]), __uint_as_float(xw[e] & 0xffff0000u), ds);
+              }
               if (MODE == 0) {
-                u.x = pack2(__uint_as_float(a1[8 * j + 0]) * sc, __uint_as_float(a1[8 * j + 1]) * sc);
-                u.y = pack2(__uint_as_float(a1[8 * j + 2]) * sc, __uint_as_float(a1[8 * j + 3]) * sc);
-                u.z = pack2(__uint_as_float(a1[8 * j + 4]) * sc, __uint_as_float(a1[8 * j + 5]) * sc);
-                u.w = pack2(__uint_as_float(a1[8 * j + 6]) * sc, __uint_as_float(a1[8 * j + 7]) * sc);
-                reinterpret_cast<uint4*>(dst1)[j] = u;
+                const uint4 y = yq[j];
+                const uint32_t yw[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  ds = fmaf(__uint_as_float(a1[8 * j + 2 * e]), __uint_as_float(yw[e] << 16), ds);
+                  ds = fmaf(__uint_as_float(a1[8 * j + 2 * e + 1]), __uint_as_float(yw[e] & 0xffff0000u), ds);
+                }
+              }
+            }
+            a.dot_out[(size_t)((MODE * a.n_heads + head) * 2 + half) * a.dot_stride + grow] = ds * sc;
+          }
+          // The gradient rows leave through this warp's own 32 rows of the (now idle) P tile: thread-per-row writes
+          // under an XOR swizzle, read back so that one store instruction covers 4 rows x 128 B (MODE 0: 64 B of dV
+          // and 64 B of dK per row) or 8 rows x 64 B (MODE 1) — 8 segments per instruction instead of 32.
+          uint8_t* stg = gbase + SM_P + half * TILE_BYTES + (w4 * 32) * 128;
+          const int sw = lane & 7;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 u;
+            u.x = pack2(__uint_as_float(a0[8 * j + 0]) * sc, __uint_as_float(a0[8 * j + 1]) * sc);
+            u.y = pack2(__uint_as_float(a0[8 * j + 2]) * sc, __uint_as_float(a0[8 * j + 3]) * sc);
+            u.z = pack2(__uint_as_float(a0[8 * j + 4]) * sc, __uint_as_float(a0[8 * j + 5]) * sc);
+            u.w = pack2(__uint_as_float(a0[8 * j + 6]) * sc, __uint_as_float(a0[8 * j + 7]) * sc);
+            *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ sw) << 4)) = u;
+            if (MODE == 0) {
+              u.x = pack2(__uint_as_float(a1[8 * j + 0]) * sc, __uint_as_float(a1[8 * j + 1]) * sc);
+              u.y = pack2(__uint_as_float(a1[8 * j + 2]) * sc, __uint_as_float(a1[8 * j + 3]) * sc);
+              u.z = pack2(__uint_as_float(a1[8 * j + 4]) * sc, __uint_as_float(a1[8 * j + 5]) * sc);
+              u.w = pack2(__uint_as_float(a1[8 * j + 6]) * sc, __uint_as_float(a1[8 * j + 7]) * sc);
+              *reinterpret_cast<uint4*>(stg + lane * 128 + (((4 + j) ^ sw) << 4)) = u;
+            }
+          }
+          __syncwarp();
+          {
+            const int blk_row0 = ob * BLK + w4 * 32;                     // first row of this warp inside the document
+            __nv_bfloat16* gout = a.dqkv + (size_t)(row0 + blk_row0) * a.ld + head * DK + half * 32;
+            if (MODE == 0) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                const int rl = k * 4 + (lane >> 3), c = lane & 7;
+                const uint4 v = *reinterpret_cast<const uint4*>(stg + rl * 128 + ((c ^ (rl & 7)) << 4));
+                if (blk_row0 + rl < S)
+                  *reinterpret_cast<uint4*>(gout + (size_t)rl * a.ld + (c < 4 ? a.v_col + c * 8 : a.k_col + (c - 4) * 8)) = v;
+              }
+            } else {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const int rl = k * 8 + (lane >> 2), c = lane & 3;
+                const uint4 v = *reinterpret_cast<const uint4*>(stg + rl * 128 + ((c ^ (rl & 7)) << 4));
+                if (blk_row0 + rl < S) *reinterpret_cast<uint4*>(gout + (size_t)rl * a.ld + a.q_col + c * 8) = v;
               }
             }
           }
+          __syncwarp();   // the staging rows are this warp's P rows of the next step
         }
       }
     }

@@ -35,6 +35,12 @@ constexpr int RES_Y_BYTES = 32 * 64;
 constexpr int RES_WARP_BYTES = kResBufs * EPI_BUF_BYTES + 2 * RES_Y_BYTES;   // 24 KB
 constexpr int EPI_BYTES_TMA = 4 * RES_WARP_BYTES;                             // 96 KB: 4 pipeline stages left
 static_assert(8 * (2 * 8 + 5 + 4 * kResBufs) <= 512, "barrier area");
+// Masked bf16 epilogue (kTmaMask): the staging tiles + a ring of kMaskBufs mask tiles per warp, requested
+// kMaskBufs - 1 chunks ahead (into the next output tile).  2 tiles (one chunk ahead) left the HBM latency of every
+// mask tile exposed: [131072 x 768] x [768 x 3072] 545 us against 443 us for the same-shape forward product.
+constexpr int kMaskBufs = 4;
+constexpr int EPI_BYTES_MASK = EPI_BYTES + 4 * kMaskBufs * EPI_BUF_BYTES;   // 96 KB: 4 pipeline stages
+static_assert(kMaskBufs <= kResBufs, "mask ring uses the residual-tile barriers");
 // Norm-backward residual epilogue (kNormRes = ring depth): per warp kNormRes fp32 tiles + as many bf16 tiles of the
 // normed stream + the two bf16 copy tiles.  3 buffers = 22 KB per warp, 88 KB: 4 pipeline stages, as the plain TMA
 // residual path; 4 buffers = 28 KB per warp, 112 KB: 3 stages.  PN_NORM_BUFS (environment) picks, default 3.
@@ -109,7 +115,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ CUtensorMap tmH, const GemmArgs args) {
   static_assert(!(kNormRes && (kTmaRes || kTmaMask)), "one epilogue variant per instantiation");
   using Cfg = GemmCfg<kCtaGroup, BLOCK_N,
-                      kNormRes ? 4 * norm_warp_bytes(kNormRes) : (kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES))>;
+                      kNormRes ? 4 * norm_warp_bytes(kNormRes) : (kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? EPI_BYTES_MASK : EPI_BYTES))>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -158,6 +164,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     kb1 = kb0 + kb_per_split < total_kb ? kb0 + kb_per_split : total_kb;
   };
 
+  asm volatile("griddepcontrol.launch_dependents;");   // the next kernel's CTAs may take SMs as this grid's CTAs exit
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -187,6 +194,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_gen;
+  // Programmatic dependent launch (launch_gemm sets the stream-serialization attribute): everything above — barrier
+  // init, tensor-map prefetch, TMEM allocation — may run while the previous kernel of the stream drains its last
+  // tiles; nothing below touches global memory before that kernel has completed and flushed.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
@@ -534,9 +545,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int rrow = lane >> 3, rj = lane & 7;        // read-back mapping: iteration i -> row 4*i + rrow, chunk rj
     int it = 0;
     uint32_t cc = 0;                                  // chunks staged so far (buffer = cc & 1)
-    // kTmaMask: two 4 KB mask tiles per warp behind the staging tiles; the tile of chunk cc + 1 is requested while
-    // chunk cc is processed (its mbarrier: res_bar(ew, (cc + 1) & 1), phase ((cc + 1) >> 1) & 1)
-    const uint32_t mstage0 = epi_smem + 4 * (2 * EPI_BUF_BYTES) + ew * (2 * EPI_BUF_BYTES);
+    // kTmaMask: a ring of kMaskBufs 4 KB mask tiles per warp behind the staging tiles; the tile of chunk cc +
+    // kMaskBufs - 1 is requested while chunk cc is processed (slot = chunk % kMaskBufs, own mbarrier per slot)
+    const uint32_t mstage0 = epi_smem + 4 * (2 * EPI_BUF_BYTES) + ew * (kMaskBufs * EPI_BUF_BYTES);
+    uint32_t mslot = 0, mph = 0;                      // ring slot and mbarrier phase of the current chunk
     auto load_mask_tile = [&](uint32_t b, int r0, int c0) {
       mbar_arrive_expect_tx(res_bar(ew, b), EPI_BUF_BYTES);
       tma_load_2d(mstage0 + b * EPI_BUF_BYTES, &tmY, res_bar(ew, b), c0, r0);
@@ -546,10 +558,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       r0 = (t_ / n_tiles) * tile_m + (int)cta_rank * BLOCK_M + ew * 32;
       c0 = (t_ % n_tiles) * BLOCK_N;
     };
+    static_assert(!kTmaMask || kMaskBufs - 1 <= BLOCK_N / 64, "mask prefetch reaches at most into the next tile");
     if (kTmaMask && lane == 0 && group_id < num_tiles) {
       int r0, c0;
       warp_origin(group_id, r0, c0);
-      load_mask_tile(0, r0, c0);
+      for (int i = 0; i + 1 < kMaskBufs; ++i) load_mask_tile(i, r0, c0 + i * 64);
     }
     for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
       const int tile = tile_of(item);
@@ -580,17 +593,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / 64; ++c, ++cc) {
           const uint32_t buf = stage0 + (cc & 1) * EPI_BUF_BYTES;
-          const uint32_t mbuf = mstage0 + (cc & 1) * EPI_BUF_BYTES + lane * 128;
+          const uint32_t mbuf = mstage0 + mslot * EPI_BUF_BYTES + lane * 128;
           uint32_t v0[32], v1[32];
           tmem_ld_32x32(t_row + c * 64, v0);
           tmem_ld_32x32(t_row + c * 64 + 32, v1);
           if (lane == 0) tma_store_wait_read<1>();   // the store that used this staging buffer two chunks ago has drained
-          __syncwarp();                              // ... and every lane is done with the other mask tile (chunk cc - 1)
-          if (lane == 0) {
-            if (c + 1 < BLOCK_N / 64) load_mask_tile((cc + 1) & 1, row0, col0 + (c + 1) * 64);
-            else if (nvalid) load_mask_tile((cc + 1) & 1, nrow0, ncol0);
+          __syncwarp();                              // ... and every lane is done with the mask tile of chunk cc - 1
+          if (lane == 0) {                           // whose slot takes chunk cc + kMaskBufs - 1
+            const uint32_t bl = mslot == 0 ? kMaskBufs - 1 : mslot - 1;
+            const int cn = c + kMaskBufs - 1;
+            if (cn < BLOCK_N / 64) load_mask_tile(bl, row0, col0 + cn * 64);
+            else if (nvalid) load_mask_tile(bl, nrow0, ncol0 + (cn - BLOCK_N / 64) * 64);
           }
-          mbar_wait(res_bar(ew, cc & 1), (cc >> 1) & 1);
+          mbar_wait(res_bar(ew, mslot), mph);
+          if (++mslot == kMaskBufs) { mslot = 0; mph ^= 1; }
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -864,7 +880,7 @@ int pn_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint
 template <int kCtaGroup, int BLOCK_N, bool kTN, bool kTmaRes = false, bool kTmaMask = false, int kNormRes = 0>
 static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs args, cudaStream_t st) {
   using Cfg = GemmCfg<kCtaGroup, BLOCK_N,
-                      kNormRes ? 4 * norm_warp_bytes(kNormRes) : (kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? 2 * EPI_BYTES : EPI_BYTES))>;
+                      kNormRes ? 4 * norm_warp_bytes(kNormRes) : (kTmaRes ? EPI_BYTES_TMA : (kTmaMask ? EPI_BYTES_MASK : EPI_BYTES))>;
   CUtensorMap tmA, tmB;
   int rc;
   if (!kTN) {
@@ -942,13 +958,17 @@ static int launch_gemm(const void* A, int lda, const void* B, int ldb, GemmArgs 
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kCtaGroup;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  // PN_GEMM_PDL=0: plain stream order (the kernel's griddepcontrol instructions are then no-ops)
+  static const int want_pdl = [] { const char* e = getenv("PN_GEMM_PDL"); return e ? atoi(e) : 1; }();
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = want_pdl ? 2 : 1;
   // launches below ~200 FLOP per byte of compulsory traffic (skinny products, the fp32 residual read-modify-write
   // of the narrow output projections) are HBM-bound: they are timed as their own class with bytes as the work
   const double flops = 2.0 * args.M * args.N * args.K;
