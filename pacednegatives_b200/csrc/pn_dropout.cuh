@@ -96,4 +96,10 @@ __device__ __forceinline__ void pn_drop_run_mul2(const PnDrop& d, const PnDropRu
   m0 = (h & 0xffffu) < d.thresh ? d.scale : 0.0f;
   m1 = (h >> 16) < d.thresh ? d.scale : 0.0f;
 }
+// run form with the rare slow path folded in: multipliers of elements (idx_even0 + 2 t, + 1)
+__device__ __forceinline__ void pn_drop_run_get(const PnDrop& d, const PnDropRun& r, unsigned long long idx_even0,
+                                                uint32_t t, float& m0, float& m1) {
+  if (r.fast) pn_drop_run_mul2(d, r, t, m0, m1);
+  else pn_drop_mul2(d, idx_even0 + 2ull * t, m0, m1);
+}
 #endif

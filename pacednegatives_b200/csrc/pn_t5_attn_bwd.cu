@@ -33,15 +33,18 @@ constexpr int BIAS_W = 2 * MAX_S - 1;
 constexpr int BIAS_STRIDE = 1032;
 constexpr float kLog2e = 1.4426950408889634f;
 
-// smem: resident pair | streamed pair x2 | P tile | dS tile | bias copies | diag accumulators | barriers
-constexpr int SM_RES = 0;                              // [0] = Q or K, [1] = dO or V
-constexpr int SM_STR = 2 * TILE_BYTES;                 // 2 buffers x (2 tiles)
+// smem: resident pair x2 | streamed pair x2 | P tile | dS tile | bias copies | diag accumulators | barriers
+// The resident pair is double-buffered by item: the next item's tiles arrive while this one is still being worked on
+// (its first S / dP products are issued before this item's last accumulating ones, and the item epilogue may still
+// read the current pair for the row dots), so no item boundary waits for a TMA load.
+constexpr int SM_RES = 0;                              // 2 buffers x ([0] = Q or K, [1] = dO or V)
+constexpr int SM_STR = 4 * TILE_BYTES;                 // 2 buffers x (2 tiles)
 constexpr int SM_P = SM_STR + 4 * TILE_BYTES;
 constexpr int SM_DS = SM_P + PT_BYTES;
 constexpr int SM_BIAS = SM_DS + PT_BYTES;
 constexpr int SM_DIAG = SM_BIAS + 4 * BIAS_STRIDE * 4;
 constexpr int SM_BAR = SM_DIAG + 1024 * 4;
-enum { B_RES_FULL = 0, B_RES_FREE, B_STR_FULL0, B_STR_FULL1, B_STR_EMPTY0, B_STR_EMPTY1, B_SP_FULL, B_SP_FREE,
+enum { B_RES_FULL0 = 0, B_RES_FULL1, B_RES_FREE0, B_RES_FREE1, B_STR_FULL0, B_STR_FULL1, B_STR_EMPTY0, B_STR_EMPTY1, B_SP_FULL, B_SP_FREE,
        B_PD_READY, B_PD_FREE, B_ACC_FULL, B_ACC_FREE, NUM_BARS };
 constexpr int BWD_SMEM = SM_BAR + NUM_BARS * 8 + 16 + 1024;
 
@@ -118,8 +121,10 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
-    mbar_init(bar(B_RES_FULL), 1);
-    mbar_init(bar(B_RES_FREE), a.dot_out ? 8 : 1);   // row dots: the compute warps read the resident tiles last
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(bar(B_RES_FULL0 + b), 1);
+      mbar_init(bar(B_RES_FREE0 + b), a.dot_out ? 8 : 1);   // row dots: the compute warps read the resident tiles last
+    }
     mbar_init(bar(B_STR_FULL0), 1);
     mbar_init(bar(B_STR_FULL1), 1);
     mbar_init(bar(B_STR_EMPTY0), 1);
@@ -163,14 +168,16 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       int g = 0;
       for (int it = 0; it < n_items; ++it) {
         const int row0 = item_doc(it) * S, ob = item_ob(it);
-        mbar_wait(bar(B_RES_FREE), (it & 1) ^ 1);
-        mbar_arrive_expect_tx(bar(B_RES_FULL), 2 * TILE_BYTES);
+        const int rbuf = it & 1;
+        const uint32_t rdst = base + SM_RES + rbuf * 2 * TILE_BYTES;
+        mbar_wait(bar(B_RES_FREE0 + rbuf), ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(bar(B_RES_FULL0 + rbuf), 2 * TILE_BYTES);
         if (MODE == 0) {
-          tma_load_2d(base + SM_RES, &tmQKV, bar(B_RES_FULL), col_k, row0 + ob * BLK);
-          tma_load_2d(base + SM_RES + TILE_BYTES, &tmQKV, bar(B_RES_FULL), col_v, row0 + ob * BLK);
+          tma_load_2d(rdst, &tmQKV, bar(B_RES_FULL0 + rbuf), col_k, row0 + ob * BLK);
+          tma_load_2d(rdst + TILE_BYTES, &tmQKV, bar(B_RES_FULL0 + rbuf), col_v, row0 + ob * BLK);
         } else {
-          tma_load_2d(base + SM_RES, &tmQKV, bar(B_RES_FULL), col_q, row0 + ob * BLK);
-          tma_load_2d(base + SM_RES + TILE_BYTES, &tmDO, bar(B_RES_FULL), col_do, row0 + ob * BLK);
+          tma_load_2d(rdst, &tmQKV, bar(B_RES_FULL0 + rbuf), col_q, row0 + ob * BLK);
+          tma_load_2d(rdst + TILE_BYTES, &tmDO, bar(B_RES_FULL0 + rbuf), col_do, row0 + ob * BLK);
         }
         for (int t = 0; t < nb; ++t, ++g) {
           const int b = g & 1;
@@ -198,22 +205,21 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     constexpr uint32_t IDESC_NN = make_idesc_bf16(128, DK, 0, 1);    // A = dS from TMEM, B = K MN-major
     const int total = n_items * nb;
     const bool leader = lane == 0;
-    const uint32_t res = base + SM_RES;
     // K-major descriptors (S = Q K^T, dP = dO V^T) and MN-major ones (accumulating products); a 16-element K step
     // advances a K-major descriptor by 2 (32 B) and an MN-major one by 128 (16 rows x 128 B)
-    const uint64_t res0_k = make_desc_kmajor_sw128(res), res1_k = make_desc_kmajor_sw128(res + TILE_BYTES);
-    const uint64_t res0_mn = make_desc_mnmajor_sw128(res, TILE_BYTES);
     const uint64_t p_mn = make_desc_mnmajor_sw128(base + SM_P, TILE_BYTES);
     const uint64_t ds_mn = make_desc_mnmajor_sw128(base + SM_DS, TILE_BYTES);
     auto issue_sp = [&](int g) {
       const int it = g / nb, t = g % nb;
       const uint32_t str = base + SM_STR + (g & 1) * 2 * TILE_BYTES;
+      const uint32_t res = base + SM_RES + (it & 1) * 2 * TILE_BYTES;
+      const uint64_t res0_k = make_desc_kmajor_sw128(res), res1_k = make_desc_kmajor_sw128(res + TILE_BYTES);
       const uint64_t str0_k = make_desc_kmajor_sw128(str), str1_k = make_desc_kmajor_sw128(str + TILE_BYTES);
       // MODE 0: streamed = (Q, dO), resident = (K, V);  MODE 1: resident = (Q, dO), streamed = (K, V)
       const uint64_t dq = MODE == 0 ? str0_k : res0_k, ddo = MODE == 0 ? str1_k : res1_k;
       const uint64_t dk = MODE == 0 ? res0_k : str0_k, dv = MODE == 0 ? res1_k : str1_k;
       mbar_wait(bar(B_STR_FULL0 + (g & 1)), (g >> 1) & 1);
-      if (t == 0) mbar_wait(bar(B_RES_FULL), it & 1);
+      if (t == 0) mbar_wait(bar(B_RES_FULL0 + (it & 1)), (it >> 1) & 1);
       if (g > 0) mbar_wait(bar(B_SP_FREE), (g - 1) & 1);   // compute threads hold S, dP of the previous step
       tc_fence_after();
       if (leader) {
@@ -253,20 +259,17 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         umma_commit<1>(bar(B_STR_EMPTY0 + (g & 1)));
         if (t == nb - 1) {
           umma_commit<1>(bar(B_ACC_FULL));
-          if (!a.dot_out) umma_commit<1>(bar(B_RES_FREE));
+          if (!a.dot_out) umma_commit<1>(bar(B_RES_FREE0 + (it & 1)));
         }
       }
       __syncwarp();
     };
-    (void)res0_mn;
     if (total > 0) issue_sp(0);
     for (int g = 0; g < total; ++g) {
-      const bool last_of_item = (g % nb) == nb - 1;
-      // S / dP of the next step are formed while the compute warps work on this one; across an item boundary
-      // the resident tiles are only released by this step's accumulating MMAs, so those go first
-      if (!last_of_item) issue_sp(g + 1);
+      // S / dP of the next step are formed while the compute warps work on this one — across item boundaries too
+      // (the next item's resident pair sits in the other buffer)
+      if (g + 1 < total) issue_sp(g + 1);
       issue_acc(g);
-      if (last_of_item && g + 1 < total) issue_sp(g + 1);
     }
   } else if (warp < 8) {
     // ===================== compute warps: thread = (query row r, 64-key half) =====================
@@ -303,7 +306,6 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const int qi = qb * BLK + r;
         const int k0 = kb * BLK + half * 64;
         const int kvalid = qi < S ? min(64, S - k0) : 0;   // keys of this half that exist (0 for a padding row)
-        row_stats(g + 1, lse_nx, dv_nx);
         const float nlse = -lse;
         const bool full = __all_sync(0xffffffffu, kvalid == 64);   // no padding rows or keys in this warp's block
         // dropout mask of row qi: element [doc, head, qi, key] at an even row pitch.  With dropout O = (P (.) M) V:
@@ -385,6 +387,10 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             }
           }
         }
+        // next step's row statistics: requested here, where S / dP have left the registers (asked for at the top of
+        // the step the two values were spilled at once, and the spill store waited for the loads: 7 % of the pass's
+        // samples), and still a barrier wait, the tile writes and the next step's TMEM loads ahead of their first use
+        row_stats(g + 1, lse_nx, dv_nx);
         if (g > 0) mbar_wait(bar(B_PD_FREE), (g - 1) & 1);   // previous step's accumulating MMAs read P, dS
         if (MODE == 0) {
 #pragma unroll
@@ -414,9 +420,10 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           // resident pair is released by these warps instead of by the last MMA's commit.
           uint4 xq[4], yq[4];
           if (a.dot_out) {
-            mbar_wait(bar(B_RES_FULL), it & 1);   // completed long ago: orders these reads after the TMA writes
-            const uint32_t t0 = base + SM_RES + (MODE == 0 ? TILE_BYTES : 0) + r * 128;
-            const uint32_t t1 = base + SM_RES + r * 128;
+            mbar_wait(bar(B_RES_FULL0 + (it & 1)), (it >> 1) & 1);   // completed long ago: orders these reads after the TMA writes
+            const uint32_t rsrc = base + SM_RES + (it & 1) * 2 * TILE_BYTES;
+            const uint32_t t0 = rsrc + (MODE == 0 ? TILE_BYTES : 0) + r * 128;
+            const uint32_t t1 = rsrc + r * 128;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               const uint32_t ch = (uint32_t)(((half * 4 + j) ^ (r & 7)) << 4);
@@ -437,7 +444,7 @@ t5_attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           __syncwarp();
           if (lane == 0) {
             mbar_arrive(bar(B_ACC_FREE));
-            if (a.dot_out) mbar_arrive(bar(B_RES_FREE));   // MMAs done (B_ACC_FULL) and this warp's reads too
+            if (a.dot_out) mbar_arrive(bar(B_RES_FREE0 + (it & 1)));   // MMAs done (B_ACC_FULL) and this warp's reads too
           }
           const int oi = ob * BLK + r;
           const bool live = oi < S;

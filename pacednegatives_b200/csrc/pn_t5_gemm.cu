@@ -43,9 +43,10 @@ constexpr int EPI_BYTES_MASK = EPI_BYTES + 4 * kMaskBufs * EPI_BUF_BYTES;   // 9
 static_assert(kMaskBufs <= kResBufs, "mask ring uses the residual-tile barriers");
 // Norm-backward residual epilogue (kNormRes = ring depth): per warp kNormRes fp32 tiles + as many bf16 tiles of the
 // normed stream + the two bf16 copy tiles.  3 buffers = 22 KB per warp, 88 KB: 4 pipeline stages, as the plain TMA
-// residual path; 4 buffers = 28 KB per warp, 112 KB: 3 stages.  PN_NORM_BUFS (environment) picks, default 3.
+// residual path; 4 buffers = 28 KB per warp, 112 KB: 3 stages; 2 buffers = 16 KB per warp, 64 KB: 5 stages.
+// PN_NORM_BUFS (environment) picks, default 3.
 __host__ __device__ constexpr int norm_warp_bytes(int bufs) { return bufs * (EPI_BUF_BYTES + RES_Y_BYTES) + 2 * RES_Y_BYTES; }
-static_assert(4 <= kResBufs && norm_warp_bytes(3) % 1024 == 0 && norm_warp_bytes(4) % 1024 == 0, "norm-backward epilogue tiles");
+static_assert(4 <= kResBufs && norm_warp_bytes(2) % 1024 == 0 && norm_warp_bytes(3) % 1024 == 0 && norm_warp_bytes(4) % 1024 == 0, "norm-backward epilogue tiles");
 
 template <int kCtaGroup, int BLOCK_N, int kEpiBytes = EPI_BYTES>
 struct GemmCfg {
@@ -367,13 +368,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                          : "memory");
             if (args.drop.thresh) {
               float m0, m1, m2, m3;
-              if (drun.fast) {
-                pn_drop_run_mul2(args.drop, drun, 2 * j, m0, m1);
-                pn_drop_run_mul2(args.drop, drun, 2 * j + 1, m2, m3);
-              } else {
-                pn_drop_mul2(args.drop, dbase + 4 * j, m0, m1);
-                pn_drop_mul2(args.drop, dbase + 4 * j + 2, m2, m3);
-              }
+              pn_drop_run_get(args.drop, drun, dbase, 2 * j, m0, m1);
+              pn_drop_run_get(args.drop, drun, dbase, 2 * j + 1, m2, m3);
               h.x *= m0; h.y *= m1; h.z *= m2; h.w *= m3;
             }
             __nv_bfloat162 lo = __floats2bfloat162_rn(h.x, h.y), hi = __floats2bfloat162_rn(h.z, h.w);
@@ -404,7 +400,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __syncwarp();
       if (lane == 0) {
         if (kCtaGroup == 1) mbar_arrive(tempty_bar(as));
-        else mbar_arrive_remote(tempty_bar(as), 0);
+        else mbar_arrive_remote_relaxed(tempty_bar(as), 0);
       }
     }
     if (lane == 0) tma_store_wait_all<0>();
@@ -475,6 +471,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(res_bar(ew, rb), rph);
         tmem_ld_wait();
         __syncwarp();   // lane 0 has seen the store of chunk q - 2 drain (its wait below) before ybuf is rewritten
+        PnDropRun drun = {};
+        unsigned long long dbase = 0;
+        if (args.drop.thresh) {   // the chunk's 16 index pairs share the inner hash of the mask (pn_drop_run)
+          dbase = (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N + (col0 + c * 32);
+          drun = pn_drop_run(args.drop, dbase, 16);
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const uint32_t addr = rbuf + ((j ^ swz) << 4);
@@ -482,11 +484,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(h.x), "=f"(h.y), "=f"(h.z), "=f"(h.w) : "r"(addr));
           float k0 = rs, k1 = rs, k2 = rs, k3 = rs;
           if (args.drop.thresh) {   // sub-layer output dropout: the mask multiplies the product, not the residual
-            const unsigned long long e0 =
-                (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N + (col0 + c * 32 + j * 4);
             float m0, m1, m2, m3;
-            pn_drop_mul2(args.drop, e0, m0, m1);
-            pn_drop_mul2(args.drop, e0 + 2, m2, m3);
+            pn_drop_run_get(args.drop, drun, dbase, 2 * j, m0, m1);
+            pn_drop_run_get(args.drop, drun, dbase, 2 * j + 1, m2, m3);
             k0 *= m0; k1 *= m1; k2 *= m2; k3 *= m3;
           }
           h.x = fmaf(__uint_as_float(v[j * 4 + 0]), k0, h.x);
@@ -526,7 +526,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __syncwarp();
       if (lane == 0) {
         if (kCtaGroup == 1) mbar_arrive(tempty_bar(as));
-        else mbar_arrive_remote(tempty_bar(as), 0);
+        else mbar_arrive_remote_relaxed(tempty_bar(as), 0);
       }
     }
     if (lane == 0) tma_store_wait_all<0>();
@@ -564,6 +564,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       warp_origin(group_id, r0, c0);
       for (int i = 0; i + 1 < kMaskBufs; ++i) load_mask_tile(i, r0, c0 + i * 64);
     }
+    float rs_next = 1.0f;        // row scale of the NEXT tile's row, requested a tile ahead (an L2 round trip otherwise
+    bool rs_next_ok = false;     // stalls the first multiply of every tile: 4 % of the masked epilogue's samples)
     for (int item = group_id; item < num_tiles; item += num_groups, ++it) {
       const int tile = tile_of(item);
       const int as = it & 1;
@@ -574,8 +576,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int col0 = n_blk * BLOCK_N;
       const bool live = row < args.M;
       float rs = args.out_scale;
+      if (live && args.row_scale) rs *= rs_next_ok ? rs_next : args.row_scale[row];
+      rs_next_ok = false;
+      if (args.row_scale && item + num_groups < num_tiles) {
+        int nr0, nc0;
+        warp_origin(item + num_groups, nr0, nc0);
+        if (nr0 + lane < args.M) { rs_next = args.row_scale[nr0 + lane]; rs_next_ok = true; }
+      }
       if (live) {
-        if (args.row_scale) rs *= args.row_scale[row];
         if (args.sumsq_in) {
           float ss = 0.0f;
           for (int p = 0; p < args.sumsq_parts; ++p) ss += args.sumsq_in[(size_t)p * args.M + row];
@@ -671,6 +679,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           if (lane == 0) tma_store_wait_read<1>();   // the store that used this buffer two chunks ago has drained
           __syncwarp();
+          PnDropRun drun = {};
+          unsigned long long dbase = 0;
+          if (args.drop.thresh) {   // the chunk's 32 index pairs share the inner hash of the mask (pn_drop_run)
+            dbase = (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N + (col0 + c * 64);
+            drun = pn_drop_run(args.drop, dbase, 32);
+          }
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -683,8 +697,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               if (args.relu) { x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
               if (args.drop.thresh) {   // FFN hidden dropout (after the activation, HF:103)
                 float m0, m1;
-                pn_drop_mul2(args.drop, (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N +
-                                            (col0 + c * 64 + j * 8 + 2 * e), m0, m1);
+                pn_drop_run_get(args.drop, drun, dbase, j * 4 + e, m0, m1);
                 x0 *= m0; x1 *= m1;
               }
               __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
@@ -759,6 +772,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               tmem_ld_32x32(t_row + c * 32, v);
               tmem_ld_wait();
               __syncwarp();                            // every lane finished reading this buffer two chunks ago
+              PnDropRun drun = {};
+              unsigned long long dbase = 0;
+              if (args.drop.thresh) {   // the chunk's 16 index pairs share the inner hash of the mask (pn_drop_run)
+                dbase = (unsigned long long)args.drop.idx_offset + (unsigned long long)row * args.N + (col0 + c * 32);
+                drun = pn_drop_run(args.drop, dbase, 16);
+              }
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 float4 f;
@@ -767,11 +786,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 f.z = __uint_as_float(v[j * 4 + 2]) * rs;
                 f.w = __uint_as_float(v[j * 4 + 3]) * rs;
                 if (args.drop.thresh) {   // sub-layer output dropout (staged thread-per-row: this thread owns `row`)
-                  const unsigned long long e0 = (unsigned long long)args.drop.idx_offset +
-                                                (unsigned long long)row * args.N + (col0 + c * 32 + j * 4);
                   float m0, m1, m2, m3;
-                  pn_drop_mul2(args.drop, e0, m0, m1);
-                  pn_drop_mul2(args.drop, e0 + 2, m2, m3);
+                  pn_drop_run_get(args.drop, drun, dbase, 2 * j, m0, m1);
+                  pn_drop_run_get(args.drop, drun, dbase, 2 * j + 1, m2, m3);
                   f.x *= m0; f.y *= m1; f.z *= m2; f.w *= m3;
                 }
                 *reinterpret_cast<float4*>(bufg + lane * 128 + ((j ^ swz) << 4)) = f;
@@ -819,7 +836,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __syncwarp();
       if (lane == 0) {
         if (kCtaGroup == 1) mbar_arrive(tempty_bar(as));
-        else mbar_arrive_remote(tempty_bar(as), 0);  // the leader's MMA warp owns the wait
+        else mbar_arrive_remote_relaxed(tempty_bar(as), 0);  // the leader's MMA warp owns the wait
       }
     }
     if (lane == 0) tma_store_wait_all<0>();            // smem must outlive the last bulk stores
@@ -1077,8 +1094,9 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
       return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: the norm-backward epilogue needs the 2-CTA residual mode with "
                                        "N %% 256 == 0, a bf16 copy output and 16-byte aligned operands");
     static const int norm_bufs = [] { const char* e = getenv("PN_NORM_BUFS"); return e ? atoi(e) : 3; }();
-    return norm_bufs == 4 ? launch_gemm<2, 256, false, false, false, 4>(A, lda, B, ldb, a, st)
-                          : launch_gemm<2, 256, false, false, false, 3>(A, lda, B, ldb, a, st);
+    return norm_bufs == 4   ? launch_gemm<2, 256, false, false, false, 4>(A, lda, B, ldb, a, st)
+           : norm_bufs == 2 ? launch_gemm<2, 256, false, false, false, 2>(A, lda, B, ldb, a, st)
+                            : launch_gemm<2, 256, false, false, false, 3>(A, lda, B, ldb, a, st);
   }
   // Deep-K residual launches over very many rows go out as row slabs: with the static tile order the CTA pairs that
   // share an A block drift apart over the ~80 waves of an M = 512 000 launch until the block has left L2 between

@@ -117,12 +117,14 @@ int pn_t5_head_prep(const float* x, const float* w, int64_t rows, int d, float e
 int pn_t5_cross_expand_q(const __nv_bfloat16* q, int ld_q, int64_t docs, int T, int H, int Mp, __nv_bfloat16* qexp,
                          cudaStream_t st);
 int pn_t5_cross_softmax(const float* scores, int lds, const float* rs, int64_t docs, int S, int TH, int Mp,
-                        __nv_bfloat16* P, cudaStream_t st, const int32_t* klen = nullptr);
+                        __nv_bfloat16* P, cudaStream_t st, const int32_t* klen = nullptr, PnDrop drop = PnDrop(),
+                        int H = 0, __nv_bfloat16* Pc = nullptr);   // drop: P carries the mask, Pc the clean values
 int pn_t5_cross_gather(const __nv_bfloat16* full, int Mp, int64_t docs, int T, int H, __nv_bfloat16* ctx, int ld_ctx,
                        cudaStream_t st);
 
 int pn_t5_cross_softmax_bwd(const __nv_bfloat16* Pp, const float* dP, int ldd, const float* rs, int64_t docs, int S,
-                            int TH, int Mp, __nv_bfloat16* U, int ldu, int u_col, __nv_bfloat16* V2, cudaStream_t st);
+                            int TH, int Mp, __nv_bfloat16* U, int ldu, int u_col, __nv_bfloat16* V2, cudaStream_t st,
+                            PnDrop drop = PnDrop(), int H = 0);   // drop: Pp = the clean probabilities (Pc above)
 int pn_t5_cross_bt_pack(const __nv_bfloat16* dC, const __nv_bfloat16* QK, int64_t docs, int d, int Mp,
                         __nv_bfloat16* BT, int ldb, int k_col, cudaStream_t st);
 

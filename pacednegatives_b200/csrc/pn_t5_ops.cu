@@ -325,7 +325,8 @@ cross_expand_q_kernel(const __nv_bfloat16* __restrict__ q, int ld_q, int64_t doc
 // P^T . X sums the normalised states); pad columns th >= TH are written as zero.  One CTA per document.
 __global__ void __launch_bounds__(256)
 cross_softmax_kernel(const float* __restrict__ scores, int lds, const float* __restrict__ rs, int S, int TH, int Mp,
-                     __nv_bfloat16* __restrict__ P, const int32_t* __restrict__ klen) {
+                     __nv_bfloat16* __restrict__ P, const int32_t* __restrict__ klen, const PnDrop drop, int H,
+                     __nv_bfloat16* __restrict__ Pc) {
   __shared__ float red[8][32];
   __shared__ float stat[32];
   const int64_t row0 = (int64_t)blockIdx.x * S;
@@ -370,10 +371,21 @@ cross_softmax_kernel(const float* __restrict__ scores, int lds, const float* __r
   __syncthreads();
   const float inv = stat[lane];
   if (th < Mp) {
+    // training with dropout (HF:331 on the cross-attention probabilities [doc, h, t, j], even row pitch): P carries the
+    // mask (it feeds P^T X), Pc keeps the clean probabilities for the softmax backward
+    const int T = TH / H;
+    const unsigned long long dbase =
+        (unsigned long long)drop.idx_offset +
+        (((unsigned long long)blockIdx.x * H + (th % H)) * T + (th / H)) * (unsigned long long)(S + (S & 1));
 #pragma unroll
     for (int i = 0; i < 64; ++i) {
       const int j = warp + 8 * i;
-      if (j < S) P[(size_t)(row0 + j) * Mp + th] = __float2bfloat16_rn(act ? v[i] * inv * rs[row0 + j] : 0.0f);
+      if (j < S) {
+        const float pv = act ? v[i] * inv * rs[row0 + j] : 0.0f;
+        if (Pc) Pc[(size_t)(row0 + j) * Mp + th] = __float2bfloat16_rn(pv);
+        const float mk = (act && drop.thresh) ? pn_drop_mul(drop, dbase + j) : 1.0f;
+        P[(size_t)(row0 + j) * Mp + th] = __float2bfloat16_rn(pv * mk);
+      }
     }
   }
 }
@@ -404,10 +416,14 @@ int pn_t5_cross_expand_q(const __nv_bfloat16* q, int ld_q, int64_t docs, int T, 
   return PN_OK;
 }
 int pn_t5_cross_softmax(const float* scores, int lds, const float* rs, int64_t docs, int S, int TH, int Mp,
-                        __nv_bfloat16* P, cudaStream_t st, const int32_t* klen) {
+                        __nv_bfloat16* P, cudaStream_t st, const int32_t* klen, PnDrop drop, int H,
+                        __nv_bfloat16* Pc) {
   if (docs == 0) return PN_OK;
   if (Mp > 32 || TH > Mp) return pn_fail(PN_E_UNSUPPORTED, "cross softmax: T*H=%d > 32", TH);
-  cross_softmax_kernel<<<(unsigned)docs, 256, 0, st>>>(scores, lds, rs, S, TH, Mp, P, klen);
+  if (drop.thresh && (H <= 0 || TH % H || !Pc))
+    return pn_fail(PN_E_BADARG, "cross softmax: dropout needs the head count and a buffer for the clean probabilities");
+  if (H <= 0) H = TH;
+  cross_softmax_kernel<<<(unsigned)docs, 256, 0, st>>>(scores, lds, rs, S, TH, Mp, P, klen, drop, H, Pc);
   PN_LAUNCHED();
   return PN_OK;
 }
@@ -432,14 +448,20 @@ template <int MP8>
 __global__ void __launch_bounds__(512)
 cross_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ Pp, const float* __restrict__ dP, int ldd,
                          const float* __restrict__ rs, int S, int TH, __nv_bfloat16* __restrict__ U, int ldu,
-                         int u_col, __nv_bfloat16* __restrict__ V2) {
+                         int u_col, __nv_bfloat16* __restrict__ V2, const PnDrop drop, int H) {
   constexpr int Mp = MP8 * 8;
   __shared__ float red[16][Mp];
   __shared__ float stat[Mp];
   const int64_t row0 = (int64_t)blockIdx.x * S;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  float p[Mp], g[Mp], dot[Mp];
+  // With dropout (Pp = the CLEAN probabilities then, times rs): out = (P (.) M)^T x, so the value path carries P (.) M,
+  // dP arrives for the dropped probabilities and dSc = P (.) (M (.) dP - sum_j P M dP).  `mm` holds the regenerated M.
+  float p[Mp], g[Mp], dot[Mp], mm[Mp];
   float r = 1.0f;
+  const int T = TH / H;
+  const unsigned long long Sp = (unsigned long long)(S + (S & 1));
+#pragma unroll
+  for (int c = 0; c < Mp; ++c) mm[c] = 1.0f;
   auto load = [&](int j) {
     if (j < S) {
       r = rs[row0 + j];
@@ -462,6 +484,15 @@ cross_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ Pp, const float* __re
 #pragma unroll
       for (int c = 0; c < Mp; ++c)
         if (c >= TH) { p[c] = 0.0f; g[c] = 0.0f; }
+      if (drop.thresh) {
+#pragma unroll
+        for (int c = 0; c < Mp; ++c)
+          if (c < TH) {
+            mm[c] = pn_drop_mul(drop, (unsigned long long)drop.idx_offset +
+                                          (((unsigned long long)blockIdx.x * H + (c % H)) * T + (c / H)) * Sp + j);
+            g[c] *= mm[c];
+          }
+      }
     } else {
 #pragma unroll
       for (int c = 0; c < Mp; ++c) { p[c] = 0.0f; g[c] = 0.0f; }
@@ -497,7 +528,7 @@ cross_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ Pp, const float* __re
 #pragma unroll
     for (int c = 0; c < Mp; c += 2) {
       const float d0 = p[c] * (g[c] - stat[c]), d1 = p[c + 1] * (g[c + 1] - stat[c + 1]);
-      __nv_bfloat162 a = __floats2bfloat162_rn(p[c], p[c + 1]);
+      __nv_bfloat162 a = __floats2bfloat162_rn(p[c] * mm[c], p[c + 1] * mm[c + 1]);
       __nv_bfloat162 b = __floats2bfloat162_rn(d0, d1);
       __nv_bfloat162 e = __floats2bfloat162_rn(d0 * r, d1 * r);
       up[c / 2] = *reinterpret_cast<uint32_t*>(&a);
@@ -540,12 +571,15 @@ cross_bt_pack_kernel(const __nv_bfloat16* __restrict__ dC, const __nv_bfloat16* 
 }  // namespace
 
 int pn_t5_cross_softmax_bwd(const __nv_bfloat16* Pp, const float* dP, int ldd, const float* rs, int64_t docs, int S,
-                            int TH, int Mp, __nv_bfloat16* U, int ldu, int u_col, __nv_bfloat16* V2, cudaStream_t st) {
+                            int TH, int Mp, __nv_bfloat16* U, int ldu, int u_col, __nv_bfloat16* V2, cudaStream_t st,
+                            PnDrop drop, int H) {
   if (docs == 0) return PN_OK;
+  if (drop.thresh && (H <= 0 || TH % H)) return pn_fail(PN_E_BADARG, "cross softmax backward: dropout needs the head count");
+  if (H <= 0) H = TH;
   if (2 * Mp > 64 || TH > Mp || (Mp % 8)) return pn_fail(PN_E_UNSUPPORTED, "cross softmax backward: T*H=%d > 32", TH);
   if ((ldd % 4) || (ldu % 8) || (u_col % 8))
     return pn_fail(PN_E_BADARG, "cross softmax backward: ldd %% 4, ldu %% 8, u_col %% 8 must be 0");
-#define PN_CSB(N) cross_softmax_bwd_kernel<N><<<(unsigned)docs, 512, 0, st>>>(Pp, dP, ldd, rs, S, TH, U, ldu, u_col, V2)
+#define PN_CSB(N) cross_softmax_bwd_kernel<N><<<(unsigned)docs, 512, 0, st>>>(Pp, dP, ldd, rs, S, TH, U, ldu, u_col, V2, drop, H)
   switch (Mp / 8) {
     case 1: PN_CSB(1); break;
     case 2: PN_CSB(2); break;

@@ -51,6 +51,7 @@ struct TrainWs {
   bool xattn;
   int Mp;
   std::vector<__nv_bfloat16*> qk, Pp, cpb;   // per decoder layer: QK [R, d], P*rs [rows, Mp], C' [R, d]
+  std::vector<__nv_bfloat16*> Pc;            // with dropout: the clean P*rs (Pp then carries the mask)
   float *scores, *cprime;                   // [rows, 128], [R, d]
   __nv_bfloat16 *qexp, *ctxfull, *dOfull, *dCp, *V2, *dQKb, *A_all, *B_all;
   __nv_bfloat16* xdrop;   // dropped bf16 copy of the encoder output (dropout of the encoder's final norm), or null
@@ -77,9 +78,7 @@ size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, Tra
   for (auto& p : w->act) p = (__nv_bfloat16*)take(rows * ff * 2);
   for (auto& p : w->lse) p = (float*)take(rows * H * 4);
   w->Mp = (T * H + 7) & ~7;
-  // dropout of the cross-attention probabilities needs them as [T, S] rows per head: the projection-free form is
-  // the eval / p = 0 path
-  w->xattn = m->xattn && (S % 128) == 0 && w->Mp <= 32 && !dropping;
+  w->xattn = m->xattn && (S % 128) == 0 && w->Mp <= 32;
   w->xdrop = dropping ? (__nv_bfloat16*)take(rows * d * 2) : nullptr;
   const size_t Mp = (size_t)w->Mp, R = (size_t)docs * Mp;
   if (!w->xattn) {
@@ -88,6 +87,11 @@ size_t carve_train(const PnT5* m, int64_t docs, int S, int T, uint8_t* base, Tra
     w->qk.resize(Ld); w->Pp.resize(Ld); w->cpb.resize(Ld);
     for (auto& p : w->qk) p = (__nv_bfloat16*)take(R * d * 2);
     for (auto& p : w->Pp) p = (__nv_bfloat16*)take(rows * Mp * 2);
+    w->Pc.clear();
+    if (dropping) {
+      w->Pc.resize(Ld);
+      for (auto& p : w->Pc) p = (__nv_bfloat16*)take(rows * Mp * 2);
+    }
     for (auto& p : w->cpb) p = (__nv_bfloat16*)take(R * d * 2);
     w->scores = (float*)take(rows * 128 * 4);
     w->cprime = (float*)take(R * d * 4);
@@ -297,11 +301,12 @@ static int train_forward_impl(PnT5* m, const int32_t* ids, const int64_t* labels
                                m->cta_group, st));
       PnGemmExtra ex = {};
       ex.row_scale = w.rs[2 * L]; ex.group_rows = S; ex.group_b_rows = Mp;
-      RC(pn_gemm_bf16_ex(w.hb[2 * L], d, w.qk[l], d, w.scores, 128, rows, 128, d, PN_EPI_F32, 0, &ex,
+      RC(pn_gemm_bf16_ex(xsrc, d, w.qk[l], d, w.scores, 128, rows, 128, d, PN_EPI_F32, 0, &ex,
                          (S % 256) == 0 ? 2 : 1, st));
-      RC(pn_t5_cross_softmax(w.scores, 128, w.rs[2 * L], docs, S, T * H, Mp, w.Pp[l], st));
+      RC(pn_t5_cross_softmax(w.scores, 128, w.rs[2 * L], docs, S, T * H, Mp, w.Pp[l], st, nullptr,
+                             DR(1, li, PN_DROP_CROSS_P, (long long)H * T * Sp), H, w.Pc.empty() ? nullptr : w.Pc[l]));
       PN_CUDA(cudaMemsetAsync(w.cprime, 0, (size_t)R * d * 4, st));
-      RC(pn_gemm_tn_batched(w.Pp[l], Mp, w.hb[2 * L], d, w.cprime, d, Mp, d, S, (int)docs, st));
+      RC(pn_gemm_tn_batched(w.Pp[l], Mp, xsrc, d, w.cprime, d, Mp, d, S, (int)docs, st));
       RC(pn_t5_f32_to_bf16(w.cprime, w.cpb[l], (int64_t)R * d, st));
       RC(pn_gemm_bf16_internal(w.cpb[l], d, D.ckv.packed + (size_t)di * d, d, w.ctxfull, di, R, di, d, PN_EPI_BF16, 0,
                                nullptr, m->cta_group, st));
@@ -453,7 +458,7 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
     if (w.xattn) {
       const int Mp = w.Mp, R = (int)docs * Mp, ldall = 64 * Ld;
       const float* rsE = w.rs[2 * L];
-      const __nv_bfloat16* X = w.hb[2 * L];
+      const __nv_bfloat16* X = w.xdrop ? w.xdrop : w.hb[2 * L];   // the (dropped) encoder output the forward read
       // d out (head blocks back on the diagonal) -> dWv' = dO^T C',  dC' = dO Wv'
       RC(pn_t5_cross_expand_q(w.ddctx, di, docs, T, H, Mp, w.dOfull, st));
       PN_CUDA(cudaMemsetAsync(w.dWtmp, 0, (size_t)2 * di * d * 4, st));
@@ -466,7 +471,8 @@ static int train_backward_impl(PnT5* m, const int32_t* ids, const float* dlogits
       RC(pn_gemm_bf16_ex(X, d, w.dCp, d, w.scores, 128, rows, 128, d, PN_EPI_F32, 0, &ex, (S % 256) == 0 ? 2 : 1, st));
       // softmax backward; its outputs and [dC'; QK] become column block l of the operands of ONE product over
       // all layers that yields the gradient of the normalised encoder states (after the loop)
-      RC(pn_t5_cross_softmax_bwd(w.Pp[l], w.scores, 128, rsE, docs, S, T * H, Mp, w.A_all, ldall, 64 * l, w.V2, st));
+      RC(pn_t5_cross_softmax_bwd(w.Pc.empty() ? w.Pp[l] : w.Pc[l], w.scores, 128, rsE, docs, S, T * H, Mp, w.A_all, ldall,
+                                 64 * l, w.V2, st, DR(1, l, PN_DROP_CROSS_P, (long long)H * T * Sp), H));
       RC(pn_t5_cross_bt_pack(w.dCp, w.qk[l], docs, d, Mp, w.B_all, ldall, 64 * l, st));
       // dQK = (rs dSc)^T X -> dWk' = Qexp^T dQK,  dQexp = dQK Wk'^T -> dq (head blocks), scaled for the fused norm
       PN_CUDA(cudaMemsetAsync(w.cprime, 0, (size_t)R * d * 4, st));

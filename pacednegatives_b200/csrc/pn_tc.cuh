@@ -45,6 +45,17 @@ __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
       "r"(cta)
       : "memory");
 }
+// Same without the release fence (MEMBAR.ALL.CTA + ERRBAR in SASS, ~1 us per use when TMA stores are in flight): for
+// arrivals that only hand back tensor memory, where tcgen05.wait::ld + tcgen05.fence::before_thread_sync have already
+// ordered the thread's TMEM reads and no generic-proxy data is published.
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar),
+      "r"(cta)
+      : "memory");
+}
 // PN_MBAR_HINT_NS (build-time, default off): suspend-time hint of try_wait in nanoseconds.  A waiting thread is put to
 // sleep for up to that long (it still wakes as soon as the phase completes) instead of re-polling every few cycles,
 // so the waiting warps stop competing for issue slots with the working warps of their scheduler.
