@@ -44,7 +44,7 @@ static_assert(kMaskBufs <= kResBufs, "mask ring uses the residual-tile barriers"
 // Norm-backward residual epilogue (kNormRes = ring depth): per warp kNormRes fp32 tiles + as many bf16 tiles of the
 // normed stream + the two bf16 copy tiles.  3 buffers = 22 KB per warp, 88 KB: 4 pipeline stages, as the plain TMA
 // residual path; 4 buffers = 28 KB per warp, 112 KB: 3 stages; 2 buffers = 16 KB per warp, 64 KB: 5 stages.
-// PN_NORM_BUFS (environment) picks, default 3.
+// PN_NORM_BUFS (environment) picks, default 2.
 __host__ __device__ constexpr int norm_warp_bytes(int bufs) { return bufs * (EPI_BUF_BYTES + RES_Y_BYTES) + 2 * RES_Y_BYTES; }
 static_assert(4 <= kResBufs && norm_warp_bytes(2) % 1024 == 0 && norm_warp_bytes(3) % 1024 == 0 && norm_warp_bytes(4) % 1024 == 0, "norm-backward epilogue tiles");
 
@@ -1093,7 +1093,9 @@ int pn_gemm_bf16_ex(const void* A, int lda, const void* B, int ldb, void* out, i
         (a.ld_hb % 8) || ((uintptr_t)a.nb_hb & 15))
       return pn_fail(PN_E_UNSUPPORTED, "pn_gemm: the norm-backward epilogue needs the 2-CTA residual mode with "
                                        "N %% 256 == 0, a bf16 copy output and 16-byte aligned operands");
-    static const int norm_bufs = [] { const char* e = getenv("PN_NORM_BUFS"); return e ? atoi(e) : 3; }();
+    // same-box A/B (profiles/r4x_ab.txt): 2 slots / 5 stages 100.7 and 102.0 ms per training step, 3 slots / 4 stages
+    // 100.9 and 102.4 ms, 4 slots / 3 stages +1.2 ms: the kernel is main-loop-bound, stages matter more than prefetch depth
+    static const int norm_bufs = [] { const char* e = getenv("PN_NORM_BUFS"); return e ? atoi(e) : 2; }();
     return norm_bufs == 4   ? launch_gemm<2, 256, false, false, false, 4>(A, lda, B, ldb, a, st)
            : norm_bufs == 2 ? launch_gemm<2, 256, false, false, false, 2>(A, lda, B, ldb, a, st)
                             : launch_gemm<2, 256, false, false, false, 3>(A, lda, B, ldb, a, st);
