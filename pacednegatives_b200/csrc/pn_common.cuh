@@ -97,6 +97,10 @@ __device__ __forceinline__ float4 pn_ldg_stream(const float4* p) {
                : "l"(p));
   return r;
 }
+// request the 128-byte line holding p into L2 (no register, no wait)
+__device__ __forceinline__ void pn_prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 // 256-bit streaming accesses (sm_100: LDG.256 / STG.256): 32-byte aligned, eight floats per thread per access
 struct __align__(32) pn_float8 { float v[8]; };
 __device__ __forceinline__ pn_float8 pn_ldg_stream8(const pn_float8* p) {

@@ -483,6 +483,298 @@ topk_warp_kernel(const float* __restrict__ scores, const int32_t* __restrict__ d
   }
 }
 
+// ---- second generation of the warp-per-query kernel (same contract, same results): O(C log R) rank work instead of
+// O(R C / 32 x 4), and the K winners from a candidate set of a few dozen keys instead of K sweeps over all C.
+//   ranks  : the R relevant keys are sorted (counting, lanes over the relevant documents); every candidate finds its
+//            position among them by a branch-free binary search in shared memory (16 searches in flight per lane);
+//            a warp-aggregated histogram of the positions (MATCH.ANY, one atomic per distinct position and pass) and
+//            its prefix sum ARE the ranks: rank(s-th best relevant) + 1 = #{candidates >= it} = sum_{p <= s} cnt[p].
+//            AP = sum_s (s + 1) / (rank_s + 1) needs no second R^2 loop.  R <= 12 keeps the direct compare loop
+//            (cheaper below ~12 documents), R > 256 too (does not fit the sorted list; only dense synthetic qrels).
+//   top-K  : tau = the K-th largest of the 32 lane maxima (K rounds of two REDUX over ONE value per lane); the K best
+//            keys are all >= tau, and usually only K..2K keys are; they are compacted (ballot) and ranked among
+//            themselves.  More than 64 survivors (the best keys crowded into few lanes) falls back to the K sweeps.
+//   loads  : C % 4 == 0 and 16-byte aligned rows -> float4 / int4 / uchar4 loads (24 instead of 96 load instructions).
+// Document ids must be unique within a query (they are the low word of the sort key), as for the kernels above.
+constexpr int kDirectMaxR = 12;
+constexpr int kSortMaxR = 256;
+constexpr int kMaxCand = 64;      // survivors of the tau filter that are ranked among themselves (two per lane)
+struct __align__(16) TopkWarp2Smem {
+  uint64_t relkey[kWarpMaxC];     // [0, R): relevant keys in load order; sort path: [512, 512 + P2) the sorted list
+  union {
+    uint16_t rel_rank[kWarpMaxC]; // direct path: 0-based ranks of the relevant documents
+    int cnt[kWarpMaxC / 2];       // sort path: histogram of the candidates' positions among the relevant keys
+  } u;
+  uint8_t srel[kWarpMaxC];
+  int hist[256];
+  uint64_t top[kFastMaxK];
+  uint64_t clist[kMaxCand];
+  int toprel[kFastMaxK];
+  uint16_t cpos[kMaxCand];
+};
+
+__device__ __forceinline__ uint64_t topk_key(float s, int32_t id) {
+  return ((uint64_t)orderable(s) << 32) | (uint32_t)(id ^ 0x80000000);
+}
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 2)
+topk_warp2_kernel(const float* __restrict__ scores, const int32_t* __restrict__ docids,
+                  const uint8_t* __restrict__ rels, int64_t Q, int32_t C, int32_t K, int32_t vec,
+                  int32_t* __restrict__ top_ids, float* __restrict__ top_scores, float* __restrict__ metrics,
+                  const int32_t* __restrict__ qrel_num, const double* __restrict__ qrel_idcg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  TopkWarp2Smem& sm = reinterpret_cast<TopkWarp2Smem*>(smem_raw)[warp];
+  for (int i = lane; i < 256; i += 32) sm.hist[i] = 0;
+  __syncwarp();
+  const uint32_t full = 0xffffffffu;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const int rounds = K < C ? K : C;
+  // DCG discount of this lane's slot: once per warp, not once per query (a double-precision log2 is ~150 instructions)
+  const double disc = lane < K ? 1.0 / log2((double)(lane + 2)) : 0.0;
+  const int64_t qstride = (int64_t)gridDim.x * kWarpsPerCta;
+  for (int64_t q = (int64_t)blockIdx.x * kWarpsPerCta + warp; q < Q; q += qstride) {
+    const float* sc = scores + q * (int64_t)C;
+    const int32_t* ids = docids ? docids + q * (int64_t)C : nullptr;
+    const uint8_t* rl = rels ? rels + q * (int64_t)C : nullptr;
+    // this warp's NEXT query into L2 while the current one is ranked (the loads of a query are one exposed DRAM round
+    // trip per warp: 27 % of the warp samples of the first version sat on them)
+    if (q + qstride < Q) {
+      const int64_t nb = (q + qstride) * (int64_t)C;
+      const char* ps = reinterpret_cast<const char*>(scores + nb);
+      for (int off = lane * 128; off < C * 4 + 127; off += 32 * 128) pn_prefetch_l2(ps + min(off, C * 4 - 1));
+      if (docids) {
+        const char* pd = reinterpret_cast<const char*>(docids + nb);
+        for (int off = lane * 128; off < C * 4 + 127; off += 32 * 128) pn_prefetch_l2(pd + min(off, C * 4 - 1));
+      }
+      if (rels) {
+        const char* pr = reinterpret_cast<const char*>(rels + nb);
+        for (int off = lane * 128; off < C + 127; off += 32 * 128) pn_prefetch_l2(pr + min(off, C - 1));
+      }
+    }
+    // register slot j of this lane holds candidate pos_of(j)
+    auto pos_of = [&](int j) { return vec ? 4 * (lane + 32 * (j >> 2)) + (j & 3) : lane + 32 * j; };
+    uint64_t k[32];
+    uint32_t rr[32];
+    if (vec) {
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        const int i0 = 4 * (lane + 32 * g);
+        float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        int4 d4 = make_int4(i0, i0 + 1, i0 + 2, i0 + 3);
+        uchar4 r4 = make_uchar4(0, 0, 0, 0);
+        const bool in = i0 < C;      // C % 4 == 0: a group of four is inside or outside as a whole
+        if (in) {
+          s4 = __ldg(reinterpret_cast<const float4*>(sc + i0));
+          if (ids) d4 = __ldg(reinterpret_cast<const int4*>(ids + i0));
+          if (rl) r4 = __ldg(reinterpret_cast<const uchar4*>(rl + i0));
+          *reinterpret_cast<uchar4*>(&sm.srel[i0]) = r4;
+        }
+        k[4 * g + 0] = in ? topk_key(s4.x, d4.x) : 0ull;
+        k[4 * g + 1] = in ? topk_key(s4.y, d4.y) : 0ull;
+        k[4 * g + 2] = in ? topk_key(s4.z, d4.z) : 0ull;
+        k[4 * g + 3] = in ? topk_key(s4.w, d4.w) : 0ull;
+        rr[4 * g + 0] = r4.x; rr[4 * g + 1] = r4.y; rr[4 * g + 2] = r4.z; rr[4 * g + 3] = r4.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int i = lane + 32 * j;
+        k[j] = 0ull;
+        rr[j] = 0u;
+        if (i < C) {
+          k[j] = topk_key(__ldg(sc + i), ids ? __ldg(ids + i) : i);
+          rr[j] = rl ? (uint32_t)__ldg(rl + i) : 0u;
+          sm.srel[i] = (uint8_t)rr[j];
+        }
+      }
+    }
+    // the list of relevant documents (ballot prefix), grade histogram
+    int R = 0;
+    uint32_t gmax = 0;
+    if (rl) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const uint32_t m = __ballot_sync(full, rr[j] != 0u);
+        if (rr[j] != 0u) {
+          sm.relkey[R + __popc(m & lt_mask)] = k[j];
+          atomicAdd(&sm.hist[rr[j]], 1);
+          gmax = max(gmax, rr[j]);
+        }
+        R += __popc(m);
+      }
+      gmax = __reduce_max_sync(full, gmax);
+    }
+    __syncwarp();
+
+    // ---- ranks of the relevant documents -> average precision, first relevant rank
+    double ap = 0.0;
+    int first = 0x7fffffff;
+    if (metrics && R > 0) {
+      if (R <= kDirectMaxR || R > kSortMaxR) {
+        for (int t = 0; t < R; ++t) {
+          const uint64_t kr = sm.relkey[t];
+          int cnt = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) cnt += k[j] > kr ? 1 : 0;
+          cnt = __reduce_add_sync(full, cnt);
+          if (lane == 0) sm.u.rel_rank[t] = (uint16_t)cnt;
+        }
+        __syncwarp();
+        for (int j = lane; j < R; j += 32) {
+          const int rk = sm.u.rel_rank[j];
+          int upto = 0;
+          for (int t = 0; t < R; ++t) upto += sm.u.rel_rank[t] <= rk ? 1 : 0;
+          ap += (double)upto / (double)(rk + 1);
+          first = min(first, rk);
+        }
+        first = __reduce_min_sync(full, first);
+      } else {
+        int P2 = 16;
+        while (P2 <= R) P2 <<= 1;                    // a power of two > R: at least one 0 sentinel ends the list
+        uint64_t* sorted = sm.relkey + 512;          // R <= 256: the unsorted list ends before entry 512, P2 <= 512
+        int* cnt = sm.u.cnt;
+        for (int i = lane; i < P2; i += 32) sorted[i] = 0ull;
+        for (int i = lane; i <= R; i += 32) cnt[i] = 0;
+        __syncwarp();
+        for (int t0 = 0; t0 < R; t0 += 32) {         // lanes over the relevant documents
+          const int t = t0 + lane;
+          if (t < R) {
+            const uint64_t mine = sm.relkey[t];
+            int s = 0;
+#pragma unroll 4
+            for (int u = 0; u < R; ++u) s += sm.relkey[u] > mine ? 1 : 0;
+            sorted[s] = mine;                        // descending; unique keys -> a permutation of [0, R)
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          int pos[16];                               // #{relevant keys > candidate}, 16 searches in flight
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) pos[jj] = 0;
+          for (int step = P2 >> 1; step >= 1; step >>= 1) {
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj) pos[jj] += sorted[pos[jj] + step - 1] > k[half * 16 + jj] ? step : 0;
+          }
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) {
+            const int p = pos[jj];                   // p == R: below every relevant document (and the padding keys)
+            const uint32_t peers = __match_any_sync(full, p);
+            if (p < R && (peers & lt_mask) == 0u) atomicAdd(&cnt[p], __popc(peers));
+          }
+        }
+        __syncwarp();
+        int carry = 0;
+        for (int base = 0; base < R; base += 32) {
+          const int s = base + lane;
+          int v = s < R ? cnt[s] : 0;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(full, v, o);
+            if (lane >= o) v += n;
+          }
+          const int rank1 = carry + v;               // rank + 1 of the s-th best relevant document
+          if (s < R) ap += (double)(s + 1) / (double)rank1;
+          if (s == 0) first = rank1 - 1;
+          carry += __shfl_sync(full, v, 31);
+        }
+        first = __shfl_sync(full, first, 0);
+      }
+    }
+
+    // ---- the K best, in order
+    if (lane < kFastMaxK) { sm.top[lane] = 0ull; sm.toprel[lane] = 0; }
+    uint64_t lb = 0ull;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) lb = k[j] > lb ? k[j] : lb;
+    uint64_t tau = 0ull;
+    {
+      uint64_t cur = lb;
+      for (int rnd = 0; rnd < rounds; ++rnd) {
+        const uint32_t whi = __reduce_max_sync(full, (uint32_t)(cur >> 32));
+        const uint32_t wlo = __reduce_max_sync(full, (uint32_t)(cur >> 32) == whi ? (uint32_t)cur : 0u);
+        tau = ((uint64_t)whi << 32) | wlo;
+        if (tau == 0ull) break;                      // fewer than K lanes hold a key: every key is a candidate
+        if (cur == tau) cur = 0ull;
+      }
+    }
+    int M = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const bool take = k[j] >= tau && k[j] != 0ull;
+      const uint32_t m = __ballot_sync(full, take);
+      if (take) {
+        const int slot = M + __popc(m & lt_mask);
+        if (slot < kMaxCand) { sm.clist[slot] = k[j]; sm.cpos[slot] = (uint16_t)pos_of(j); }
+      }
+      M += __popc(m);
+    }
+    __syncwarp();
+    if (M <= kMaxCand) {
+      for (int e = lane; e < M; e += 32) {
+        const uint64_t mine = sm.clist[e];
+        int r = 0;
+        for (int u = 0; u < M; ++u) r += sm.clist[u] > mine ? 1 : 0;
+        if (r < rounds) { sm.top[r] = mine; sm.toprel[r] = sm.srel[sm.cpos[e]]; }
+      }
+    } else {
+      for (int rnd = 0; rnd < rounds; ++rnd) {
+        uint64_t b = 0ull;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) b = k[j] > b ? k[j] : b;
+        const uint32_t whi = __reduce_max_sync(full, (uint32_t)(b >> 32));
+        const uint32_t wlo = __reduce_max_sync(full, (uint32_t)(b >> 32) == whi ? (uint32_t)b : 0u);
+        const uint64_t best = ((uint64_t)whi << 32) | wlo;
+        if (best == 0ull) break;
+        if (b == best) {
+          int wpos = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (k[j] == best) { k[j] = 0ull; wpos = pos_of(j); }
+          sm.top[rnd] = best;
+          sm.toprel[rnd] = sm.srel[wpos];
+        }
+      }
+    }
+    __syncwarp();
+    if (lane < K) {
+      const uint64_t kk = lane < kFastMaxK ? sm.top[lane] : 0ull;
+      const bool live = kk != 0ull;
+      if (top_ids) top_ids[q * K + lane] = live ? (int32_t)((uint32_t)kk ^ 0x80000000u) : -1;
+      if (top_scores) top_scores[q * K + lane] = live ? unorderable((uint32_t)(kk >> 32)) : 0.0f;
+    }
+    if (metrics) {
+      ap = pn_warp_sum(ap);
+      // DCG@K from the winners' grades; ideal DCG@K from the grade histogram, high to low: lane = slot
+      double dcg = 0.0, idcg = 0.0;
+      if (lane < K) {
+        if (sm.toprel[lane]) dcg = (double)sm.toprel[lane] * disc;
+        int cum = 0, grade = 0;
+        for (int g = (int)gmax; g >= 1; --g) {
+          cum += sm.hist[g];
+          if (cum > lane) { grade = g; break; }
+        }
+        idcg = (double)grade * disc;
+      }
+      dcg = pn_warp_sum(dcg);
+      idcg = pn_warp_sum(idcg);
+      if (lane == 0) {
+        if (qrel_idcg) idcg = qrel_idcg[q];
+        const int nrel = qrel_num ? qrel_num[q] : R;
+        float* m = metrics + q * 4;
+        m[0] = idcg > 0.0 ? (float)(dcg / idcg) : 0.0f;
+        m[1] = first < C ? (float)(1.0 / (double)(first + 1)) : 0.0f;
+        m[2] = first < K ? (float)(1.0 / (double)(first + 1)) : 0.0f;
+        m[3] = nrel > 0 ? (float)(ap / (double)nrel) : 0.0f;
+      }
+    }
+    __syncwarp();
+    for (int g = 1 + lane; g <= (int)gmax; g += 32) sm.hist[g] = 0;   // only the touched entries
+    __syncwarp();
+  }
+}
+
 }  // namespace
 
 extern "C" int pn_topk_metrics(const float* scores, const int32_t* docids, const uint8_t* rels,
@@ -499,7 +791,25 @@ extern "C" int pn_topk_metrics_qrels(const float* scores, const int32_t* docids,
   PN_CHECK_ARG(Q >= 0 && C >= 1 && C <= 4096 && K >= 1);
   if (Q == 0) return PN_OK;
   PN_CHECK_ARG(scores != nullptr);
-  static const int want_warp = [] { const char* e = getenv("PN_TOPK_WARP"); return e ? atoi(e) : 1; }();
+  // PN_TOPK_WARP (measurement knob): 2 = second-generation warp kernel (default), 1 = first generation, 0 = block per query
+  static const int want_warp = [] { const char* e = getenv("PN_TOPK_WARP"); return e ? atoi(e) : 2; }();
+  if (K <= kFastMaxK && C <= kWarpMaxC && want_warp >= 2) {
+    const size_t smem = sizeof(TopkWarp2Smem) * kWarpsPerCta;
+    static bool attr2_done = false;
+    if (!attr2_done) {
+      PN_CUDA(cudaFuncSetAttribute(topk_warp2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr2_done = true;
+    }
+    // vector loads need C % 4 == 0 (whole groups of four, 16-byte row pitch) and aligned base pointers
+    const int vec = (C % 4 == 0) && ((uintptr_t)scores % 16 == 0) && (!docids || (uintptr_t)docids % 16 == 0) &&
+                    (!rels || (uintptr_t)rels % 4 == 0);
+    const int64_t want = (Q + kWarpsPerCta - 1) / kWarpsPerCta;
+    const int grid = (int)(want < PN_SM_COUNT * 2 ? want : PN_SM_COUNT * 2);
+    topk_warp2_kernel<<<grid, kWarpsPerCta * 32, smem, (cudaStream_t)stream>>>(
+        scores, docids, rels, Q, C, K, vec, top_ids, top_scores, metrics_out, qrel_num, qrel_idcg);
+    PN_LAUNCHED();
+    return PN_OK;
+  }
   if (K <= kFastMaxK && C <= kWarpMaxC && want_warp) {
     const size_t smem = sizeof(TopkWarpSmem) * kWarpsPerCta;
     static bool attr_done = false;

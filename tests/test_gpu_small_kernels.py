@@ -403,6 +403,63 @@ def test_topk_metrics(pn, Q, C, K):
     np.testing.assert_allclose(out["metrics"].cpu().numpy(), em, rtol=1e-6, atol=1e-7)
 
 
+@pytest.mark.parametrize("C", [1000, 999, 1024, 64])
+def test_topk_metrics_warp_kernel_paths(pn, C):
+    """Every branch of the second-generation warp kernel (csrc/pn_topk_metrics.cu, topk_warp2_kernel): the number of
+    relevant documents on both sides of the direct / sorted-list / too-many thresholds (12 | 13, 256 | 257), none and
+    all; the tau filter with few survivors (scores falling with the position, either lane layout), 33..64 survivors and
+    the fall-back to the K sweeps (the best keys crowded into one lane's slots); vector (C % 4 == 0, aligned) and scalar
+    loads (odd C, rows starting off a 16-byte boundary); no docids.  Bit-exact ranking against the oracle."""
+    rng = np.random.RandomState(77 + C)
+    K = 10
+    rows = []
+    def lane_slots(vec):      # candidate positions in the order lane 0's slots, lane 1's slots, ...
+        if vec:
+            p = [4 * (lane + 32 * (j >> 2)) + (j & 3) for lane in range(32) for j in range(32)]
+        else:
+            p = [lane + 32 * j for lane in range(32) for j in range(32)]
+        return [x for x in p if x < C]
+    for nrel in [0, 1, 12, 13, 40, 256, 257, C]:
+        nrel = min(nrel, C)
+        s = rng.randn(C).astype(np.float32)
+        s[: C // 4] = np.round(s[: C // 4], 1)
+        r = np.zeros(C, np.uint8)
+        r[rng.permutation(C)[:nrel]] = rng.randint(1, 4, size=nrel)
+        rows.append((s, r))
+    for crowd in ["falling", "vec", "scalar"]:
+        s = np.empty(C, np.float32)
+        order = np.arange(C) if crowd == "falling" else np.array(lane_slots(crowd == "vec"))
+        s[order] = np.linspace(5.0, -5.0, C, dtype=np.float32) + (rng.randn(C) * 1e-4).astype(np.float32)
+        r = (rng.rand(C) < 0.05).astype(np.uint8) * 2
+        rows.append((s, r))
+    scores = np.stack([x for x, _ in rows])
+    rels = np.stack([x for _, x in rows])
+    Q = len(rows)
+    docids = np.stack([rng.permutation(8841823)[:C] for _ in range(Q)]).astype(np.int32)
+    for ids in (docids, None):
+        eids, esc, em = om.batch_metrics(scores, docids if ids is not None else np.tile(np.arange(C), (Q, 1)), rels, K)
+        out = pn.m.topk_metrics(torch.tensor(scores).cuda(), None if ids is None else torch.tensor(ids).cuda(),
+                                torch.tensor(rels).cuda(), K)
+        np.testing.assert_array_equal(out["top_ids"].cpu().numpy(), eids)
+        np.testing.assert_array_equal(out["top_scores"].cpu().numpy(), esc)
+        np.testing.assert_allclose(out["metrics"].cpu().numpy(), em, rtol=1e-6, atol=1e-7)
+    # rows that start off a 16-byte boundary (a view into a larger buffer): the scalar-load path, same results
+    flat_s = torch.zeros(Q * C + 1).cuda()
+    flat_d = torch.zeros(Q * C + 1, dtype=torch.int32).cuda()
+    flat_r = torch.zeros(Q * C + 1, dtype=torch.uint8).cuda()
+    flat_s[1:] = torch.tensor(scores).cuda().reshape(-1)
+    flat_d[1:] = torch.tensor(docids).cuda().reshape(-1)
+    flat_r[1:] = torch.tensor(rels).cuda().reshape(-1)
+    eids, esc, em = om.batch_metrics(scores, docids, rels, K)
+    out = pn.m.topk_metrics(flat_s[1:].view(Q, C), flat_d[1:].view(Q, C), flat_r[1:].view(Q, C), K)
+    np.testing.assert_array_equal(out["top_ids"].cpu().numpy(), eids)
+    np.testing.assert_allclose(out["metrics"].cpu().numpy(), em, rtol=1e-6, atol=1e-7)
+    # no relevance labels: ranking only
+    out = pn.m.topk_metrics(torch.tensor(scores).cuda(), torch.tensor(docids).cuda(), None, 32)
+    eids32, _, _ = om.batch_metrics(scores, docids, np.zeros_like(rels), 32)
+    np.testing.assert_array_equal(out["top_ids"].cpu().numpy(), eids32)
+
+
 def test_topk_metrics_with_qrel_totals(pn):
     """AP / nDCG denominators from the queries' full qrels (relevant documents missing from the candidate list):
     hand case of tests/test_oracle_golden.py + a random batch against the oracle, both kernel variants (K <= 32 and

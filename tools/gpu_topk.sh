@@ -2,7 +2,7 @@
 TAG=${1:-r4k}
 mkdir -p gpurun_out
 timeout 300 python -m pytest tests/test_gpu_small_kernels.py tests/test_gpu_t5.py -q -m gpu -k "topk or rerank or empty or argument" > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/${TAG}_pytest.log | cut -c1-300
-for v in 1 0; do
+for v in 2 1 0; do
 PN_TOPK_WARP=$v timeout 120 python - <<PY
 import torch, sys
 sys.path.insert(0, '.')
