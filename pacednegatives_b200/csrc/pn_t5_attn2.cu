@@ -206,56 +206,75 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
         }
         for (int qb = 2; qb < n_qb; ++qb) load_q(qb);
       }
-    } else if ((warp == 9 || warp == 11) && lane == 0) {
+    } else if (warp == 9 || warp == 11) {
       // ===================== MMA issuers: warp 9 drives stream A, warp 11 stream B =====================
-      // Each stream alternates QK(n+1) / PV(n); a dedicated issuing thread per stream means a slow softmax
+      // Each stream alternates QK(n+1) / PV(n); a dedicated issuing warp per stream means a slow softmax
       // warpgroup never delays the other one's MMAs (the two streams touch disjoint TMEM columns and only
       // read the shared K/V tiles; each commits its own last use of a tile to the tile's empty barrier).
+      // The WHOLE warp runs the loop and one lane issues: every descriptor is then warp-uniform and sits in a uniform
+      // register.  With a single divergent thread each tcgen05.mma was wrapped in its own vector->uniform waterfall
+      // (4 dependent R2UR + ELECT + branch, ~80 cycles per instruction: profiles/r5b_attn_fwd_source_summary.md) and the
+      // eight [128 x 64 x 16] products of P V — 32 tensor-core cycles each — took ~700 cycles to ISSUE, all of it on
+      // the softmax warps' critical path (P buffer hand-back every step, O hand-over at the end of a query block).
+      const bool leader = lane == 0;
       constexpr uint32_t IDESC_QK = make_idesc_bf16(128, KC, 0, 0);  // A = Q K-major, B = K K-major
       constexpr uint32_t IDESC_PV = make_idesc_bf16(128, DK, 0, 1);  // A = P (TMEM),  B = V MN-major
-      const int wg = warp == 9 ? 0 : 1;
+      // warp index and TMEM base through a lane-0 shuffle: values the compiler can prove warp-uniform
+      const int wg = __shfl_sync(0xffffffffu, warp, 0) == 9 ? 0 : 1;
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
       const int my_rounds = wg == 0 ? rounds : n_qb / 2;             // rounds in which this stream has a block
       const int steps = n_items * my_rounds * n_kc;
-      const uint32_t s_tmem = tmem + TM_S + wg * 128, p_tmem = tmem + TM_P + wg * 64,
-                     o_tmem = tmem + TM_O + wg * DK;
+      const uint32_t s_tmem = tmem_u + TM_S + wg * 128, p_tmem = tmem_u + TM_P + wg * 64,
+                     o_tmem = tmem_u + TM_O + wg * DK;
       struct Cur { int it, rd, c; };
       auto advance = [&](Cur& u) {
         if (++u.c == n_kc) { u.c = 0; if (++u.rd == my_rounds) { u.rd = 0; ++u.it; } }
       };
-      auto issue_qk = [&](const Cur& u, int n) {       // n = index of this step in the stream
+      auto uni = [](const Cur& v) {                    // the walk's state, provably warp-uniform for the compiler
+        return Cur{__shfl_sync(0xffffffffu, v.it, 0), __shfl_sync(0xffffffffu, v.rd, 0),
+                   __shfl_sync(0xffffffffu, v.c, 0)};
+      };
+      auto issue_qk = [&](const Cur& uu, int n) {      // n = index of this step in the stream
+        const Cur u = uni(uu);
         const int qb = 2 * u.rd + wg;
         const uint32_t ph = u.it & 1;
         if (n > 0) mbar_wait(bar(BAR_SFREE + wg), (n - 1) & 1);     // softmax holds S(n-1) in registers
-        if (wg == 0) DBG_STAMP(1, n, 0);
+        if (wg == 0 && leader) DBG_STAMP(1, n, 0);
         if (u.c == 0) mbar_wait(bar(BAR_QFULL + qb), ph);
         mbar_wait(bar(BAR_KFULL + u.c), ph);
         tc_fence_after();
         const uint64_t adesc = make_desc_kmajor_sw128(base + SM_Q + qb * TILE_BYTES);
         const uint64_t bdesc = make_desc_kmajor_sw128(base + SM_K + u.c * TILE_BYTES);
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < DK / 16; ++k)
-          umma_bf16<1>(s_tmem, adesc + 2u * k, bdesc + 2u * k, IDESC_QK, k ? 1u : 0u);
-        umma_commit<1>(bar(BAR_SFULL + wg));
-        if (wg == 0) DBG_STAMP(1, n, 1);
-        if (u.c == n_kc - 1) umma_commit<1>(bar(BAR_QEMPTY + qb));
-        if (u.rd == my_rounds - 1) umma_commit<1>(bar(BAR_KEMPTY + u.c));   // stream's last use of K_c
+          for (int k = 0; k < DK / 16; ++k)
+            umma_bf16<1>(s_tmem, adesc + 2u * k, bdesc + 2u * k, IDESC_QK, k ? 1u : 0u);
+          umma_commit<1>(bar(BAR_SFULL + wg));
+          if (wg == 0) DBG_STAMP(1, n, 1);
+          if (u.c == n_kc - 1) umma_commit<1>(bar(BAR_QEMPTY + qb));
+          if (u.rd == my_rounds - 1) umma_commit<1>(bar(BAR_KEMPTY + u.c));   // stream's last use of K_c
+        }
+        __syncwarp();
       };
-      auto issue_pv = [&](const Cur& u, int n) {
+      auto issue_pv = [&](const Cur& uu, int n) {
+        const Cur u = uni(uu);
         mbar_wait(bar(BAR_PREADY + wg), n & 1);
-        if (wg == 0) DBG_STAMP(1, n, 2);
+        if (wg == 0 && leader) DBG_STAMP(1, n, 2);
         if (u.c == 0) mbar_wait(bar(BAR_OEMPTY + wg), ((n / n_kc) & 1) ^ 1);
         mbar_wait(bar(BAR_VFULL + u.c), u.it & 1);
         tc_fence_after();
-        const uint32_t vbase = base + SM_V + u.c * TILE_BYTES;
+        // a 16-key step advances the MN-major descriptor of V by 16 rows x 128 B = 128 address units of 16 B
+        const uint64_t vdesc = make_desc_mnmajor_sw128(base + SM_V + u.c * TILE_BYTES, 1024);
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < KC / 16; ++k) {
-          const uint64_t bdesc = make_desc_mnmajor_sw128(vbase + k * 16 * 128, 1024);
-          umma_bf16_ts(o_tmem, p_tmem + k * 8, bdesc, IDESC_PV, (u.c | k) ? 1u : 0u);
+          for (int k = 0; k < KC / 16; ++k)
+            umma_bf16_ts(o_tmem, p_tmem + k * 8, vdesc + 128u * k, IDESC_PV, (u.c | k) ? 1u : 0u);
+          umma_commit<1>(bar(BAR_PFREE + wg));                             // P buffer / O readable again
+          if (wg == 0) DBG_STAMP(1, n, 3);
+          if (u.c == n_kc - 1) umma_commit<1>(bar(BAR_OFULL + wg));
+          if (u.rd == my_rounds - 1) umma_commit<1>(bar(BAR_VEMPTY + u.c));
         }
-        umma_commit<1>(bar(BAR_PFREE + wg));                               // P buffer / O readable again
-        if (wg == 0) DBG_STAMP(1, n, 3);
-        if (u.c == n_kc - 1) umma_commit<1>(bar(BAR_OFULL + wg));
-        if (u.rd == my_rounds - 1) umma_commit<1>(bar(BAR_VEMPTY + u.c));
+        __syncwarp();
       };
       if (steps > 0) {
         Cur pv{0, 0, 0}, qk{0, 0, 0};
