@@ -97,6 +97,13 @@ __device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
 // (n in the low mantissa bits of t = x + 1.5 * 2^23), a cubic minimax polynomial for 2^f on [-0.5, 0.5] (relative
 // error 7.5e-5, far below the bf16 rounding of P) and n added into the exponent field.  x is clamped at -125 (2^-125
 // is 0 for every purpose here and keeps the exponent arithmetic in range); x <= ~+60 by the redo threshold.
+#ifndef PN_ATTN_DEFER_EPI
+// 1: a query block's epilogue runs one step late, after the first step of the stream's next block (see the step loop).
+// Measured and left off (profiles/r5e_attn_defer_epilogue_ab.txt, same box): 508-510 TFLOP/s with the immediate epilogue,
+// 469 with the deferred one (-8 %; re-rank 9 058 -> 8 915 pairs/s): the next block's first P V then waits for the O read
+// (BAR_OEMPTY) and lands ~2 200 cycles after its P was ready, and the epilogue itself is no shorter.
+#define PN_ATTN_DEFER_EPI 0
+#endif
 #ifndef PN_ATTN_POLY
 // Measured (same box, profiles/r4h_attn_poly_ab.txt; 250 docs x 12 heads x 512): 0 -> 496.7 TFLOP/s, 1 -> 501.5 (+1 %),
 // 2 -> 434.7 (-12 %); re-rank step 8 581 / 8 575 / 8 352 pairs/s.  The kernel is not MUFU-bound (two softmax warps per
@@ -301,6 +308,53 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
     const float* bcopy = sbias + sh * BIAS_STRIDE;
     float m_used = 0.0f, l = 0.0f, mx_prev = 0.0f;
     int n = 0;                                      // valid steps done by this stream
+    // epilogue of query block qb_ of document doc_ (the blk_-th block this stream finishes): ctx[row, head*64..] = O / l
+    auto epilogue = [&](float l_, float m_, int qb_, int doc_, int blk_) {
+      mbar_wait(bar(BAR_OFULL + wg), blk_ & 1);
+      tc_fence_after();
+      if (warp == 0 && lane == 0) DBG_STAMP(0, (blk_ + 1) * n_kc - 1, 7);
+      uint32_t o0[32], o1[32];
+      tmem_ld_32x32(o_addr, o0);
+      tmem_ld_32x32(o_addr + 32, o1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(BAR_OEMPTY + wg));
+      // rows -> bf16, transposed through a 2 KB per-warp staging tile so that every store instruction writes
+      // 8 rows x 64 contiguous bytes instead of 32 rows x 16 bytes
+      const float inv = 1.0f / l_;
+      const int qi_ = qb_ * QB + r;
+      if (a.lse && qi_ < S) a.lse[(size_t)(doc_ * S + qi_) * a.n_heads + head] = m_ + log2f(l_);
+      uint8_t* stage = gbase + SM_STAGE + warp * 2048;
+      const int doc_row0 = doc_ * S + qb_ * QB + w4 * 32;
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        const uint32_t(&o)[32] = h2 ? o1 : o0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 u;
+          u.x = pack_bf16x2(__uint_as_float(o[j * 8 + 0]) * inv, __uint_as_float(o[j * 8 + 1]) * inv);
+          u.y = pack_bf16x2(__uint_as_float(o[j * 8 + 2]) * inv, __uint_as_float(o[j * 8 + 3]) * inv);
+          u.z = pack_bf16x2(__uint_as_float(o[j * 8 + 4]) * inv, __uint_as_float(o[j * 8 + 5]) * inv);
+          u.w = pack_bf16x2(__uint_as_float(o[j * 8 + 6]) * inv, __uint_as_float(o[j * 8 + 7]) * inv);
+          *reinterpret_cast<uint4*>(stage + ((lane * 4 + (j ^ ((lane >> 1) & 3))) << 4)) = u;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int row = 8 * i + (lane >> 2), j = lane & 3;
+          const uint4 u = *reinterpret_cast<const uint4*>(stage + ((row * 4 + (j ^ ((row >> 1) & 3))) << 4));
+          if (qb_ * QB + w4 * 32 + row < S)
+            *reinterpret_cast<uint4*>(a.out + (size_t)(doc_row0 + row) * a.ld_out + head * DK + h2 * 32 + j * 8) = u;
+        }
+        __syncwarp();
+      }
+    };
+#if PN_ATTN_DEFER_EPI
+    bool pend = false;
+    float pend_l = 1.0f, pend_m = 0.0f;
+    int pend_qb = 0, pend_doc = 0, pend_blk = 0;
+#endif
     int it = 0, rd = 0, c = 0;
     for (int s = 0; s < total_steps; ++s, (++c == n_kc ? (c = 0, (++rd == rounds ? (rd = 0, ++it) : 0)) : 0)) {
       const int qb = 2 * rd + wg;
@@ -501,51 +555,26 @@ t5_self_attn2_kernel(const __grid_constant__ CUtensorMap tmQKV, const Attn2Args 
       if (lane == 0) mbar_arrive(bar(BAR_PREADY + wg));
       if (warp == 0 && lane == 0) DBG_STAMP(0, n, 6);
       ++n;
-      if (c == n_kc - 1) {
-        // epilogue of this query block: ctx[row, head*64..] = O / l
-        mbar_wait(bar(BAR_OFULL + wg), ((n / n_kc) - 1) & 1);
-        tc_fence_after();
-        if (warp == 0 && lane == 0) DBG_STAMP(0, n - 1, 7);
-        uint32_t o0[32], o1[32];
-        tmem_ld_32x32(o_addr, o0);
-        tmem_ld_32x32(o_addr + 32, o1);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar(BAR_OEMPTY + wg));
-        {
-          // rows -> bf16, transposed through a 2 KB per-warp staging tile so that every store instruction writes
-          // 8 rows x 64 contiguous bytes instead of 32 rows x 16 bytes
-          const float inv = 1.0f / l;
-          if (a.lse && qi < S)
-            a.lse[(size_t)((doc0 + it * a.cph) * S + qi) * a.n_heads + head] = m_used + log2f(l);
-          uint8_t* stage = gbase + SM_STAGE + warp * 2048;
-          const int doc_row0 = (doc0 + it * a.cph) * S + qb * QB + w4 * 32;
-#pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2) {
-            const uint32_t(&o)[32] = h2 ? o1 : o0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 u;
-              u.x = pack_bf16x2(__uint_as_float(o[j * 8 + 0]) * inv, __uint_as_float(o[j * 8 + 1]) * inv);
-              u.y = pack_bf16x2(__uint_as_float(o[j * 8 + 2]) * inv, __uint_as_float(o[j * 8 + 3]) * inv);
-              u.z = pack_bf16x2(__uint_as_float(o[j * 8 + 4]) * inv, __uint_as_float(o[j * 8 + 5]) * inv);
-              u.w = pack_bf16x2(__uint_as_float(o[j * 8 + 6]) * inv, __uint_as_float(o[j * 8 + 7]) * inv);
-              *reinterpret_cast<uint4*>(stage + ((lane * 4 + (j ^ ((lane >> 1) & 3))) << 4)) = u;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int row = 8 * i + (lane >> 2), j = lane & 3;
-              const uint4 u = *reinterpret_cast<const uint4*>(stage + ((row * 4 + (j ^ ((row >> 1) & 3))) << 4));
-              if (qb * QB + w4 * 32 + row < S)
-                *reinterpret_cast<uint4*>(a.out + (size_t)(doc_row0 + row) * a.ld_out + head * DK + h2 * 32 + j * 8) = u;
-            }
-            __syncwarp();
-          }
-        }
+#if PN_ATTN_DEFER_EPI
+      // the epilogue of a finished query block runs one step late: after the FIRST step of the stream's next block has
+      // handed its P over.  By then the block's last P V has long retired (waiting for it right away cost ~1 050
+      // cycles per block, profiles/r5b_attn_source_summary.md), and a step with c == 0 never touches O itself: the
+      // issuer holds that step's P V (accumulate = 0, it overwrites O) until the epilogue has read O (BAR_OEMPTY)
+      if (pend) {
+        epilogue(pend_l, pend_m, pend_qb, pend_doc, pend_blk);
+        pend = false;
       }
+      if (c == n_kc - 1) {
+        pend = true;
+        pend_l = l; pend_m = m_used; pend_qb = qb; pend_doc = doc0 + it * a.cph; pend_blk = n / n_kc - 1;
+      }
+#else
+      if (c == n_kc - 1) epilogue(l, m_used, qb, doc0 + it * a.cph, n / n_kc - 1);
+#endif
     }
+#if PN_ATTN_DEFER_EPI
+    if (pend) epilogue(pend_l, pend_m, pend_qb, pend_doc, pend_blk);
+#endif
   }
 
   // ---- teardown

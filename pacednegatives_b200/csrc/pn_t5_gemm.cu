@@ -419,7 +419,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t swz = (uint32_t)(lane & 7), yswz = (uint32_t)((lane >> 1) & 3);
     // lane 0 requests tiles kResBufs - 1 chunks ahead; the origin of the NEXT work item is formed once per tile, so
     // the per-chunk issue path has no divisions (it sits on the warp's critical path: the others wait at __syncwarp)
-    static_assert(kResBufs - 1 <= kChunks, "prefetch distance reaches at most into the next tile");
+    // ring slots this instantiation cycles through (the layout always holds kResBufs of them): the prefetch distance
+    // reaches at most into the next tile
+    constexpr int kRing = kResBufs - 1 <= kChunks ? kResBufs : kChunks + 1;
     auto load_tile = [&](uint32_t b, int r0, int c0) {
       mbar_arrive_expect_tx(res_bar(ew, b), EPI_BUF_BYTES);
       tma_load_2d(wbase + b * EPI_BUF_BYTES, &tmC, res_bar(ew, b), c0, r0);
@@ -432,7 +434,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0 && group_id < num_tiles) {
       int r0, c0;
       tile_origin(group_id, r0, c0);
-      for (int i = 0; i + 1 < kResBufs; ++i) load_tile(i, r0, c0 + i * 32);
+      for (int i = 0; i + 1 < kRing; ++i) load_tile(i, r0, c0 + i * 32);
     }
     uint32_t rb = 0, rph = 0;   // ring slot and mbarrier phase of the current chunk
     int it = 0;
@@ -513,13 +515,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_store_2d(&tmC, wbase + rb * EPI_BUF_BYTES, col0 + c * 32, row0);
           if (args.copy_out) tma_store_2d(&tmY, ybase + (q & 1) * RES_Y_BYTES, col0 + c * 32, row0);
           tma_store_commit();
-          tma_store_wait_read<1>();   // chunk q - 1 has left shared memory: its fp32 tile takes chunk q + kResBufs - 1
-          const uint32_t bl = rb == 0 ? kResBufs - 1 : rb - 1;
-          const int cn = c + kResBufs - 1;
+          tma_store_wait_read<1>();   // chunk q - 1 has left shared memory: its fp32 tile takes chunk q + kRing - 1
+          const uint32_t bl = rb == 0 ? kRing - 1 : rb - 1;
+          const int cn = c + kRing - 1;
           if (cn < kChunks) load_tile(bl, row0, col0 + cn * 32);
           else if (nvalid) load_tile(bl, nrow0, ncol0 + (cn - kChunks) * 32);
         }
-        if (++rb == kResBufs) { rb = 0; rph ^= 1; }
+        if (++rb == kRing) { rb = 0; rph ^= 1; }
       }
       if (args.sumsq_out && live) args.sumsq_out[(size_t)n_blk * args.ss_stride + row] = ssq;
       tc_fence_before();
