@@ -47,6 +47,42 @@ def test_self_attention_kernel_vs_torch():
         assert err < 2e-2, f"docs={docs} S={S} H={H}: max err {err}"
 
 
+@pytest.mark.parametrize("sat_hi,sat_lo,scale", [(91, 91, 0.5), (40, 130, 0.5), (0, 0, 0.5), (91, 600, 0.5), (91, 91, 6.0),
+                                                 (33, 65, 3.0)])
+def test_self_attention_kernel_with_saturated_bias(sat_hi, sat_lo, scale):
+    """Bias tables shaped like T5's bucketed bias (constant beyond a saturation distance: 91 positions for 32 buckets and
+    max_distance 128), asymmetric, constant everywhere and saturated on one side only, at ragged lengths; large logits
+    drive the lazy rescale and the exact-redo path.  Output and the base-2 logsumexp the backward pass consumes, against
+    torch.  (Written for a variant of the kernel that took a register constant in the saturated sub-blocks, measured at no
+    gain and not kept: profiles/r5i_attn_const_bias_ab.txt; the shapes stay as coverage.)"""
+    from pacednegatives_b200 import _lib
+    _lib.require_gpu()
+    lib = _lib.lib()
+    torch.manual_seed(sat_hi * 7 + sat_lo)
+    for docs, S, H in [(3, 512, 2), (2, 384, 3), (1, 200, 2), (2, 128, 1), (1, 333, 2)]:
+        di = H * 64
+        qkv = (torch.randn(docs * S, 3 * di, device="cuda") * scale).bfloat16()
+        bias = torch.randn(H, 1023, device="cuda") * 2.0
+        if sat_hi < 512:
+            bias[:, 511 + sat_hi:] = bias[:, 1022:1023]
+        if sat_lo < 512:
+            bias[:, :511 - sat_lo + 1] = bias[:, 0:1]
+        out = torch.zeros(docs * S, di, device="cuda", dtype=torch.bfloat16)
+        lse = torch.zeros(docs * S, H, device="cuda")
+        _lib.check(lib.pn_t5_self_attention_lse(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(out), _lib.ptr(lse),
+                                                _lib.stream()))
+        q, k, v = [t.float().view(docs, S, H, 64).transpose(1, 2) for t in qkv.split(di, dim=1)]
+        pos = torch.arange(S, device="cuda")
+        b = bias[:, (pos[None, :] - pos[:, None]) + 511]
+        sc = q @ k.transpose(2, 3) + b[None]
+        ref = (torch.softmax(sc, dim=-1) @ v).transpose(1, 2).reshape(docs * S, di)
+        err = (out.float() - ref).abs().max().item()
+        assert err < (2e-2 if scale < 3 else 1e-1), f"sat=({sat_hi},{sat_lo}) docs={docs} S={S} H={H}: max err {err}"
+        ref_lse = (torch.logsumexp(sc, dim=-1) * 1.4426950408889634).permute(0, 2, 1).reshape(docs * S, H)
+        lerr = (lse - ref_lse).abs().max().item()
+        assert lerr < 2e-2, f"sat=({sat_hi},{sat_lo}) docs={docs} S={S} H={H}: logsumexp err {lerr}"
+
+
 @pytest.mark.parametrize("cta_group", [1, 2])
 def test_score_tiny_golden(golden_dir, cta_group):
     g = np.load(os.path.join(golden_dir, "t5_tiny_golden.npz"))

@@ -10,6 +10,10 @@ def run(docs, S, H, check=True, iters=0, scale=0.5):
     di = H * 64
     qkv = (torch.randn(docs * S, 3 * di, device="cuda") * scale).bfloat16()
     bias = torch.randn(H, 1023, device="cuda")
+    DC = int(os.environ.get("DC", 0))          # DC=91: a table that saturates like T5's bucketed bias
+    if DC:
+        bias[:, 511 + DC:] = bias[:, 1022:1023]
+        bias[:, :511 - DC + 1] = bias[:, 0:1]
     out = torch.zeros(docs * S, di, device="cuda", dtype=torch.bfloat16)
     _lib.check(lib.pn_t5_self_attention(_lib.ptr(qkv), docs, S, H, _lib.ptr(bias), _lib.ptr(out), _lib.stream()))
     torch.cuda.synchronize()
@@ -36,7 +40,7 @@ def run(docs, S, H, check=True, iters=0, scale=0.5):
         e1.record(); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / iters
     fl = 4.0 * docs * H * S * S * 64
-    print(f"impl={os.environ.get('PN_ATTN_IMPL','2')} docs={docs} S={S} H={H} scale={scale} err={err} ms={ms} "
+    print(f"impl={os.environ.get('PN_ATTN_IMPL','2')} DC={os.environ.get('DC','0')} docs={docs} S={S} H={H} scale={scale} err={err} ms={ms} "
           f"TFLOP/s={(fl / ms / 1e9) if ms else None}", flush=True)
 
 for cfg in [(3, 512, 2), (2, 128, 4), (2, 384, 1), (1, 200, 2), (2, 77, 2), (40, 512, 12), (7, 300, 8)]:
