@@ -216,6 +216,9 @@ class MonoT5Scorer:
         _lib.require_gpu()
         self.dims, self.rel_id, self.nrel_id = dims, int(rel_id), int(nrel_id)
         self.chunk_docs = int(chunk_docs)
+        # measurement knob (PN_OVERLAP_CHUNKS=1): score() alternates its chunks between two streams
+        self.overlap_chunks = os.environ.get("PN_OVERLAP_CHUNKS", "0") not in ("", "0")
+        self._side, self._side_ws = None, [None, None]
         lib = _lib.lib()
         cfg = _Cfg(dims.vocab, dims.d_model, dims.d_kv, dims.d_ff, dims.n_layers, dims.n_dec_layers,
                    dims.n_heads, dims.rel_buckets, dims.rel_max_dist, dims.pad_id, dims.eps)
@@ -367,6 +370,9 @@ class MonoT5Scorer:
         score = torch.empty(N, dtype=torch.float32, device="cuda")
         z2 = torch.empty(N, 2, dtype=torch.float32, device="cuda")
         lib = _lib.lib()
+        if self.overlap_chunks and N > self.chunk_docs:
+            self._score_two_streams(ids, lens, N, S, score, z2)
+            return (score, z2) if return_z2 else score
         for lo in range(0, N, self.chunk_docs):
             n = min(self.chunk_docs, N - lo)
             ws, need = self._workspace(min(self.chunk_docs, N), S, 1)
@@ -375,6 +381,34 @@ class MonoT5Scorer:
                                             self.rel_id, self.nrel_id, _lib.ptr(score[lo:lo + n]),
                                             _lib.ptr(z2[lo:lo + n]), _lib.ptr(ws), ws.numel(), _lib.stream()))
         return (score, z2) if return_z2 else score
+
+    def _score_two_streams(self, ids, lens, N, S, score, z2):
+        """Chunks alternate between two side streams with a workspace each (option ``overlap_chunks``): the decoder of
+        chunk i — ~240 launches on a handful of CTAs — shares the GPU with the encoder of chunk i + 1 instead of
+        running alone.  Same kernels, same results; the caller's stream waits for both side streams at the end."""
+        lib = _lib.lib()
+        cur = torch.cuda.current_stream()
+        if self._side is None:
+            self._side = [torch.cuda.Stream(), torch.cuda.Stream()]
+        need = int(lib.pn_t5_workspace_bytes(self._h, self.chunk_docs, S, 1, 0))
+        for i in range(2):
+            if self._side_ws[i] is None or self._side_ws[i].numel() < need:
+                self._side_ws[i] = torch.empty(need, dtype=torch.uint8, device="cuda")
+        start = torch.cuda.Event()
+        start.record(cur)
+        for st in self._side:
+            st.wait_event(start)
+        for i, lo in enumerate(range(0, N, self.chunk_docs)):
+            n = min(self.chunk_docs, N - lo)
+            ws, st = self._side_ws[i & 1], self._side[i & 1]
+            _lib.check(lib.pn_t5_score_lens(self._h, _lib.ptr(ids[lo:lo + n]),
+                                            _lib.ptr(lens[lo:lo + n]) if lens is not None else None, n, S,
+                                            self.rel_id, self.nrel_id, _lib.ptr(score[lo:lo + n]),
+                                            _lib.ptr(z2[lo:lo + n]), _lib.ptr(ws), ws.numel(), st.cuda_stream))
+        for st in self._side:
+            done = torch.cuda.Event()
+            done.record(st)
+            cur.wait_event(done)
 
     def logits(self, input_ids, labels, want_logits=True):
         """model(input_ids=, labels=).logits for T = 1 or 2 label positions.
