@@ -5,9 +5,11 @@
 //   ndcg_cut_K: gain = rel (linear), discount log2(rank+1), ideal = the query's rels sorted desc
 //   recip_rank: 1 / rank of the first doc with rel >= 1 (whole list); rr@K the same cut at K
 //   map       : mean over relevant docs of precision at their rank
-// One CTA per query: C candidates (<= 4096) are packed to 64-bit keys in shared memory; HBM traffic is the
-// C*(4+4+1) input bytes once.  K <= 32 (the nDCG@10 / MRR@10 case) takes the sort-free topk_count_kernel below;
-// larger K sorts the keys with a bitonic network.
+// Candidates (C <= 4096) become 64-bit keys (orderable score, docid); HBM traffic is the C*(4+4+1) input bytes once.
+//   C <= 1024, K <= 32 (BM25 top-1000, nDCG@10 / MRR@10): topk_warp2_kernel, one WARP per query, keys in registers,
+//                      O(C log R) rank work (the first generation topk_warp_kernel stays behind PN_TOPK_WARP=1)
+//   K <= 32, larger C : topk_count_kernel, one CTA per query, keys in shared memory, sort-free
+//   K > 32            : topk_metrics_kernel, bitonic sort of the keys in shared memory
 #include "pn_common.cuh"
 #include <stdlib.h>
 
