@@ -9,6 +9,8 @@
 
 #include "../../include/pn_b200.h"
 
+// SMs of a B200 (the only target: sm_100a).  A compile-time constant on purpose: persistent grids, CTAs per head and
+// k-split counts are sized from it in constant expressions; pn_device_check() (pn_api.cu) refuses other devices.
 #define PN_SM_COUNT 148
 
 extern thread_local char g_pn_err[512];

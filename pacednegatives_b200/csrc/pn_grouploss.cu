@@ -253,7 +253,7 @@ extern "C" int pn_token_ce_fwd(const void* logits, int dtype, int64_t rows, int3
   PN_CHECK_ARG(dtype == 0 || dtype == 1);
   if (rows == 0) return PN_OK;
   PN_CHECK_ARG(logits && target && ce_out);
-  const int grid = (int)(rows < 148 * 8 ? rows : 148 * 8);
+  const int grid = (int)(rows < PN_SM_COUNT * 8 ? rows : PN_SM_COUNT * 8);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == 0) {
     const bool vec = ((uintptr_t)logits & 15) == 0 && (V % 4) == 0;
@@ -275,7 +275,7 @@ extern "C" int pn_token_ce_bwd(const void* logits, int dtype, int64_t rows, int3
   PN_CHECK_ARG(dtype == 0 || dtype == 1);
   if (rows == 0) return PN_OK;
   PN_CHECK_ARG(logits && target && lse && g && dlogits);
-  const int grid = (int)(rows < 148 * 8 ? rows : 148 * 8);
+  const int grid = (int)(rows < PN_SM_COUNT * 8 ? rows : PN_SM_COUNT * 8);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == 0)
     token_ce_bwd_kernel<float><<<grid, kThreads, 0, st>>>((const float*)logits, rows, V, target,

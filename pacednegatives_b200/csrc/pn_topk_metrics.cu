@@ -830,7 +830,7 @@ extern "C" int pn_topk_metrics_qrels(const float* scores, const int32_t* docids,
     const int Cp = (C + 3) & ~3;
     const size_t smem = (size_t)Cp * (8 + 2 + 2 + 1);
     PN_CUDA(cudaFuncSetAttribute(topk_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int grid = (int)(Q < 148 * 8 ? Q : 148 * 8);
+    const int grid = (int)(Q < PN_SM_COUNT * 8 ? Q : PN_SM_COUNT * 8);
     topk_count_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(scores, docids, rels, Q, C, K, top_ids,
                                                                       top_scores, metrics_out, qrel_num, qrel_idcg);
     PN_LAUNCHED();
@@ -841,7 +841,7 @@ extern "C" int pn_topk_metrics_qrels(const float* scores, const int32_t* docids,
   const size_t smem = (size_t)P * (8 + 2 + 1);
   PN_CUDA(cudaFuncSetAttribute(topk_metrics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                (int)smem));
-  const int grid = (int)(Q < 148 * 4 ? Q : 148 * 4);
+  const int grid = (int)(Q < PN_SM_COUNT * 4 ? Q : PN_SM_COUNT * 4);
   topk_metrics_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(
       scores, docids, rels, Q, C, P, K, top_ids, top_scores, metrics_out, qrel_num, qrel_idcg);
   PN_LAUNCHED();
